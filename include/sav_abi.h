@@ -1,0 +1,184 @@
+/* sav_abi.h -- C ABI of the B200-native transformer-block kernels (libsav_b200.so).
+ *
+ * The reference (NZ99/self-attention-experiments-vision) has NO native interface: its only seams
+ * are Python call signatures of Flax modules whose arithmetic XLA lowers.  Each entry point below
+ * therefore cites the reference call site whose XLA-lowered computation it replaces; these are
+ * exactly the symbols an XLA-FFI / ctypes binding for this path binds.
+ *
+ * Conventions (all entry points):
+ *   - plain C, POD args; every pointer is a DEVICE pointer owned by the caller
+ *   - the callee never allocates, frees, synchronises or switches device; all work is enqueued on
+ *     `stream` (a cudaStream_t passed as void*); CUDA-graph-capture safe; thread-safe
+ *   - return 0 on success, negative sav_status otherwise; sav_last_error() is thread-local
+ *   - bf16 = IEEE bfloat16 (2 bytes); "row-major [R,C] ld" = element (r,c) at r*ld + c
+ */
+#ifndef SAV_ABI_H_
+#define SAV_ABI_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SAV_ABI_VERSION 1
+
+enum sav_status {
+  SAV_OK = 0,
+  SAV_ERR_SHAPE = -1,
+  SAV_ERR_ALIGN = -2,
+  SAV_ERR_ARCH = -3,
+  SAV_ERR_CUDA = -4,
+  SAV_ERR_ARG = -5
+};
+
+int sav_abi_version(void);
+const char* sav_last_error(void);
+/* 0 when the current device is sm_100 (B200); SAV_ERR_ARCH otherwise. */
+int sav_device_check(void);
+/* number of kernels launched by this library in this process (bench.py: "gpu_launches") */
+int64_t sav_launch_count(void);
+
+/* ---------------------------------------------------------------- GEMM (tcgen05 / TMEM / TMA)
+ * D[M,N] = epilogue( sum_k A[m,k] * B[n,k] )           bf16 x bf16 -> fp32 accumulate
+ * Replaces nn.Dense / nn.DenseGeneral dot_generals and their reverse-mode products:
+ *   attention.py:29-37,60-63 (queries/keys/values/out projections), ff.py:24,27 (Dense_0/Dense_1),
+ *   patch_embed.py:23-25, vit.py:96-98 (head), and jax.value_and_grad of those (train.py:94).
+ * Operand storage:
+ *   a_mn=0: A is row-major [M,K] (K contiguous);  a_mn=1: A is row-major [K,M] (M contiguous)
+ *   b_mn=0: B is row-major [N,K] (K contiguous);  b_mn=1: B is row-major [K,N] (N contiguous)
+ * Epilogue, in this order (each optional):
+ *   v = acc + bias[n]; aux_out[m,n] = bf16(v); v = gelu_tanh(v) if act==1;
+ *   v *= dgelu_tanh(aux_in[m,n]); v *= col_scale[n]; v *= row_scale[m / rows_per_scale];
+ *   v += residual[m,n]; D[m,n] = v  (bf16, or fp32 when d_fp32)
+ * split_k > 1: K is partitioned, fp32 partials go to `workspace` ([split_k,M,N] fp32) and a second
+ *   kernel reduces them into D (requires d_fp32=1 and no epilogue except bias-free identity);
+ *   used for dW = X^T dY where K = tokens.
+ * Alignment: all base pointers 16 B aligned; lda/ldb/ldd/ldr multiples of 8 elements; N % 8 == 0.
+ */
+typedef struct {
+  const void* A;
+  const void* B;
+  void* D;
+  int64_t M, N, K;
+  int64_t lda, ldb, ldd;
+  int32_t a_mn, b_mn, d_fp32, split_k;
+  const float* bias;       /* [N] fp32 or NULL */
+  int32_t act;             /* 0 none, 1 tanh-GELU (ff.py:12, jax.nn.gelu approximate=True) */
+  int32_t accumulate;      /* d_fp32 only: D += result (gradient accumulation) */
+  void* aux_out;           /* bf16 [M,N] ld=ldd: pre-activation, or NULL */
+  const void* aux_in;      /* bf16 [M,N] ld=ldd: multiply by gelu'(aux_in), or NULL */
+  const float* col_scale;  /* [N] LayerScale (layerscale.py:20-23) or NULL */
+  const float* row_scale;  /* [ceil(M/rows_per_scale)] drop-path (stochastic_depth.py:16-27) */
+  int64_t rows_per_scale;
+  const void* residual;    /* bf16 [M,N] ld=ldr or NULL (vit.py:24,31) */
+  int64_t ldr;
+  void* workspace;         /* split_k>1: >= split_k*M*N*4 bytes */
+  int64_t workspace_bytes;
+} sav_gemm_args;
+int64_t sav_gemm_workspace_bytes(const sav_gemm_args* a);
+int sav_gemm(const sav_gemm_args* a, void* stream);
+
+/* column sums: out[n] (+)= sum_m X[m,n]   (bias gradients; ff.py:24,27 reverse-mode) */
+int sav_colsum_bf16(const void* X, int64_t M, int64_t N, int64_t ldx, float* out,
+                    int32_t accumulate, void* stream);
+
+/* ---------------------------------------------------------------- LayerNorm (vit.py:19,26,57)
+ * Flax nn.LayerNorm: fp32 stats, var = E[x^2]-E[x]^2, eps inside rsqrt, y = xhat*scale + bias.
+ * x,y bf16 [rows,C]; scale,bias fp32 [C]; mean,rstd fp32 [rows] (saved for backward). C % 8 == 0.
+ */
+int sav_layernorm_fwd(const void* x, const float* scale, const float* bias, void* y, float* mean,
+                      float* rstd, int64_t rows, int64_t C, float eps, void* stream);
+/* dx = LNbwd(dy) (+ dx_add if non-NULL; fuses the residual-branch gradient, vit.py:24,31);
+ * dscale/dbias [C] fp32 are accumulated when accumulate!=0, else overwritten.
+ * partials: fp32 workspace of sav_layernorm_bwd_workspace_bytes(rows, C). */
+int64_t sav_layernorm_bwd_workspace_bytes(int64_t rows, int64_t C);
+int sav_layernorm_bwd(const void* dy, const void* x, const float* scale, const float* mean,
+                      const float* rstd, const void* dx_add, void* dx, float* dscale, float* dbias,
+                      float* partials, int64_t rows, int64_t C, int32_t accumulate, void* stream);
+
+/* ---------------------------------------------------------------- patch embedding stem
+ * train.py:80-81 + patch_embed.py:19-22: images fp32 [H,W,C,N] (reference batch layout) ->
+ * patches bf16 [N*(H/ph)*(W/pw), ph*pw*C] with feature order (ph, pw, c).  hwcn=0: input is
+ * [N,H,W,C] instead. */
+int sav_patchify(const float* images, void* patches, int64_t N, int64_t H, int64_t W, int64_t C,
+                 int64_t ph, int64_t pw, int32_t hwcn, void* stream);
+/* vit.py:81-85 + position_embed.py:54-56: x[b,0,:] = cls + pos[0]; x[b,1+i,:] = tok[b,i,:] +
+ * pos[1+i].  has_cls=0: x[b,i,:] = tok[b,i,:] + pos[i] (cait.py:69).  tok,x bf16; cls,pos fp32. */
+int sav_embed_fwd(const void* tok, const float* cls, const float* pos, void* x, int64_t B,
+                  int64_t n_tok, int64_t C, int32_t has_cls, void* stream);
+/* reverse-mode of the above: dtok (bf16), dcls [C], dpos [n_tok+has_cls, C] fp32 */
+int sav_embed_bwd(const void* dx, void* dtok, float* dcls, float* dpos, int64_t B, int64_t n_tok,
+                  int64_t C, int32_t has_cls, int32_t accumulate, void* stream);
+
+/* ---------------------------------------------------------------- fused attention core
+ * attention.py:39-58: q/sqrt(d); S = q k^T; softmax over keys; O = P v.   One pass, S never
+ * leaves the SM (TMEM).  q,k,v,o are bf16 with element (b, token, h, :) at
+ *   ptr + b*batch_stride + token*row_stride + h*D           (strides in elements)
+ * so they can alias slices of a fused [B,N,3,H,D] QKV buffer.  lse fp32 [B,H,Nq] (natural log of
+ * the softmax denominator incl. max) is saved for backward.
+ * rel_w / rel_h (BoTNet, botnet.py:70-141): optional fp32-free bf16 tables [2W-1,D],[2H-1,D];
+ * NULL for plain attention.  D in {64}.  (D=48/128: see DESIGN.md status table.)
+ */
+typedef struct {
+  const void* q;
+  const void* k;
+  const void* v;
+  void* o;
+  float* lse;
+  int64_t B, H, Nq, Nk, D;
+  int64_t q_batch_stride, q_row_stride;
+  int64_t k_batch_stride, k_row_stride;
+  int64_t v_batch_stride, v_row_stride;
+  int64_t o_batch_stride, o_row_stride;
+  float scale; /* 1/sqrt(D) (attention.py:39) */
+} sav_attn_fwd_args;
+int sav_attn_fwd(const sav_attn_fwd_args* a, void* stream);
+
+typedef struct {
+  const void* q;
+  const void* k;
+  const void* v;
+  const void* o;
+  const void* d_o;
+  const float* lse;
+  void* dq;
+  void* dk;
+  void* dv;
+  float* delta;      /* workspace fp32 [B,H,Nq] */
+  float* dq_accum;   /* workspace fp32 [B,Nq,H,D] (zeroed by the callee) */
+  int64_t B, H, Nq, Nk, D;
+  int64_t q_batch_stride, q_row_stride; /* shared by q and dq */
+  int64_t k_batch_stride, k_row_stride; /* shared by k and dk */
+  int64_t v_batch_stride, v_row_stride; /* shared by v and dv */
+  int64_t o_batch_stride, o_row_stride; /* shared by o and d_o */
+  float scale;
+} sav_attn_bwd_args;
+int sav_attn_bwd(const sav_attn_bwd_args* a, void* stream);
+
+/* ---------------------------------------------------------------- loss head (train.py:83-91)
+ * one_hot -> smooth_labels(alpha) -> softmax_cross_entropy -> mean; writes dlogits = dloss/dlogits
+ * (bf16 [B,classes]) and accumulates loss into loss_out[0] (zeroed by the callee), top1 count into
+ * loss_out[1].  logits bf16 [B, classes] ld. loss_scale multiplies the gradient (1/B/world). */
+int sav_softmax_xent(const void* logits, int64_t ld, const int32_t* labels, int64_t B,
+                     int64_t classes, float label_smoothing, float grad_scale, void* dlogits,
+                     float* loss_out, void* stream);
+
+/* ---------------------------------------------------------------- parameters / optimizer
+ * fp32 -> bf16 shadow copy of the flat parameter arena */
+int sav_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
+/* out[0] += sum(g^2) over n elements (global-norm clip, train.py:25, optax.clip_by_global_norm) */
+int sav_sumsq(const float* g, int64_t n, float* out, void* stream);
+/* optax chain of train.py:25-27 / simple_train.py:25-27 as one pass over the arena:
+ * g *= min(1, max_norm/||g||) (sumsq[0] holds ||g||^2; max_norm<=0 disables) -> Adam(b1,b2,eps,
+ * bias-corrected with step t) -> + wd*p -> * (-lr) -> p += update; also refreshes bf16 shadow. */
+int sav_adam_step(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n,
+                  const float* sumsq, float max_norm, float lr, float b1, float b2, float eps,
+                  float wd, int64_t t, void* stream);
+
+/* elementwise helpers (bf16): y = a + b ; used only where no GEMM epilogue can absorb the add */
+int sav_add_bf16(const void* a, const void* b, void* y, int64_t n, void* stream);
+int sav_fill_f32(float* p, float v, int64_t n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SAV_ABI_H_ */

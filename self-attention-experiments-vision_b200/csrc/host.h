@@ -1,0 +1,24 @@
+// Host-side helpers shared by the launchers: thread-local error string, launch counter,
+// TMA tensor-map encoding through the driver entry point (no link-time libcuda dependency).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/sav_abi.h"
+
+namespace sav {
+
+int set_error(int code, const char* fmt, ...);
+void count_launch(int n = 1);
+int check_launch(const char* what);
+
+// Encode a rank-`rank` bf16 tensor map with 128-byte swizzle.
+//   dims[i], box[i] in elements (dim 0 innermost, contiguous); strides_bytes[i] for i>=1
+// Returns 0 or a negative sav_status.
+int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                   const uint64_t* strides_bytes, const uint32_t* box);
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace sav

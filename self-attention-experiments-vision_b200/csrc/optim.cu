@@ -1,0 +1,201 @@
+// Loss head (train.py:83-91) and optimizer chain (train.py:25-27,100; simple_train.py:25-27,90)
+// as HBM-bound single-pass kernels over the flat parameter arena (28 B/param for the Adam step).
+#include "common.cuh"
+#include "host.h"
+
+namespace sav {
+
+__device__ __forceinline__ float wsum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float wmax(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// warp per sample.  target = (1-a)*onehot + a/classes (optax.smooth_labels);
+// loss_b = -sum target*log_softmax;  dlogits = (softmax - target) * grad_scale.
+__global__ void __launch_bounds__(128)
+xent_kernel(const bf16* __restrict__ logits, int64_t ld, const int32_t* __restrict__ labels,
+            int B, int classes, float alpha, float grad_scale, bf16* __restrict__ dlogits,
+            float* __restrict__ loss_out) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (b >= B) return;
+  const bf16* row = logits + (int64_t)b * ld;
+  float mx = -INFINITY;
+  for (int c = lane; c < classes; c += 32) mx = fmaxf(mx, __bfloat162float(row[c]));
+  mx = wmax(mx);
+  float se = 0.f, sl = 0.f;
+  int arg = 0x7fffffff;
+  for (int c = lane; c < classes; c += 32) {
+    const float l = __bfloat162float(row[c]);
+    se += __expf(l - mx);
+    sl += l;
+    if (l == mx && c < arg) arg = c;
+  }
+  se = wsum(se);
+  sl = wsum(sl);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) arg = min(arg, __shfl_xor_sync(0xffffffffu, arg, o));
+  const float lse = mx + logf(se);
+  const int lab = labels[b];
+  const float l_lab = __bfloat162float(row[lab]);
+  // -sum_c t_c (l_c - lse) = lse - (1-a) l_lab - a/classes * sum_c l_c
+  const float loss = lse - (1.f - alpha) * l_lab - alpha / classes * sl;
+  const float inv = 1.f / se;
+  for (int c = lane; c < classes; c += 32) {
+    const float l = __bfloat162float(row[c]);
+    const float t = (c == lab ? (1.f - alpha) : 0.f) + alpha / classes;
+    dlogits[(int64_t)b * ld + c] = __float2bfloat16((__expf(l - mx) * inv - t) * grad_scale);
+  }
+  if (lane == 0) {
+    atomicAdd(loss_out, loss);
+    if (arg == lab) atomicAdd(loss_out + 1, 1.f);
+  }
+}
+
+__global__ void cast_kernel(const float* __restrict__ s, bf16* __restrict__ d, int64_t n) {
+  const int64_t n4 = n / 4;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 v = *reinterpret_cast<const float4*>(s + i * 4);
+    *reinterpret_cast<uint2*>(d + i * 4) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const int64_t i = n4 * 4 + threadIdx.x;
+    d[i] = __float2bfloat16(s[i]);
+  }
+}
+
+__global__ void sumsq_kernel(const float* __restrict__ g, int64_t n, float* __restrict__ out) {
+  float acc = 0.f;
+  const int64_t n4 = n / 4;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 v = *reinterpret_cast<const float4*>(g + i * 4);
+    acc += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const float v = g[n4 * 4 + threadIdx.x];
+    acc += v * v;
+  }
+  acc = wsum(acc);
+  __shared__ float red[8];
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) s += red[i];
+    atomicAdd(out, s);
+  }
+}
+
+// clip_by_global_norm -> scale_by_adam -> additive_weight_decay -> scale(-lr) -> apply_updates
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g,
+                            float* __restrict__ m, float* __restrict__ v, bf16* __restrict__ pb,
+                            int64_t n, const float* __restrict__ sumsq, float max_norm, float lr,
+                            float b1, float b2, float eps, float wd, float bc1, float bc2) {
+  float clip = 1.f;
+  if (max_norm > 0.f && sumsq) {
+    const float gn = sqrtf(sumsq[0]);
+    if (gn >= max_norm) clip = max_norm / gn;  // optax: g * max_norm / ||g|| when ||g|| >= max_norm
+  }
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const float gi = g[i] * clip;
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    const float pi = p[i];
+    const float upd = (mi / bc1) / (sqrtf(vi / bc2) + eps) + wd * pi;
+    const float np = pi - lr * upd;
+    p[i] = np;
+    if (pb) pb[i] = __float2bfloat16(np);
+  }
+}
+
+__global__ void add_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b,
+                           bf16* __restrict__ y, int64_t n8) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n8;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 ua = reinterpret_cast<const uint4*>(a)[i];
+    const uint4 ub = reinterpret_cast<const uint4*>(b)[i];
+    const uint32_t wa[4] = {ua.x, ua.y, ua.z, ua.w}, wb[4] = {ub.x, ub.y, ub.z, ub.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 fa = unpack_bf16(wa[j]), fb = unpack_bf16(wb[j]);
+      o[j] = pack_bf16(fa.x + fb.x, fa.y + fb.y);
+    }
+    reinterpret_cast<uint4*>(y)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+static int grid_for(int64_t work, int threads) {
+  int64_t b = (work + threads - 1) / threads;
+  const int64_t cap = 148 * 8;
+  return (int)(b < 1 ? 1 : (b < cap ? b : cap));
+}
+
+}  // namespace sav
+
+using namespace sav;
+
+extern "C" int sav_softmax_xent(const void* logits, int64_t ld, const int32_t* labels, int64_t B,
+                                int64_t classes, float label_smoothing, float grad_scale,
+                                void* dlogits, float* loss_out, void* stream) {
+  if (B <= 0 || classes <= 0) return set_error(SAV_ERR_SHAPE, "sav_softmax_xent: bad shape");
+  int rc = sav_fill_f32(loss_out, 0.f, 2, stream);
+  if (rc) return rc;
+  xent_kernel<<<(int)((B + 3) / 4), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const bf16*>(logits), ld, labels, (int)B, (int)classes, label_smoothing,
+      grad_scale, reinterpret_cast<bf16*>(dlogits), loss_out);
+  count_launch();
+  return check_launch("sav_softmax_xent");
+}
+
+extern "C" int sav_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {
+  if (n <= 0) return SAV_OK;
+  if (!aligned16(src) || (reinterpret_cast<uintptr_t>(dst) & 7))
+    return set_error(SAV_ERR_ALIGN, "sav_cast_f32_bf16: alignment");
+  cast_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      src, reinterpret_cast<bf16*>(dst), n);
+  count_launch();
+  return check_launch("sav_cast_f32_bf16");
+}
+
+extern "C" int sav_sumsq(const float* g, int64_t n, float* out, void* stream) {
+  if (n <= 0) return SAV_OK;
+  if (!aligned16(g)) return set_error(SAV_ERR_ALIGN, "sav_sumsq: alignment");
+  sumsq_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(g, n, out);
+  count_launch();
+  return check_launch("sav_sumsq");
+}
+
+extern "C" int sav_adam_step(float* p, const float* g, float* m, float* v, void* p_bf16,
+                             int64_t n, const float* sumsq, float max_norm, float lr, float b1,
+                             float b2, float eps, float wd, int64_t t, void* stream) {
+  if (n <= 0) return SAV_OK;
+  if (t < 1) return set_error(SAV_ERR_ARG, "sav_adam_step: step count t starts at 1");
+  const float bc1 = 1.f - powf(b1, (float)t), bc2 = 1.f - powf(b2, (float)t);
+  adam_kernel<<<grid_for(n, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      p, g, m, v, reinterpret_cast<bf16*>(p_bf16), n, sumsq, max_norm, lr, b1, b2, eps, wd, bc1, bc2);
+  count_launch();
+  return check_launch("sav_adam_step");
+}
+
+extern "C" int sav_add_bf16(const void* a, const void* b, void* y, int64_t n, void* stream) {
+  if (n <= 0) return SAV_OK;
+  if (n % 8 || !aligned16(a) || !aligned16(b) || !aligned16(y))
+    return set_error(SAV_ERR_ALIGN, "sav_add_bf16: n %% 8 and 16 B alignment required");
+  add_kernel<<<grid_for(n / 8, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const bf16*>(a), reinterpret_cast<const bf16*>(b),
+      reinterpret_cast<bf16*>(y), n / 8);
+  count_launch();
+  return check_launch("sav_add_bf16");
+}

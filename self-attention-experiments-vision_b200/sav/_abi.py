@@ -1,0 +1,115 @@
+"""ctypes binding of include/sav_abi.h (libsav_b200.so).
+
+This is the only door from Python to the device: every call enqueues hand-written sm_100a
+kernels on the current torch CUDA stream.  There is NO fallback: if the shared library is missing
+or the device is not a B200, importing/using these functions raises.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libsav_b200.so")
+
+_lib = None
+
+
+class SavError(RuntimeError):
+    pass
+
+
+class GemmArgs(C.Structure):
+    _fields_ = [
+        ("A", C.c_void_p), ("B", C.c_void_p), ("D", C.c_void_p),
+        ("M", C.c_int64), ("N", C.c_int64), ("K", C.c_int64),
+        ("lda", C.c_int64), ("ldb", C.c_int64), ("ldd", C.c_int64),
+        ("a_mn", C.c_int32), ("b_mn", C.c_int32), ("d_fp32", C.c_int32), ("split_k", C.c_int32),
+        ("bias", C.c_void_p), ("act", C.c_int32), ("accumulate", C.c_int32),
+        ("aux_out", C.c_void_p), ("aux_in", C.c_void_p),
+        ("col_scale", C.c_void_p), ("row_scale", C.c_void_p), ("rows_per_scale", C.c_int64),
+        ("residual", C.c_void_p), ("ldr", C.c_int64),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_int64),
+    ]
+
+
+class AttnFwdArgs(C.Structure):
+    _fields_ = [
+        ("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("o", C.c_void_p),
+        ("lse", C.c_void_p),
+        ("B", C.c_int64), ("H", C.c_int64), ("Nq", C.c_int64), ("Nk", C.c_int64), ("D", C.c_int64),
+        ("q_batch_stride", C.c_int64), ("q_row_stride", C.c_int64),
+        ("k_batch_stride", C.c_int64), ("k_row_stride", C.c_int64),
+        ("v_batch_stride", C.c_int64), ("v_row_stride", C.c_int64),
+        ("o_batch_stride", C.c_int64), ("o_row_stride", C.c_int64),
+        ("scale", C.c_float),
+    ]
+
+
+class AttnBwdArgs(C.Structure):
+    _fields_ = [
+        ("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("o", C.c_void_p),
+        ("d_o", C.c_void_p), ("lse", C.c_void_p),
+        ("dq", C.c_void_p), ("dk", C.c_void_p), ("dv", C.c_void_p),
+        ("delta", C.c_void_p), ("dq_accum", C.c_void_p),
+        ("B", C.c_int64), ("H", C.c_int64), ("Nq", C.c_int64), ("Nk", C.c_int64), ("D", C.c_int64),
+        ("q_batch_stride", C.c_int64), ("q_row_stride", C.c_int64),
+        ("k_batch_stride", C.c_int64), ("k_row_stride", C.c_int64),
+        ("v_batch_stride", C.c_int64), ("v_row_stride", C.c_int64),
+        ("o_batch_stride", C.c_int64), ("o_row_stride", C.c_int64),
+        ("scale", C.c_float),
+    ]
+
+
+_P, _I64, _I32, _F = C.c_void_p, C.c_int64, C.c_int32, C.c_float
+
+# name -> (restype, argtypes); also the list the CPU test checks against include/sav_abi.h
+SIGNATURES = {
+    "sav_abi_version": (C.c_int, []),
+    "sav_last_error": (C.c_char_p, []),
+    "sav_device_check": (C.c_int, []),
+    "sav_launch_count": (C.c_int64, []),
+    "sav_gemm_workspace_bytes": (C.c_int64, [C.POINTER(GemmArgs)]),
+    "sav_gemm": (C.c_int, [C.POINTER(GemmArgs), _P]),
+    "sav_colsum_bf16": (C.c_int, [_P, _I64, _I64, _I64, _P, _I32, _P]),
+    "sav_layernorm_fwd": (C.c_int, [_P, _P, _P, _P, _P, _P, _I64, _I64, _F, _P]),
+    "sav_layernorm_bwd_workspace_bytes": (C.c_int64, [_I64, _I64]),
+    "sav_layernorm_bwd": (C.c_int, [_P] * 10 + [_I64, _I64, _I32, _P]),
+    "sav_patchify": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _I64, _I64, _I32, _P]),
+    "sav_embed_fwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I32, _P]),
+    "sav_embed_bwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I32, _I32, _P]),
+    "sav_attn_fwd": (C.c_int, [C.POINTER(AttnFwdArgs), _P]),
+    "sav_attn_bwd": (C.c_int, [C.POINTER(AttnBwdArgs), _P]),
+    "sav_softmax_xent": (C.c_int, [_P, _I64, _P, _I64, _I64, _F, _F, _P, _P, _P]),
+    "sav_cast_f32_bf16": (C.c_int, [_P, _P, _I64, _P]),
+    "sav_sumsq": (C.c_int, [_P, _I64, _P, _P]),
+    "sav_adam_step": (C.c_int, [_P, _P, _P, _P, _P, _I64, _P, _F, _F, _F, _F, _F, _F, _I64, _P]),
+    "sav_add_bf16": (C.c_int, [_P, _P, _P, _I64, _P]),
+    "sav_fill_f32": (C.c_int, [_P, _F, _I64, _P]),
+}
+
+
+def lib():
+    """Load (once) and return the shared library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise SavError(
+                f"{LIB_PATH} not found: run `python __graft_entry__.py` (build()) first. "
+                "There is no CPU or PyTorch fallback for the hot path.")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        if l.sav_abi_version() != 1:
+            raise SavError("libsav_b200.so ABI version mismatch")
+        _lib = l
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise SavError(f"sav error {rc}: {lib().sav_last_error().decode()}")
+
+
+def launch_count():
+    return int(lib().sav_launch_count())

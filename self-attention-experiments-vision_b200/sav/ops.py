@@ -1,0 +1,231 @@
+"""Functional forward/backward ops over torch device buffers; each is one C-ABI call.
+
+torch is used only as the device allocator / stream owner.  All arithmetic runs in
+libsav_b200.so; nothing here falls back to torch ops.
+"""
+import ctypes as C
+import math
+
+import torch
+
+from . import _abi
+from ._abi import AttnBwdArgs, AttnFwdArgs, GemmArgs, check, lib
+
+BF16 = torch.bfloat16
+F32 = torch.float32
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _req(t, dtype, name):
+    if t.dtype != dtype or not t.is_cuda:
+        raise _abi.SavError(f"{name}: expected CUDA {dtype}, got {t.dtype} on {t.device}")
+
+
+_ws_cache = {}
+
+
+def _workspace(nbytes, device, tag="gemm"):
+    """Grow-only scratch per (device, tag, stream); reused across calls on the same stream."""
+    key = (device, tag, torch.cuda.current_stream().cuda_stream)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+def gemm(A, B, *, a_mn=False, b_mn=False, out=None, out_fp32=False, bias=None, act=0,
+         aux_out=None, aux_in=None, col_scale=None, row_scale=None, rows_per_scale=1,
+         residual=None, accumulate=False, split_k=1):
+    """D[M,N] = epi(sum_k A[m,k] B[n,k]).  A: [M,K] (or [K,M] if a_mn); B: [N,K] (or [K,N] if b_mn).
+
+    2-D bf16 tensors with unit inner stride; row strides are taken from the tensors, so column
+    slices of a wider buffer are fine.
+    """
+    _req(A, BF16, "A"); _req(B, BF16, "B")
+    assert A.dim() == 2 and B.dim() == 2 and A.stride(1) == 1 and B.stride(1) == 1
+    M, K = (A.shape[1], A.shape[0]) if a_mn else (A.shape[0], A.shape[1])
+    N, Kb = (B.shape[1], B.shape[0]) if b_mn else (B.shape[0], B.shape[1])
+    if K != Kb:
+        raise _abi.SavError(f"gemm: contraction mismatch {K} vs {Kb}")
+    if out is None:
+        out = torch.empty((M, N), dtype=F32 if out_fp32 else BF16, device=A.device)
+    assert out.shape == (M, N) and out.stride(1) == 1
+    a = GemmArgs()
+    a.A, a.B, a.D = A.data_ptr(), B.data_ptr(), out.data_ptr()
+    a.M, a.N, a.K = M, N, K
+    a.lda, a.ldb, a.ldd = A.stride(0), B.stride(0), out.stride(0)
+    a.a_mn, a.b_mn = int(a_mn), int(b_mn)
+    a.d_fp32 = int(out.dtype == F32)
+    a.split_k = split_k
+    a.bias = bias.data_ptr() if bias is not None else None
+    a.act = act
+    a.accumulate = int(accumulate)
+    for name, t in (("aux_out", aux_out), ("aux_in", aux_in)):
+        if t is not None:
+            assert t.shape == (M, N) and t.stride(0) == out.stride(0) and t.dtype == BF16
+            setattr(a, name, t.data_ptr())
+    if col_scale is not None:
+        _req(col_scale, F32, "col_scale"); a.col_scale = col_scale.data_ptr()
+    if row_scale is not None:
+        _req(row_scale, F32, "row_scale"); a.row_scale = row_scale.data_ptr()
+    a.rows_per_scale = rows_per_scale
+    if residual is not None:
+        _req(residual, BF16, "residual")
+        assert residual.shape == (M, N) and residual.stride(1) == 1
+        a.residual, a.ldr = residual.data_ptr(), residual.stride(0)
+    need = lib().sav_gemm_workspace_bytes(C.byref(a))
+    if need:
+        ws = _workspace(need, A.device)
+        a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+    check(lib().sav_gemm(C.byref(a), _stream()))
+    return out
+
+
+def colsum(X, out=None, accumulate=False):
+    _req(X, BF16, "X")
+    M, N = X.shape
+    if out is None:
+        out = torch.empty(N, dtype=F32, device=X.device)
+    check(lib().sav_colsum_bf16(_p(X), M, N, X.stride(0), _p(out), int(accumulate), _stream()))
+    return out
+
+
+def layernorm_fwd(x, scale, bias, eps=1e-6):
+    _req(x, BF16, "x")
+    C_ = x.shape[-1]
+    rows = x.numel() // C_
+    assert x.is_contiguous()
+    y = torch.empty_like(x)
+    mean = torch.empty(rows, dtype=F32, device=x.device)
+    rstd = torch.empty(rows, dtype=F32, device=x.device)
+    check(lib().sav_layernorm_fwd(_p(x), _p(scale), _p(bias), _p(y), _p(mean), _p(rstd), rows, C_,
+                                  eps, _stream()))
+    return y, mean, rstd
+
+
+def layernorm_bwd(dy, x, scale, mean, rstd, dscale, dbias, dx_add=None, accumulate=False):
+    C_ = x.shape[-1]
+    rows = x.numel() // C_
+    assert dy.is_contiguous() and x.is_contiguous()
+    dx = torch.empty_like(x)
+    ws = _workspace(lib().sav_layernorm_bwd_workspace_bytes(rows, C_), x.device, "ln")
+    check(lib().sav_layernorm_bwd(_p(dy), _p(x), _p(scale), _p(mean), _p(rstd), _p(dx_add), _p(dx),
+                                  _p(dscale), _p(dbias), _p(ws), rows, C_, int(accumulate),
+                                  _stream()))
+    return dx
+
+
+def patchify(images, ph, pw, hwcn=True):
+    """images fp32 [H,W,C,N] (hwcn) or [N,H,W,C] -> bf16 [N*gh*gw, ph*pw*C]."""
+    _req(images, F32, "images")
+    assert images.is_contiguous()
+    if hwcn:
+        H, W, Cc, N = images.shape
+    else:
+        N, H, W, Cc = images.shape
+    out = torch.empty((N * (H // ph) * (W // pw), ph * pw * Cc), dtype=BF16, device=images.device)
+    check(lib().sav_patchify(_p(images), _p(out), N, H, W, Cc, ph, pw, int(hwcn), _stream()))
+    return out
+
+
+def embed_fwd(tok, cls, pos, B, n_tok, C_):
+    has_cls = cls is not None
+    x = torch.empty((B, n_tok + int(has_cls), C_), dtype=BF16, device=tok.device)
+    check(lib().sav_embed_fwd(_p(tok), _p(cls), _p(pos), _p(x), B, n_tok, C_, int(has_cls), _stream()))
+    return x
+
+
+def embed_bwd(dx, dcls, dpos, B, n_tok, C_, accumulate=False):
+    has_cls = dcls is not None
+    dtok = torch.empty((B * n_tok, C_), dtype=BF16, device=dx.device)
+    check(lib().sav_embed_bwd(_p(dx), _p(dtok), _p(dcls), _p(dpos), B, n_tok, C_, int(has_cls),
+                              int(accumulate), _stream()))
+    return dtok
+
+
+def _bnhd_strides(t):
+    """t: [B,N,H,D] view with D contiguous and H stride == D."""
+    assert t.dim() == 4 and t.stride(3) == 1 and t.stride(2) == t.shape[3]
+    return t.stride(0), t.stride(1)
+
+
+def attn_fwd(q, k, v, scale=None):
+    """q [B,Nq,H,D], k/v [B,Nk,H,D] bf16 (strided views ok) -> o [B,Nq,H,D], lse [B,H,Nq]."""
+    B, Nq, H, D = q.shape
+    Nk = k.shape[1]
+    o = torch.empty((B, Nq, H, D), dtype=BF16, device=q.device)
+    lse = torch.empty((B, H, Nq), dtype=F32, device=q.device)
+    a = AttnFwdArgs()
+    a.q, a.k, a.v, a.o, a.lse = q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr()
+    a.B, a.H, a.Nq, a.Nk, a.D = B, H, Nq, Nk, D
+    a.q_batch_stride, a.q_row_stride = _bnhd_strides(q)
+    a.k_batch_stride, a.k_row_stride = _bnhd_strides(k)
+    a.v_batch_stride, a.v_row_stride = _bnhd_strides(v)
+    a.o_batch_stride, a.o_row_stride = _bnhd_strides(o)
+    a.scale = scale if scale is not None else 1.0 / math.sqrt(D)
+    check(lib().sav_attn_fwd(C.byref(a), _stream()))
+    return o, lse
+
+
+def attn_bwd(q, k, v, o, d_o, lse, dq, dk, dv, scale=None):
+    """Writes dq/dk/dv (views with the same strides as q/k/v)."""
+    B, Nq, H, D = q.shape
+    Nk = k.shape[1]
+    assert d_o.stride() == o.stride()
+    assert dq.stride() == q.stride() and dk.stride() == k.stride() and dv.stride() == v.stride()
+    delta = torch.empty((B, H, Nq), dtype=F32, device=q.device)
+    dq_acc = torch.empty((B, Nq, H, D), dtype=F32, device=q.device)
+    a = AttnBwdArgs()
+    a.q, a.k, a.v, a.o, a.d_o, a.lse = (q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(),
+                                        d_o.data_ptr(), lse.data_ptr())
+    a.dq, a.dk, a.dv = dq.data_ptr(), dk.data_ptr(), dv.data_ptr()
+    a.delta, a.dq_accum = delta.data_ptr(), dq_acc.data_ptr()
+    a.B, a.H, a.Nq, a.Nk, a.D = B, H, Nq, Nk, D
+    a.q_batch_stride, a.q_row_stride = _bnhd_strides(q)
+    a.k_batch_stride, a.k_row_stride = _bnhd_strides(k)
+    a.v_batch_stride, a.v_row_stride = _bnhd_strides(v)
+    a.o_batch_stride, a.o_row_stride = _bnhd_strides(o)
+    a.scale = scale if scale is not None else 1.0 / math.sqrt(D)
+    check(lib().sav_attn_bwd(C.byref(a), _stream()))
+
+
+def softmax_xent(logits, labels, label_smoothing=0.0, grad_scale=1.0):
+    """logits bf16 [B,classes], labels int32 [B] -> (dlogits bf16, stats fp32 [loss_sum, top1])."""
+    _req(logits, BF16, "logits")
+    B, classes = logits.shape
+    dl = torch.empty_like(logits)
+    stats = torch.empty(2, dtype=F32, device=logits.device)
+    check(lib().sav_softmax_xent(_p(logits), logits.stride(0), _p(labels), B, classes,
+                                 label_smoothing, grad_scale, _p(dl), _p(stats), _stream()))
+    return dl, stats
+
+
+def cast_bf16(src, dst):
+    check(lib().sav_cast_f32_bf16(_p(src), _p(dst), src.numel(), _stream()))
+
+
+def sumsq(g, out):
+    check(lib().sav_sumsq(_p(g), g.numel(), _p(out), _stream()))
+
+
+def fill(t, v):
+    check(lib().sav_fill_f32(_p(t), float(v), t.numel(), _stream()))
+
+
+def adam_step(p, g, m, v, p_bf16, sumsq_buf, max_norm, lr, b1, b2, eps, wd, t):
+    check(lib().sav_adam_step(_p(p), _p(g), _p(m), _p(v), _p(p_bf16), p.numel(), _p(sumsq_buf),
+                              max_norm, lr, b1, b2, eps, wd, t, _stream()))
+
+
+def add(a, b):
+    y = torch.empty_like(a)
+    check(lib().sav_add_bf16(_p(a), _p(b), _p(y), a.numel(), _stream()))
+    return y

@@ -1,0 +1,188 @@
+"""GPU bring-up diagnostics: each kernel family against a torch-on-GPU fp32 restatement, one
+subprocess per case (a hang or fault in one case cannot take the others down).
+
+    python tests/gpu_diag.py            # run all cases, print a table, exit 1 on any failure
+    python tests/gpu_diag.py --case gemm_kk_128
+This is a development tool; the parity tests proper are tests/test_*_gpu.py (vs the oracle).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "self-attention-experiments-vision_b200"))
+
+
+def rel_err(a, b):
+    import torch
+    a = a.float(); b = b.float()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-12))
+
+
+def case_gemm(a_mn, b_mn, N, epi="none", M=300, K=192, split_k=1):
+    import torch
+    from sav import ops
+    torch.manual_seed(0)
+    dev = "cuda"
+    A = torch.randn(M, K, device=dev).bfloat16()
+    B = torch.randn(N, K, device=dev).bfloat16()
+    ref = A.float() @ B.float().t()
+    Ain = A.t().contiguous() if a_mn else A
+    Bin = B.t().contiguous() if b_mn else B
+    kw = {}
+    if epi == "bias_gelu":
+        bias = torch.randn(N, device=dev)
+        aux = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+        kw = dict(bias=bias, act=1, aux_out=aux)
+        pre = ref + bias
+        ref = torch.nn.functional.gelu(pre, approximate="tanh")
+    elif epi == "full":
+        bias = torch.randn(N, device=dev)
+        cs = torch.rand(N, device=dev) + 0.5
+        rs = torch.rand((M + 49) // 50, device=dev) + 0.5
+        res = torch.randn(M, N, device=dev).bfloat16()
+        kw = dict(bias=bias, col_scale=cs, row_scale=rs, rows_per_scale=50, residual=res)
+        ref = (ref + bias) * cs * rs.repeat_interleave(50)[:M, None] + res.float()
+    elif epi == "dgelu":
+        h = torch.randn(M, N, device=dev).bfloat16()
+        kw = dict(aux_in=h)
+        hf = h.float().requires_grad_(True)
+        g, = torch.autograd.grad(torch.nn.functional.gelu(hf, approximate="tanh").sum(), hf)
+        ref = ref * g
+    elif epi == "fp32":
+        kw = dict(out_fp32=True, split_k=split_k)
+    out = ops.gemm(Ain, Bin, a_mn=a_mn, b_mn=b_mn, **kw)
+    torch.cuda.synchronize()
+    errs = {"out": rel_err(out, ref)}
+    if epi == "bias_gelu":
+        errs["aux"] = rel_err(kw["aux_out"], pre)
+    return errs
+
+
+def case_ln():
+    import torch
+    from sav import ops
+    torch.manual_seed(0)
+    rows, C = 1000, 384
+    x = (torch.randn(rows, C, device="cuda") * 2 + 0.5).bfloat16()
+    g = torch.randn(C, device="cuda"); b = torch.randn(C, device="cuda")
+    y, mean, rstd = ops.layernorm_fwd(x, g, b)
+    xf = x.float().requires_grad_(True)
+    gf = g.clone().requires_grad_(True); bf = b.clone().requires_grad_(True)
+    ref = torch.nn.functional.layer_norm(xf, (C,), gf, bf, eps=1e-6)
+    dy = torch.randn(rows, C, device="cuda").bfloat16()
+    add = torch.randn(rows, C, device="cuda").bfloat16()
+    ref.backward(dy.float())
+    ds = torch.empty(C, device="cuda"); db = torch.empty(C, device="cuda")
+    dx = ops.layernorm_bwd(dy, x, g, mean, rstd, ds, db, dx_add=add)
+    torch.cuda.synchronize()
+    return {"y": rel_err(y, ref), "dx": rel_err(dx, xf.grad + add.float()),
+            "dscale": rel_err(ds, gf.grad), "dbias": rel_err(db, bf.grad)}
+
+
+def case_attn(B=2, H=3, Nq=197, Nk=197, bwd=True):
+    import torch
+    from sav import ops
+    torch.manual_seed(0)
+    D = 64
+    C = H * D
+    qkv = torch.randn(B, max(Nq, Nk), 3, H, D, device="cuda").bfloat16()
+    q, k, v = qkv[:, :Nq, 0], qkv[:, :Nk, 1], qkv[:, :Nk, 2]
+    o, lse = ops.attn_fwd(q, k, v)
+    qf, kf, vf = (t.float().permute(0, 2, 1, 3).detach().requires_grad_(True) for t in (q, k, v))
+    s = (qf / 8.0) @ kf.transpose(-1, -2)
+    pr = torch.softmax(s, -1)
+    ref = (pr @ vf).permute(0, 2, 1, 3)
+    errs = {"o": rel_err(o, ref),
+            "lse": rel_err(lse, torch.logsumexp(s, -1))}
+    if bwd:
+        d_o = torch.randn(B, Nq, H, D, device="cuda").bfloat16()
+        ref.backward(d_o.float())
+        dqkv = torch.zeros_like(qkv)
+        ops.attn_bwd(q, k, v, o, d_o, lse, dqkv[:, :Nq, 0], dqkv[:, :Nk, 1], dqkv[:, :Nk, 2])
+        torch.cuda.synchronize()
+        errs["dq"] = rel_err(dqkv[:, :Nq, 0], qf.grad.permute(0, 2, 1, 3))
+        errs["dk"] = rel_err(dqkv[:, :Nk, 1], kf.grad.permute(0, 2, 1, 3))
+        errs["dv"] = rel_err(dqkv[:, :Nk, 2], vf.grad.permute(0, 2, 1, 3))
+    torch.cuda.synchronize()
+    return errs
+
+
+def case_stem():
+    import torch
+    from sav import ops
+    torch.manual_seed(0)
+    N, H, W, Cc, p = 70, 32, 48, 3, 16
+    img = torch.randn(H, W, Cc, N, device="cuda")
+    out = ops.patchify(img, p, p, hwcn=True)
+    nhwc = img.permute(3, 0, 1, 2).contiguous()
+    ref = nhwc.reshape(N, H // p, p, W // p, p, Cc).permute(0, 1, 3, 2, 4, 5).reshape(-1, p * p * Cc)
+    out2 = ops.patchify(nhwc, p, p, hwcn=False)
+    torch.cuda.synchronize()
+    return {"hwcn": rel_err(out, ref.bfloat16()), "nhwc": rel_err(out2, ref.bfloat16())}
+
+
+CASES = {}
+for am in (0, 1):
+    for bm in (0, 1):
+        for n in (384, 256):
+            tag = f"gemm_{'m' if am else 'k'}{'m' if bm else 'k'}_{128 if n % 256 else 256}"
+            CASES[tag] = (case_gemm, dict(a_mn=bool(am), b_mn=bool(bm), N=n))
+CASES["gemm_bias_gelu"] = (case_gemm, dict(a_mn=False, b_mn=True, N=384, epi="bias_gelu"))
+CASES["gemm_full_epi"] = (case_gemm, dict(a_mn=False, b_mn=True, N=384, epi="full"))
+CASES["gemm_dgelu"] = (case_gemm, dict(a_mn=False, b_mn=False, N=384, epi="dgelu"))
+CASES["gemm_fp32"] = (case_gemm, dict(a_mn=True, b_mn=True, N=384, epi="fp32", M=192, K=3000))
+CASES["gemm_splitk"] = (case_gemm, dict(a_mn=True, b_mn=True, N=384, epi="fp32", M=192, K=3000, split_k=5))
+CASES["gemm_big"] = (case_gemm, dict(a_mn=False, b_mn=True, N=1152, M=4000, K=384))
+CASES["ln"] = (case_ln, {})
+CASES["stem"] = (case_stem, {})
+CASES["attn_fwd_197"] = (case_attn, dict(bwd=False))
+CASES["attn_fwd_64"] = (case_attn, dict(Nq=64, Nk=64, bwd=False))
+CASES["attn_197"] = (case_attn, {})
+CASES["attn_577"] = (case_attn, dict(B=1, H=2, Nq=577, Nk=577))
+CASES["attn_cross"] = (case_attn, dict(B=2, H=2, Nq=225, Nk=64))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--case")
+    ap.add_argument("--tol", type=float, default=2e-2)
+    ap.add_argument("--only", default="")
+    args = ap.parse_args()
+    if args.case:
+        fn, kw = CASES[args.case]
+        print("RESULT " + json.dumps(fn(**kw)))
+        return 0
+    bad = 0
+    results = {}
+    for name in CASES:
+        if args.only and args.only not in name:
+            continue
+        try:
+            r = subprocess.run([sys.executable, __file__, "--case", name], capture_output=True,
+                               text=True, timeout=90)
+            line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")]
+            if r.returncode == 0 and line:
+                errs = json.loads(line[-1][7:])
+                ok = all(e == e and e < args.tol for e in errs.values())
+                results[name] = errs
+                print(f"{'ok  ' if ok else 'FAIL'} {name:18s} " +
+                      " ".join(f"{k}={v:.2e}" for k, v in errs.items()), flush=True)
+                bad += not ok
+            else:
+                bad += 1
+                tail = (r.stderr or r.stdout).strip().splitlines()[-3:]
+                print(f"FAIL {name:18s} rc={r.returncode} {' | '.join(tail)}", flush=True)
+        except subprocess.TimeoutExpired:
+            bad += 1
+            print(f"HANG {name:18s} (timeout)", flush=True)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "diag.json"), "w") as f:
+        json.dump(results, f, indent=1)
+    return 1 if bad else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
