@@ -21,7 +21,7 @@ def rel_err(a, b):
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-12))
 
 
-def case_gemm(a_mn, b_mn, N, epi="none", M=300, K=192, split_k=1):
+def case_gemm(a_mn, b_mn, N, epi="none", M=296, K=192, split_k=1):
     import torch
     from sav import ops
     torch.manual_seed(0)
