@@ -177,6 +177,9 @@ int sav_adam_step(float* p, const float* g, float* m, float* v, void* p_bf16, in
 /* elementwise helpers (bf16): y = a + b ; used only where no GEMM epilogue can absorb the add */
 int sav_add_bf16(const void* a, const void* b, void* y, int64_t n, void* stream);
 int sav_fill_f32(float* p, float v, int64_t n, void* stream);
+/* strided row copy dst[r, 0:cols] = src[r, 0:cols] (class-token gather/scatter, vit.py:95) */
+int sav_copy2d_bf16(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t rows,
+                    int64_t cols, void* stream);
 
 #ifdef __cplusplus
 }

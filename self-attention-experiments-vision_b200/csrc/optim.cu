@@ -136,6 +136,17 @@ __global__ void add_kernel(const bf16* __restrict__ a, const bf16* __restrict__ 
   }
 }
 
+__global__ void copy2d_kernel(const bf16* __restrict__ src, int64_t lds, bf16* __restrict__ dst,
+                              int64_t ldd, int64_t rows, int cols8) {
+  const int64_t total = rows * cols8;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / cols8;
+    const int c = (int)(i - r * cols8) * 8;
+    *reinterpret_cast<uint4*>(dst + r * ldd + c) = *reinterpret_cast<const uint4*>(src + r * lds + c);
+  }
+}
+
 static int grid_for(int64_t work, int threads) {
   int64_t b = (work + threads - 1) / threads;
   const int64_t cap = 148 * 8;
@@ -198,4 +209,15 @@ extern "C" int sav_add_bf16(const void* a, const void* b, void* y, int64_t n, vo
       reinterpret_cast<bf16*>(y), n / 8);
   count_launch();
   return check_launch("sav_add_bf16");
+}
+
+extern "C" int sav_copy2d_bf16(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t rows,
+                               int64_t cols, void* stream) {
+  if (rows <= 0 || cols <= 0) return SAV_OK;
+  if (cols % 8 || lds % 8 || ldd % 8 || !aligned16(src) || !aligned16(dst))
+    return set_error(SAV_ERR_ALIGN, "sav_copy2d_bf16: cols/ld %% 8 and 16 B alignment required");
+  copy2d_kernel<<<grid_for(rows * (cols / 8), 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const bf16*>(src), lds, reinterpret_cast<bf16*>(dst), ldd, rows, (int)(cols / 8));
+  count_launch();
+  return check_launch("sav_copy2d_bf16");
 }

@@ -1,0 +1,2 @@
+from models.vit import ViT  # noqa: F401
+from models.create_model import create_model  # noqa: F401

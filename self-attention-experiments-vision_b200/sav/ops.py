@@ -229,3 +229,10 @@ def add(a, b):
     y = torch.empty_like(a)
     check(lib().sav_add_bf16(_p(a), _p(b), _p(y), a.numel(), _stream()))
     return y
+
+
+def copy2d(src, dst):
+    """dst[r, :] = src[r, :] for 2-D bf16 views with unit inner stride."""
+    rows, cols = src.shape
+    assert dst.shape == src.shape and src.stride(1) == 1 and dst.stride(1) == 1
+    check(lib().sav_copy2d_bf16(_p(src), src.stride(0), _p(dst), dst.stride(0), rows, cols, _stream()))
