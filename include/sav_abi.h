@@ -115,8 +115,7 @@ int sav_embed_bwd(const void* dx, void* dtok, float* dcls, float* dpos, int64_t 
  *   ptr + b*batch_stride + token*row_stride + h*D           (strides in elements)
  * so they can alias slices of a fused [B,N,3,H,D] QKV buffer.  lse fp32 [B,H,Nq] (natural log of
  * the softmax denominator incl. max) is saved for backward.
- * rel_w / rel_h (BoTNet, botnet.py:70-141): optional fp32-free bf16 tables [2W-1,D],[2H-1,D];
- * NULL for plain attention.  D in {64}.  (D=48/128: see DESIGN.md status table.)
+ * D = 64 (D=48/128 and BoTNet relative logits: see DESIGN.md status table).
  */
 typedef struct {
   const void* q;
@@ -169,10 +168,12 @@ int sav_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
 int sav_sumsq(const float* g, int64_t n, float* out, void* stream);
 /* optax chain of train.py:25-27 / simple_train.py:25-27 as one pass over the arena:
  * g *= min(1, max_norm/||g||) (sumsq[0] holds ||g||^2; max_norm<=0 disables) -> Adam(b1,b2,eps,
- * bias-corrected with step t) -> + wd*p -> * (-lr) -> p += update; also refreshes bf16 shadow. */
+ * bias-corrected with step t) -> + wd*p -> * (-lr) -> p += update; also refreshes bf16 shadow.
+ * hyper (optional, device fp32[3] = {lr, 1-b1^t, 1-b2^t}) overrides lr/t so that the step can be
+ * replayed from a CUDA graph while the schedule advances. */
 int sav_adam_step(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n,
                   const float* sumsq, float max_norm, float lr, float b1, float b2, float eps,
-                  float wd, int64_t t, void* stream);
+                  float wd, int64_t t, const float* hyper, void* stream);
 
 /* elementwise helpers (bf16): y = a + b ; used only where no GEMM epilogue can absorb the add */
 int sav_add_bf16(const void* a, const void* b, void* y, int64_t n, void* stream);

@@ -98,7 +98,9 @@ __global__ void sumsq_kernel(const float* __restrict__ g, int64_t n, float* __re
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g,
                             float* __restrict__ m, float* __restrict__ v, bf16* __restrict__ pb,
                             int64_t n, const float* __restrict__ sumsq, float max_norm, float lr,
-                            float b1, float b2, float eps, float wd, float bc1, float bc2) {
+                            float b1, float b2, float eps, float wd, float bc1, float bc2,
+                            const float* __restrict__ hyper) {
+  if (hyper) { lr = hyper[0]; bc1 = hyper[1]; bc2 = hyper[2]; }
   float clip = 1.f;
   if (max_norm > 0.f && sumsq) {
     const float gn = sqrtf(sumsq[0]);
@@ -190,12 +192,14 @@ extern "C" int sav_sumsq(const float* g, int64_t n, float* out, void* stream) {
 
 extern "C" int sav_adam_step(float* p, const float* g, float* m, float* v, void* p_bf16,
                              int64_t n, const float* sumsq, float max_norm, float lr, float b1,
-                             float b2, float eps, float wd, int64_t t, void* stream) {
+                             float b2, float eps, float wd, int64_t t, const float* hyper,
+                             void* stream) {
   if (n <= 0) return SAV_OK;
-  if (t < 1) return set_error(SAV_ERR_ARG, "sav_adam_step: step count t starts at 1");
+  if (t < 1 && !hyper) return set_error(SAV_ERR_ARG, "sav_adam_step: step count t starts at 1");
   const float bc1 = 1.f - powf(b1, (float)t), bc2 = 1.f - powf(b2, (float)t);
   adam_kernel<<<grid_for(n, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      p, g, m, v, reinterpret_cast<bf16*>(p_bf16), n, sumsq, max_norm, lr, b1, b2, eps, wd, bc1, bc2);
+      p, g, m, v, reinterpret_cast<bf16*>(p_bf16), n, sumsq, max_norm, lr, b1, b2, eps, wd, bc1, bc2,
+      hyper);
   count_launch();
   return check_launch("sav_adam_step");
 }

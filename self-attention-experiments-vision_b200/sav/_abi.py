@@ -81,7 +81,7 @@ SIGNATURES = {
     "sav_softmax_xent": (C.c_int, [_P, _I64, _P, _I64, _I64, _F, _F, _P, _P, _P]),
     "sav_cast_f32_bf16": (C.c_int, [_P, _P, _I64, _P]),
     "sav_sumsq": (C.c_int, [_P, _I64, _P, _P]),
-    "sav_adam_step": (C.c_int, [_P, _P, _P, _P, _P, _I64, _P, _F, _F, _F, _F, _F, _F, _I64, _P]),
+    "sav_adam_step": (C.c_int, [_P, _P, _P, _P, _P, _I64, _P, _F, _F, _F, _F, _F, _F, _I64, _P, _P]),
     "sav_add_bf16": (C.c_int, [_P, _P, _P, _I64, _P]),
     "sav_fill_f32": (C.c_int, [_P, _F, _I64, _P]),
     "sav_copy2d_bf16": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, _P]),

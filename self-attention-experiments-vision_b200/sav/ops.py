@@ -220,9 +220,9 @@ def fill(t, v):
     check(lib().sav_fill_f32(_p(t), float(v), t.numel(), _stream()))
 
 
-def adam_step(p, g, m, v, p_bf16, sumsq_buf, max_norm, lr, b1, b2, eps, wd, t):
+def adam_step(p, g, m, v, p_bf16, sumsq_buf, max_norm, lr, b1, b2, eps, wd, t, hyper=None):
     check(lib().sav_adam_step(_p(p), _p(g), _p(m), _p(v), _p(p_bf16), p.numel(), _p(sumsq_buf),
-                              max_norm, lr, b1, b2, eps, wd, t, _stream()))
+                              max_norm, lr, b1, b2, eps, wd, t, _p(hyper), _stream()))
 
 
 def add(a, b):

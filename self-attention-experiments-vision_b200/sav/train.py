@@ -48,19 +48,31 @@ class TrainState:
         self.lr, self.wd, self.clip = lr, weight_decay, clip_grad
         self.b1, self.b2, self.eps = b1, b2, eps
         self.sumsq = torch.zeros(1, dtype=torch.float32, device=self.arena.device)
+        # {lr, 1-b1^t, 1-b2^t}: lives on the device so a captured step can be replayed
+        self.hyper = torch.zeros(3, dtype=torch.float32, device=self.arena.device)
+        self._hyper_host = torch.zeros(3, dtype=torch.float32).pin_memory()
 
-    def apply_gradients(self, lr=None):
-        a = self.arena
+    def advance_schedule(self):
+        """Host side of scale_by_schedule / Adam bias correction for the NEXT apply_gradients;
+        enqueue before the (possibly graph-replayed) step."""
         self.step += 1
+        lr_t = self.lr(self.step) if callable(self.lr) else self.lr
+        self._hyper_host[0] = float(lr_t)
+        self._hyper_host[1] = 1.0 - self.b1 ** self.step
+        self._hyper_host[2] = 1.0 - self.b2 ** self.step
+        self.hyper.copy_(self._hyper_host, non_blocking=True)
+
+    def apply_gradients(self):
+        """clip -> Adam -> +wd*p -> *(-lr) -> apply (train.py:25-27,100), one pass over the arena.
+        Reads lr / bias corrections from self.hyper (call advance_schedule() first)."""
+        a = self.arena
         use_clip = self.clip is not None and self.clip > 0
         if use_clip:
             ops.fill(self.sumsq, 0.0)
             ops.sumsq(a.grad, self.sumsq)
-        lr_t = lr(self.step) if callable(lr) else (lr if lr is not None else
-                                                   (self.lr(self.step) if callable(self.lr) else self.lr))
         ops.adam_step(a.master, a.grad, a.m, a.v, a.shadow, self.sumsq,
-                      float(self.clip) if use_clip else 0.0, float(lr_t), self.b1, self.b2,
-                      self.eps, self.wd, self.step)
+                      float(self.clip) if use_clip else 0.0, 0.0, self.b1, self.b2,
+                      self.eps, self.wd, 1, hyper=self.hyper)
 
 
 def train_step(state, images, labels, label_smoothing=0.0, dp=None):
@@ -73,3 +85,30 @@ def train_step(state, images, labels, label_smoothing=0.0, dp=None):
         dp.all_reduce_grads(state.arena)
     state.apply_gradients()
     return loss
+
+
+class GraphedTrainStep:
+    """One full training step (patchify .. optimizer) captured into a CUDA graph and replayed:
+    launch-bound host work disappears (SURVEY 3.1's XLA executable, done with streams + graphs)."""
+
+    def __init__(self, state, images, labels, label_smoothing=0.0, dp=None, warmup=2):
+        self.state, self.images, self.labels = state, images, labels
+        self.stream = torch.cuda.Stream()
+        self.stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.stream):
+            for _ in range(warmup):
+                state.advance_schedule()
+                self.loss = train_step(state, images, labels, label_smoothing, dp)
+        torch.cuda.current_stream().wait_stream(self.stream)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        from . import _abi
+        n0 = _abi.launch_count()
+        with torch.cuda.graph(self.graph, stream=self.stream):
+            self.loss = train_step(state, images, labels, label_smoothing, dp)
+        self.launches_per_step = _abi.launch_count() - n0
+
+    def __call__(self):
+        self.state.advance_schedule()
+        self.graph.replay()
+        return self.loss
