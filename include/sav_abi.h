@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define SAV_ABI_VERSION 1
+#define SAV_ABI_VERSION 2
 
 enum sav_status {
   SAV_OK = 0,
@@ -45,14 +45,22 @@ int64_t sav_launch_count(void);
  * Operand storage:
  *   a_mn=0: A is row-major [M,K] (K contiguous);  a_mn=1: A is row-major [K,M] (M contiguous)
  *   b_mn=0: B is row-major [N,K] (K contiguous);  b_mn=1: B is row-major [K,N] (N contiguous)
- * Epilogue, in this order (each optional):
- *   v = acc + bias[n]; aux_out[m,n] = bf16(v); v = gelu_tanh(v) if act==1;
- *   v *= dgelu_tanh(aux_in[m,n]); v *= col_scale[n]; v *= row_scale[m / rows_per_scale];
- *   v += residual[m,n]; D[m,n] = v  (bf16, or fp32 when d_fp32)
- * split_k > 1: K is partitioned, fp32 partials go to `workspace` ([split_k,M,N] fp32) and a second
- *   kernel reduces them into D (requires d_fp32=1 and no epilogue except bias-free identity);
- *   used for dW = X^T dY where K = tokens.
- * Alignment: all base pointers 16 B aligned; lda/ldb/ldd/ldr multiples of 8 elements; N % 8 == 0.
+ * Output / epilogue modes (selected from the arguments; anything else is SAV_ERR_ARG):
+ *   bf16 D           : v = acc + bias[n]; v *= col_scale[n]; v *= row_scale[m / rows_per_scale];
+ *                      D = bf16(act ? gelu_tanh(v) : v)
+ *   bf16 D + aux_out : (act=1) aux_out = bf16(acc + bias) [pre-activation saved for backward],
+ *                      D = bf16(gelu_tanh(acc + bias))                       (ff.py:24-25)
+ *   bf16 D + aux_in  : D = bf16(acc * gelu_tanh'(aux_in[m,n]))               (reverse of ff.py:25)
+ *   fp32 D           : v = acc + bias; v *= col_scale; v *= row_scale; v += residual[m,n] (fp32);
+ *                      D = v        -- the fp32 residual stream (vit.py:24,31; layerscale.py:20-23;
+ *                      stochastic_depth.py:16-27)
+ *   fp32 D, accumulate or split_k != 1 : D += acc, K partitioned over split_k CTAs groups whose
+ *                      partial tiles are combined with TMA reduce-add in L2 (dW = X^T dY where
+ *                      K = tokens).  split_k = 0 picks the split automatically.  With
+ *                      accumulate=0 the callee zero-fills D first.
+ * All D / aux / residual traffic goes through TMA (row pitches must be multiples of 16 bytes).
+ * Alignment: all base pointers 16 B aligned; lda/ldb/ldd(bf16) multiples of 8, ldd(fp32)/ldr
+ * multiples of 4 elements; N % 8 == 0.
  */
 typedef struct {
   const void* A;
@@ -69,9 +77,9 @@ typedef struct {
   const float* col_scale;  /* [N] LayerScale (layerscale.py:20-23) or NULL */
   const float* row_scale;  /* [ceil(M/rows_per_scale)] drop-path (stochastic_depth.py:16-27) */
   int64_t rows_per_scale;
-  const void* residual;    /* bf16 [M,N] ld=ldr or NULL (vit.py:24,31) */
+  const void* residual;    /* fp32 [M,N] ld=ldr or NULL (vit.py:24,31); needs d_fp32 */
   int64_t ldr;
-  void* workspace;         /* split_k>1: >= split_k*M*N*4 bytes */
+  void* workspace;         /* unused (kept for ABI stability); may be NULL */
   int64_t workspace_bytes;
 } sav_gemm_args;
 int64_t sav_gemm_workspace_bytes(const sav_gemm_args* a);
@@ -83,17 +91,21 @@ int sav_colsum_bf16(const void* X, int64_t M, int64_t N, int64_t ldx, float* out
 
 /* ---------------------------------------------------------------- LayerNorm (vit.py:19,26,57)
  * Flax nn.LayerNorm: fp32 stats, var = E[x^2]-E[x]^2, eps inside rsqrt, y = xhat*scale + bias.
- * x,y bf16 [rows,C]; scale,bias fp32 [C]; mean,rstd fp32 [rows] (saved for backward). C % 8 == 0.
+ * x is the fp32 residual stream, row r at x + r*ldx (ldx lets the final LayerNorm run on the
+ * class-token rows only, vit.py:57,95); y bf16, row r at y + r*ldy; scale,bias fp32 [C];
+ * mean,rstd fp32 [rows] (saved for backward).  C % 8 == 0, C <= 1024.
  */
-int sav_layernorm_fwd(const void* x, const float* scale, const float* bias, void* y, float* mean,
-                      float* rstd, int64_t rows, int64_t C, float eps, void* stream);
-/* dx = LNbwd(dy) (+ dx_add if non-NULL; fuses the residual-branch gradient, vit.py:24,31);
- * dscale/dbias [C] fp32 are accumulated when accumulate!=0, else overwritten.
- * partials: fp32 workspace of sav_layernorm_bwd_workspace_bytes(rows, C). */
-int64_t sav_layernorm_bwd_workspace_bytes(int64_t rows, int64_t C);
-int sav_layernorm_bwd(const void* dy, const void* x, const float* scale, const float* mean,
-                      const float* rstd, const void* dx_add, void* dx, float* dscale, float* dbias,
-                      float* partials, int64_t rows, int64_t C, int32_t accumulate, void* stream);
+int sav_layernorm_fwd(const float* x, int64_t ldx, const float* scale, const float* bias, void* y,
+                      int64_t ldy, float* mean, float* rstd, int64_t rows, int64_t C, float eps,
+                      void* stream);
+/* dx = LNbwd(dy) (+ dx_add if non-NULL: the residual-branch gradient, vit.py:24,31), written as the
+ * fp32 stream gradient `dx` and, if dx_bf16 != NULL, also as a bf16 copy (the MMA operand of the
+ * preceding block's dX / dW GEMMs).  dx_add, dx, dx_bf16 share the row pitch ldx with x; dy (bf16)
+ * has row pitch ldy.  dscale/dbias [C] fp32 are ACCUMULATED (red.add); the caller zeroes them. */
+int sav_layernorm_bwd(const void* dy, int64_t ldy, const float* x, int64_t ldx, const float* scale,
+                      const float* mean, const float* rstd, const float* dx_add, float* dx,
+                      void* dx_bf16, float* dscale, float* dbias, int64_t rows, int64_t C,
+                      void* stream);
 
 /* ---------------------------------------------------------------- patch embedding stem
  * train.py:80-81 + patch_embed.py:19-22: images fp32 [H,W,C,N] (reference batch layout) ->
@@ -102,10 +114,11 @@ int sav_layernorm_bwd(const void* dy, const void* x, const float* scale, const f
 int sav_patchify(const float* images, void* patches, int64_t N, int64_t H, int64_t W, int64_t C,
                  int64_t ph, int64_t pw, int32_t hwcn, void* stream);
 /* vit.py:81-85 + position_embed.py:54-56: x[b,0,:] = cls + pos[0]; x[b,1+i,:] = tok[b,i,:] +
- * pos[1+i].  has_cls=0: x[b,i,:] = tok[b,i,:] + pos[i] (cait.py:69).  tok,x bf16; cls,pos fp32. */
+ * pos[1+i].  has_cls=0: x[b,i,:] = tok[b,i,:] + pos[i] (cait.py:69).  tok bf16; x fp32 (the
+ * residual stream); cls,pos fp32. */
 int sav_embed_fwd(const void* tok, const float* cls, const float* pos, void* x, int64_t B,
                   int64_t n_tok, int64_t C, int32_t has_cls, void* stream);
-/* reverse-mode of the above: dtok (bf16), dcls [C], dpos [n_tok+has_cls, C] fp32 */
+/* reverse-mode of the above: dx fp32 -> dtok (bf16), dcls [C], dpos [n_tok+has_cls, C] fp32 */
 int sav_embed_bwd(const void* dx, void* dtok, float* dcls, float* dpos, int64_t B, int64_t n_tok,
                   int64_t C, int32_t has_cls, int32_t accumulate, void* stream);
 
@@ -122,6 +135,7 @@ typedef struct {
   const void* k;
   const void* v;
   void* o;
+  void* o_lo;  /* optional (training): bf16(o_fp32 - bf16(o_fp32)), same strides as o; NULL to skip */
   float* lse;
   int64_t B, H, Nq, Nk, D;
   int64_t q_batch_stride, q_row_stride;
@@ -137,6 +151,7 @@ typedef struct {
   const void* k;
   const void* v;
   const void* o;
+  const void* o_lo; /* optional low half of o saved by sav_attn_fwd (sharper delta), or NULL */
   const void* d_o;
   const float* lse;
   void* dq;

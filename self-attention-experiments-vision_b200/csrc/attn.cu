@@ -22,6 +22,7 @@ __device__ __forceinline__ uint32_t sw128(int r, int g16) {
 
 struct AttnFwdParams {
   bf16* o;
+  bf16* o_lo;
   float* lse;
   int B, H, Nq, Nk;
   int64_t o_bs, o_rs;
@@ -174,14 +175,27 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
   const int row = qt * AT + tid;
   if (row < p.Nq) {
     const float inv = 1.f / l_run;
-    bf16* dst = p.o + (int64_t)b * p.o_bs + (int64_t)row * p.o_rs + h * AD;
+    const int64_t off = (int64_t)b * p.o_bs + (int64_t)row * p.o_rs + h * AD;
+    bf16* dst = p.o + off;
+#pragma unroll
+    for (int i = 0; i < AD; ++i) o_acc[i] *= inv;
 #pragma unroll
     for (int g = 0; g < AD / 8; ++g)
       *reinterpret_cast<uint4*>(dst + g * 8) = make_uint4(
-          pack_bf16(o_acc[g * 8 + 0] * inv, o_acc[g * 8 + 1] * inv),
-          pack_bf16(o_acc[g * 8 + 2] * inv, o_acc[g * 8 + 3] * inv),
-          pack_bf16(o_acc[g * 8 + 4] * inv, o_acc[g * 8 + 5] * inv),
-          pack_bf16(o_acc[g * 8 + 6] * inv, o_acc[g * 8 + 7] * inv));
+          pack_bf16(o_acc[g * 8 + 0], o_acc[g * 8 + 1]), pack_bf16(o_acc[g * 8 + 2], o_acc[g * 8 + 3]),
+          pack_bf16(o_acc[g * 8 + 4], o_acc[g * 8 + 5]), pack_bf16(o_acc[g * 8 + 6], o_acc[g * 8 + 7]));
+    if (p.o_lo) {
+      // low half of O (o - bf16(o)): lets backward form delta = rowsum(dO * O) from a ~16-bit
+      // mantissa O; the bf16-rounded O alone costs ~0.5e-2 of the 2e-2 gradient parity budget
+      bf16* dlo = p.o_lo + off;
+#pragma unroll
+      for (int i = 0; i < AD; ++i) o_acc[i] -= __bfloat162float(__float2bfloat16(o_acc[i]));
+#pragma unroll
+      for (int g = 0; g < AD / 8; ++g)
+        *reinterpret_cast<uint4*>(dlo + g * 8) = make_uint4(
+            pack_bf16(o_acc[g * 8 + 0], o_acc[g * 8 + 1]), pack_bf16(o_acc[g * 8 + 2], o_acc[g * 8 + 3]),
+            pack_bf16(o_acc[g * 8 + 4], o_acc[g * 8 + 5]), pack_bf16(o_acc[g * 8 + 6], o_acc[g * 8 + 7]));
+    }
     p.lse[((int64_t)b * p.H + h) * p.Nq + row] = m_run * LN2 + logf(l_run);
   }
   __syncthreads();
@@ -410,9 +424,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
 }
 
 // delta[b,h,q] = sum_d dO[b,q,h,d] * O[b,q,h,d]   (warp per (b,q): lanes over H*D/2 pairs)
-__global__ void attn_delta_kernel(const bf16* __restrict__ o, const bf16* __restrict__ d_o,
-                                  float* __restrict__ delta, int B, int H, int Nq, int64_t o_bs,
-                                  int64_t o_rs) {
+__global__ void attn_delta_kernel(const bf16* __restrict__ o, const bf16* __restrict__ o_lo,
+                                  const bf16* __restrict__ d_o, float* __restrict__ delta, int B,
+                                  int H, int Nq, int64_t o_bs, int64_t o_rs) {
   const int lane = threadIdx.x & 31;
   const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (w >= (int64_t)B * Nq * H) return;
@@ -420,7 +434,12 @@ __global__ void attn_delta_kernel(const bf16* __restrict__ o, const bf16* __rest
   const int q = (int)((w / H) % Nq);
   const int b = (int)(w / ((int64_t)H * Nq));
   const int64_t off = (int64_t)b * o_bs + (int64_t)q * o_rs + hh * AD + lane * 2;
-  const float2 a = unpack_bf16(*reinterpret_cast<const uint32_t*>(o + off));
+  float2 a = unpack_bf16(*reinterpret_cast<const uint32_t*>(o + off));
+  if (o_lo) {
+    const float2 l = unpack_bf16(*reinterpret_cast<const uint32_t*>(o_lo + off));
+    a.x += l.x;
+    a.y += l.y;
+  }
   const float2 g = unpack_bf16(*reinterpret_cast<const uint32_t*>(d_o + off));
   float s = a.x * g.x + a.y * g.y;
 #pragma unroll
@@ -478,7 +497,7 @@ extern "C" int sav_attn_fwd(const sav_attn_fwd_args* a, void* stream) {
     attr = true;
   }
   AttnFwdParams p;
-  p.o = reinterpret_cast<bf16*>(a->o); p.lse = a->lse;
+  p.o = reinterpret_cast<bf16*>(a->o); p.o_lo = reinterpret_cast<bf16*>(a->o_lo); p.lse = a->lse;
   p.B = (int)a->B; p.H = (int)a->H; p.Nq = (int)a->Nq; p.Nk = (int)a->Nk;
   p.o_bs = a->o_batch_stride; p.o_rs = a->o_row_stride;
   p.scale_log2 = a->scale * LOG2E;
@@ -508,7 +527,8 @@ extern "C" int sav_attn_bwd(const sav_attn_bwd_args* a, void* stream) {
   }
   const int64_t rows = a->B * a->Nq * a->H;
   attn_delta_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(
-      reinterpret_cast<const bf16*>(a->o), reinterpret_cast<const bf16*>(a->d_o), a->delta,
+      reinterpret_cast<const bf16*>(a->o), reinterpret_cast<const bf16*>(a->o_lo),
+      reinterpret_cast<const bf16*>(a->d_o), a->delta,
       (int)a->B, (int)a->H, (int)a->Nq, a->o_batch_stride, a->o_row_stride);
   count_launch();
   const int64_t nacc = a->B * a->Nq * a->H * AD;

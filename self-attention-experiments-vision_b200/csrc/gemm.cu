@@ -1,10 +1,18 @@
 // Persistent warp-specialised bf16 GEMM for sm_100a: TMA -> 128B-swizzled smem ring -> tcgen05.mma
-// (accumulators double-buffered in TMEM) -> fused epilogue.  One CTA per SM, 192 threads:
+// (accumulators double-buffered in TMEM) -> fused epilogue -> swizzled smem slab -> TMA store.
+// One CTA per SM, 320 threads:
 //   warp 0     TMA producer (one elected lane)
 //   warp 1     MMA issuer (one lane) + TMEM allocator
-//   warps 2-5  epilogue: tcgen05.ld -> bias / GELU / dGELU / LayerScale / drop-path / residual -> HBM
+//   warps 2-9  epilogue: every 128-row x 128-byte output slab is produced by all 8 warps (two warps
+//              per TMEM sub-partition, half of the slab's columns each): tcgen05.ld -> bias / GELU /
+//              dGELU / LayerScale / drop-path / residual -> smem slab -> one TMA store (coalesced,
+//              clipped at the M/N edges).  Epilogue *inputs* (fp32 residual stream, saved GELU
+//              pre-activation) are TMA-loaded into the very slab buffer they are combined in, a few
+//              slabs ahead, so the K=384 GEMMs of the block -- which sit on the HBM/tensor ridge --
+//              stream their epilogue traffic at full width.
 // Operands may be K-major or MN-major (selected by the smem + instruction descriptors), so
-// forward (X W), dX (dY W^T) and dW (X^T dY) all run here without any transposed copies.
+// forward (X W), dX (dY W^T) and dW (X^T dY) all run here without any transposed copies.  dW is
+// split over K (tokens) and the partial tiles are combined with TMA reduce-add (fp32) in L2.
 #include "common.cuh"
 #include "host.h"
 
@@ -12,114 +20,123 @@ namespace sav {
 
 constexpr int BM = 128;  // UMMA M
 constexpr int BK = 64;   // 64 bf16 = one 128-byte swizzle row
+constexpr int kEpiWarps = 8;
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kGemmThreads = 64 + kEpiThreads;
+constexpr int SLAB_BYTES = BM * 128;        // 128 rows x 128 B
+constexpr int kOutBytes = 4 * SLAB_BYTES;   // epilogue slab ring: 4 x 16 KB (or 2 x 32 KB)
+
+enum EpiMode { EPI_PLAIN = 0, EPI_GELU2 = 1, EPI_F32 = 2, EPI_DGELU = 3, EPI_ACCUM = 4 };
 
 struct GemmParams {
   int64_t M, N, K;
   int m_blocks, n_blocks, split_k, k_blocks, k_per_split;
-  void* D;
-  int64_t ldd;
-  int d_fp32, accumulate;
+  int epi;          // EpiMode
+  int act;          // EPI_PLAIN: 1 = tanh-GELU on the single output
+  int has_aux_in;   // EPI_F32: fp32 residual present; EPI_DGELU: always
   const float* bias;
-  int act;
-  bf16* aux_out;
-  const bf16* aux_in;
   const float* col_scale;
   const float* row_scale;
   int64_t rows_per_scale;
-  const bf16* residual;
-  int64_t ldr;
-  float* workspace;
 };
 
 template <int BN>
 struct GemmCfg {
-  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kStages = (BN == 256) ? 3 : 4;
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kSmem = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-  static constexpr uint32_t kTmemCols = 2 * BN;  // 256 or 512, power of two
+  static constexpr int kSmem = kStages * kStageBytes + kOutBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr uint32_t kTmemCols = 512;  // 2 accumulators of BN <= 256 fp32 columns
 };
 
-__device__ __forceinline__ void epilogue_group8(const GemmParams& p, float (&v)[8], int64_t row,
-                                                int col, float rs, void* Dbase, int64_t ldd) {
-  if (p.bias) {
-    const float4 b0 = *reinterpret_cast<const float4*>(p.bias + col);
-    const float4 b1 = *reinterpret_cast<const float4*>(p.bias + col + 4);
-    v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-    v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
-  }
-  if (p.aux_out) {
-    uint4 o = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
-                         pack_bf16(v[6], v[7]));
-    *reinterpret_cast<uint4*>(p.aux_out + row * p.ldd + col) = o;
-  }
-  if (p.act == 1) {
+__device__ __forceinline__ void named_bar_sync(int id, int count) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const void* src, int c0,
+                                                  int c1) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::
+          "l"(reinterpret_cast<uint64_t>(m)),
+      "r"(smem_u32(src)), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+// tanh-GELU with the hardware tanh (MUFU): the result is rounded to bf16 right after, so the
+// 2^-11 relative error of tanh.approx is below the output rounding.
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float u = x * (0.7978845608028654f + 0.035677408136300125f * x * x);
+  return 0.5f * x * (1.f + tanh_fast(u));
+}
+__device__ __forceinline__ float dgelu_fast(float x) {
+  const float x2 = x * x;
+  const float u = x * (0.7978845608028654f + 0.035677408136300125f * x2);
+  const float t = tanh_fast(u);
+  const float du = 0.7978845608028654f + 0.10703222440890037f * x2;
+  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
+}
+
+// bias / LayerScale / drop-path on NV consecutive columns starting at `col`
+template <int NV>
+__device__ __forceinline__ void epi_affine(const GemmParams& p, float (&v)[NV], int col, float rs) {
+  if (col + NV <= p.N) {
+    if (p.bias) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = gelu_tanh(v[j]);
-  }
-  if (p.aux_in) {
-    const uint4 a = *reinterpret_cast<const uint4*>(p.aux_in + row * p.ldd + col);
-    const uint32_t w[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float2 h = unpack_bf16(w[j]);
-      v[2 * j] *= dgelu_tanh(h.x);
-      v[2 * j + 1] *= dgelu_tanh(h.y);
+      for (int j = 0; j < NV; j += 4) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
+        v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+      }
     }
-  }
-  if (p.col_scale) {
-    const float4 s0 = *reinterpret_cast<const float4*>(p.col_scale + col);
-    const float4 s1 = *reinterpret_cast<const float4*>(p.col_scale + col + 4);
-    v[0] *= s0.x; v[1] *= s0.y; v[2] *= s0.z; v[3] *= s0.w;
-    v[4] *= s1.x; v[5] *= s1.y; v[6] *= s1.z; v[7] *= s1.w;
+    if (p.col_scale) {
+#pragma unroll
+      for (int j = 0; j < NV; j += 4) {
+        const float4 s = __ldg(reinterpret_cast<const float4*>(p.col_scale + col + j));
+        v[j] *= s.x; v[j + 1] *= s.y; v[j + 2] *= s.z; v[j + 3] *= s.w;
+      }
+    }
+  } else {  // N edge: columns >= N are clipped by the TMA store, only guard the loads
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      if (col + j < p.N) {
+        if (p.bias) v[j] += p.bias[col + j];
+        if (p.col_scale) v[j] *= p.col_scale[col + j];
+      }
+    }
   }
   if (p.row_scale) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] *= rs;
-  }
-  if (p.residual) {
-    const uint4 a = *reinterpret_cast<const uint4*>(p.residual + row * p.ldr + col);
-    const uint32_t w[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float2 h = unpack_bf16(w[j]);
-      v[2 * j] += h.x;
-      v[2 * j + 1] += h.y;
-    }
-  }
-  if (p.d_fp32) {
-    float* d = reinterpret_cast<float*>(Dbase) + row * ldd + col;
-    float4 o0 = make_float4(v[0], v[1], v[2], v[3]);
-    float4 o1 = make_float4(v[4], v[5], v[6], v[7]);
-    if (p.accumulate && p.split_k == 1) {
-      const float4 c0 = *reinterpret_cast<const float4*>(d);
-      const float4 c1 = *reinterpret_cast<const float4*>(d + 4);
-      o0.x += c0.x; o0.y += c0.y; o0.z += c0.z; o0.w += c0.w;
-      o1.x += c1.x; o1.y += c1.y; o1.z += c1.z; o1.w += c1.w;
-    }
-    *reinterpret_cast<float4*>(d) = o0;
-    *reinterpret_cast<float4*>(d + 4) = o1;
-  } else {
-    bf16* d = reinterpret_cast<bf16*>(Dbase) + row * ldd + col;
-    *reinterpret_cast<uint4*>(d) = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]),
-                                              pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+    for (int j = 0; j < NV; ++j) v[j] *= rs;
   }
 }
 
+// 16-byte chunk `c` (0..7) of row `r` of a [128 x 128 B] slab laid out for a SWIZZLE_128B TMA box
+__device__ __forceinline__ uint32_t slab_off(int r, int c) {
+  return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4));
+}
+__device__ __forceinline__ void st_bf16x32(uint8_t* slab, int r, int cb, const float (&v)[32]) {
+#pragma unroll
+  for (int g = 0; g < 4; ++g)
+    *reinterpret_cast<uint4*>(slab + slab_off(r, cb + g)) =
+        make_uint4(pack_bf16(v[g * 8 + 0], v[g * 8 + 1]), pack_bf16(v[g * 8 + 2], v[g * 8 + 3]),
+                   pack_bf16(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16(v[g * 8 + 6], v[g * 8 + 7]));
+}
+
 template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+            const __grid_constant__ CUtensorMap tma_d, const __grid_constant__ CUtensorMap tma_x,
             const GemmParams p) {
   using Cfg = GemmCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint8_t* smem_out = smem + Cfg::kStages * Cfg::kStageBytes;  // 1024-aligned (stage bytes % 1024 == 0)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + kOutBytes);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* aux_bar = tempty_bar + 2;  // [4]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + 4);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -127,14 +144,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
+    tma_prefetch_desc(&tma_d);
+    if (p.epi == EPI_GELU2 || p.has_aux_in) tma_prefetch_desc(&tma_x);
     for (int s = 0; s < Cfg::kStages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 128);
+      mbar_init(&tempty_bar[s], kEpiThreads);
     }
+    for (int s = 0; s < 4; ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
@@ -216,50 +236,137 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       }
     }
   } else {
-    const int sub = warp & 3;  // TMEM sub-partition of this warp
-    int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int split = tile / tiles_mn;
-      const int mn = tile - split * tiles_mn;
-      const int m_idx = (mn / p.n_blocks) * BM;
-      const int n_idx = (mn % p.n_blocks) * BN;
-      const int acc = it & 1;
-      const uint32_t acc_phase = (it >> 1) & 1;
-      mbar_wait(&tfull_bar[acc], acc_phase);
-      tc_fence_after();
-      const int64_t row = m_idx + sub * 32 + lane;
-      const bool row_ok = row < p.M;
-      float rs = 1.f;
-      if (p.row_scale && row_ok) rs = p.row_scale[row / p.rows_per_scale];
-      void* Dbase = p.D;
-      int64_t ldd = p.ldd;
-      if (p.split_k > 1) {
-        Dbase = p.workspace + (int64_t)split * p.M * p.N;
-        ldd = p.N;
-      }
-      const uint32_t taddr = tmem_base + ((uint32_t)(sub * 32) << 16) + acc * BN;
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        if (n_idx + c * 32 >= p.N) break;  // warp-uniform
-        uint32_t r[32];
-        tmem_ld32(taddr + c * 32, r);
-        tmem_ld_wait();
-        if (row_ok) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const int col = n_idx + c * 32 + g * 8;
-            if (col < p.N) {
-              float v[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
-              epilogue_group8(p, v, row, col, rs, Dbase, ldd);
-            }
-          }
+    // ------------------------------------------------------------------ epilogue (warps 2..9)
+    const int ew = warp - 2;
+    const int sub = warp & 3;                 // TMEM sub-partition this warp may read
+    const int half = ew >> 2;                 // which half of the slab's columns
+    const int r = sub * 32 + lane;            // row inside the tile (TMEM lane)
+    const bool leader = (ew == 0 && lane == 0);
+    const bool f32 = (p.epi == EPI_F32 || p.epi == EPI_ACCUM);
+    const int SC = f32 ? 32 : 64;             // accumulator columns per slab
+    const int slabs_per_tile = BN / SC;
+    const bool two_out = (p.epi == EPI_GELU2);
+    const int nslot = two_out ? 2 : 4;
+    const int slot_bytes = two_out ? 2 * SLAB_BYTES : SLAB_BYTES;
+    const bool aux_in = p.has_aux_in != 0;
+    const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const uint32_t total_slabs = (uint32_t)my_tiles * slabs_per_tile;
+
+    auto issue_aux = [&](uint32_t sg) {  // leader only: TMA-load the epilogue input of slab sg
+      const int t = blockIdx.x + (sg / slabs_per_tile) * gridDim.x;
+      const int mn = t % tiles_mn;
+      const int col = (mn % p.n_blocks) * BN + (sg % slabs_per_tile) * SC;
+      const int row = (mn / p.n_blocks) * BM;
+      const int slot = sg % nslot;
+      mbar_expect_tx(&aux_bar[slot], SLAB_BYTES);
+      tma_load_2d(smem_out + slot * slot_bytes, &tma_x, &aux_bar[slot], col, row);
+    };
+    if (aux_in && leader)
+      for (uint32_t sg = 0; sg + 1 < (uint32_t)nslot && sg < total_slabs; ++sg) issue_aux(sg);
+
+    int m_idx = 0, n_idx = 0, acc = 0;
+    float rs = 1.f;
+    for (uint32_t sg = 0; sg < total_slabs; ++sg) {
+      const int it = sg / slabs_per_tile;
+      const int j = sg - it * slabs_per_tile;
+      if (j == 0) {
+        const int tile = blockIdx.x + it * gridDim.x;
+        const int mn = tile % tiles_mn;
+        m_idx = (mn / p.n_blocks) * BM;
+        n_idx = (mn % p.n_blocks) * BN;
+        acc = it & 1;
+        mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
+        tc_fence_after();
+        if (p.row_scale) {
+          const int64_t row = (int64_t)m_idx + r;
+          rs = row < p.M ? p.row_scale[row / p.rows_per_scale] : 0.f;
         }
       }
-      tc_fence_before();
-      mbar_arrive(&tempty_bar[acc]);
+      const int slot = sg % nslot;
+      uint8_t* slab = smem_out + slot * slot_bytes;
+      const uint32_t taddr = tmem_base + ((uint32_t)(sub * 32) << 16) + acc * BN + j * SC + half * (SC / 2);
+      const int col = n_idx + j * SC + half * (SC / 2);
+      if (!f32) {
+        uint32_t rr[32];
+        tmem_ld32(taddr, rr);
+        tmem_ld_wait();
+        if (j == slabs_per_tile - 1) { tc_fence_before(); mbar_arrive(&tempty_bar[acc]); }
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(rr[i]);
+        if (p.epi == EPI_DGELU) {
+          mbar_wait(&aux_bar[slot], (sg / nslot) & 1);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const uint4 a = *reinterpret_cast<const uint4*>(slab + slab_off(r, half * 4 + g));
+            const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float2 h = unpack_bf16(w[q]);
+              v[g * 8 + 2 * q] *= dgelu_fast(h.x);
+              v[g * 8 + 2 * q + 1] *= dgelu_fast(h.y);
+            }
+          }
+          st_bf16x32(slab, r, half * 4, v);
+        } else {
+          epi_affine<32>(p, v, col, rs);
+          if (two_out) {
+            st_bf16x32(slab, r, half * 4, v);  // pre-activation (saved for backward)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = gelu_fast(v[i]);
+            st_bf16x32(slab + SLAB_BYTES, r, half * 4, v);
+          } else {
+            if (p.act == 1) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = gelu_fast(v[i]);
+            }
+            st_bf16x32(slab, r, half * 4, v);
+          }
+        }
+      } else {
+        uint32_t rr[16];
+        tmem_ld16(taddr, rr);
+        tmem_ld_wait();
+        if (j == slabs_per_tile - 1) { tc_fence_before(); mbar_arrive(&tempty_bar[acc]); }
+        float v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(rr[i]);
+        if (p.epi == EPI_F32) epi_affine<16>(p, v, col, rs);
+        if (aux_in) {
+          mbar_wait(&aux_bar[slot], (sg / nslot) & 1);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const float4 a = *reinterpret_cast<const float4*>(slab + slab_off(r, half * 4 + g));
+            v[g * 4] += a.x; v[g * 4 + 1] += a.y; v[g * 4 + 2] += a.z; v[g * 4 + 3] += a.w;
+          }
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          *reinterpret_cast<float4*>(slab + slab_off(r, half * 4 + g)) =
+              make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+      }
+      fence_proxy_async_smem();
+      if (leader) {
+        // every earlier store has finished READING its slab => the slot of slab sg-1 (which
+        // slab sg+nslot-1 reuses; at sg == 0 that slot has never been used) is free
+        tma_store_wait_read<0>();
+        if (aux_in && sg + nslot - 1 < total_slabs) issue_aux(sg + nslot - 1);
+      }
+      named_bar_sync(1, kEpiThreads);
+      if (leader) {
+        const int c0 = n_idx + j * SC;
+        if (p.epi == EPI_ACCUM) {
+          tma_reduce_add_2d(&tma_d, slab, c0, m_idx);
+        } else if (two_out) {
+          tma_store_2d(&tma_x, slab, c0, m_idx);
+          tma_store_2d(&tma_d, slab + SLAB_BYTES, c0, m_idx);
+        } else {
+          tma_store_2d(&tma_d, slab, c0, m_idx);
+        }
+        tma_store_commit();
+      }
     }
+    if (leader) tma_store_wait<0>();
   }
   tc_fence_before();
   __syncthreads();
@@ -269,32 +376,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   }
 }
 
-// ---- split-K reduction: D (+)= sum_s ws[s]  (fp32, vectorised, HBM-bound)
-__global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __restrict__ D,
-                                     int64_t M, int64_t N, int64_t ldd, int splits,
-                                     int accumulate) {
-  const int64_t n4 = N / 4;
-  const int64_t total = M * n4;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / n4, c = (i - r * n4) * 4;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int s = 0; s < splits; ++s) {
-      const float4 v = *reinterpret_cast<const float4*>(ws + ((int64_t)s * M + r) * N + c);
-      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-    }
-    float* d = D + r * ldd + c;
-    if (accumulate) {
-      const float4 o = *reinterpret_cast<const float4*>(d);
-      acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;
-    }
-    *reinterpret_cast<float4*>(d) = acc;
-  }
-}
-
-// ---- column sums of a bf16 [M,N] matrix (bias gradients). grid = (N/64 col-groups, row-splits);
-// each thread owns 2 adjacent columns, 8 row-lanes per block, smem reduce, one atomicAdd per
-// column per block.  `out` must be zeroed by the caller path (done in the launcher).
+// ---- column sums of a bf16 [M,N] matrix (bias gradients; ff.py:24,27 reverse-mode).
+// grid = (N/64 col-groups, row-splits); each thread owns 2 adjacent columns, 8 row-lanes per
+// block, smem reduce, one red.add per column per block (out is an accumulator).
 __global__ void colsum_kernel(const bf16* __restrict__ X, int64_t M, int64_t N, int64_t ldx,
                               float* __restrict__ out) {
   __shared__ float2 red[8][32];
@@ -323,6 +407,12 @@ __global__ void fill_kernel(float* p, float v, int64_t n) {
        i += (int64_t)gridDim.x * blockDim.x)
     p[i] = v;
 }
+__global__ void fill2d_kernel(float* p, float v, int64_t rows, int64_t cols, int64_t ld) {
+  const int64_t total = rows * cols;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x)
+    p[(i / cols) * ld + (i % cols)] = v;
+}
 
 static int num_sms() {
   static int n = 0;
@@ -335,7 +425,12 @@ static int num_sms() {
   return n;
 }
 
-static int pick_bn(int64_t N) { return (N % 256 == 0) ? 256 : 128; }
+static int pick_bn(int64_t N) {
+  if (N % 256 == 0) return 256;
+  if (N % 192 == 0) return 192;
+  if (N > 128 && N % 128 != 0 && N <= 192) return 192;
+  return 128;
+}
 
 static int plan_split(const sav_gemm_args* a, int bn) {
   if (a->split_k > 0) return a->split_k;
@@ -349,8 +444,8 @@ static int plan_split(const sav_gemm_args* a, int bn) {
 }
 
 template <int BN, bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
-                       cudaStream_t st) {
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
+                       const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
   using Cfg = GemmCfg<BN>;
   auto kern = gemm_kernel<BN, A_MN, B_MN>;
   static bool attr_set = false;  // benign race: idempotent
@@ -362,7 +457,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   }
   const int tiles = p.m_blocks * p.n_blocks * p.split_k;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, 192, Cfg::kSmem, st>>>(ta, tb, p);
+  kern<<<grid, kGemmThreads, Cfg::kSmem, st>>>(ta, tb, td, tx, p);
   count_launch();
   return check_launch("sav_gemm");
 }
@@ -372,8 +467,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
 using namespace sav;
 
 extern "C" int64_t sav_gemm_workspace_bytes(const sav_gemm_args* a) {
-  const int s = plan_split(a, pick_bn(a->N));
-  return s > 1 ? (int64_t)s * a->M * a->N * 4 : 0;
+  (void)a;
+  return 0;  // split-K partials are combined with TMA reduce-add directly in D
 }
 
 extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
@@ -381,7 +476,7 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
   if (!a || a->M <= 0 || a->N <= 0 || a->K <= 0)
     return set_error(SAV_ERR_SHAPE, "sav_gemm: M,N,K must be positive");
   if (a->N % 8 || a->lda % 8 || a->ldb % 8 || a->ldd % (a->d_fp32 ? 4 : 8) ||
-      (a->residual && a->ldr % 8))
+      (a->residual && a->ldr % 4))
     return set_error(SAV_ERR_ALIGN, "sav_gemm: N, lda, ldb, ldd, ldr must be multiples of 8");
   if (!aligned16(a->A) || !aligned16(a->B) || !aligned16(a->D) || !aligned16(a->bias) ||
       !aligned16(a->aux_in) || !aligned16(a->aux_out) || !aligned16(a->residual) ||
@@ -389,14 +484,18 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
     return set_error(SAV_ERR_ALIGN, "sav_gemm: pointers must be 16 B aligned");
   const int bn = pick_bn(a->N);
   const int split = plan_split(a, bn);
-  if (split > 1) {
-    if (!a->d_fp32 || a->bias || a->act || a->aux_in || a->aux_out || a->col_scale ||
-        a->row_scale || a->residual)
-      return set_error(SAV_ERR_ARG, "sav_gemm: split_k>1 needs d_fp32 and no epilogue");
-    if (!a->workspace || a->workspace_bytes < (int64_t)split * a->M * a->N * 4)
-      return set_error(SAV_ERR_ARG, "sav_gemm: workspace too small for split_k=%d", split);
-  }
-  if (a->accumulate && !a->d_fp32) return set_error(SAV_ERR_ARG, "sav_gemm: accumulate needs d_fp32");
+  const bool accum = a->accumulate || split > 1;
+  const bool any_affine = a->bias || a->col_scale || a->row_scale;
+  if (accum && (!a->d_fp32 || any_affine || a->act || a->aux_in || a->aux_out || a->residual))
+    return set_error(SAV_ERR_ARG, "sav_gemm: accumulate / split_k need d_fp32 and no epilogue");
+  if (a->d_fp32 && (a->act || a->aux_in || a->aux_out))
+    return set_error(SAV_ERR_ARG, "sav_gemm: activation epilogues need a bf16 output");
+  if (a->residual && !a->d_fp32)
+    return set_error(SAV_ERR_ARG, "sav_gemm: residual (fp32 residual stream) needs d_fp32");
+  if (a->aux_in && (a->act || a->aux_out || any_affine))
+    return set_error(SAV_ERR_ARG, "sav_gemm: aux_in (dGELU) cannot be combined with bias/act/scales");
+  if (a->aux_out && a->act != 1)
+    return set_error(SAV_ERR_ARG, "sav_gemm: aux_out is the pre-activation of act=1");
 
   GemmParams p;
   p.M = a->M; p.N = a->N; p.K = a->K;
@@ -405,16 +504,13 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
   p.k_blocks = (int)((a->K + BK - 1) / BK);
   p.k_per_split = (p.k_blocks + split - 1) / split;
   p.split_k = (p.k_blocks + p.k_per_split - 1) / p.k_per_split;
-  p.D = a->D; p.ldd = a->ldd; p.d_fp32 = a->d_fp32; p.accumulate = a->accumulate;
-  p.bias = a->bias; p.act = a->act;
-  p.aux_out = reinterpret_cast<bf16*>(a->aux_out);
-  p.aux_in = reinterpret_cast<const bf16*>(a->aux_in);
-  p.col_scale = a->col_scale; p.row_scale = a->row_scale;
+  p.epi = accum ? EPI_ACCUM : a->d_fp32 ? EPI_F32 : a->aux_in ? EPI_DGELU : a->aux_out ? EPI_GELU2 : EPI_PLAIN;
+  p.act = a->act;
+  p.has_aux_in = (a->aux_in || a->residual) ? 1 : 0;
+  p.bias = a->bias; p.col_scale = a->col_scale; p.row_scale = a->row_scale;
   p.rows_per_scale = a->rows_per_scale > 0 ? a->rows_per_scale : 1;
-  p.residual = reinterpret_cast<const bf16*>(a->residual); p.ldr = a->ldr;
-  p.workspace = reinterpret_cast<float*>(a->workspace);
 
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, td, tx;
   int rc;
   {
     uint64_t dims[2], str[2];
@@ -428,26 +524,32 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
     str[1] = (uint64_t)a->ldb * 2;
     if ((rc = make_tmap_bf16(&tb, a->B, 2, dims, str, box))) return rc;
   }
+  const int es = a->d_fp32 ? 4 : 2;
+  if ((rc = make_tmap_2d(&td, a->D, es, a->N, a->M, a->ldd, 128 / es, BM))) return rc;
+  tx = td;
+  if (a->aux_out) rc = make_tmap_2d(&tx, a->aux_out, 2, a->N, a->M, a->ldd, 64, BM);
+  else if (a->aux_in) rc = make_tmap_2d(&tx, a->aux_in, 2, a->N, a->M, a->ldd, 64, BM);
+  else if (a->residual) rc = make_tmap_2d(&tx, a->residual, 4, a->N, a->M, a->ldr, 32, BM);
+  if (rc) return rc;
+
+  if (split > 1 && !a->accumulate) {  // reduce-add target must start from zero
+    const int64_t total = a->M * a->N;
+    int blocks = (int)((total + 255) / 256 < num_sms() * 8 ? (total + 255) / 256 : num_sms() * 8);
+    fill2d_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<float*>(a->D), 0.f, a->M, a->N, a->ldd);
+    count_launch();
+  }
 #define SAV_GEMM_CASE(BNv, AM, BMj)                                                  \
   if (bn == BNv && (a->a_mn != 0) == AM && (a->b_mn != 0) == BMj)                     \
-    rc = launch_gemm<BNv, AM, BMj>(ta, tb, p, st);
+    rc = launch_gemm<BNv, AM, BMj>(ta, tb, td, tx, p, st);
   rc = SAV_ERR_ARG;
   SAV_GEMM_CASE(128, false, false) SAV_GEMM_CASE(128, false, true)
   SAV_GEMM_CASE(128, true, false)  SAV_GEMM_CASE(128, true, true)
+  SAV_GEMM_CASE(192, false, false) SAV_GEMM_CASE(192, false, true)
+  SAV_GEMM_CASE(192, true, false)  SAV_GEMM_CASE(192, true, true)
   SAV_GEMM_CASE(256, false, false) SAV_GEMM_CASE(256, false, true)
   SAV_GEMM_CASE(256, true, false)  SAV_GEMM_CASE(256, true, true)
 #undef SAV_GEMM_CASE
-  if (rc) return rc;
-  if (p.split_k > 1) {
-    const int64_t total = a->M * (a->N / 4);
-    int blocks = (int)((total + 255) / 256);
-    if (blocks > num_sms() * 8) blocks = num_sms() * 8;
-    splitk_reduce_kernel<<<blocks, 256, 0, st>>>(p.workspace, reinterpret_cast<float*>(a->D),
-                                                 a->M, a->N, a->ldd, p.split_k, a->accumulate);
-    count_launch();
-    return check_launch("sav_gemm split-K reduce");
-  }
-  return SAV_OK;
+  return rc;
 }
 
 extern "C" int sav_fill_f32(float* ptr, float v, int64_t n, void* stream) {

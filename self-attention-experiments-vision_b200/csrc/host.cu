@@ -76,6 +76,25 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
   return SAV_OK;
 }
 
+int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, int64_t cols, int64_t rows,
+                 int64_t ld, uint32_t box_cols, uint32_t box_rows) {
+  encode_fn_t enc = get_encode();
+  if (!enc) return set_error(SAV_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  if (!aligned16(base) || (ld * elem_bytes) % 16)
+    return set_error(SAV_ERR_ALIGN, "tensor-map base / row pitch not 16 B aligned");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstr[1] = {(cuuint64_t)ld * elem_bytes};
+  cuuint32_t bx[2] = {box_cols, box_rows};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = enc(out, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
+                   2, const_cast<void*>(base), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return set_error(SAV_ERR_CUDA, "cuTensorMapEncodeTiled (2d) failed (%d)", (int)r);
+  return SAV_OK;
+}
+
 }  // namespace sav
 
 extern "C" {

@@ -19,6 +19,11 @@ int check_launch(const char* what);
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                    const uint64_t* strides_bytes, const uint32_t* box);
 
+// 2-D row-major tensor [rows, cols] (elem_bytes 2 = bf16, 4 = fp32), row pitch ld elements,
+// box [box_rows, box_cols] with box_cols * elem_bytes == 128 (one swizzle row).
+int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, int64_t cols, int64_t rows,
+                 int64_t ld, uint32_t box_cols, uint32_t box_rows);
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 }  // namespace sav

@@ -1,13 +1,17 @@
-// LayerNorm forward / backward: warp-per-row, 16-byte vector loads, fp32 statistics via warp
-// shuffles.  HBM-roofline kernels (algorithmic bytes: fwd 2*rows*C*2 B, bwd 3*rows*C*2 B).
+// LayerNorm forward / backward over the fp32 residual stream: warp-per-row, 16/32-byte vector
+// loads, fp32 statistics via warp shuffles.  HBM-roofline kernels.  Algorithmic bytes per element:
+//   fwd  4 (x fp32) + 2 (y bf16)                                   = 6 B
+//   bwd  2 (dy) + 4 (x) + 4 (dx_add) + 4 (dx) + 2 (dx bf16 copy)   = 16 B
 // Semantics follow Flax nn.LayerNorm as used at vit.py:19,26,57: var = E[x^2] - E[x]^2,
 // y = (x - mean) * rsqrt(var + eps) * scale + bias, computed in fp32, stored bf16.
+// The residual stream and its gradient stay fp32 (DESIGN.md "precision"): a bf16 stream costs
+// 1.5e-2 of the 2e-2 parity budget on its own (tests/tools/bf16_error_budget.py).
 #include "common.cuh"
 #include "host.h"
 
 namespace sav {
 
-constexpr int LN_MAX_CHUNKS = 4;  // 16-byte chunks per lane -> C <= 32*4*8 = 1024
+constexpr int LN_MAX_CHUNKS = 4;  // 8-element chunks per lane -> C <= 32*4*8 = 1024
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -25,20 +29,40 @@ __device__ __forceinline__ void load8(const bf16* p, float (&f)[8]) {
     f[2 * j + 1] = t.y;
   }
 }
+__device__ __forceinline__ void load8(const float* p, float (&f)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  const float4 b = *reinterpret_cast<const float4*>(p + 4);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+  f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
 __device__ __forceinline__ void store8(bf16* p, const float (&f)[8]) {
   *reinterpret_cast<uint4*>(p) = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]),
                                             pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
 }
+__device__ __forceinline__ void store8(float* p, const float (&f)[8]) {
+  *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
+  *reinterpret_cast<float4*>(p + 4) = make_float4(f[4], f[5], f[6], f[7]);
+}
 
 template <int CHUNKS>
 __global__ void __launch_bounds__(256)
-ln_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ scale,
-              const float* __restrict__ bias, bf16* __restrict__ y, float* __restrict__ mean_out,
-              float* __restrict__ rstd_out, int64_t rows, int C, float eps) {
+ln_fwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ scale,
+              const float* __restrict__ bias, bf16* __restrict__ y, int64_t ldy,
+              float* __restrict__ mean_out, float* __restrict__ rstd_out, int64_t rows, int C,
+              float eps) {
   const int lane = threadIdx.x & 31;
   const int64_t warp_global = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int64_t warps_total = (int64_t)gridDim.x * 8;
   const int nchunk = C / 8;
+  float g[CHUNKS][8], b[CHUNKS][8];
+#pragma unroll
+  for (int i = 0; i < CHUNKS; ++i) {
+    const int ch = lane + i * 32;
+    if (ch < nchunk) {
+      load8(scale + ch * 8, g[i]);
+      load8(bias + ch * 8, b[i]);
+    }
+  }
   for (int64_t row = warp_global; row < rows; row += warps_total) {
     float v[CHUNKS][8];
     float s = 0.f, ss = 0.f;
@@ -46,7 +70,7 @@ ln_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ scale,
     for (int i = 0; i < CHUNKS; ++i) {
       const int ch = lane + i * 32;
       if (ch < nchunk) {
-        load8(x + row * C + ch * 8, v[i]);
+        load8(x + row * ldx + ch * 8, v[i]);
 #pragma unroll
         for (int j = 0; j < 8; ++j) { s += v[i][j]; ss += v[i][j] * v[i][j]; }
       }
@@ -62,28 +86,24 @@ ln_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ scale,
       const int ch = lane + i * 32;
       if (ch < nchunk) {
         float o[8];
-        const float4 g0 = *reinterpret_cast<const float4*>(scale + ch * 8);
-        const float4 g1 = *reinterpret_cast<const float4*>(scale + ch * 8 + 4);
-        const float4 b0 = *reinterpret_cast<const float4*>(bias + ch * 8);
-        const float4 b1 = *reinterpret_cast<const float4*>(bias + ch * 8 + 4);
-        const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-        const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * g[j] + b[j];
-        store8(y + row * C + ch * 8, o);
+        for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * g[i][j] + b[i][j];
+        store8(y + row * ldy + ch * 8, o);
       }
     }
   }
 }
 
 // dx = rstd * (g - mean_c(g) - xhat * mean_c(g * xhat)),  g = dy * scale   (+ dx_add)
-// per-block partial dscale/dbias -> partials[block][2][C]
+// dscale / dbias: per-warp register partials -> shared-memory reduce -> one red.add per column
+// per block into the (zero-initialised or accumulating) gradient arena.
 template <int CHUNKS>
 __global__ void __launch_bounds__(256)
-ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+ln_bwd_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __restrict__ x, int64_t ldx,
               const float* __restrict__ scale, const float* __restrict__ mean_in,
-              const float* __restrict__ rstd_in, const bf16* __restrict__ dx_add,
-              bf16* __restrict__ dx, float* __restrict__ partials, int64_t rows, int C) {
+              const float* __restrict__ rstd_in, const float* __restrict__ dx_add,
+              float* __restrict__ dx, bf16* __restrict__ dx16, float* __restrict__ dscale,
+              float* __restrict__ dbias, int64_t rows, int C) {
   extern __shared__ float sacc[];  // [2][C]
   const int lane = threadIdx.x & 31;
   const int64_t warp_global = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -111,8 +131,8 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
       const int ch = lane + i * 32;
       if (ch < nchunk) {
         float xv[8], dv[8];
-        load8(x + row * C + ch * 8, xv);
-        load8(dy + row * C + ch * 8, dv);
+        load8(x + row * ldx + ch * 8, xv);
+        load8(dy + row * ldy + ch * 8, dv);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           xh[i][j] = (xv[j] - mean) * rstd;
@@ -135,11 +155,12 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
         for (int j = 0; j < 8; ++j) o[j] = rstd * (gy[i][j] - s1 - xh[i][j] * s2);
         if (dx_add) {
           float a[8];
-          load8(dx_add + row * C + ch * 8, a);
+          load8(dx_add + row * ldx + ch * 8, a);
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] += a[j];
         }
-        store8(dx + row * C + ch * 8, o);
+        store8(dx + row * ldx + ch * 8, o);
+        if (dx16) store8(dx16 + row * ldx + ch * 8, o);
       }
     }
   }
@@ -155,19 +176,10 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x)
-    partials[(int64_t)blockIdx.x * 2 * C + i] = sacc[i];
-}
-
-__global__ void ln_bwd_reduce_kernel(const float* __restrict__ partials, int nblocks, int C,
-                                     float* __restrict__ dscale, float* __restrict__ dbias,
-                                     int accumulate) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;  // over 2*C
-  if (i >= 2 * C) return;
-  float s = 0.f;
-  for (int b = 0; b < nblocks; ++b) s += partials[(int64_t)b * 2 * C + i];
-  float* out = (i < C) ? (dscale + i) : (dbias + (i - C));
-  *out = accumulate ? (*out + s) : s;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) {
+    float* out = (i < C) ? (dscale + i) : (dbias + (i - C));
+    atomicAdd(out, sacc[i]);
+  }
 }
 
 static int ln_grid(int64_t rows) {
@@ -180,19 +192,19 @@ static int ln_grid(int64_t rows) {
 
 using namespace sav;
 
-extern "C" int sav_layernorm_fwd(const void* x, const float* scale, const float* bias, void* y,
-                                 float* mean, float* rstd, int64_t rows, int64_t C, float eps,
-                                 void* stream) {
-  if (rows <= 0 || C <= 0 || C % 8 || C > 32 * LN_MAX_CHUNKS * 8)
+extern "C" int sav_layernorm_fwd(const float* x, int64_t ldx, const float* scale,
+                                 const float* bias, void* y, int64_t ldy, float* mean,
+                                 float* rstd, int64_t rows, int64_t C, float eps, void* stream) {
+  if (rows <= 0 || C <= 0 || C % 8 || C > 32 * LN_MAX_CHUNKS * 8 || ldx % 4 || ldy % 8)
     return set_error(SAV_ERR_SHAPE, "sav_layernorm_fwd: need C %% 8 == 0 and C <= 1024 (C=%lld)", (long long)C);
   if (!aligned16(x) || !aligned16(y) || !aligned16(scale) || !aligned16(bias))
     return set_error(SAV_ERR_ALIGN, "sav_layernorm_fwd: pointers must be 16 B aligned");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int grid = ln_grid(rows);
   const int chunks = (int)((C / 8 + 31) / 32);
-#define LN_FWD(CH)                                                                              \
-  ln_fwd_kernel<CH><<<grid, 256, 0, st>>>(reinterpret_cast<const bf16*>(x), scale, bias,        \
-                                           reinterpret_cast<bf16*>(y), mean, rstd, rows, (int)C, eps)
+#define LN_FWD(CH)                                                                          \
+  ln_fwd_kernel<CH><<<grid, 256, 0, st>>>(x, ldx, scale, bias, reinterpret_cast<bf16*>(y), ldy, \
+                                           mean, rstd, rows, (int)C, eps)
   switch (chunks) {
     case 1: LN_FWD(1); break;
     case 2: LN_FWD(2); break;
@@ -204,27 +216,22 @@ extern "C" int sav_layernorm_fwd(const void* x, const float* scale, const float*
   return check_launch("sav_layernorm_fwd");
 }
 
-extern "C" int64_t sav_layernorm_bwd_workspace_bytes(int64_t rows, int64_t C) {
-  return (int64_t)ln_grid(rows) * 2 * C * 4;
-}
-
-extern "C" int sav_layernorm_bwd(const void* dy, const void* x, const float* scale,
-                                 const float* mean, const float* rstd, const void* dx_add,
-                                 void* dx, float* dscale, float* dbias, float* partials,
-                                 int64_t rows, int64_t C, int32_t accumulate, void* stream) {
-  if (rows <= 0 || C <= 0 || C % 8 || C > 32 * LN_MAX_CHUNKS * 8)
+extern "C" int sav_layernorm_bwd(const void* dy, int64_t ldy, const float* x, int64_t ldx,
+                                 const float* scale, const float* mean, const float* rstd,
+                                 const float* dx_add, float* dx, void* dx_bf16, float* dscale,
+                                 float* dbias, int64_t rows, int64_t C, void* stream) {
+  if (rows <= 0 || C <= 0 || C % 8 || C > 32 * LN_MAX_CHUNKS * 8 || ldx % 8 || ldy % 8)
     return set_error(SAV_ERR_SHAPE, "sav_layernorm_bwd: need C %% 8 == 0 and C <= 1024");
-  if (!aligned16(dy) || !aligned16(x) || !aligned16(dx) || !aligned16(dx_add))
+  if (!aligned16(dy) || !aligned16(x) || !aligned16(dx) || !aligned16(dx_add) || !aligned16(dx_bf16))
     return set_error(SAV_ERR_ALIGN, "sav_layernorm_bwd: pointers must be 16 B aligned");
-  if (!partials) return set_error(SAV_ERR_ARG, "sav_layernorm_bwd: workspace required");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int grid = ln_grid(rows);
   const int chunks = (int)((C / 8 + 31) / 32);
   const size_t sm = 2 * C * sizeof(float);
-#define LN_BWD(CH)                                                                             \
-  ln_bwd_kernel<CH><<<grid, 256, sm, st>>>(                                                    \
-      reinterpret_cast<const bf16*>(dy), reinterpret_cast<const bf16*>(x), scale, mean, rstd,  \
-      reinterpret_cast<const bf16*>(dx_add), reinterpret_cast<bf16*>(dx), partials, rows, (int)C)
+#define LN_BWD(CH)                                                                            \
+  ln_bwd_kernel<CH><<<grid, 256, sm, st>>>(reinterpret_cast<const bf16*>(dy), ldy, x, ldx, scale, \
+                                            mean, rstd, dx_add, dx,                            \
+                                            reinterpret_cast<bf16*>(dx_bf16), dscale, dbias, rows, (int)C)
   switch (chunks) {
     case 1: LN_BWD(1); break;
     case 2: LN_BWD(2); break;
@@ -233,10 +240,5 @@ extern "C" int sav_layernorm_bwd(const void* dy, const void* x, const float* sca
   }
 #undef LN_BWD
   count_launch();
-  int rc = check_launch("sav_layernorm_bwd");
-  if (rc) return rc;
-  ln_bwd_reduce_kernel<<<(int)((2 * C + 255) / 256), 256, 0, st>>>(partials, grid, (int)C, dscale,
-                                                                  dbias, accumulate);
-  count_launch();
-  return check_launch("sav_layernorm_bwd reduce");
+  return check_launch("sav_layernorm_bwd");
 }

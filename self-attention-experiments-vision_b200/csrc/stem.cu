@@ -1,6 +1,6 @@
 // Patch-embedding stem data movement (HBM-bound): HWCN fp32 images -> token-major bf16 patches
 // (train.py:80-81 + patch_embed.py:19-22), cls/pos-embed add (vit.py:81-85,
-// position_embed.py:54-56) and its reverse-mode.
+// position_embed.py:54-56) -> fp32 residual stream, and its reverse-mode.
 #include "common.cuh"
 #include "host.h"
 
@@ -58,7 +58,7 @@ __global__ void patchify_nhwc_kernel(const float* __restrict__ img, bf16* __rest
 
 // x[b, has_cls + i, :] = tok[b, i, :] + pos[has_cls + i, :];  x[b, 0, :] = cls + pos[0]
 __global__ void embed_fwd_kernel(const bf16* __restrict__ tok, const float* __restrict__ cls,
-                                 const float* __restrict__ pos, bf16* __restrict__ x, int64_t B,
+                                 const float* __restrict__ pos, float* __restrict__ x, int64_t B,
                                  int n_tok, int C, int has_cls) {
   const int NT = n_tok + has_cls;
   const int64_t total2 = B * NT * (int64_t)C / 2;
@@ -77,12 +77,12 @@ __global__ void embed_fwd_kernel(const bf16* __restrict__ tok, const float* __re
     }
     v.x += pos[(int64_t)t * C + c];
     v.y += pos[(int64_t)t * C + c + 1];
-    *reinterpret_cast<uint32_t*>(x + e) = pack_bf16(v.x, v.y);
+    *reinterpret_cast<float2*>(x + e) = v;
   }
 }
 
 // thread per (t, c-pair): loops over b; writes dpos[t,c], dcls (t==0), copies dtok.
-__global__ void embed_bwd_kernel(const bf16* __restrict__ dx, bf16* __restrict__ dtok,
+__global__ void embed_bwd_kernel(const float* __restrict__ dx, bf16* __restrict__ dtok,
                                  float* __restrict__ dcls, float* __restrict__ dpos, int64_t B,
                                  int n_tok, int C, int has_cls, int accumulate) {
   const int NT = n_tok + has_cls;
@@ -92,12 +92,11 @@ __global__ void embed_bwd_kernel(const bf16* __restrict__ dx, bf16* __restrict__
   const int t = (int)((i * 2) / C);
   float2 acc = make_float2(0.f, 0.f);
   for (int64_t b = 0; b < B; ++b) {
-    const uint32_t u = *reinterpret_cast<const uint32_t*>(dx + (b * NT + t) * C + c);
-    const float2 f = unpack_bf16(u);
+    const float2 f = *reinterpret_cast<const float2*>(dx + (b * NT + t) * C + c);
     acc.x += f.x;
     acc.y += f.y;
     if (dtok && t >= has_cls)
-      *reinterpret_cast<uint32_t*>(dtok + (b * n_tok + (t - has_cls)) * C + c) = u;
+      *reinterpret_cast<uint32_t*>(dtok + (b * n_tok + (t - has_cls)) * C + c) = pack_bf16(f.x, f.y);
   }
   float* p = dpos + (int64_t)t * C + c;
   if (accumulate) { p[0] += acc.x; p[1] += acc.y; } else { p[0] = acc.x; p[1] = acc.y; }
@@ -138,7 +137,7 @@ extern "C" int sav_embed_fwd(const void* tok, const float* cls, const float* pos
   const int64_t total2 = B * (n_tok + has_cls) * C / 2;
   int blocks = (int)((total2 + 255) / 256 < 148 * 16 ? (total2 + 255) / 256 : 148 * 16);
   embed_fwd_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const bf16*>(tok), cls, pos, reinterpret_cast<bf16*>(x), B, (int)n_tok,
+      reinterpret_cast<const bf16*>(tok), cls, pos, reinterpret_cast<float*>(x), B, (int)n_tok,
       (int)C, has_cls);
   count_launch();
   return check_launch("sav_embed_fwd");
@@ -150,7 +149,7 @@ extern "C" int sav_embed_bwd(const void* dx, void* dtok, float* dcls, float* dpo
   if (B <= 0 || n_tok <= 0 || C % 2) return set_error(SAV_ERR_SHAPE, "sav_embed_bwd: bad shape");
   const int64_t work = (n_tok + has_cls) * C / 2;
   embed_bwd_kernel<<<(int)((work + 127) / 128), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const bf16*>(dx), reinterpret_cast<bf16*>(dtok), dcls, dpos, B, (int)n_tok,
+      reinterpret_cast<const float*>(dx), reinterpret_cast<bf16*>(dtok), dcls, dpos, B, (int)n_tok,
       (int)C, has_cls, accumulate);
   count_launch();
   return check_launch("sav_embed_bwd");

@@ -34,7 +34,7 @@ class GemmArgs(C.Structure):
 class AttnFwdArgs(C.Structure):
     _fields_ = [
         ("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("o", C.c_void_p),
-        ("lse", C.c_void_p),
+        ("o_lo", C.c_void_p), ("lse", C.c_void_p),
         ("B", C.c_int64), ("H", C.c_int64), ("Nq", C.c_int64), ("Nk", C.c_int64), ("D", C.c_int64),
         ("q_batch_stride", C.c_int64), ("q_row_stride", C.c_int64),
         ("k_batch_stride", C.c_int64), ("k_row_stride", C.c_int64),
@@ -47,7 +47,7 @@ class AttnFwdArgs(C.Structure):
 class AttnBwdArgs(C.Structure):
     _fields_ = [
         ("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("o", C.c_void_p),
-        ("d_o", C.c_void_p), ("lse", C.c_void_p),
+        ("o_lo", C.c_void_p), ("d_o", C.c_void_p), ("lse", C.c_void_p),
         ("dq", C.c_void_p), ("dk", C.c_void_p), ("dv", C.c_void_p),
         ("delta", C.c_void_p), ("dq_accum", C.c_void_p),
         ("B", C.c_int64), ("H", C.c_int64), ("Nq", C.c_int64), ("Nk", C.c_int64), ("D", C.c_int64),
@@ -70,9 +70,8 @@ SIGNATURES = {
     "sav_gemm_workspace_bytes": (C.c_int64, [C.POINTER(GemmArgs)]),
     "sav_gemm": (C.c_int, [C.POINTER(GemmArgs), _P]),
     "sav_colsum_bf16": (C.c_int, [_P, _I64, _I64, _I64, _P, _I32, _P]),
-    "sav_layernorm_fwd": (C.c_int, [_P, _P, _P, _P, _P, _P, _I64, _I64, _F, _P]),
-    "sav_layernorm_bwd_workspace_bytes": (C.c_int64, [_I64, _I64]),
-    "sav_layernorm_bwd": (C.c_int, [_P] * 10 + [_I64, _I64, _I32, _P]),
+    "sav_layernorm_fwd": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _P, _P, _I64, _I64, _F, _P]),
+    "sav_layernorm_bwd": (C.c_int, [_P, _I64, _P, _I64] + [_P] * 8 + [_I64, _I64, _P]),
     "sav_patchify": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _I64, _I64, _I32, _P]),
     "sav_embed_fwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I32, _P]),
     "sav_embed_bwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I32, _I32, _P]),
@@ -101,7 +100,7 @@ def lib():
             fn = getattr(l, name)
             fn.restype = res
             fn.argtypes = args
-        if l.sav_abi_version() != 1:
+        if l.sav_abi_version() != 2:
             raise SavError("libsav_b200.so ABI version mismatch")
         _lib = l
     return _lib

@@ -33,13 +33,15 @@ class Param:
     def grad(self):
         return self._view(self.arena.grad)
 
-    def grad_accumulate_flag(self):
-        """False the first time a gradient is written in this backward pass (overwrite), True after."""
-        w = self.arena._written
-        if self.path in w:
-            return True
-        w.add(self.path)
-        return False
+    def touch_grad(self):
+        """Record that a kernel accumulating into this leaf's gradient is about to be enqueued.
+        Every gradient kernel ACCUMULATES (TMA reduce-add / red.add) into the arena's fp32 gradient
+        buffer, which begin_grad() zero-fills once per step; the record feeds the data-parallel
+        bucket schedule (dp.py)."""
+        a = self.arena
+        a._written.add(self.path)
+        if a.grad_hook is not None:
+            a.grad_hook.wrote(self.path)
 
 
 class ParamTree(dict):
@@ -100,6 +102,7 @@ class ParamArena:
         self.v = None
         self.params = {}
         self._written = set()
+        self.grad_hook = None
 
     @property
     def abstract(self):
@@ -115,7 +118,11 @@ class ParamArena:
             raise RuntimeError("parameter arena must live on a CUDA device (no CPU fallback)")
 
     def begin_grad(self):
+        """Zero the whole gradient arena with one fill kernel (all gradient kernels accumulate)."""
         self._written = set()
+        if not self.abstract:
+            from . import ops
+            ops.fill(self.grad, 0.0)
 
     def _tree(self, attr):
         root = ParamTree()
@@ -131,11 +138,6 @@ class ParamArena:
         return self._tree("master")
 
     def grad_tree(self):
-        # leaves never touched by the backward pass must read as zero
-        if not self.abstract:
-            for path, p in self.params.items():
-                if path not in self._written:
-                    p.grad.zero_()
         return self._tree("grad")
 
     def load_tree(self, tree):

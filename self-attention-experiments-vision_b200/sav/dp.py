@@ -105,12 +105,8 @@ class DataParallel:
                 self._launch(b)
 
     def finish(self):
-        """Called after the last backward node: zero never-written leaves, reduce what is left,
-        and make the compute stream wait for every bucket."""
-        arena = self._arena
-        for path, p in arena.params.items():
-            if path not in arena._written:
-                p.grad.zero_()
+        """Called after the last backward node: reduce what is left and make the compute stream
+        wait for every bucket (never-written leaves are already zero: arena.begin_grad())."""
         if self.fire_after is None:
             # learning pass: derive the firing schedule for the following steps
             sched = {}

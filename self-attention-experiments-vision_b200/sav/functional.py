@@ -1,9 +1,17 @@
 """Var-level ops: forward launches + recorded backward closures, with define-by-run fusion.
 
+Precision layout: the residual stream (embed output, every `x + branch(x)` result) and
+its gradient are fp32 `Var`s; everything that feeds a tensor-core MMA (LayerNorm outputs, q/k/v,
+attention context, MLP hidden, and their gradients) is bf16.  A residual-stream Var carries its
+gradient twice: `g` (fp32, what flows on) and `g16` (bf16 copy written by the same LayerNorm-
+backward kernel, the MMA operand of the dX / dW GEMMs).
+
 `linear` returns a LazyLinear that absorbs a following gelu / LayerScale / drop-path scale /
 residual add into its GEMM epilogue before it is materialised, so `x + FFBlock(LN(x))` written like
-the reference (vit.py:24,31) runs as fused kernels.  Abstract ('meta' device) inputs only propagate
-shapes (the analogue of jax.eval_shape) -- used by the CPU shape tests; there is no CPU compute.
+the reference (vit.py:24,31) runs as fused kernels; `layernorm` is lazy in the same way so that
+`LayerNorm(x)[:, 0]` (vit.py:57,95) only normalises the class-token rows.  Abstract ('meta' device)
+inputs only propagate shapes (the analogue of jax.eval_shape) -- used by the CPU shape tests; there
+is no CPU compute.
 """
 import math
 
@@ -13,6 +21,7 @@ from . import ops
 from .tape import Var, record
 
 BF16 = torch.bfloat16
+F32 = torch.float32
 
 
 def _meta(t):
@@ -26,9 +35,24 @@ class Weight:
     def __init__(self, w, gw, params):
         self.w, self.gw, self.params = w, gw, params
 
-    def accumulate_flag(self):
-        flags = [p.grad_accumulate_flag() for p in self.params]
-        return all(flags)
+    def touch(self):
+        for p in self.params:
+            p.touch_grad()
+
+
+def _grad16(var):
+    """bf16 form of a Var's gradient (for MMA operands); consumes the bf16 copy if there is one."""
+    g16 = var.take_grad16()
+    if g16 is not None:
+        return g16
+    g = var.g
+    if g is None:
+        return None
+    if g.dtype == BF16:
+        return g
+    out = torch.empty(g.shape, dtype=BF16, device=g.device)
+    ops.cast_bf16(g.contiguous(), out)
+    return out
 
 
 class LazyLinear(Var):
@@ -53,6 +77,10 @@ class LazyLinear(Var):
         return len(self.out_shape)
 
     @property
+    def dtype(self):
+        return F32 if self.residual is not None else BF16
+
+    @property
     def v(self):
         if not self._done:
             self._materialize()
@@ -63,14 +91,23 @@ class LazyLinear(Var):
         x, W = self.x, self.weight
         xin = x.v
         K, N = W.w.shape
+        stream = self.residual is not None
         if _meta(xin):
-            self._v = torch.empty(self.out_shape, dtype=BF16, device="meta")
+            self._v = torch.empty(self.out_shape, dtype=F32 if stream else BF16, device="meta")
             return
+        if xin.dtype != BF16:
+            raise TypeError("linear: the input of a Dense must be a bf16 activation (apply LayerNorm "
+                            "to the fp32 residual stream first)")
         x2 = xin.reshape(-1, K) if xin.is_contiguous() else xin  # strided 2-D views pass through
         M = x2.shape[0]
-        out = torch.empty((M, N), dtype=BF16, device=x2.device)
+        out = torch.empty((M, N), dtype=F32 if stream else BF16, device=x2.device)
         pre = torch.empty((M, N), dtype=BF16, device=x2.device) if self.act else None
-        res = self.residual.v.reshape(M, N) if self.residual is not None else None
+        res = None
+        if stream:
+            res = self.residual.v
+            if res.dtype != F32:
+                raise TypeError("residual add: the skip input must be the fp32 residual stream")
+            res = res.reshape(M, N)
         ops.gemm(x2, W.w, b_mn=True, out=out,
                  bias=self.bias.master if self.bias is not None else None, act=self.act,
                  aux_out=pre,
@@ -81,38 +118,45 @@ class LazyLinear(Var):
         record(self._backward)
 
     def _backward(self):
-        dy = self.take_grad()
-        if dy is None:
+        if self.g is None and self.g16 is None:
             return
         x, W = self.x, self.weight
         K, N = W.w.shape
-        dy2 = dy.reshape(-1, N)
         if self.residual is not None and self.residual.requires_grad:
-            _add_grad(self.residual, dy.view(self.residual.v.shape))
+            # the skip path passes the fp32 stream gradient on; the branch below uses the bf16 copy
+            if self.residual.g is not None:
+                raise NotImplementedError("residual-stream Var with a second consumer before its "
+                                          "LayerNorm backward")
+            self.residual.g = self.g.view(self.residual.v.shape)
+        dy = _grad16(self)
+        self.g = None
+        dy2 = dy.reshape(-1, N)
         if self.col_scale is not None or self.row_scale is not None:
             raise NotImplementedError("backward through LayerScale / drop-path epilogue")
         if self.act and not self.g_is_pre:
             raise NotImplementedError("activated linear output must be consumed by a linear op")
         x2 = x.v.reshape(-1, K) if x.v.is_contiguous() else x.v
-        # dW[K,N] = X^T dY : both operands token-major (MN-major), split-K over tokens, fp32 out
-        ops.gemm(x2, dy2, a_mn=True, b_mn=True, out=W.gw, accumulate=W.accumulate_flag(), split_k=0)
+        # dW[K,N] += X^T dY : both operands token-major (MN-major), split-K over tokens, TMA
+        # reduce-add into the (zeroed) fp32 gradient arena
+        W.touch()
+        ops.gemm(x2, dy2, a_mn=True, b_mn=True, out=W.gw, accumulate=True, split_k=0)
         if self.bias is not None:
-            b = self.bias
-            ops.colsum(dy2, out=b.grad, accumulate=b.grad_accumulate_flag())
+            self.bias.touch_grad()
+            ops.colsum(dy2, out=self.bias.grad, accumulate=True)
         if x.requires_grad:
-            # dX[M,K] = dY W^T (+ gelu'(pre) when x is a fused-GELU output) (+ x.g fan-in)
-            prev = x.take_grad()
-            dx = ops.gemm(dy2, W.w, b_mn=False, aux_in=x.pre_act,
-                          residual=prev.reshape(-1, K) if prev is not None else None)
-            x.g = dx.view(x.v.shape) if x.v.is_contiguous() else dx
+            # dX[M,K] = dY W^T (x gelu'(pre) when x is a fused-GELU output)
+            dx = ops.gemm(dy2, W.w, b_mn=False, aux_in=x.pre_act)
+            _add_grad(x, dx.view(x.v.shape) if x.v.is_contiguous() else dx)
             x.g_is_pre = x.pre_act is not None
 
 
 def _add_grad(var, g):
     if var.g is None:
         var.g = g
-    else:
+    elif g.dtype == BF16 and var.g.dtype == BF16:
         var.g = ops.add(var.g.contiguous(), g.contiguous()).view(var.g.shape)
+    else:
+        raise NotImplementedError("fan-in of fp32 stream gradients outside LayerNorm backward")
 
 
 def linear(x, weight, bias=None, out_features_shape=None):
@@ -146,49 +190,113 @@ def scale_rows(x, per_sample_scale, rows_per_sample):
 
 
 def add(a, b):
-    """Residual add (vit.py:24,31): folded into a pending linear when possible."""
+    """Residual add (vit.py:24,31): folded into the pending linear's epilogue (fp32 stream out)."""
     for lazy, other in ((a, b), (b, a)):
         if isinstance(lazy, LazyLinear) and not lazy._done and lazy.residual is None and \
-                isinstance(other, Var) and tuple(other.shape) == tuple(lazy.shape):
+                lazy.act == 0 and isinstance(other, Var) and tuple(other.shape) == tuple(lazy.shape):
             lazy.residual = other
             lazy.v  # materialise now so program order is preserved
             return lazy
-    av, bv = a.v, b.v
-    if _meta(av):
-        return Var(torch.empty(av.shape, dtype=BF16, device="meta"))
-    out = Var(ops.add(av.contiguous(), bv.contiguous()).view(av.shape))
+    raise NotImplementedError("standalone add: one side must be a pending Dense output")
 
-    def bwd():
-        g = out.take_grad()
-        if g is not None:
-            _add_grad(a, g)
-            _add_grad(b, g)
-    record(bwd)
-    return out
+
+class LazyLayerNorm(Var):
+    """LayerNorm over the fp32 residual stream -> bf16.  Materialised over all rows when `.v` is
+    read; `x[:, 0]` on a still-pending instance normalises only the class-token rows."""
+    __slots__ = ("x", "scale", "bias", "eps", "_done")
+
+    def __init__(self, x, scale, bias, eps):
+        super().__init__(None)
+        self.x, self.scale, self.bias, self.eps = x, scale, bias, eps
+        self._done = False
+
+    @property
+    def shape(self):
+        return tuple(self.x.shape)
+
+    @property
+    def ndim(self):
+        return len(self.x.shape)
+
+    @property
+    def dtype(self):
+        return BF16
+
+    @property
+    def v(self):
+        if not self._done:
+            self._materialize()
+        return self._v
+
+    def _check(self, xv):
+        if xv.dtype != F32:
+            raise TypeError("layernorm: input must be the fp32 residual stream")
+
+    def _materialize(self):
+        self._done = True
+        x, xv = self.x, self.x.v
+        if _meta(xv):
+            self._v = torch.empty(xv.shape, dtype=BF16, device="meta")
+            return
+        self._check(xv)
+        xc = xv.contiguous()
+        C = xc.shape[-1]
+        x2 = xc.view(-1, C)
+        y, mean, rstd = ops.layernorm_fwd(x2, self.scale.master, self.bias.master, self.eps)
+        self._v = y.view(xc.shape)
+        scale, bias = self.scale, self.bias
+
+        def bwd():
+            dy = self.take_grad()
+            if dy is None:
+                return
+            scale.touch_grad()
+            bias.touch_grad()
+            prev = x.take_grad() if x.requires_grad else None
+            x.g16 = None
+            dx, dx16 = ops.layernorm_bwd(dy.contiguous().view(-1, C), x2, scale.master, mean, rstd,
+                                         scale.grad, bias.grad,
+                                         dx_add=prev.contiguous().view(-1, C) if prev is not None else None)
+            if x.requires_grad:
+                x.g, x.g16 = dx.view(xc.shape), dx16.view(xc.shape)
+        record(bwd)
+
+    def first_token(self):
+        """LayerNorm(x)[:, 0] without normalising the other tokens (vit.py:57,95)."""
+        self._done = True
+        x, xv = self.x, self.x.v
+        B, N, C = xv.shape
+        if _meta(xv):
+            return Var(torch.empty((B, C), dtype=BF16, device="meta"))
+        self._check(xv)
+        xc = xv.contiguous()
+        rows = xc.view(B * N, C)[::N]          # [B, C] view, row pitch N*C
+        y, mean, rstd = ops.layernorm_fwd(rows, self.scale.master, self.bias.master, self.eps)
+        out = Var(y)
+        scale, bias = self.scale, self.bias
+
+        def bwd():
+            dy = out.take_grad()
+            if dy is None or not x.requires_grad:
+                return
+            if x.g is not None:
+                raise NotImplementedError("class-token LayerNorm on a stream Var with another consumer")
+            scale.touch_grad()
+            bias.touch_grad()
+            # the stream gradient is zero except on the class-token rows
+            g = torch.empty((B * N, C), dtype=F32, device=xc.device)
+            g16 = torch.empty((B * N, C), dtype=BF16, device=xc.device)
+            ops.fill(g, 0.0)
+            ops.fill(g16.view(F32), 0.0)
+            ops.layernorm_bwd(dy.contiguous(), rows, scale.master, mean, rstd, scale.grad, bias.grad,
+                              dx=g[::N], dx16=g16[::N])
+            x.g, x.g16 = g.view(B, N, C), g16.view(B, N, C)
+        record(bwd)
+        return out
 
 
 def layernorm(x, scale, bias, eps=1e-6):
-    xv = x.v
-    if _meta(xv):
-        return Var(torch.empty(xv.shape, dtype=BF16, device="meta"))
-    xc = xv.contiguous()
-    y, mean, rstd = ops.layernorm_fwd(xc, scale.master, bias.master, eps)
-    out = Var(y)
-
-    def bwd():
-        dy = out.take_grad()
-        if dy is None:
-            return
-        acc = scale.grad_accumulate_flag()
-        bias.grad_accumulate_flag()
-        prev = x.take_grad() if x.requires_grad else None
-        dx = ops.layernorm_bwd(dy.contiguous(), xc, scale.master, mean, rstd, scale.grad, bias.grad,
-                               dx_add=prev.contiguous() if prev is not None else None,
-                               accumulate=acc)
-        if x.requires_grad:
-            x.g = dx
-    record(bwd)
-    return out
+    return LazyLayerNorm(x, scale, bias, eps)
 
 
 def self_attention_core(qkv, num_heads, head_ch):
@@ -202,7 +310,7 @@ def self_attention_core(qkv, num_heads, head_ch):
     q, k, v = t5[:, :, 0], t5[:, :, 1], t5[:, :, 2]
     scale = 1.0 / math.sqrt(D)
     o, lse = ops.attn_fwd(q, k, v, scale)
-    out = Var(o.view(B, N, H * D))
+    out = Var(o[0].view(B, N, H * D))
 
     def bwd():
         d_o = out.take_grad()
@@ -229,7 +337,7 @@ def cross_attention_core(q, kv, num_heads, head_ch):
     k, v = kv5[:, :, 0], kv5[:, :, 1]
     scale = 1.0 / math.sqrt(D)
     o, lse = ops.attn_fwd(q4, k, v, scale)
-    out = Var(o.view(B, Nq, H * D))
+    out = Var(o[0].view(B, Nq, H * D))
 
     def bwd():
         d_o = out.take_grad()
@@ -259,24 +367,26 @@ def patchify(images, ph, pw, hwcn):
 
 
 def embed(tok, cls, pos):
-    """[cls; tok] + pos (vit.py:81-85, position_embed.py:54-56); cls may be None (cait.py:69)."""
+    """[cls; tok] + pos (vit.py:81-85, position_embed.py:54-56) -> fp32 residual stream;
+    cls may be None (cait.py:69)."""
     t = tok.v
     B, n, C = t.shape
     has_cls = cls is not None
     if _meta(t):
-        return Var(torch.empty((B, n + int(has_cls), C), dtype=BF16, device="meta"))
+        return Var(torch.empty((B, n + int(has_cls), C), dtype=F32, device="meta"))
     x = ops.embed_fwd(t.contiguous(), cls.master if has_cls else None, pos.master, B, n, C)
     out = Var(x)
 
     def bwd():
         dx = out.take_grad()
+        out.g16 = None
         if dx is None:
             return
-        acc = pos.grad_accumulate_flag()
+        pos.touch_grad()
         if has_cls:
-            cls.grad_accumulate_flag()
+            cls.touch_grad()
         dtok = ops.embed_bwd(dx.contiguous(), cls.grad if has_cls else None, pos.grad, B, n, C,
-                             accumulate=acc)
+                             accumulate=True)
         if tok.requires_grad:
             _add_grad(tok, dtok.view(B, n, C))
     record(bwd)
@@ -287,10 +397,14 @@ def getitem(x, idx):
     """Only the class-token select x[:, 0] (vit.py:95) is needed on the hot path."""
     if not (isinstance(idx, tuple) and len(idx) == 2 and idx[0] == slice(None) and idx[1] == 0):
         raise NotImplementedError("Var indexing supports x[:, 0] only")
+    if isinstance(x, LazyLayerNorm) and not x._done:
+        return x.first_token()
     t = x.v
     B, N, C = t.shape
     if _meta(t):
-        return Var(torch.empty((B, C), dtype=BF16, device="meta"))
+        return Var(torch.empty((B, C), dtype=t.dtype, device="meta"))
+    if t.dtype != BF16:
+        raise NotImplementedError("x[:, 0] on the fp32 stream: apply LayerNorm first")
     out = Var(t[:, 0])  # strided [B,C] view (row stride N*C): a valid GEMM A operand, no copy
 
     def bwd():

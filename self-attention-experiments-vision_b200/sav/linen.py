@@ -94,7 +94,7 @@ class _TempParam:
         self.master, self.shadow = master, shadow
         self.grad = None
 
-    def grad_accumulate_flag(self):
+    def touch_grad(self):
         return False
 
 

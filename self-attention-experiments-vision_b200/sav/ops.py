@@ -78,13 +78,9 @@ def gemm(A, B, *, a_mn=False, b_mn=False, out=None, out_fp32=False, bias=None, a
         _req(row_scale, F32, "row_scale"); a.row_scale = row_scale.data_ptr()
     a.rows_per_scale = rows_per_scale
     if residual is not None:
-        _req(residual, BF16, "residual")
+        _req(residual, F32, "residual")
         assert residual.shape == (M, N) and residual.stride(1) == 1
         a.residual, a.ldr = residual.data_ptr(), residual.stride(0)
-    need = lib().sav_gemm_workspace_bytes(C.byref(a))
-    if need:
-        ws = _workspace(need, A.device)
-        a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
     check(lib().sav_gemm(C.byref(a), _stream()))
     return out
 
@@ -99,28 +95,34 @@ def colsum(X, out=None, accumulate=False):
 
 
 def layernorm_fwd(x, scale, bias, eps=1e-6):
-    _req(x, BF16, "x")
-    C_ = x.shape[-1]
-    rows = x.numel() // C_
-    assert x.is_contiguous()
-    y = torch.empty_like(x)
+    """x: fp32 [rows, C] view of the residual stream (unit inner stride, any row pitch)."""
+    _req(x, F32, "x")
+    assert x.dim() == 2 and x.stride(1) == 1
+    rows, C_ = x.shape
+    y = torch.empty((rows, C_), dtype=BF16, device=x.device)
     mean = torch.empty(rows, dtype=F32, device=x.device)
     rstd = torch.empty(rows, dtype=F32, device=x.device)
-    check(lib().sav_layernorm_fwd(_p(x), _p(scale), _p(bias), _p(y), _p(mean), _p(rstd), rows, C_,
-                                  eps, _stream()))
+    check(lib().sav_layernorm_fwd(_p(x), x.stride(0), _p(scale), _p(bias), _p(y), y.stride(0),
+                                  _p(mean), _p(rstd), rows, C_, eps, _stream()))
     return y, mean, rstd
 
 
-def layernorm_bwd(dy, x, scale, mean, rstd, dscale, dbias, dx_add=None, accumulate=False):
-    C_ = x.shape[-1]
-    rows = x.numel() // C_
-    assert dy.is_contiguous() and x.is_contiguous()
-    dx = torch.empty_like(x)
-    ws = _workspace(lib().sav_layernorm_bwd_workspace_bytes(rows, C_), x.device, "ln")
-    check(lib().sav_layernorm_bwd(_p(dy), _p(x), _p(scale), _p(mean), _p(rstd), _p(dx_add), _p(dx),
-                                  _p(dscale), _p(dbias), _p(ws), rows, C_, int(accumulate),
-                                  _stream()))
-    return dx
+def layernorm_bwd(dy, x, scale, mean, rstd, dscale, dbias, dx_add=None, dx=None, dx16=None):
+    """dy bf16 [rows,C]; x fp32 [rows,C] view; returns (dx fp32, dx16 bf16) with x's row pitch.
+    dscale / dbias are accumulated."""
+    _req(dy, BF16, "dy"); _req(x, F32, "x")
+    assert dy.dim() == 2 and x.dim() == 2 and dy.stride(1) == 1 and x.stride(1) == 1
+    rows, C_ = x.shape
+    if dx is None:
+        assert x.is_contiguous()
+        dx = torch.empty_like(x)
+        dx16 = torch.empty((rows, C_), dtype=BF16, device=x.device)
+    assert dx.stride(0) == x.stride(0) and (dx16 is None or dx16.stride(0) == x.stride(0))
+    assert dx_add is None or (dx_add.dtype == F32 and dx_add.stride(0) == x.stride(0))
+    check(lib().sav_layernorm_bwd(_p(dy), dy.stride(0), _p(x), x.stride(0), _p(scale), _p(mean),
+                                  _p(rstd), _p(dx_add), _p(dx), _p(dx16), _p(dscale), _p(dbias),
+                                  rows, C_, _stream()))
+    return dx, dx16
 
 
 def patchify(images, ph, pw, hwcn=True):
@@ -138,7 +140,7 @@ def patchify(images, ph, pw, hwcn=True):
 
 def embed_fwd(tok, cls, pos, B, n_tok, C_):
     has_cls = cls is not None
-    x = torch.empty((B, n_tok + int(has_cls), C_), dtype=BF16, device=tok.device)
+    x = torch.empty((B, n_tok + int(has_cls), C_), dtype=F32, device=tok.device)
     check(lib().sav_embed_fwd(_p(tok), _p(cls), _p(pos), _p(x), B, n_tok, C_, int(has_cls), _stream()))
     return x
 
@@ -157,14 +159,17 @@ def _bnhd_strides(t):
     return t.stride(0), t.stride(1)
 
 
-def attn_fwd(q, k, v, scale=None):
-    """q [B,Nq,H,D], k/v [B,Nk,H,D] bf16 (strided views ok) -> o [B,Nq,H,D], lse [B,H,Nq]."""
+def attn_fwd(q, k, v, scale=None, save_lo=True):
+    """q [B,Nq,H,D], k/v [B,Nk,H,D] bf16 (strided views ok) -> o [2,B,Nq,H,D] (o[0] = output,
+    o[1] = its low half for backward when save_lo), lse [B,H,Nq]."""
     B, Nq, H, D = q.shape
     Nk = k.shape[1]
-    o = torch.empty((B, Nq, H, D), dtype=BF16, device=q.device)
+    o2 = torch.empty((2 if save_lo else 1, B, Nq, H, D), dtype=BF16, device=q.device)
+    o = o2[0]
     lse = torch.empty((B, H, Nq), dtype=F32, device=q.device)
     a = AttnFwdArgs()
     a.q, a.k, a.v, a.o, a.lse = q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr()
+    a.o_lo = o2[1].data_ptr() if save_lo else None
     a.B, a.H, a.Nq, a.Nk, a.D = B, H, Nq, Nk, D
     a.q_batch_stride, a.q_row_stride = _bnhd_strides(q)
     a.k_batch_stride, a.k_row_stride = _bnhd_strides(k)
@@ -172,13 +177,14 @@ def attn_fwd(q, k, v, scale=None):
     a.o_batch_stride, a.o_row_stride = _bnhd_strides(o)
     a.scale = scale if scale is not None else 1.0 / math.sqrt(D)
     check(lib().sav_attn_fwd(C.byref(a), _stream()))
-    return o, lse
+    return o2, lse
 
 
-def attn_bwd(q, k, v, o, d_o, lse, dq, dk, dv, scale=None):
-    """Writes dq/dk/dv (views with the same strides as q/k/v)."""
+def attn_bwd(q, k, v, o2, d_o, lse, dq, dk, dv, scale=None):
+    """Writes dq/dk/dv (views with the same strides as q/k/v).  o2: what attn_fwd returned."""
     B, Nq, H, D = q.shape
     Nk = k.shape[1]
+    o = o2[0]
     assert d_o.stride() == o.stride()
     assert dq.stride() == q.stride() and dk.stride() == k.stride() and dv.stride() == v.stride()
     delta = torch.empty((B, H, Nq), dtype=F32, device=q.device)
@@ -186,6 +192,7 @@ def attn_bwd(q, k, v, o, d_o, lse, dq, dk, dv, scale=None):
     a = AttnBwdArgs()
     a.q, a.k, a.v, a.o, a.d_o, a.lse = (q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(),
                                         d_o.data_ptr(), lse.data_ptr())
+    a.o_lo = o2[1].data_ptr() if o2.shape[0] > 1 else None
     a.dq, a.dk, a.dv = dq.data_ptr(), dk.data_ptr(), dv.data_ptr()
     a.delta, a.dq_accum = delta.data_ptr(), dq_acc.data_ptr()
     a.B, a.H, a.Nq, a.Nk, a.D = B, H, Nq, Nk, D

@@ -28,19 +28,22 @@ class Tape:
     def __exit__(self, *exc):
         _state.tape = self._prev
 
-    def backward(self):
+    def backward(self, after_node=None):
         nodes, self.nodes = self.nodes, []
-        for fn in reversed(nodes):
+        for i, fn in enumerate(reversed(nodes)):
             fn()
+            if after_node is not None:
+                after_node(i)
 
 
 class Var:
     """A device activation (bf16 unless noted) plus its gradient slot."""
-    __slots__ = ("_v", "g", "requires_grad", "pre_act", "g_is_pre", "shape3")
+    __slots__ = ("_v", "g", "g16", "requires_grad", "pre_act", "g_is_pre", "shape3")
 
     def __init__(self, v=None, requires_grad=True):
         self._v = v
-        self.g = None
+        self.g = None      # gradient: bf16 for activations, fp32 for residual-stream Vars
+        self.g16 = None    # residual-stream Vars only: bf16 copy of g (MMA operand)
         self.requires_grad = requires_grad
         self.pre_act = None    # bf16 pre-activation saved by a fused GELU epilogue
         self.g_is_pre = False  # g already multiplied by gelu'(pre_act)
@@ -66,6 +69,10 @@ class Var:
         g, self.g = self.g, None
         return g
 
+    def take_grad16(self):
+        g, self.g16 = self.g16, None
+        return g
+
     def __add__(self, other):
         from . import functional as F
         return F.add(self, other)
@@ -83,18 +90,28 @@ def record(fn):
         t.record(fn)
 
 
-def value_and_grad(fn, has_aux=False):
+def value_and_grad(fn, has_aux=False, grad_hook=None):
     """value_and_grad(loss_fn)(params) -> (value, grads).  `params` must be a ParamTree (arena-backed);
     grads is a ParamTree of views into the arena's fp32 gradient buffer.  The loss function must
-    return a `LossVar` produced by functional.softmax_cross_entropy (it seeds the backward)."""
+    return a `LossVar` produced by functional.softmax_cross_entropy (it seeds the backward).
+    grad_hook (dp.DataParallel): begin(arena) / wrote(path) / after_node(i) / finish() -- lets the
+    gradient all-reduce of finished buckets overlap the rest of the backward pass."""
     def wrapped(params, *args, **kw):
         arena = params.arena
         arena.begin_grad()
-        with Tape() as tape:
-            out = fn(params, *args, **kw)
-            loss = out[0] if has_aux else out
-            loss.seed()
-            tape.backward()
+        arena.grad_hook = grad_hook
+        if grad_hook is not None:
+            grad_hook.begin(arena)
+        try:
+            with Tape() as tape:
+                out = fn(params, *args, **kw)
+                loss = out[0] if has_aux else out
+                loss.seed()
+                tape.backward(grad_hook.after_node if grad_hook is not None else None)
+            if grad_hook is not None:
+                grad_hook.finish()
+        finally:
+            arena.grad_hook = None
         grads = arena.grad_tree()
         return ((loss, out[1]), grads) if has_aux else (loss, grads)
     return wrapped

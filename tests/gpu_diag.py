@@ -38,13 +38,22 @@ def case_gemm(a_mn, b_mn, N, epi="none", M=296, K=192, split_k=1):
         kw = dict(bias=bias, act=1, aux_out=aux)
         pre = ref + bias
         ref = torch.nn.functional.gelu(pre, approximate="tanh")
-    elif epi == "full":
+    elif epi == "full":   # fp32 residual-stream epilogue: bias, LayerScale, drop-path, residual
         bias = torch.randn(N, device=dev)
         cs = torch.rand(N, device=dev) + 0.5
         rs = torch.rand((M + 49) // 50, device=dev) + 0.5
-        res = torch.randn(M, N, device=dev).bfloat16()
-        kw = dict(bias=bias, col_scale=cs, row_scale=rs, rows_per_scale=50, residual=res)
-        ref = (ref + bias) * cs * rs.repeat_interleave(50)[:M, None] + res.float()
+        res = torch.randn(M, N, device=dev)
+        kw = dict(bias=bias, col_scale=cs, row_scale=rs, rows_per_scale=50, residual=res,
+                  out_fp32=True)
+        ref = (ref + bias) * cs * rs.repeat_interleave(50)[:M, None] + res
+    elif epi == "bias_act":   # single-output GELU (inference form)
+        bias = torch.randn(N, device=dev)
+        kw = dict(bias=bias, act=1)
+        ref = torch.nn.functional.gelu(ref + bias, approximate="tanh")
+    elif epi == "accum":
+        d0 = torch.randn(M, N, device=dev)
+        kw = dict(out=d0.clone(), accumulate=True, split_k=split_k)
+        ref = ref + d0
     elif epi == "dgelu":
         h = torch.randn(M, N, device=dev).bfloat16()
         kw = dict(aux_in=h)
@@ -61,25 +70,70 @@ def case_gemm(a_mn, b_mn, N, epi="none", M=296, K=192, split_k=1):
     return errs
 
 
-def case_ln():
+def case_ln(strided=False):
     import torch
     from sav import ops
     torch.manual_seed(0)
     rows, C = 1000, 384
-    x = (torch.randn(rows, C, device="cuda") * 2 + 0.5).bfloat16()
+    pitch = 3 * C if strided else C
+    xbuf = torch.randn(rows, pitch, device="cuda") * 2 + 0.5
+    x = xbuf[:, :C]
     g = torch.randn(C, device="cuda"); b = torch.randn(C, device="cuda")
     y, mean, rstd = ops.layernorm_fwd(x, g, b)
-    xf = x.float().requires_grad_(True)
+    xf = x.detach().clone().requires_grad_(True)
     gf = g.clone().requires_grad_(True); bf = b.clone().requires_grad_(True)
     ref = torch.nn.functional.layer_norm(xf, (C,), gf, bf, eps=1e-6)
     dy = torch.randn(rows, C, device="cuda").bfloat16()
-    add = torch.randn(rows, C, device="cuda").bfloat16()
+    add = torch.randn(rows, pitch, device="cuda")[:, :C]
     ref.backward(dy.float())
-    ds = torch.empty(C, device="cuda"); db = torch.empty(C, device="cuda")
-    dx = ops.layernorm_bwd(dy, x, g, mean, rstd, ds, db, dx_add=add)
+    ds = torch.zeros(C, device="cuda"); db = torch.zeros(C, device="cuda")
+    dxb = torch.zeros(rows, pitch, device="cuda")
+    dx16b = torch.zeros(rows, pitch, device="cuda", dtype=torch.bfloat16)
+    dx, dx16 = ops.layernorm_bwd(dy, x, g, mean, rstd, ds, db, dx_add=add, dx=dxb[:, :C],
+                                 dx16=dx16b[:, :C])
     torch.cuda.synchronize()
-    return {"y": rel_err(y, ref), "dx": rel_err(dx, xf.grad + add.float()),
-            "dscale": rel_err(ds, gf.grad), "dbias": rel_err(db, bf.grad)}
+    return {"y": rel_err(y, ref), "dx": rel_err(dx, xf.grad + add), "dx16": rel_err(dx16, xf.grad + add),
+            "dscale": rel_err(ds, gf.grad), "dbias": rel_err(db, bf.grad),
+            "untouched": float(dxb[:, C:].abs().max()) if strided else 0.0}
+
+
+def case_gemm_time(M=50432, N=1536, K=384, mode="gelu2", a_mn=False, b_mn=True, reps=20):
+    """Times one GEMM shape of the DeiT-S block; returns TFLOP/s and effective GB/s (not an error
+    metric: reported through the same table with tol ignored)."""
+    import torch
+    from sav import ops
+    dev = "cuda"
+    A = torch.randn((K, M) if a_mn else (M, K), device=dev).bfloat16()
+    B = torch.randn((K, N) if b_mn else (N, K), device=dev).bfloat16()
+    kw = {}
+    byt = (M * K + N * K) * 2
+    if mode == "gelu2":
+        kw = dict(bias=torch.randn(N, device=dev), act=1,
+                  aux_out=torch.empty(M, N, device=dev, dtype=torch.bfloat16)); byt += 4 * M * N
+    elif mode == "plain":
+        byt += 2 * M * N
+    elif mode == "dgelu":
+        kw = dict(aux_in=torch.randn(M, N, device=dev).bfloat16()); byt += 4 * M * N
+    elif mode == "resid":
+        kw = dict(bias=torch.randn(N, device=dev), residual=torch.randn(M, N, device=dev),
+                  out_fp32=True); byt += 8 * M * N
+    elif mode == "dw":
+        kw = dict(out=torch.zeros(M, N, device=dev), accumulate=True, split_k=0); byt += 4 * M * N
+    out = kw.pop("out", None)
+    if out is None:
+        out = torch.empty(M, N, device=dev, dtype=torch.float32 if kw.get("out_fp32") else torch.bfloat16)
+    kw.pop("out_fp32", None)
+    for _ in range(3):
+        ops.gemm(A, B, a_mn=a_mn, b_mn=b_mn, out=out, **kw)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        ops.gemm(A, B, a_mn=a_mn, b_mn=b_mn, out=out, **kw)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    return {"us": ms * 1e3, "tflops": 2.0 * M * N * K / ms / 1e9, "gbs": byt / ms / 1e6}
 
 
 def case_attn(B=2, H=3, Nq=197, Nk=197, bwd=True):
@@ -95,13 +149,15 @@ def case_attn(B=2, H=3, Nq=197, Nk=197, bwd=True):
     s = (qf / 8.0) @ kf.transpose(-1, -2)
     pr = torch.softmax(s, -1)
     ref = (pr @ vf).permute(0, 2, 1, 3)
-    errs = {"o": rel_err(o, ref),
+    o2 = o
+    o = o2[0]
+    errs = {"o": rel_err(o, ref), "o_lo": rel_err(o2[0].float() + o2[1].float(), ref),
             "lse": rel_err(lse, torch.logsumexp(s, -1))}
     if bwd:
         d_o = torch.randn(B, Nq, H, D, device="cuda").bfloat16()
         ref.backward(d_o.float())
         dqkv = torch.zeros_like(qkv)
-        ops.attn_bwd(q, k, v, o, d_o, lse, dqkv[:, :Nq, 0], dqkv[:, :Nk, 1], dqkv[:, :Nk, 2])
+        ops.attn_bwd(q, k, v, o2, d_o, lse, dqkv[:, :Nq, 0], dqkv[:, :Nk, 1], dqkv[:, :Nk, 2])
         torch.cuda.synchronize()
         errs["dq"] = rel_err(dqkv[:, :Nq, 0], qf.grad.permute(0, 2, 1, 3))
         errs["dk"] = rel_err(dqkv[:, :Nk, 1], kf.grad.permute(0, 2, 1, 3))
@@ -133,10 +189,15 @@ for am in (0, 1):
 CASES["gemm_bias_gelu"] = (case_gemm, dict(a_mn=False, b_mn=True, N=384, epi="bias_gelu"))
 CASES["gemm_full_epi"] = (case_gemm, dict(a_mn=False, b_mn=True, N=384, epi="full"))
 CASES["gemm_dgelu"] = (case_gemm, dict(a_mn=False, b_mn=False, N=384, epi="dgelu"))
+CASES["gemm_bias_act"] = (case_gemm, dict(a_mn=False, b_mn=True, N=384, epi="bias_act"))
+CASES["gemm_ntail"] = (case_gemm, dict(a_mn=False, b_mn=True, N=1000, M=256, K=384, epi="bias_act"))
+CASES["gemm_ktail"] = (case_gemm, dict(a_mn=False, b_mn=False, N=384, M=256, K=1000))
+CASES["gemm_accum"] = (case_gemm, dict(a_mn=True, b_mn=True, N=384, epi="accum", M=192, K=3000, split_k=0))
 CASES["gemm_fp32"] = (case_gemm, dict(a_mn=True, b_mn=True, N=384, epi="fp32", M=192, K=3000))
 CASES["gemm_splitk"] = (case_gemm, dict(a_mn=True, b_mn=True, N=384, epi="fp32", M=192, K=3000, split_k=5))
 CASES["gemm_big"] = (case_gemm, dict(a_mn=False, b_mn=True, N=1152, M=4000, K=384))
 CASES["ln"] = (case_ln, {})
+CASES["ln_strided"] = (case_ln, dict(strided=True))
 CASES["stem"] = (case_stem, {})
 CASES["attn_fwd_197"] = (case_attn, dict(bwd=False))
 CASES["attn_fwd_64"] = (case_attn, dict(Nq=64, Nk=64, bwd=False))
@@ -145,7 +206,35 @@ CASES["attn_577"] = (case_attn, dict(B=1, H=2, Nq=577, Nk=577))
 CASES["attn_cross"] = (case_attn, dict(B=2, H=2, Nq=225, Nk=64))
 
 
+TIMING = {
+    "t_qkv_fwd": dict(N=1152, K=384, mode="plain"),
+    "t_out_fwd": dict(N=384, K=384, mode="resid"),
+    "t_fc1_fwd": dict(N=1536, K=384, mode="gelu2"),
+    "t_fc2_fwd": dict(N=384, K=1536, mode="resid"),
+    "t_fc2_dx": dict(N=1536, K=384, mode="dgelu", b_mn=False),
+    "t_fc1_dx": dict(N=384, K=1536, mode="plain", b_mn=False),
+    "t_qkv_dx": dict(N=384, K=1152, mode="plain", b_mn=False),
+    "t_fc1_dw": dict(M=384, N=1536, K=50432, mode="dw", a_mn=True),
+    "t_fc2_dw": dict(M=1536, N=384, K=50432, mode="dw", a_mn=True),
+    "t_qkv_dw": dict(M=384, N=1152, K=50432, mode="dw", a_mn=True),
+    "t_out_dw": dict(M=384, N=384, K=50432, mode="dw", a_mn=True),
+}
+
+
 def main():
+    if "--time" in sys.argv:
+        for name, kw in TIMING.items():
+            try:
+                r = subprocess.run([sys.executable, __file__, "--timecase", name], capture_output=True,
+                                   text=True, timeout=120)
+                line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")]
+                print(f"{name:12s} {line[-1][7:] if line else (r.stderr or r.stdout).strip().splitlines()[-2:]}", flush=True)
+            except subprocess.TimeoutExpired:
+                print(f"{name:12s} HANG", flush=True)
+        return 0
+    if "--timecase" in sys.argv:
+        print("RESULT " + json.dumps(case_gemm_time(**TIMING[sys.argv[sys.argv.index("--timecase") + 1]])))
+        return 0
     ap = argparse.ArgumentParser()
     ap.add_argument("--case")
     ap.add_argument("--tol", type=float, default=2e-2)

@@ -29,6 +29,44 @@ class _R(torch.autograd.Function):
         return (g.bfloat16().float() if ctx.bwd else g), None, None
 
 
+class _AttnCore(torch.autograd.Function):
+    """Mimics csrc/attn.cu: bf16 P for PV and dV, bf16 dS for dK/dQ, fp32 softmax statistics;
+    delta = rowsum(dO * O) from the bf16-rounded O (mode 'o16'), from O kept in fp32 ('o32'), or
+    the exact rowsum(P * dP) ('exact')."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, scale, delta_mode):
+        s = torch.einsum("bqhd,bkhd->bhqk", q, k) * scale
+        p = O.softmax_last(s)
+        o32 = torch.einsum("bhqk,bkhd->bqhd", p.bfloat16().float(), v)
+        o = o32.bfloat16().float()
+        ctx.save_for_backward(q, k, v, p, o, o32)
+        ctx.scale, ctx.mode = scale, delta_mode
+        return o
+
+    @staticmethod
+    def backward(ctx, d_o):
+        q, k, v, p, o, o32 = ctx.saved_tensors
+        d_o = d_o.bfloat16().float()
+        dp = torch.einsum("bqhd,bkhd->bhqk", d_o, v)
+        if ctx.mode == "o16":
+            delta = (d_o * o).sum(-1)
+        elif ctx.mode == "o32":
+            delta = (d_o * o32).sum(-1)
+        else:
+            delta = None
+        if delta is None:
+            dl = (p * dp).sum(-1, keepdim=True)
+        else:
+            dl = delta.permute(0, 2, 1).unsqueeze(-1)
+        ds = (p * (dp - dl) * ctx.scale).bfloat16().float()
+        dv = torch.einsum("bhqk,bqhd->bkhd", p.bfloat16().float(), d_o)
+        dk = torch.einsum("bhqk,bqhd->bkhd", ds, q)
+        dq = torch.einsum("bhqk,bkhd->bqhd", ds, k)
+        return dq.bfloat16().float(), dk.bfloat16().float(), dv.bfloat16().float(), None, None
+
+
+ATTN_MODE = [None]
 SITES = {}  # site name -> (round forward value, round gradient); missing = follow the group switch
 
 
@@ -61,9 +99,12 @@ def forward(params, images_nhwc, cfg, act=True, stream=True, weights=True, attn=
         q = R(torch.einsum("bqc,chd->bqhd", y, Wt(a["queries"]["kernel"])), act, site="qkv")
         k = R(torch.einsum("bkc,chd->bkhd", y, Wt(a["keys"]["kernel"])), act, site="qkv")
         v = R(torch.einsum("bkc,chd->bkhd", y, Wt(a["values"]["kernel"])), act, site="qkv")
-        s = R(torch.einsum("bqhd,bkhd->bhqk", q, k) / math.sqrt(d), False, attn)
-        pr = R(O.softmax_last(s), attn, False)
-        o = R(torch.einsum("bhqk,bkhd->bqhd", pr, v), act, site="ctx")
+        if ATTN_MODE[0]:
+            o = _AttnCore.apply(q, k, v, 1.0 / math.sqrt(d), ATTN_MODE[0])
+        else:
+            s = R(torch.einsum("bqhd,bkhd->bhqk", q, k) / math.sqrt(d), False, attn)
+            pr = R(O.softmax_last(s), attn, False)
+            o = R(torch.einsum("bhqk,bkhd->bqhd", pr, v), act, site="ctx")
         y = torch.einsum("bqhd,hdc->bqc", o, Wt(a["DenseGeneral_0"]["kernel"]))
         x = R(y + x, stream, site="stream")
         y = R(O.layer_norm(x, p["LayerNorm_1"]["scale"], p["LayerNorm_1"]["bias"]), act, site="ln")
@@ -91,6 +132,7 @@ def main():
     ap.add_argument("--model", default="deit_ti_patch16")
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--img", type=int, default=224)
+    ap.add_argument("--only", default="")
     a = ap.parse_args()
     cfg = O.vit_config(a.model)
     params = O.synthetic_vit_params(cfg, a.img, seed=42)
@@ -120,8 +162,13 @@ def main():
         cases[name] = dict(stream=False, _sites=sites)
     cases["stream: fwd fp32, grad bf16"] = dict(_sites={"stream": (False, True)})
     cases["stream: fwd bf16, grad fp32"] = dict(_sites={"stream": (True, False)})
+    for m in ("o16", "o32", "exact"):
+        cases[f"fp32 stream, kernel-like attn, delta {m}"] = dict(stream=False, _attn=m)
+    if a.only:
+        cases = {k: v for k, v in cases.items() if a.only in k}
     for name, kw in cases.items():
         kw = dict(kw)
+        ATTN_MODE[0] = kw.pop("_attn", None)
         SITES.clear()
         SITES.update(kw.pop("_sites", {}))
         logits, grads = run(cfg, params, images, labels, **kw)
