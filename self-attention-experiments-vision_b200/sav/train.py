@@ -80,9 +80,9 @@ def train_step(state, images, labels, label_smoothing=0.0, dp=None):
     (device-resident loss sum and top-1 count)."""
     world = dp.world_size if dp is not None else 1
     loss_fn = make_loss_fn(state.model, label_smoothing, world)
-    (loss, _logits), _grads = value_and_grad(loss_fn, has_aux=True)(state.params, images, labels)
-    if dp is not None:
-        dp.all_reduce_grads(state.arena)
+    # dp is the gradient hook: finished buckets are all-reduced while backward is still running
+    (loss, _logits), _grads = value_and_grad(loss_fn, has_aux=True, grad_hook=dp)(
+        state.params, images, labels)
     state.apply_gradients()
     return loss
 
