@@ -86,7 +86,7 @@ def forward(params, images_nhwc, cfg, act=True, stream=True, weights=True, attn=
     b, Hh, Ww, c = images_nhwc.shape
     gh, gw = Hh // ph, Ww // pw
     x = images_nhwc.reshape(b, gh, ph, gw, pw, c).permute(0, 1, 3, 2, 4, 5).reshape(b, gh * gw, -1)
-    x = R(x, act, False)
+    x = R(x, act, False, site="img")
     tok = R(x @ Wt(params["PatchEmbedBlock_0"]["Dense_0"]["kernel"]), act, site="tok")
     enc = params["Encoder_0"]
     x = torch.cat([params["cls"].expand(b, -1, -1), tok], 1) + enc["AddAbsPosEmbed_0"]["pos_embed"]
@@ -113,8 +113,8 @@ def forward(params, images_nhwc, cfg, act=True, stream=True, weights=True, attn=
         h = R(O.gelu_tanh(h), act, site="hid")
         y = h @ Wt(f["Dense_1"]["kernel"]) + f["Dense_1"]["bias"]
         x = R(x + y, stream, site="stream")
-    x = R(O.layer_norm(x, enc["LayerNorm_0"]["scale"], enc["LayerNorm_0"]["bias"]), act)
-    return R(x[:, 0] @ Wt(params["Dense_0"]["kernel"]) + params["Dense_0"]["bias"], act)
+    x = R(O.layer_norm(x, enc["LayerNorm_0"]["scale"], enc["LayerNorm_0"]["bias"]), act, site="ln_f")
+    return R(x[:, 0] @ Wt(params["Dense_0"]["kernel"]) + params["Dense_0"]["bias"], act, site="logits")
 
 
 def run(cfg, params, images, labels, **kw):
