@@ -282,7 +282,12 @@ def main():
                                              f"installable in this image"}
         print(json.dumps(out), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # the captured step holds NCCL kernels; tearing the communicator down under a live CUDA graph
+        # can block, so leave together and let process exit release everything
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":

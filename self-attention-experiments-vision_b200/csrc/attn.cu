@@ -20,191 +20,6 @@ __device__ __forceinline__ uint32_t sw128(int r, int g16) {
   return (uint32_t)(r * 128 + ((g16 ^ (r & 7)) << 4));
 }
 
-struct AttnFwdParams {
-  bf16* o;
-  bf16* o_lo;
-  float* lse;
-  int B, H, Nq, Nk;
-  int64_t o_bs, o_rs;
-  float scale_log2;  // scale * log2(e)
-};
-
-// grid (q_tiles, H, B); 128 threads; thread t owns query row t of the tile (TMEM lane t).
-__global__ void __launch_bounds__(128)
-attn_fwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
-                const __grid_constant__ CUtensorMap tv, const AttnFwdParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~uintptr_t(1023));
-  uint8_t* sQ = smem;                   // 16 KB
-  uint8_t* sK = sQ + TILE_B;            // 2 x 16 KB
-  uint8_t* sV = sK + 2 * TILE_B;        // 2 x 16 KB
-  uint8_t* sP = sV + 2 * TILE_B;        // 2 chunks x 16 KB  ([128 q rows] x [64 keys])
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * TILE_B);
-  uint64_t* q_full = bars;
-  uint64_t* kv_full = bars + 1;  // [2]
-  uint64_t* s_full = bars + 3;
-  uint64_t* o_full = bars + 4;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
-
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
-  const int nblk = (p.Nk + AT - 1) / AT;
-
-  if (tid == 0) {
-    tma_prefetch_desc(&tq);
-    tma_prefetch_desc(&tk);
-    tma_prefetch_desc(&tv);
-    mbar_init(q_full, 1);
-    mbar_init(&kv_full[0], 1);
-    mbar_init(&kv_full[1], 1);
-    mbar_init(s_full, 1);
-    mbar_init(o_full, 1);
-    fence_barrier_init();
-  }
-  if (warp == 0) tmem_alloc<256>(tmem_slot);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  const uint32_t tS = tmem, tO = tmem + AT;
-  const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
-
-  if (tid == 0) {
-    mbar_expect_tx(q_full, TILE_B);
-    tma_load_3d(sQ, &tq, q_full, h * AD, qt * AT, b);
-    mbar_expect_tx(&kv_full[0], 2 * TILE_B);
-    tma_load_3d(sK, &tk, &kv_full[0], h * AD, 0, b);
-    tma_load_3d(sV, &tv, &kv_full[0], h * AD, 0, b);
-  }
-
-  float m_run = -INFINITY, l_run = 0.f;
-  float o_acc[AD];
-#pragma unroll
-  for (int i = 0; i < AD; ++i) o_acc[i] = 0.f;
-
-  for (int j = 0; j < nblk; ++j) {
-    const int buf = j & 1;
-    const int k0 = j * AT;
-    const int n_valid = min(AT, p.Nk - k0);
-    const int n_cur = (n_valid + 15) & ~15;  // UMMA N / PV K extent
-    if (tid == 0) {
-      if (j + 1 < nblk) {
-        const int nb = (j + 1) & 1;
-        mbar_expect_tx(&kv_full[nb], 2 * TILE_B);
-        tma_load_3d(sK + nb * TILE_B, &tk, &kv_full[nb], h * AD, (j + 1) * AT, b);
-        tma_load_3d(sV + nb * TILE_B, &tv, &kv_full[nb], h * AD, (j + 1) * AT, b);
-      }
-      if (j == 0) mbar_wait(q_full, 0);
-      mbar_wait(&kv_full[buf], (j >> 1) & 1);
-      tc_fence_after();
-      const uint32_t idesc = make_idesc_bf16(AT, n_cur, false, false);
-      const uint32_t aq = smem_u32(sQ), bk = smem_u32(sK + buf * TILE_B);
-#pragma unroll
-      for (int k = 0; k < AD / 16; ++k)
-        umma_f16(tS, make_smem_desc(aq + k * 32, 16, 1024), make_smem_desc(bk + k * 32, 16, 1024),
-                 idesc, k > 0);
-      umma_commit(s_full);
-    }
-    __syncwarp();
-    mbar_wait(s_full, j & 1);
-    tc_fence_after();
-
-    // pass 1: row max over valid keys
-    float mx = -INFINITY;
-    for (int c = 0; c < n_cur; c += 32) {
-      uint32_t r[32];
-      tmem_ld32(tS + lane_off + c, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; ++i)
-        if (c + i < n_valid) mx = fmaxf(mx, __uint_as_float(r[i]));
-    }
-    const float m_new = fmaxf(m_run, mx * p.scale_log2);
-    const float alpha = exp2f(m_run - m_new);  // m_run = -inf on first block -> 0
-    // pass 2: p = exp2(s*c - m_new), row sum, bf16 P -> swizzled smem (K-major A operand)
-    float psum = 0.f;
-    for (int c = 0; c < n_cur; c += 32) {
-      uint32_t r[32];
-      tmem_ld32(tS + lane_off + c, r);
-      tmem_ld_wait();
-      float e[32];
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const float v = exp2f(__uint_as_float(r[i]) * p.scale_log2 - m_new);
-        e[i] = (c + i < n_valid) ? v : 0.f;
-        psum += e[i];
-      }
-      uint8_t* chunk = sP + (c >> 6) * TILE_B;
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const int g16 = ((c & 63) >> 3) + g;
-        *reinterpret_cast<uint4*>(chunk + sw128(tid, g16)) =
-            make_uint4(pack_bf16(e[g * 8 + 0], e[g * 8 + 1]), pack_bf16(e[g * 8 + 2], e[g * 8 + 3]),
-                       pack_bf16(e[g * 8 + 4], e[g * 8 + 5]), pack_bf16(e[g * 8 + 6], e[g * 8 + 7]));
-      }
-    }
-    l_run = l_run * alpha + psum;
-    m_run = m_new;
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after();
-      const uint32_t idesc = make_idesc_bf16(AT, AD, false, true);  // B = V is MN-major
-      const uint32_t ap = smem_u32(sP), bv = smem_u32(sV + buf * TILE_B);
-      for (int ks = 0; ks < n_cur / 16; ++ks)
-        umma_f16(tO, make_smem_desc(ap + (ks >> 2) * TILE_B + (ks & 3) * 32, 16, 1024),
-                 make_smem_desc(bv + ks * 2048, TILE_B, 1024), idesc, ks > 0);
-      umma_commit(o_full);
-    }
-    __syncwarp();
-    mbar_wait(o_full, j & 1);
-    tc_fence_after();
-#pragma unroll
-    for (int c = 0; c < AD; c += 32) {
-      uint32_t r[32];
-      tmem_ld32(tO + lane_off + c, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; ++i) o_acc[c + i] = o_acc[c + i] * alpha + __uint_as_float(r[i]);
-    }
-    tc_fence_before();
-  }
-
-  const int row = qt * AT + tid;
-  if (row < p.Nq) {
-    const float inv = 1.f / l_run;
-    const int64_t off = (int64_t)b * p.o_bs + (int64_t)row * p.o_rs + h * AD;
-    bf16* dst = p.o + off;
-#pragma unroll
-    for (int i = 0; i < AD; ++i) o_acc[i] *= inv;
-#pragma unroll
-    for (int g = 0; g < AD / 8; ++g)
-      *reinterpret_cast<uint4*>(dst + g * 8) = make_uint4(
-          pack_bf16(o_acc[g * 8 + 0], o_acc[g * 8 + 1]), pack_bf16(o_acc[g * 8 + 2], o_acc[g * 8 + 3]),
-          pack_bf16(o_acc[g * 8 + 4], o_acc[g * 8 + 5]), pack_bf16(o_acc[g * 8 + 6], o_acc[g * 8 + 7]));
-    if (p.o_lo) {
-      // low half of O (o - bf16(o)): lets backward form delta = rowsum(dO * O) from a ~16-bit
-      // mantissa O; the bf16-rounded O alone costs ~0.5e-2 of the 2e-2 gradient parity budget
-      bf16* dlo = p.o_lo + off;
-#pragma unroll
-      for (int i = 0; i < AD; ++i) o_acc[i] -= __bfloat162float(__float2bfloat16(o_acc[i]));
-#pragma unroll
-      for (int g = 0; g < AD / 8; ++g)
-        *reinterpret_cast<uint4*>(dlo + g * 8) = make_uint4(
-            pack_bf16(o_acc[g * 8 + 0], o_acc[g * 8 + 1]), pack_bf16(o_acc[g * 8 + 2], o_acc[g * 8 + 3]),
-            pack_bf16(o_acc[g * 8 + 4], o_acc[g * 8 + 5]), pack_bf16(o_acc[g * 8 + 6], o_acc[g * 8 + 7]));
-    }
-    p.lse[((int64_t)b * p.H + h) * p.Nq + row] = m_run * LN2 + logf(l_run);
-  }
-  __syncthreads();
-  if (warp == 0) {
-    tc_fence_after();
-    tmem_dealloc<256>(tmem);
-  }
-}
-
 // ------------------------------------------------------------------------------- backward
 struct AttnBwdParams {
   const float* lse;
@@ -471,41 +286,11 @@ static int make_qkv_map(CUtensorMap* m, const void* base, int64_t H, int64_t N, 
   return make_tmap_bf16(m, base, 3, dims, str, box);
 }
 
-constexpr int kFwdSmem = 7 * TILE_B + 1024 + 128;
 constexpr int kBwdSmem = 10 * TILE_B + 2 * AT * 4 + 1024 + 128;
 
 }  // namespace sav
 
 using namespace sav;
-
-extern "C" int sav_attn_fwd(const sav_attn_fwd_args* a, void* stream) {
-  if (!a || a->D != AD) return set_error(SAV_ERR_SHAPE, "sav_attn_fwd: head dim must be 64");
-  if (a->B <= 0 || a->H <= 0 || a->Nq <= 0 || a->Nk <= 0)
-    return set_error(SAV_ERR_SHAPE, "sav_attn_fwd: empty shape");
-  if (a->o_row_stride % 8 || a->o_batch_stride % 8 || !aligned16(a->o))
-    return set_error(SAV_ERR_ALIGN, "sav_attn_fwd: output strides/pointer alignment");
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  CUtensorMap tq, tk, tv;
-  int rc;
-  if ((rc = make_qkv_map(&tq, a->q, a->H, a->Nq, a->B, a->q_batch_stride, a->q_row_stride))) return rc;
-  if ((rc = make_qkv_map(&tk, a->k, a->H, a->Nk, a->B, a->k_batch_stride, a->k_row_stride))) return rc;
-  if ((rc = make_qkv_map(&tv, a->v, a->H, a->Nk, a->B, a->v_batch_stride, a->v_row_stride))) return rc;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem);
-    if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "attn fwd smem attr: %s", cudaGetErrorString(e));
-    attr = true;
-  }
-  AttnFwdParams p;
-  p.o = reinterpret_cast<bf16*>(a->o); p.o_lo = reinterpret_cast<bf16*>(a->o_lo); p.lse = a->lse;
-  p.B = (int)a->B; p.H = (int)a->H; p.Nq = (int)a->Nq; p.Nk = (int)a->Nk;
-  p.o_bs = a->o_batch_stride; p.o_rs = a->o_row_stride;
-  p.scale_log2 = a->scale * LOG2E;
-  dim3 grid((unsigned)((a->Nq + AT - 1) / AT), (unsigned)a->H, (unsigned)a->B);
-  attn_fwd_kernel<<<grid, 128, kFwdSmem, st>>>(tq, tk, tv, p);
-  count_launch();
-  return check_launch("sav_attn_fwd");
-}
 
 extern "C" int sav_attn_bwd(const sav_attn_bwd_args* a, void* stream) {
   if (!a || a->D != AD) return set_error(SAV_ERR_SHAPE, "sav_attn_bwd: head dim must be 64");

@@ -206,7 +206,39 @@ CASES["attn_577"] = (case_attn, dict(B=1, H=2, Nq=577, Nk=577))
 CASES["attn_cross"] = (case_attn, dict(B=2, H=2, Nq=225, Nk=64))
 
 
+def case_attn_time(B=256, H=6, N=197, bwd=False, reps=20):
+    import torch
+    from sav import ops
+    D = 64
+    qkv = torch.randn(B, N, 3, H, D, device="cuda").bfloat16()
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    o2, lse = ops.attn_fwd(q, k, v)
+    d_o = torch.randn(B, N, H, D, device="cuda").bfloat16()
+    dqkv = torch.empty_like(qkv)
+    if bwd:
+        fn = lambda: ops.attn_bwd(q, k, v, o2, d_o, lse, dqkv[:, :, 0], dqkv[:, :, 1], dqkv[:, :, 2])
+        flops, byt = 8.0 * B * H * N * N * D, 9 * B * N * H * D * 2
+    else:
+        fn = lambda: ops.attn_fwd(q, k, v)
+        flops, byt = 4.0 * B * H * N * N * D, 5 * B * N * H * D * 2
+    for _ in range(3):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    return {"us": ms * 1e3, "tflops": flops / ms / 1e9, "gbs": byt / ms / 1e6}
+
+
 TIMING = {
+    "t_attn_fwd": dict(_attn=True),
+    "t_attn_bwd": dict(_attn=True, bwd=True),
+    "t_attn_fwd577": dict(_attn=True, B=64, H=12, N=577),
+    "t_attn_bwd577": dict(_attn=True, B=64, H=12, N=577, bwd=True),
     "t_qkv_fwd": dict(N=1152, K=384, mode="plain"),
     "t_out_fwd": dict(N=384, K=384, mode="resid"),
     "t_fc1_fwd": dict(N=1536, K=384, mode="gelu2"),
@@ -233,7 +265,9 @@ def main():
                 print(f"{name:12s} HANG", flush=True)
         return 0
     if "--timecase" in sys.argv:
-        print("RESULT " + json.dumps(case_gemm_time(**TIMING[sys.argv[sys.argv.index("--timecase") + 1]])))
+        kw = dict(TIMING[sys.argv[sys.argv.index("--timecase") + 1]])
+        fn = case_attn_time if kw.pop("_attn", False) else case_gemm_time
+        print("RESULT " + json.dumps(fn(**kw)))
         return 0
     ap = argparse.ArgumentParser()
     ap.add_argument("--case")
