@@ -95,9 +95,15 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, int64_t col
   return SAV_OK;
 }
 
+static void* g_debug_buffer = nullptr;
+void* sav_debug_buffer() { return g_debug_buffer; }
+void set_debug_buffer(void* p) { g_debug_buffer = p; }
+
 }  // namespace sav
 
 extern "C" {
+/* development aid: device buffer (>= 6*512 int64) receiving a kernel phase timeline; NULL disables */
+void sav_set_debug_buffer(void* p) { sav::set_debug_buffer(p); }
 int sav_abi_version(void) { return SAV_ABI_VERSION; }
 const char* sav_last_error(void) { return sav::g_err; }
 int64_t sav_launch_count(void) { return sav::g_launches.load(); }

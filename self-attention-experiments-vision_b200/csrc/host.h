@@ -24,6 +24,9 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, int64_t cols, int64_t rows,
                  int64_t ld, uint32_t box_cols, uint32_t box_rows);
 
+// development timeline buffer (NULL unless sav_set_debug_buffer was called)
+void* sav_debug_buffer();
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 }  // namespace sav
