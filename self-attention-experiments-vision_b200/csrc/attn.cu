@@ -296,8 +296,10 @@ extern "C" int sav_attn_bwd(const sav_attn_bwd_args* a, void* stream) {
   if (!a || a->D != AD) return set_error(SAV_ERR_SHAPE, "sav_attn_bwd: head dim must be 64");
   if (a->B <= 0 || a->H <= 0 || a->Nq <= 0 || a->Nk <= 0)
     return set_error(SAV_ERR_SHAPE, "sav_attn_bwd: empty shape");
-  if (!a->delta || !a->dq_accum) return set_error(SAV_ERR_ARG, "sav_attn_bwd: workspaces required");
+  if (!a->delta) return set_error(SAV_ERR_ARG, "sav_attn_bwd: delta workspace required");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (a->Nq <= 256) return launch_attn_bwd2(a, st);  // whole (b,h) per CTA, dQ accumulated in TMEM
+  if (!a->dq_accum) return set_error(SAV_ERR_ARG, "sav_attn_bwd: dq_accum workspace required for Nq > 256");
   CUtensorMap tq, tk, tv, tdo;
   int rc;
   if ((rc = make_qkv_map(&tq, a->q, a->H, a->Nq, a->B, a->q_batch_stride, a->q_row_stride))) return rc;

@@ -27,6 +27,9 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, int64_t col
 // development timeline buffer (NULL unless sav_set_debug_buffer was called)
 void* sav_debug_buffer();
 
+// attention backward, Nq <= 256 path (attn_bwd.cu)
+int launch_attn_bwd2(const sav_attn_bwd_args* a, cudaStream_t st);
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 }  // namespace sav

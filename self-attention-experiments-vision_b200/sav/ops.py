@@ -188,13 +188,13 @@ def attn_bwd(q, k, v, o2, d_o, lse, dq, dk, dv, scale=None):
     assert d_o.stride() == o.stride()
     assert dq.stride() == q.stride() and dk.stride() == k.stride() and dv.stride() == v.stride()
     delta = torch.empty((B, H, Nq), dtype=F32, device=q.device)
-    dq_acc = torch.empty((B, Nq, H, D), dtype=F32, device=q.device)
+    dq_acc = torch.empty((B, Nq, H, D), dtype=F32, device=q.device) if Nq > 256 else None
     a = AttnBwdArgs()
     a.q, a.k, a.v, a.o, a.d_o, a.lse = (q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(),
                                         d_o.data_ptr(), lse.data_ptr())
     a.o_lo = o2[1].data_ptr() if o2.shape[0] > 1 else None
     a.dq, a.dk, a.dv = dq.data_ptr(), dk.data_ptr(), dv.data_ptr()
-    a.delta, a.dq_accum = delta.data_ptr(), dq_acc.data_ptr()
+    a.delta, a.dq_accum = delta.data_ptr(), (dq_acc.data_ptr() if dq_acc is not None else None)
     a.B, a.H, a.Nq, a.Nk, a.D = B, H, Nq, Nk, D
     a.q_batch_stride, a.q_row_stride = _bnhd_strides(q)
     a.k_batch_stride, a.k_row_stride = _bnhd_strides(k)
