@@ -12,7 +12,8 @@
 //   warp 1      MMA issuer: S^T = K_j Q_i^T and dP^T = V_j dO_i^T (the transposed problem: TMEM lane =
 //               key row, so P^T / dS^T rows come out K-major for dV += P^T dO_i, dK += dS^T Q_i, and
 //               the same dS^T buffer read MN-major is the A operand of dQ_i += dS K_j)
-//   warp 2      TMEM allocator
+//   warp 2      second MMA issuer (dV, dK); warp 1 issues S^T, dP^T and dQ
+//   warp 3      TMEM allocator
 //   warps 4-11  compute: thread = (key row, half of the tile's query columns):
 //               p = exp2(s*c - lse), ds = p (dp - delta) with packed f32x2 math, bf16 P^T / dS^T into
 //               swizzled shared memory; the S^T/dP^T MMAs of the next (j, i) pair are issued as soon
@@ -40,6 +41,15 @@ struct AttnBwd2Params {
   float scale, scale_log2;
   long long* dbg;
 };
+
+#define SAV_RECB(role, ev)                                                        \
+  do {                                                                            \
+    if (p.dbg && blockIdx.x == 0 && dbg_n < 255) {                                \
+      p.dbg[(role) * 512 + 2 * dbg_n] = (ev);                                     \
+      p.dbg[(role) * 512 + 2 * dbg_n + 1] = clock64();                            \
+      ++dbg_n;                                                                    \
+    }                                                                             \
+  } while (0)
 
 // byte offset of 16-byte group `g16` (0..7) of row `r` inside a [rows x 128 B] SW128 tile
 __device__ __forceinline__ uint32_t bsw128(int r, int g16) {
@@ -89,16 +99,16 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     tma_prefetch_desc(&tq); tma_prefetch_desc(&tk); tma_prefetch_desc(&tv); tma_prefetch_desc(&tdo);
     tma_prefetch_desc(&tdq); tma_prefetch_desc(&tdk); tma_prefetch_desc(&tdv);
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&qdo_full[i], 1); mbar_init(&qdo_empty[i], 1);
+      mbar_init(&qdo_full[i], 1); mbar_init(&qdo_empty[i], 2);
       mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1);
     }
     mbar_init(st_full, 1); mbar_init(st_free, 256);
-    mbar_init(pds_full, 256); mbar_init(pds_free, 1);
+    mbar_init(pds_full, 256); mbar_init(pds_free, 2);
     mbar_init(dkv_full, 1); mbar_init(dkv_free, 256);
     mbar_init(dq_full, 1); mbar_init(dq_free, 256);
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  if (warp == 3) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -147,8 +157,11 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       const uint64_t ddSm0 = make_smem_desc(smem_u32(sdSt), BT_BYTES, 1024);  // MN-major A of dQ
       constexpr uint32_t id_kmn = make_idesc_bf16(BT, BD, false, true);
       constexpr uint32_t id_mnmn = make_idesc_bf16(BT, BD, true, true);
-      constexpr uint64_t TILE16 = BT_BYTES >> 4;  // descriptor address units (16 B)
+      constexpr uint32_t TILE16 = BT_BYTES >> 4;  // descriptor address units (16 B)
+      int dbg_n = 0;
 
+      auto lo = [](uint64_t d) { return (uint32_t)d; };
+      auto hi = [](uint64_t d) { return (uint32_t)(d >> 32); };
       // kv tile bookkeeping is derived from the linear pair index q of this CTA
       auto issue_sdp = [&](int q) {
         const int itl = q / ppi, rem = q - itl * ppi;
@@ -157,46 +170,47 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         const int st = gk & 1;
         if (i == 0) mbar_wait_sleep(&kv_full[st], (gk >> 1) & 1);
         if (j == 0) mbar_wait_sleep(&qdo_full[i], itl & 1);
+        SAV_RECB(1, 40);
         if (q > 0) mbar_wait_sleep(st_free, (q - 1) & 1);
+        SAV_RECB(1, 41);
         tc_fence_after();
         const int nq_cur = (min(BT, p.Nq - i * BT) + 15) & ~15;
         const uint32_t id_s = make_idesc_bf16(BT, nq_cur, false, false);
-        const uint64_t a_k = dK0 + (uint64_t)st * 2 * TILE16, a_v = dV0 + (uint64_t)st * 2 * TILE16;
-        const uint64_t b_q = dQ0 + (uint64_t)i * TILE16, b_do = ddO0 + (uint64_t)i * TILE16;
+        const uint32_t a_k = lo(dK0) + st * 2 * TILE16, a_v = lo(dV0) + st * 2 * TILE16;
+        const uint32_t b_q = lo(dQ0) + i * TILE16, b_do = lo(ddO0) + i * TILE16;
 #pragma unroll
-        for (int k = 0; k < BD / 16; ++k) umma_f16(tSt, a_k + k * 2, b_q + k * 2, id_s, k > 0);
+        for (int k = 0; k < BD / 16; ++k)
+          umma_f16_lh(tSt, a_k + k * 2, hi(dK0), b_q + k * 2, hi(dQ0), id_s, k > 0);
 #pragma unroll
-        for (int k = 0; k < BD / 16; ++k) umma_f16(tdPt, a_v + k * 2, b_do + k * 2, id_s, k > 0);
+        for (int k = 0; k < BD / 16; ++k)
+          umma_f16_lh(tdPt, a_v + k * 2, hi(dV0), b_do + k * 2, hi(ddO0), id_s, k > 0);
         umma_commit(st_full);
+        SAV_RECB(1, 42);
       };
       auto issue_grads = [&](int q) {
         const int itl = q / ppi, rem = q - itl * ppi;
         const int j = rem / p.nqt, i = rem - j * p.nqt;
         const uint32_t gk = (uint32_t)(itl * p.nkt + j);
         const int st = gk & 1;
+        SAV_RECB(1, 43);
         mbar_wait_sleep(pds_full, q & 1);
-        if (i == 0 && gk > 0) mbar_wait_sleep(dkv_free, (gk - 1) & 1);
+        SAV_RECB(1, 44);
         if (j == 0 && i == 0 && itl > 0) mbar_wait_sleep(dq_free, (itl - 1) & 1);
         tc_fence_after();
-        const int nq_steps = ((min(BT, p.Nq - i * BT) + 15) & ~15) >> 4;
         const int nk_steps = ((min(BT, p.Nk - j * BT) + 15) & ~15) >> 4;
-        const uint64_t b_do = ddOm0 + (uint64_t)i * TILE16, b_q = dQm0 + (uint64_t)i * TILE16;
-        const uint64_t b_k = dKm0 + (uint64_t)st * 2 * TILE16;
-        // dV[keys,d] += P^T[keys,q] dO_i[q,d];  dK[keys,d] += dS^T[keys,q] Q_i[q,d]   (K = queries)
-        for (int ks = 0; ks < nq_steps; ++ks)
-          umma_f16(tdV, dPt0 + (uint64_t)((ks >> 2) * TILE16 + (ks & 3) * 2), b_do + (uint64_t)ks * 128,
-                   id_kmn, (i > 0 || ks > 0));
-        for (int ks = 0; ks < nq_steps; ++ks)
-          umma_f16(tdK, ddSt0 + (uint64_t)((ks >> 2) * TILE16 + (ks & 3) * 2), b_q + (uint64_t)ks * 128,
-                   id_kmn, (i > 0 || ks > 0));
+        const uint32_t b_k = lo(dKm0) + st * 2 * TILE16;
+        const uint32_t acc_j = j > 0;
         // dQ_i[q,d] += dS[q,keys] K_j[keys,d]   (K = keys; A = the dS^T buffer read MN-major)
-        for (int ks = 0; ks < nk_steps; ++ks)
-          umma_f16(tdQ + i * BD, ddSm0 + (uint64_t)ks * 128, b_k + (uint64_t)ks * 128, id_mnmn,
-                   (j > 0 || ks > 0));
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < nk_steps)
+            umma_f16_lh(tdQ + i * BD, lo(ddSm0) + ks * 128, hi(ddSm0), b_k + ks * 128, hi(dKm0),
+                        id_mnmn, ks > 0 ? 1u : acc_j);
         umma_commit(pds_free);
-        if (i == p.nqt - 1) { umma_commit(dkv_full); umma_commit(&kv_empty[st]); }
+        if (i == p.nqt - 1) umma_commit(&kv_empty[st]);
         if (j == p.nkt - 1) umma_commit(&qdo_empty[i]);
         if (rem == ppi - 1) umma_commit(dq_full);
+        SAV_RECB(1, 45);
       };
       if (total_pairs > 0) issue_sdp(0);
       for (int q = 0; q < total_pairs; ++q) {
@@ -207,6 +221,46 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         if (early) issue_sdp(q + 1);
         issue_grads(q);
         if (more && !early) issue_sdp(q + 1);
+      }
+    }
+  }
+  else if (warp == 2) {
+    // ------------------------------------------------------------------ second MMA issuer: dV, dK
+    // (tcgen05.mma dispatch from one thread is latency-bound at ~90 cycles per instruction for
+    //  these N = 64 shapes, so the gradient MMAs are split over two issuing warps)
+    if (lane == 0) {
+      const uint64_t dQm0 = make_smem_desc(smem_u32(sQ), BT_BYTES, 1024);     // MN-major B of dK
+      const uint64_t ddOm0 = make_smem_desc(smem_u32(sdO), BT_BYTES, 1024);   // MN-major B of dV
+      const uint64_t dPt0 = make_smem_desc(smem_u32(sPt), 16, 1024);          // K-major A of dV
+      const uint64_t ddSt0 = make_smem_desc(smem_u32(sdSt), 16, 1024);        // K-major A of dK
+      constexpr uint32_t id_kmn = make_idesc_bf16(BT, BD, false, true);
+      constexpr uint32_t TILE16 = BT_BYTES >> 4;
+      auto lo = [](uint64_t d) { return (uint32_t)d; };
+      auto hi = [](uint64_t d) { return (uint32_t)(d >> 32); };
+      for (int q = 0; q < total_pairs; ++q) {
+        const int itl = q / ppi, rem = q - itl * ppi;
+        const int j = rem / p.nqt, i = rem - j * p.nqt;
+        const uint32_t gk = (uint32_t)(itl * p.nkt + j);
+        mbar_wait_sleep(pds_full, q & 1);
+        if (i == 0 && gk > 0) mbar_wait_sleep(dkv_free, (gk - 1) & 1);
+        tc_fence_after();
+        const int nq_steps = ((min(BT, p.Nq - i * BT) + 15) & ~15) >> 4;
+        const uint32_t b_do = lo(ddOm0) + i * TILE16, b_q = lo(dQm0) + i * TILE16;
+        const uint32_t acc_i = i > 0;
+        // dV[keys,d] += P^T[keys,q] dO_i[q,d];  dK[keys,d] += dS^T[keys,q] Q_i[q,d]   (K = queries)
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < nq_steps)
+            umma_f16_lh(tdV, lo(dPt0) + (ks >> 2) * TILE16 + (ks & 3) * 2, hi(dPt0), b_do + ks * 128,
+                        hi(ddOm0), id_kmn, ks > 0 ? 1u : acc_i);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < nq_steps)
+            umma_f16_lh(tdK, lo(ddSt0) + (ks >> 2) * TILE16 + (ks & 3) * 2, hi(ddSt0), b_q + ks * 128,
+                        hi(dQm0), id_kmn, ks > 0 ? 1u : acc_i);
+        umma_commit(pds_free);
+        if (i == p.nqt - 1) umma_commit(dkv_full);
+        if (j == p.nkt - 1) umma_commit(&qdo_empty[i]);
       }
     }
   }
@@ -221,6 +275,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     const uint64_t sc2 = f2_pack(p.scale_log2, p.scale_log2);
     uint32_t gk = 0;
     int q = 0;
+    int dbg_n = (lane == 0 && sub == 0) ? 0 : 1000;
     for (int itl = 0; itl < my_items; ++itl) {
       const int item = blockIdx.x + itl * gridDim.x;
       const int h = item % p.H, b = item / p.H;
@@ -236,7 +291,9 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         for (int i = 0; i < p.nqt; ++i, ++q) {
           const int nq_cur = (min(BT, p.Nq - i * BT) + 15) & ~15;
           const int ncols = max(0, min(64, nq_cur - hf * 64));  // my share of the query columns
+          SAV_RECB(3 + hf, 50);
           mbar_wait(st_full, q & 1);
+          SAV_RECB(3 + hf, 51);
           tc_fence_after();
           uint32_t pk_p[32], pk_ds[32];
 #pragma unroll
@@ -268,8 +325,10 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
             }
           }
           tc_fence_before();
+          SAV_RECB(3 + hf, 52);
           mbar_arrive(st_free);  // S^T / dP^T of the next pair may overwrite TMEM
           if (q > 0) mbar_wait(pds_free, (q - 1) & 1);  // previous pair's MMAs are done with smem
+          SAV_RECB(3 + hf, 53);
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
             if (half * 32 < ncols) {
@@ -285,10 +344,12 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
             }
           }
           fence_proxy_async_smem();
+          SAV_RECB(3 + hf, 54);
           mbar_arrive(pds_full);
         }
         // ---- key tile j finished: dV_j (warps 4-7) and dK_j (warps 8-11) out of TMEM
         mbar_wait(dkv_full, gk & 1);
+        SAV_RECB(3 + hf, 55);
         tc_fence_after();
         {
           uint32_t r0[32], r1[32];
@@ -323,9 +384,11 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           tma_store_wait_read<0>();
         }
         named_barrier_sync(1, 256);  // the staging buffers may be overwritten again
+        SAV_RECB(3 + hf, 56);
       }
       // ---- item finished: dQ_0 (warps 4-7) and dQ_1 (warps 8-11) out of TMEM
       mbar_wait(dq_full, itl & 1);
+      SAV_RECB(3 + hf, 57);
       tc_fence_after();
       if (hf < p.nqt) {
         uint32_t r0[32], r1[32];
@@ -365,7 +428,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (warp == 3) {
     tc_fence_after();
     tmem_dealloc<512>(tmem);
   }

@@ -278,7 +278,8 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           const uint32_t id_s = make_idesc_bf16(FQ, n_cur, false, false);
 #pragma unroll
           for (int k = 0; k < FD / 16; ++k)  // +32 B per 16-element K step
-            umma_f16(region, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), id_s, k > 0);
+            umma_f16_lh(region, (uint32_t)dq + k * 2, (uint32_t)(dq >> 32), (uint32_t)dk + k * 2,
+                        (uint32_t)(dk >> 32), id_s, k > 0);
           umma_commit(&s_full[w]);
           if (j == p.nkb - 1) umma_commit(&q_empty[qb]);
           SAV_REC(1 + w, 13);
@@ -286,8 +287,11 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           SAV_REC(1 + w, 14);
           tc_fence_after();
           const int ksteps = n_cur >> 4;
-          for (int ks = 0; ks < ksteps; ++ks)  // +8 TMEM columns of P, +2048 B of V per 16 keys
-            umma_f16_ts(region + 128, region + ks * 8, dv + (uint64_t)(ks * 128), id_pv, ks > 0);
+#pragma unroll
+          for (int ks = 0; ks < FK / 16; ++ks)  // +8 TMEM columns of P, +2048 B of V per 16 keys
+            if (ks < ksteps)
+              umma_f16_ts_lh(region + 128, region + ks * 8, (uint32_t)dv + ks * 128, (uint32_t)(dv >> 32),
+                             id_pv, ks > 0);
           umma_commit(&o_full[w]);
           umma_commit(&kv_empty[st]);
           SAV_REC(1 + w, 15);

@@ -124,8 +124,16 @@ ln_bwd_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __restrict_
   }
   for (int64_t row = warp_global; row < rows; row += warps_total) {
     const float mean = mean_in[row], rstd = rstd_in[row];
-    float xh[CHUNKS][8], gy[CHUNKS][8];
+    float xh[CHUNKS][8], gy[CHUNKS][8], add[CHUNKS][8];
     float s1 = 0.f, s2 = 0.f;
+    // all global loads of the row are issued before the first reduction (one latency per row)
+    if (dx_add) {
+#pragma unroll
+      for (int i = 0; i < CHUNKS; ++i) {
+        const int ch = lane + i * 32;
+        if (ch < nchunk) load8(dx_add + row * ldx + ch * 8, add[i]);
+      }
+    }
 #pragma unroll
     for (int i = 0; i < CHUNKS; ++i) {
       const int ch = lane + i * 32;
@@ -154,10 +162,8 @@ ln_bwd_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __restrict_
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = rstd * (gy[i][j] - s1 - xh[i][j] * s2);
         if (dx_add) {
-          float a[8];
-          load8(dx_add + row * ldx + ch * 8, a);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) o[j] += a[j];
+          for (int j = 0; j < 8; ++j) o[j] += add[i][j];
         }
         store8(dx + row * ldx + ch * 8, o);
         if (dx16) store8(dx16 + row * ldx + ch * 8, o);

@@ -15,8 +15,10 @@ from sav import _abi, ops  # noqa: E402
 
 EV = {1: "P kv_empty wait", 2: "P kv_empty ok", 10: "M kv_full wait", 11: "M kv_full ok", 12: "M s_free ok",
       13: "M S issued", 14: "M p_full ok", 15: "M PV issued", 20: "S s_full wait", 21: "S s_full ok",
-      22: "S pass1 done", 30: "E o_full g0", 31: "E o_full g1", 32: "E stored", 23: "S pass2 done", 24: "S o_full ok", 25: "S O read", 26: "S stored"}
+      22: "S pass1 done", 40: "M sdp wait st_free", 41: "M st_free ok", 42: "M sdp issued", 43: "M grads wait pds", 44: "M pds_full ok", 45: "M grads issued", 50: "C wait st_full", 51: "C st_full ok", 52: "C math done", 53: "C pds_free ok", 54: "C smem written", 55: "C dkv_full ok", 56: "C dkv stored", 57: "C dq_full ok", 30: "E o_full g0", 31: "E o_full g1", 32: "E stored", 23: "S pass2 done", 24: "S o_full ok", 25: "S O read", 26: "S stored"}
 ROLES = ["producer", "mma0", "mma1", "softmax0", "softmax1", "epilogue"]
+if "--bwd" in sys.argv:
+    ROLES[1], ROLES[3], ROLES[4] = "mma", "comp_h0", "comp_h1"
 
 
 def main():
