@@ -85,6 +85,28 @@ typedef struct {
 int64_t sav_gemm_workspace_bytes(const sav_gemm_args* a);
 int sav_gemm(const sav_gemm_args* a, void* stream);
 
+/* ---------------------------------------------------------------- batched GEMM (same kernel)
+ * D[o,i][M,N] = sum_k A[o,i][m,k] * B[o,i][n,k] for every (outer o, inner i) batch; operand
+ * element (o, i, row, col) at ptr + o*stride_outer + i*stride_inner + row*ld + col (elements; all
+ * byte strides multiples of 16).  a_mn / b_mn as in sav_gemm.  D bf16 or fp32, no epilogue.
+ * Out-of-range rows / columns / K of a batch are zero-filled on load and clipped on store, so one
+ * batch never reads or writes its neighbour (M, N, K need not be tile multiples).
+ * Replaces the einsums of the materialised-logits attention path: attention.py:41-42,57-58 when
+ * talking heads (attention.py:44-52) sit between them, cait.py:10-15 (class attention, Nq = 1),
+ * botnet.py:187-197 (+ relative logits) and any head dim the fused kernel does not cover. */
+typedef struct {
+  const void* A;
+  const void* B;
+  void* D;
+  int64_t M, N, K;
+  int64_t batch_outer, batch_inner;
+  int64_t lda, a_stride_inner, a_stride_outer;
+  int64_t ldb, b_stride_inner, b_stride_outer;
+  int64_t ldd, d_stride_inner, d_stride_outer;
+  int32_t a_mn, b_mn, d_fp32, reserved;
+} sav_bgemm_args;
+int sav_bgemm(const sav_bgemm_args* a, void* stream);
+
 /* column sums: out[n] (+)= sum_m X[m,n]   (bias gradients; ff.py:24,27 reverse-mode) */
 int sav_colsum_bf16(const void* X, int64_t M, int64_t N, int64_t ldx, float* out,
                     int32_t accumulate, void* stream);
@@ -168,6 +190,38 @@ typedef struct {
 } sav_attn_bwd_args;
 int sav_attn_bwd(const sav_attn_bwd_args* a, void* stream);
 
+/* ---------------------------------------------------------------- materialised-logits attention rows
+ * Between S = q k^T and O = P v (both sav_bgemm) for the attention variants that couple heads or
+ * add position logits.  S fp32 [B,H,Nq,ld] holds the RAW q.k products (ld >= Nk, ld % 8 == 0);
+ *   logits[b,i,q,k] = scale * ( sum_h mix_pre[h,i] * S[b,h,q,k]      (talking_heads.py:13, pre)
+ *                               + rel[b,q,i, kx-qx+W-1] + rel[b,q,i, (2W-1)+ky-qy+Hh-1] )
+ *                                                       (botnet.py:78-141; q = qy*W+qx, k = ky*W+kx)
+ *   p = softmax_k(logits)                                             (attention.py:48)
+ *   P[b,j,q,k] = sum_i mix_post[i,j] * p[b,i,q,k]   -> bf16 [B,H,Nq,ld], columns >= Nk zeroed
+ * mix_pre/mix_post [H,H] fp32 (both or neither; NULL = identity; H in {2,3,4,6,8} when given);
+ * rel fp32 [B,Nq,H,ldr] = unscaled q.r^W (first 2W-1 columns) | q.r^H (next 2Hh-1), or NULL.
+ * Backward takes dP = dO v^T (fp32, same layout), recomputes p from S, and writes dS (bf16, the
+ * gradient of the raw q.k products, scale folded in), drel (fp32 [B,Nq,H,ldr], overwritten) and
+ * ACCUMULATES dmix_pre / dmix_post [H,H]. */
+typedef struct {
+  const float* S;
+  void* P;             /* fwd out */
+  const float* dP;     /* bwd in */
+  void* dS;            /* bwd out */
+  const float* mix_pre;
+  const float* mix_post;
+  float* dmix_pre;     /* bwd, accumulated */
+  float* dmix_post;
+  const float* rel;
+  float* drel;         /* bwd out */
+  int64_t B, H, Nq, Nk, ld, ldr;
+  int32_t rel_w, rel_h;
+  float scale;
+  int32_t reserved;
+} sav_thsoftmax_args;
+int sav_thsoftmax_fwd(const sav_thsoftmax_args* a, void* stream);
+int sav_thsoftmax_bwd(const sav_thsoftmax_args* a, void* stream);
+
 /* ---------------------------------------------------------------- loss head (train.py:83-91)
  * one_hot -> smooth_labels(alpha) -> softmax_cross_entropy -> mean; writes dlogits = dloss/dlogits
  * (bf16 [B,classes]) and accumulates loss into loss_out[0] (zeroed by the callee), top1 count into
@@ -196,6 +250,22 @@ int sav_fill_f32(float* p, float v, int64_t n, void* stream);
 /* strided row copy dst[r, 0:cols] = src[r, 0:cols] (class-token gather/scatter, vit.py:95) */
 int sav_copy2d_bf16(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t rows,
                     int64_t cols, void* stream);
+
+/* reverse mode of the LayerScale / drop-path GEMM epilogue (layerscale.py:20-23,
+ * stochastic_depth.py:16-27): out[m,n] = bf16(g[m,n] * col_scale[n] * row_scale[m/rows_per_scale])
+ * from the fp32 stream gradient g; either scale may be NULL. */
+int sav_scale_rows_cols(const float* g, int64_t ldg, const float* col_scale, const float* row_scale,
+                        int64_t rows_per_scale, void* out, int64_t ldo, int64_t rows, int64_t cols,
+                        void* stream);
+/* LayerScale gradient from the finished weight / bias gradients of the scaled Dense (no saved
+ * activation): dcol_scale[n] += (sum_k W[k,n] dW[k,n] + bias[n] dbias[n]) / col_scale[n]. */
+int sav_layerscale_grad(const float* W, int64_t ldw, const float* dW, int64_t ldg, int64_t K,
+                        int64_t N, const float* bias, const float* dbias, const float* col_scale,
+                        float* dcol_scale, void* stream);
+/* strided fp32 row copy / accumulate: dst[r, 0:cols] (+)= src[r, 0:cols] (class-token concat of
+ * cait.py:97,175 and its reverse mode; fan-in of fp32 stream gradients) */
+int sav_copy2d_f32(const float* src, int64_t lds, float* dst, int64_t ldd, int64_t rows,
+                   int64_t cols, int32_t accumulate, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,256 @@
+"""ORACLE (test infrastructure, NOT product code) -- fp32 CPU restatement of the CaiT path
+(models/cait.py) and of the BoTNet MHSA with 2-D relative position logits (models/botnet.py:70-199).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline legs may import this module.
+
+PARITY UNPINNED for the same reason as oracle/vit_oracle.py: the reference ships no golden values
+(cait_test.py / botnet_test.py assert logits shape only) and jax / flax are not installable here.
+Validated by float64 finite differences (tests/test_variants_oracle_cpu.py), by the index identity
+abs[i, j] = rel[i, j - i + l - 1] of `_to_absolute_logits` (botnet.py:78-93, restated literally
+below as pad / reshape / slice and compared with the direct gather), and by the zero-head KAT.
+
+BoTNet is broken as written; `bot_mhsa` follows the intended math: softmax over all
+H*W keys, O = P V with V indexed by key, relative terms computed from the scaled query.
+"""
+import math
+
+import torch
+
+from oracle.vit_oracle import (attention, ff_block, layer_norm, loss_fn, hwcn_to_nhwc, patch_embed,
+                               softmax_last, tree_map)
+
+
+# ----------------------------------------------------------------------------- CaiT
+def drop_path(x, factor):
+    """StochasticDepthBlock (stochastic_depth.py:16-27) with the per-sample factor
+    floor(keep + U) / keep supplied explicitly; None = eval / rate 0."""
+    if factor is None:
+        return x
+    return x * factor.view(-1, *([1] * (x.dim() - 1)))
+
+
+def cait_encoder_block(x, p, num_heads, factors=(None, None)):
+    """cait.py EncoderBlock.__call__ (cait.py:29-53)."""
+    sa = p["SelfAttentionBlock_0"]
+    talking = (sa["TalkingHeadsBlock_0"]["talking_heads_transform"],
+               sa["TalkingHeadsBlock_1"]["talking_heads_transform"])
+    y = layer_norm(x, p["LayerNorm_0"]["scale"], p["LayerNorm_0"]["bias"])        # cait.py:30
+    y = attention(y, y, sa, num_heads, talking=talking)                            # cait.py:31-35
+    y = y * p["LayerScaleBlock_0"]["layerscale"]                                   # cait.py:36
+    x = drop_path(y, factors[0]) + x                                               # cait.py:38-40
+    y = layer_norm(x, p["LayerNorm_1"]["scale"], p["LayerNorm_1"]["bias"])        # cait.py:42
+    y = ff_block(y, p["FFBlock_0"])                                                # cait.py:43-46
+    y = y * p["LayerScaleBlock_1"]["layerscale"]                                   # cait.py:47
+    return x + drop_path(y, factors[1])                                            # cait.py:49-52
+
+
+def cait_ca_block(x, cls_token, p, num_heads, factors=(None, None)):
+    """CAEncoderBlock.__call__ (cait.py:96-122); ClassSelfAttentionBlock = q from row 0 only
+    (cait.py:10-15)."""
+    z = torch.cat([cls_token, x], dim=1)                                           # cait.py:97
+    z = layer_norm(z, p["LayerNorm_0"]["scale"], p["LayerNorm_0"]["bias"])        # cait.py:98
+    a = attention(z[:, 0:1, :], z, p["ClassSelfAttentionBlock_0"], num_heads)     # cait.py:99-103
+    a = a * p["LayerScaleBlock_0"]["layerscale"]                                   # cait.py:105
+    cls_token = cls_token + drop_path(a, factors[0])                               # cait.py:107-109
+    y = layer_norm(cls_token, p["LayerNorm_1"]["scale"], p["LayerNorm_1"]["bias"])
+    y = ff_block(y, p["FFBlock_0"])
+    y = y * p["LayerScaleBlock_1"]["layerscale"]                                   # cait.py:116
+    return cls_token + drop_path(y, factors[1])                                    # cait.py:121
+
+
+def cait_forward(params, images_nhwc, cfg, factors=None):
+    """CaiT.__call__ (cait.py:141-183) + Encoder.__call__ (cait.py:68-83).  factors: optional
+    list of per-sample drop-path factor tensors [B], two per block in execution order."""
+    ph, pw = cfg["patch_shape"]
+    it = iter(factors) if factors is not None else None
+    nxt = (lambda: (next(it), next(it))) if it is not None else (lambda: (None, None))
+    x = patch_embed(images_nhwc, params["PatchEmbedBlock_0"]["Dense_0"]["kernel"], ph, pw)  # :143
+    enc = params["Encoder_0"]
+    x = x + enc["AddAbsPosEmbed_0"]["pos_embed"]                                   # cait.py:69
+    for i in range(cfg["num_layers"]):                                             # cait.py:72-80
+        x = cait_encoder_block(x, enc[f"EncoderBlock_{i}"], cfg["num_heads"], nxt())
+    cls_token = params["cls"].expand(x.shape[0], -1, -1)                           # cait.py:157-160
+    for i in range(cfg["num_layers_token_only"]):                                  # cait.py:162-173
+        cls_token = cait_ca_block(x, cls_token, params[f"CAEncoderBlock_{i}"], cfg["num_heads"],
+                                  nxt())
+    z = torch.cat([cls_token, x], dim=1)                                           # cait.py:175
+    z = layer_norm(z, params["LayerNorm_0"]["scale"], params["LayerNorm_0"]["bias"])
+    return z[:, 0] @ params["Dense_0"]["kernel"] + params["Dense_0"]["bias"]       # cait.py:178-182
+
+
+def cait_config(name):
+    cfgs = {
+        "cait_xxs_24": dict(num_layers=24, num_heads=4, embed_dim=192, layerscale_eps=1e-5),
+        "cait_xs_24": dict(num_layers=24, num_heads=6, embed_dim=288, layerscale_eps=1e-5),
+        "cait_s_24": dict(num_layers=24, num_heads=8, embed_dim=384, layerscale_eps=1e-6),
+    }
+    c = dict(cfgs[name])
+    c.update(num_layers_token_only=2, patch_shape=(16, 16), num_classes=1000, expand_ratio=4)
+    return c
+
+
+def _orthogonal(g, n, dtype):
+    a = torch.randn((n, n), generator=g, dtype=torch.float64)
+    q, r = torch.linalg.qr(a)
+    return (q * torch.sign(torch.diagonal(r))).to(dtype)
+
+
+def synthetic_cait_params(cfg, img_size=224, seed=42, layerscale=None, dtype=torch.float32):
+    """SURVEY 8d synthetic (non-default) init with the Flax auto-names of cait.py; talking-heads
+    transforms are random orthogonal plus N(0, 0.1) so they are not exactly orthogonal; layerscale
+    = cfg eps unless given (the parity tests also use 0.1, SURVEY 7 'Tolerance')."""
+    g = torch.Generator().manual_seed(seed)
+    C, H = cfg["embed_dim"], cfg["num_heads"]
+    d = C // H
+    ph, pw = cfg["patch_shape"]
+    n_tok = (img_size // ph) * (img_size // pw)
+    hid = int(cfg["expand_ratio"] * C)
+    ls = cfg["layerscale_eps"] if layerscale is None else layerscale
+
+    def normal(shape, std):
+        return (torch.randn(shape, generator=g, dtype=torch.float64) * std).to(dtype)
+
+    def kern(shape, fan_in):
+        return normal(shape, 1.0 / math.sqrt(fan_in))
+
+    def ln():
+        return {"scale": 1.0 + normal((C,), 0.02), "bias": normal((C,), 0.02)}
+
+    def attn(talking):
+        p = {"queries": {"kernel": kern((C, H, d), C)}, "keys": {"kernel": kern((C, H, d), C)},
+             "values": {"kernel": kern((C, H, d), C)},
+             "DenseGeneral_0": {"kernel": kern((H, d, C), C)}}
+        if talking:
+            for j in range(2):
+                p[f"TalkingHeadsBlock_{j}"] = {
+                    "talking_heads_transform": _orthogonal(g, H, dtype) + normal((H, H), 0.1)}
+        return p
+
+    def lscale():
+        return {"layerscale": torch.full((C,), ls, dtype=dtype) * (1.0 + normal((C,), 0.1))}
+
+    def ffn():
+        return {"Dense_0": {"kernel": kern((C, hid), C), "bias": normal((hid,), 0.02)},
+                "Dense_1": {"kernel": kern((hid, C), hid), "bias": normal((C,), 0.02)}}
+
+    enc = {"AddAbsPosEmbed_0": {"pos_embed": normal((1, n_tok, C), 0.02)}}
+    for i in range(cfg["num_layers"]):
+        enc[f"EncoderBlock_{i}"] = {"LayerNorm_0": ln(), "SelfAttentionBlock_0": attn(True),
+                                    "LayerScaleBlock_0": lscale(), "LayerNorm_1": ln(),
+                                    "FFBlock_0": ffn(), "LayerScaleBlock_1": lscale()}
+    params = {
+        "PatchEmbedBlock_0": {"Dense_0": {"kernel": kern((ph * pw * 3, C), ph * pw * 3)}},
+        "Encoder_0": enc,
+        "cls": normal((1, 1, C), 0.02),
+    }
+    for i in range(cfg["num_layers_token_only"]):
+        params[f"CAEncoderBlock_{i}"] = {"LayerNorm_0": ln(), "ClassSelfAttentionBlock_0": attn(False),
+                                         "LayerScaleBlock_0": lscale(), "LayerNorm_1": ln(),
+                                         "FFBlock_0": ffn(), "LayerScaleBlock_1": lscale()}
+    params["LayerNorm_0"] = ln()
+    nc = cfg["num_classes"]
+    params["Dense_0"] = {"kernel": normal((C, nc), 0.02), "bias": normal((nc,), 0.02)}
+    return params
+
+
+def cait_loss_and_grads(params, images_hwcn, labels, cfg, label_smoothing=0.0, factors=None):
+    """train.py:79-95 applied to CaiT."""
+    def req(t):
+        return t.detach().clone().requires_grad_(True)
+    p = tree_map(req, params)
+    logits = cait_forward(p, hwcn_to_nhwc(images_hwcn), cfg, factors)
+    loss = loss_fn(logits, labels, cfg["num_classes"], label_smoothing)
+    loss.backward()
+    grads = tree_map(lambda t: t.grad if t.grad is not None else torch.zeros_like(t), p)
+    return loss.detach(), logits.detach(), grads
+
+
+# ----------------------------------------------------------------------------- BoTNet MHSA
+def to_absolute_logits(rel):
+    """RelativeLogits._to_absolute_logits (botnet.py:78-93), restated literally: rel
+    [b, h, l, 2l-1] -> abs [b, h, l, l] by zero-pad one column, flatten, pad l-1, reshape to
+    [l+1, 2l-1], keep [:l, l-1:]."""
+    b, h, l, _ = rel.shape
+    x = torch.cat([rel, rel.new_zeros(b, h, l, 1)], dim=3)                         # botnet.py:81-82
+    x = x.reshape(b, h, l * 2 * l)                                                 # botnet.py:84
+    x = torch.cat([x, rel.new_zeros(b, h, l - 1)], dim=2)                          # botnet.py:85-86
+    x = x.reshape(b, h, l + 1, 2 * l - 1)                                          # botnet.py:88-89
+    return x[:, :, :l, l - 1:]                                                     # botnet.py:90-92
+
+
+def relative_logits_1d(q, rel_k):
+    """RelativeLogits._relative_logits_1d (botnet.py:96-111) for q [b, h, H, W, d] along W:
+    returns [b, h, H, W, W] with out[..., x, kx] = q[..., x, :] . rel_k[kx - x + W - 1]."""
+    b, h, H, W, d = q.shape
+    rel = torch.einsum("bhxyd,md->bhxym", q, rel_k)                                # botnet.py:105
+    rel = rel.reshape(b, h * H, W, 2 * W - 1)                                      # botnet.py:106
+    return to_absolute_logits(rel).reshape(b, h, H, W, W)                          # botnet.py:107-108
+
+
+def relative_logits_2d(q, rel_w, rel_h):
+    """RelativeLogits.__call__ (botnet.py:114-141): [b, h, H, W, H, W] (query y,x ; key y,x)."""
+    b, h, H, W, d = q.shape
+    lw = relative_logits_1d(q, rel_w)                                              # [b,h,H,W,Wk]
+    lh = relative_logits_1d(q.permute(0, 1, 3, 2, 4), rel_h)                       # [b,h,W,H,Hk]
+    lw = lw[:, :, :, :, None, :].expand(b, h, H, W, H, W)                          # tile over key rows
+    lh = lh.permute(0, 1, 3, 2, 4)[:, :, :, :, :, None].expand(b, h, H, W, H, W)   # over key cols
+    return lw + lh
+
+
+def bot_mhsa(x, p, num_heads, head_ch):
+    """BoTMHSA.__call__ intended semantics (botnet.py:158-199).  x [b, H, W, C];
+    p: {'query','key','value': {'kernel' [1, 1, C, h*d]} (1x1 nn.Conv, no bias, botnet.py:165-174),
+    'RelativeLogits_0': {'rel_pos_emb_w' [2W-1, d], 'rel_pos_emb_h' [2H-1, d]}} (botnet.py:124-132)."""
+    b, H, W, C = x.shape
+    h, d = num_heads, head_ch
+
+    def proj(name):
+        y = x.reshape(b, H * W, C) @ p[name]["kernel"].reshape(C, h * d)           # 1x1 conv
+        return y.reshape(b, H, W, h, d).permute(0, 3, 1, 2, 4)                     # b h H W d
+    q, k, v = proj("query"), proj("key"), proj("value")                            # botnet.py:175-183
+    q = q / math.sqrt(d)                                                           # botnet.py:185
+    logits = torch.einsum("bhxyd,bhpqd->bhxypq", q, k)                             # botnet.py:187-190
+    rl = p["RelativeLogits_0"]
+    logits = logits + relative_logits_2d(q, rl["rel_pos_emb_w"], rl["rel_pos_emb_h"])      # botnet.py:191-192
+    w = softmax_last(logits.reshape(b, h, H, W, H * W))                            # intended (D2)
+    o = torch.einsum("bhxyk,bhkd->bhxyd", w, v.reshape(b, h, H * W, d))            # O = P V
+    return o.permute(0, 2, 3, 1, 4).reshape(b, H, W, h * d)                        # botnet.py:198
+
+
+def bot_mhsa_direct(x, p, num_heads, head_ch):
+    """Same result by direct gather logits += q.r^W[kx-qx+W-1] + q.r^H[ky-qy+H-1] --
+    the form the kernel implements; used to pin the pad/reshape restatement above."""
+    b, H, W, C = x.shape
+    h, d = num_heads, head_ch
+    xf = x.reshape(b, H * W, C)
+    q = (xf @ p["query"]["kernel"].reshape(C, h * d)).reshape(b, H * W, h, d) / math.sqrt(d)
+    k = (xf @ p["key"]["kernel"].reshape(C, h * d)).reshape(b, H * W, h, d)
+    v = (xf @ p["value"]["kernel"].reshape(C, h * d)).reshape(b, H * W, h, d)
+    s = torch.einsum("bqhd,bkhd->bhqk", q, k)
+    rl = p["RelativeLogits_0"]
+    rw = torch.einsum("bqhd,md->bhqm", q, rl["rel_pos_emb_w"])
+    rh = torch.einsum("bqhd,md->bhqm", q, rl["rel_pos_emb_h"])
+    idx = torch.arange(H * W)
+    qy, qx = idx // W, idx % W
+    iw = (qx[None, :] - qx[:, None]) + W - 1          # [q, k] -> kx - qx + W - 1
+    ih = (qy[None, :] - qy[:, None]) + H - 1
+    s = s + torch.gather(rw, 3, iw.expand(b, h, -1, -1)) + torch.gather(rh, 3, ih.expand(b, h, -1, -1))
+    w = softmax_last(s)
+    o = torch.einsum("bhqk,bkhd->bqhd", w, v)
+    return o.reshape(b, H, W, h * d)
+
+
+def synthetic_bot_params(C, num_heads, head_ch, H, W, seed=42, dtype=torch.float32):
+    """1x1-conv kernels N(0, 1/C); relative tables N(0, d^-1/2) (botnet.py:124-132)."""
+    g = torch.Generator().manual_seed(seed)
+
+    def normal(shape, std):
+        return (torch.randn(shape, generator=g, dtype=torch.float64) * std).to(dtype)
+    hd = num_heads * head_ch
+    return {
+        "query": {"kernel": normal((1, 1, C, hd), 1.0 / math.sqrt(C))},
+        "key": {"kernel": normal((1, 1, C, hd), 1.0 / math.sqrt(C))},
+        "value": {"kernel": normal((1, 1, C, hd), 1.0 / math.sqrt(C))},
+        "RelativeLogits_0": {"rel_pos_emb_w": normal((2 * W - 1, head_ch), head_ch ** -0.5),
+                             "rel_pos_emb_h": normal((2 * H - 1, head_ch), head_ch ** -0.5)},
+    }

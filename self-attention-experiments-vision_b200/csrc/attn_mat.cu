@@ -1,0 +1,409 @@
+// Row kernels of the materialised-logits attention path.  The fused TMEM kernel
+// (attn_fwd.cu / attn_bwd.cu) covers plain attention with head dim 64; the variants that couple
+// heads or add position logits run as  batched GEMM (S = q k^T, sav_bgemm)  ->  THIS FILE  ->
+// batched GEMM (O = P v):
+//   * talking heads (attention.py:44-52, talking_heads.py:10-13): H x H mixing of the logits before
+//     the softmax and of the probabilities after it -- all H heads of one (image, query) row are
+//     handled by one warp, so both mixes, the softmax and (backward) both transform gradients are
+//     one pass over the logits;
+//   * BoTNet 2-D relative position logits (botnet.py:70-141): the per-query tables q.r^W, q.r^H
+//     (one skinny GEMM) are gathered into the logits here, and their gradient is scattered back;
+//   * class attention (cait.py:10-15, Nq = 1) and head dims other than 64 need nothing special.
+// One warp per row, lanes stride over the keys (coalesced 128-byte accesses per head), fp32
+// statistics by warp shuffle, three passes over L1/L2-resident rows (max+sum, delta, outputs).
+#include "common.cuh"
+#include "host.h"
+
+namespace sav {
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr int kRowWarps = 4;
+
+struct SoftArgs {
+  const float* S;     // [B,H,Nq,ld] raw q.k logits
+  bf16* P;            // fwd: [B,H,Nq,ld] probabilities (post-mix)
+  const float* dP;    // bwd: [B,H,Nq,ld] gradient of the post-mix probabilities
+  bf16* dS;           // bwd: [B,H,Nq,ld] gradient of the raw logits
+  const float* mix_pre;   // [H,H] (h -> i) or null
+  const float* mix_post;  // [H,H] (i -> j) or null
+  float* dmix_pre;
+  float* dmix_post;
+  const float* rel;   // [B,Nq,H,ldr] or null
+  float* drel;
+  int B, H, Nq, Nk, ld, ldr, rel_w, rel_h;
+  float scale;
+};
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// relative-logit column indices of key k for query q on a rel_w x rel_h grid (botnet.py:78-141:
+// abs[i,j] = rel[i, j-i+l-1] along each axis)
+__device__ __forceinline__ void rel_index(const SoftArgs& a, int q, int k, int& iw, int& ih) {
+  const int qx = q % a.rel_w, qy = q / a.rel_w;
+  const int kx = k % a.rel_w, ky = k / a.rel_w;
+  iw = kx - qx + a.rel_w - 1;
+  ih = (2 * a.rel_w - 1) + ky - qy + a.rel_h - 1;
+}
+
+// ------------------------------------------------------------------------------ independent heads
+// row = (b, h, q)
+__global__ void __launch_bounds__(kRowWarps * 32)
+softmax_rows_fwd_kernel(const SoftArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t rows = (int64_t)a.B * a.H * a.Nq;
+  const float sc = a.scale * kLog2e;
+  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + (threadIdx.x >> 5); row < rows;
+       row += (int64_t)gridDim.x * kRowWarps) {
+    const int q = (int)(row % a.Nq);
+    const int h = (int)((row / a.Nq) % a.H);
+    const int64_t b = row / ((int64_t)a.Nq * a.H);
+    const float* s = a.S + row * a.ld;
+    const float* r = a.rel ? a.rel + ((b * a.Nq + q) * a.H + h) * (int64_t)a.ldr : nullptr;
+    auto logit = [&](int k) {
+      float t = s[k];
+      if (r) { int iw, ih; rel_index(a, q, k, iw, ih); t += r[iw] + r[ih]; }
+      return t * sc;
+    };
+    float m = -INFINITY;
+    for (int k = lane; k < a.Nk; k += 32) m = fmaxf(m, logit(k));
+    m = warp_max(m);
+    float l = 0.f;
+    for (int k = lane; k < a.Nk; k += 32) l += ex2_fast(logit(k) - m);
+    l = warp_sum(l);
+    const float inv = 1.f / l;
+    bf16* p = a.P + row * a.ld;
+    for (int k = lane; k < a.ld; k += 32)
+      p[k] = __float2bfloat16(k < a.Nk ? ex2_fast(logit(k) - m) * inv : 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(kRowWarps * 32)
+softmax_rows_bwd_kernel(const SoftArgs a) {
+  extern __shared__ float sm_rel[];  // [kRowWarps][ldr]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* dr_s = sm_rel + warp * a.ldr;
+  const int64_t rows = (int64_t)a.B * a.H * a.Nq;
+  const float sc = a.scale * kLog2e;
+  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + warp; row < rows;
+       row += (int64_t)gridDim.x * kRowWarps) {
+    const int q = (int)(row % a.Nq);
+    const int h = (int)((row / a.Nq) % a.H);
+    const int64_t b = row / ((int64_t)a.Nq * a.H);
+    const float* s = a.S + row * a.ld;
+    const float* dp = a.dP + row * a.ld;
+    const int64_t roff = ((b * a.Nq + q) * a.H + h) * (int64_t)a.ldr;
+    const float* r = a.rel ? a.rel + roff : nullptr;
+    auto logit = [&](int k) {
+      float t = s[k];
+      if (r) { int iw, ih; rel_index(a, q, k, iw, ih); t += r[iw] + r[ih]; }
+      return t * sc;
+    };
+    float m = -INFINITY;
+    for (int k = lane; k < a.Nk; k += 32) m = fmaxf(m, logit(k));
+    m = warp_max(m);
+    float l = 0.f, dl = 0.f;
+    for (int k = lane; k < a.Nk; k += 32) {
+      const float e = ex2_fast(logit(k) - m);
+      l += e;
+      dl += e * dp[k];
+    }
+    l = warp_sum(l);
+    dl = warp_sum(dl);
+    const float inv = 1.f / l;
+    const float delta = dl * inv;
+    if (r) {
+      for (int j = lane; j < a.ldr; j += 32) dr_s[j] = 0.f;
+      __syncwarp();
+    }
+    bf16* ds = a.dS + row * a.ld;
+    for (int k = lane; k < a.ld; k += 32) {
+      float g = 0.f;
+      if (k < a.Nk) {
+        const float pk = ex2_fast(logit(k) - m) * inv;
+        g = pk * (dp[k] - delta) * a.scale;
+        if (r) {
+          int iw, ih;
+          rel_index(a, q, k, iw, ih);
+          atomicAdd(&dr_s[iw], g);
+          atomicAdd(&dr_s[ih], g);
+        }
+      }
+      ds[k] = __float2bfloat16(g);
+    }
+    if (r) {
+      __syncwarp();
+      for (int j = lane; j < a.ldr; j += 32) a.drel[roff + j] = dr_s[j];
+      __syncwarp();
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------ talking heads
+// row = (b, q); one warp owns all H heads of the row.
+template <int H>
+__device__ __forceinline__ void th_logits(const SoftArgs& a, const float* s0, int64_t hs, int k,
+                                          const float* t1, float sc, float (&s)[H], float (&t)[H]) {
+#pragma unroll
+  for (int h = 0; h < H; ++h) s[h] = s0[h * hs + k];
+#pragma unroll
+  for (int i = 0; i < H; ++i) {
+    float acc = 0.f;
+#pragma unroll
+    for (int h = 0; h < H; ++h) acc = fmaf(t1[h * H + i], s[h], acc);
+    t[i] = acc * sc;
+  }
+}
+
+template <int H>
+__device__ __forceinline__ void th_stats(const SoftArgs& a, const float* s0, int64_t hs, int lane,
+                                         const float* t1, float sc, float (&m)[H], float (&inv)[H]) {
+  float s[H], t[H];
+#pragma unroll
+  for (int i = 0; i < H; ++i) m[i] = -INFINITY;
+  for (int k = lane; k < a.Nk; k += 32) {
+    th_logits<H>(a, s0, hs, k, t1, sc, s, t);
+#pragma unroll
+    for (int i = 0; i < H; ++i) m[i] = fmaxf(m[i], t[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < H; ++i) { m[i] = warp_max(m[i]); inv[i] = 0.f; }
+  for (int k = lane; k < a.Nk; k += 32) {
+    th_logits<H>(a, s0, hs, k, t1, sc, s, t);
+#pragma unroll
+    for (int i = 0; i < H; ++i) inv[i] += ex2_fast(t[i] - m[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < H; ++i) inv[i] = 1.f / warp_sum(inv[i]);
+}
+
+template <int H>
+__global__ void __launch_bounds__(kRowWarps * 32)
+thsoftmax_fwd_kernel(const SoftArgs a) {
+  __shared__ float t1[H * H], t2[H * H];
+  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
+    t1[i] = a.mix_pre[i];
+    t2[i] = a.mix_post[i];
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int64_t rows = (int64_t)a.B * a.Nq;
+  const int64_t hs = (int64_t)a.Nq * a.ld;  // head stride
+  const float sc = a.scale * kLog2e;
+  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + (threadIdx.x >> 5); row < rows;
+       row += (int64_t)gridDim.x * kRowWarps) {
+    const int q = (int)(row % a.Nq);
+    const int64_t b = row / a.Nq;
+    const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
+    const float* s0 = a.S + off;
+    bf16* p0 = a.P + off;
+    float m[H], inv[H];
+    th_stats<H>(a, s0, hs, lane, t1, sc, m, inv);
+    for (int k = lane; k < a.ld; k += 32) {
+      float s[H], t[H], pr[H];
+      if (k < a.Nk) {
+        th_logits<H>(a, s0, hs, k, t1, sc, s, t);
+#pragma unroll
+        for (int i = 0; i < H; ++i) pr[i] = ex2_fast(t[i] - m[i]) * inv[i];
+      } else {
+#pragma unroll
+        for (int i = 0; i < H; ++i) pr[i] = 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < H; ++j) {
+        float acc = 0.f;
+#pragma unroll
+        for (int i = 0; i < H; ++i) acc = fmaf(t2[i * H + j], pr[i], acc);
+        p0[j * hs + k] = __float2bfloat16(acc);
+      }
+    }
+  }
+}
+
+template <int H>
+__global__ void __launch_bounds__(kRowWarps * 32)
+thsoftmax_bwd_kernel(const SoftArgs a) {
+  __shared__ float t1[H * H], t2[H * H];
+  __shared__ float red1[H * H], red2[H * H];
+  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
+    t1[i] = a.mix_pre[i];
+    t2[i] = a.mix_post[i];
+    red1[i] = 0.f;
+    red2[i] = 0.f;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int64_t rows = (int64_t)a.B * a.Nq;
+  const int64_t hs = (int64_t)a.Nq * a.ld;
+  const float sc = a.scale * kLog2e;
+  float g1[H * H], g2[H * H];  // lane-local partial sums of d mix_pre[h,i], d mix_post[i,j]
+#pragma unroll
+  for (int i = 0; i < H * H; ++i) { g1[i] = 0.f; g2[i] = 0.f; }
+  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + (threadIdx.x >> 5); row < rows;
+       row += (int64_t)gridDim.x * kRowWarps) {
+    const int q = (int)(row % a.Nq);
+    const int64_t b = row / a.Nq;
+    const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
+    const float* s0 = a.S + off;
+    const float* d0 = a.dP + off;
+    bf16* ds0 = a.dS + off;
+    float m[H], inv[H], delta[H];
+    th_stats<H>(a, s0, hs, lane, t1, sc, m, inv);
+#pragma unroll
+    for (int i = 0; i < H; ++i) delta[i] = 0.f;
+    for (int k = lane; k < a.Nk; k += 32) {
+      float s[H], t[H], dpo[H];
+      th_logits<H>(a, s0, hs, k, t1, sc, s, t);
+#pragma unroll
+      for (int j = 0; j < H; ++j) dpo[j] = d0[j * hs + k];
+#pragma unroll
+      for (int i = 0; i < H; ++i) {
+        const float pi = ex2_fast(t[i] - m[i]) * inv[i];
+        float dpi = 0.f;
+#pragma unroll
+        for (int j = 0; j < H; ++j) {
+          dpi = fmaf(t2[i * H + j], dpo[j], dpi);
+          g2[i * H + j] = fmaf(pi, dpo[j], g2[i * H + j]);
+        }
+        delta[i] = fmaf(pi, dpi, delta[i]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < H; ++i) delta[i] = warp_sum(delta[i]);
+    for (int k = lane; k < a.ld; k += 32) {
+      float dt[H], s[H], t[H];
+      if (k < a.Nk) {
+        float dpo[H];
+        th_logits<H>(a, s0, hs, k, t1, sc, s, t);
+#pragma unroll
+        for (int j = 0; j < H; ++j) dpo[j] = d0[j * hs + k];
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+          const float pi = ex2_fast(t[i] - m[i]) * inv[i];
+          float dpi = 0.f;
+#pragma unroll
+          for (int j = 0; j < H; ++j) dpi = fmaf(t2[i * H + j], dpo[j], dpi);
+          dt[i] = pi * (dpi - delta[i]) * a.scale;   // d(logit_i) * scale
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < H; ++i) { dt[i] = 0.f; s[i] = 0.f; }
+      }
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        float acc = 0.f;
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+          acc = fmaf(t1[h * H + i], dt[i], acc);
+          g1[h * H + i] = fmaf(s[h], dt[i], g1[h * H + i]);
+        }
+        ds0[h * hs + k] = __float2bfloat16(acc);
+      }
+    }
+  }
+  // lane -> warp -> block -> global
+#pragma unroll
+  for (int i = 0; i < H * H; ++i) {
+    const float v1 = warp_sum(g1[i]);
+    const float v2 = warp_sum(g2[i]);
+    if (lane == 0) {
+      atomicAdd(&red1[i], v1);
+      atomicAdd(&red2[i], v2);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
+    atomicAdd(a.dmix_pre + i, red1[i]);
+    atomicAdd(a.dmix_post + i, red2[i]);
+  }
+}
+
+static int soft_grid(int64_t rows) {
+  int64_t blocks = (rows + kRowWarps - 1) / kRowWarps;
+  const int64_t cap = 148 * 8;
+  return (int)(blocks < cap ? blocks : cap);
+}
+
+static int fill_args(const sav_thsoftmax_args* x, SoftArgs& a, const char* who) {
+  if (!x || x->B <= 0 || x->H <= 0 || x->Nq <= 0 || x->Nk <= 0 || x->ld < x->Nk)
+    return set_error(SAV_ERR_SHAPE, "%s: bad shape", who);
+  if ((x->mix_pre == nullptr) != (x->mix_post == nullptr))
+    return set_error(SAV_ERR_ARG, "%s: mix_pre and mix_post come together", who);
+  if (x->mix_pre && x->rel)
+    return set_error(SAV_ERR_ARG, "%s: talking heads and relative logits are not combined", who);
+  if (x->rel && ((int64_t)x->rel_w * x->rel_h != x->Nk || x->Nq != x->Nk ||
+                 x->ldr < 2 * x->rel_w - 1 + 2 * x->rel_h - 1))
+    return set_error(SAV_ERR_SHAPE, "%s: relative logits need Nq == Nk == rel_w*rel_h", who);
+  a.S = x->S; a.P = reinterpret_cast<bf16*>(x->P); a.dP = x->dP;
+  a.dS = reinterpret_cast<bf16*>(x->dS);
+  a.mix_pre = x->mix_pre; a.mix_post = x->mix_post;
+  a.dmix_pre = x->dmix_pre; a.dmix_post = x->dmix_post;
+  a.rel = x->rel; a.drel = x->drel;
+  a.B = (int)x->B; a.H = (int)x->H; a.Nq = (int)x->Nq; a.Nk = (int)x->Nk; a.ld = (int)x->ld;
+  a.ldr = (int)x->ldr; a.rel_w = x->rel_w; a.rel_h = x->rel_h;
+  a.scale = x->scale;
+  return SAV_OK;
+}
+
+}  // namespace sav
+
+using namespace sav;
+
+extern "C" int sav_thsoftmax_fwd(const sav_thsoftmax_args* x, void* stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  SoftArgs a;
+  int rc = fill_args(x, a, "sav_thsoftmax_fwd");
+  if (rc) return rc;
+  if (!a.S || !a.P) return set_error(SAV_ERR_ARG, "sav_thsoftmax_fwd: S and P required");
+  if (!a.mix_pre) {
+    softmax_rows_fwd_kernel<<<soft_grid((int64_t)a.B * a.H * a.Nq), kRowWarps * 32, 0, st>>>(a);
+  } else {
+    const int grid = soft_grid((int64_t)a.B * a.Nq);
+    switch (a.H) {
+#define SAV_TH_CASE(Hv) case Hv: thsoftmax_fwd_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a); break;
+      SAV_TH_CASE(2) SAV_TH_CASE(3) SAV_TH_CASE(4) SAV_TH_CASE(6) SAV_TH_CASE(8)
+#undef SAV_TH_CASE
+      default:
+        return set_error(SAV_ERR_SHAPE, "sav_thsoftmax_fwd: talking heads built for H in {2,3,4,6,8}");
+    }
+  }
+  count_launch();
+  return check_launch("sav_thsoftmax_fwd");
+}
+
+extern "C" int sav_thsoftmax_bwd(const sav_thsoftmax_args* x, void* stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  SoftArgs a;
+  int rc = fill_args(x, a, "sav_thsoftmax_bwd");
+  if (rc) return rc;
+  if (!a.S || !a.dP || !a.dS) return set_error(SAV_ERR_ARG, "sav_thsoftmax_bwd: S, dP, dS required");
+  if (a.rel && !a.drel) return set_error(SAV_ERR_ARG, "sav_thsoftmax_bwd: drel required with rel");
+  if (!a.mix_pre) {
+    const size_t sm = a.rel ? (size_t)kRowWarps * a.ldr * sizeof(float) : 0;
+    if (sm > 48 * 1024) return set_error(SAV_ERR_SHAPE, "sav_thsoftmax_bwd: relative table too wide");
+    softmax_rows_bwd_kernel<<<soft_grid((int64_t)a.B * a.H * a.Nq), kRowWarps * 32, sm, st>>>(a);
+  } else {
+    if (!a.dmix_pre || !a.dmix_post)
+      return set_error(SAV_ERR_ARG, "sav_thsoftmax_bwd: dmix_pre / dmix_post required");
+    // few, fat blocks: every block ends with H*H atomics per transform
+    int64_t blocks = ((int64_t)a.B * a.Nq + kRowWarps - 1) / kRowWarps;
+    const int grid = (int)(blocks < 148 * 4 ? blocks : 148 * 4);
+    switch (a.H) {
+#define SAV_TH_CASE(Hv) case Hv: thsoftmax_bwd_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a); break;
+      SAV_TH_CASE(2) SAV_TH_CASE(3) SAV_TH_CASE(4) SAV_TH_CASE(6) SAV_TH_CASE(8)
+#undef SAV_TH_CASE
+      default:
+        return set_error(SAV_ERR_SHAPE, "sav_thsoftmax_bwd: talking heads built for H in {2,3,4,6,8}");
+    }
+  }
+  count_launch();
+  return check_launch("sav_thsoftmax_bwd");
+}

@@ -13,6 +13,8 @@
 // Operands may be K-major or MN-major (selected by the smem + instruction descriptors), so
 // forward (X W), dX (dY W^T) and dW (X^T dY) all run here without any transposed copies.  dW is
 // split over K (tokens) and the partial tiles are combined with TMA reduce-add (fp32) in L2.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "host.h"
 
@@ -38,16 +40,27 @@ struct GemmParams {
   const float* col_scale;
   const float* row_scale;
   int64_t rows_per_scale;
+  int batch_inner;  // batched (BATCH=true) only: size of the inner batch dim (heads)
+  int nbatch;       // total batches (1 when not batched)
+  int debug;        // development only (SAV_GEMM_DEBUG): 1 = skip TMA loads, 2 = skip MMAs
 };
 
-template <int BN>
+constexpr int kSmemBudget = 232448;  // 227 KB opt-in limit per CTA
+
+template <int BN, bool B_MN, int CTAS>
 struct GemmCfg {
-  static constexpr int kStages = (BN == 256) ? 3 : 4;
+  static constexpr int kBCols = BN / CTAS;  // B columns (n) staged by this CTA
   static constexpr int kABytes = BM * BK * 2;
-  static constexpr int kBBytes = BN * BK * 2;
+  // MN-major B is staged as whole 64-column swizzle atoms (a 96-column half over-fetches 32)
+  static constexpr int kBBoxes = (kBCols + 63) / 64;
+  static constexpr int kBBytes = B_MN ? kBBoxes * (BK * 128) : kBCols * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kFit = (kSmemBudget - kOutBytes - 1024 - 256) / kStageBytes;
+  static constexpr int kStages = kFit > 6 ? 6 : kFit;
   static constexpr int kSmem = kStages * kStageBytes + kOutBytes + 1024 /*align*/ + 256 /*barriers*/;
   static constexpr uint32_t kTmemCols = 512;  // 2 accumulators of BN <= 256 fp32 columns
+  static_assert(kStageBytes % 1024 == 0, "stage must keep 1024 B alignment");
+  static_assert(kStages >= 3, "too few stages");
 };
 
 __device__ __forceinline__ void named_bar_sync(int id, int count) {
@@ -121,12 +134,12 @@ __device__ __forceinline__ void st_bf16x32(uint8_t* slab, int r, int cb, const f
                    pack_bf16(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16(v[g * 8 + 6], v[g * 8 + 7]));
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int CTAS, bool BATCH>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
             const __grid_constant__ CUtensorMap tma_d, const __grid_constant__ CUtensorMap tma_x,
             const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, B_MN, CTAS>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
@@ -152,63 +165,85 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], kEpiThreads);
+      mbar_init(&tempty_bar[s], kEpiWarps * CTAS);  // one arrival per epilogue warp (both CTAs)
     }
     for (int s = 0; s < 4; ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  if (warp == 1) {
+    if (CTAS == 2) tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot);
+    else tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  }
   tc_fence_before();
   __syncthreads();
+  if (CTAS == 2) cluster_sync_all();  // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // a "tile" is BM*CTAS rows x BN columns, owned by one CTA (pair); rank = CTA inside the pair
+  const int rank = CTAS == 2 ? (int)cluster_ctarank() : 0;
+  const int unit = (int)blockIdx.x / CTAS;          // which CTA (pair) of the grid
+  const int units = (int)gridDim.x / CTAS;
   const int tiles_mn = p.m_blocks * p.n_blocks;
-  const int num_tiles = tiles_mn * p.split_k;
+  const int tiles_per_batch = tiles_mn * p.split_k;
+  const int num_tiles = tiles_per_batch * (BATCH ? p.nbatch : 1);
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int split = tile / tiles_mn;
-        const int mn = tile - split * tiles_mn;
-        const int m_idx = (mn / p.n_blocks) * BM;
-        const int n_idx = (mn % p.n_blocks) * BN;
+      for (int tile = unit; tile < num_tiles; tile += units) {
+        const int z = BATCH ? tile / tiles_per_batch : 0;
+        const int zi = BATCH ? z % p.batch_inner : 0, zo = BATCH ? z / p.batch_inner : 0;
+        const int tl = tile - z * tiles_per_batch;
+        const int split = tl / tiles_mn;
+        const int mn = tl - split * tiles_mn;
+        const int m_idx = (mn / p.n_blocks) * (BM * CTAS) + rank * BM;
+        const int n_idx = (mn % p.n_blocks) * BN + rank * Cfg::kBCols;
         const int kb0 = split * p.k_per_split;
         const int kb1 = min(kb0 + p.k_per_split, p.k_blocks);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
-          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          // the leader's full barrier collects the bytes of both CTAs' loads
+          if (p.debug & 1) {  // MMA-only rate: operands are whatever the smem holds
+            if (rank == 0) mbar_arrive(&full_bar[stage]);
+            if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+            continue;
+          }
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * CTAS);
           const int k_idx = kb * BK;
+          auto load = [&](void* dst, const CUtensorMap* m, int c0, int c1) {
+            if (BATCH) tma_load_4d(dst, m, &full_bar[stage], c0, c1, zi, zo);
+            else if (CTAS == 2) tma_load_2d_pair(dst, m, &full_bar[stage], c0, c1);
+            else tma_load_2d(dst, m, &full_bar[stage], c0, c1);
+          };
           if (!A_MN) {
-            tma_load_2d(sa, &tma_a, &full_bar[stage], k_idx, m_idx);
+            load(sa, &tma_a, k_idx, m_idx);
           } else {
 #pragma unroll
-            for (int j = 0; j < BM / 64; ++j)
-              tma_load_2d(sa + j * (BK * 128), &tma_a, &full_bar[stage], m_idx + j * 64, k_idx);
+            for (int j = 0; j < BM / 64; ++j) load(sa + j * (BK * 128), &tma_a, m_idx + j * 64, k_idx);
           }
           if (!B_MN) {
-            tma_load_2d(sb, &tma_b, &full_bar[stage], k_idx, n_idx);
+            load(sb, &tma_b, k_idx, n_idx);
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(sb + j * (BK * 128), &tma_b, &full_bar[stage], n_idx + j * 64, k_idx);
+            for (int j = 0; j < Cfg::kBBoxes; ++j)
+              load(sb + j * (BK * 128), &tma_b, n_idx + j * 64, k_idx);
           }
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM * CTAS, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        const int split = tile / tiles_mn;
+      for (int tile = unit; tile < num_tiles; tile += units, ++it) {
+        const int split = (tile % tiles_per_batch) / tiles_mn;
         const int kb0 = split * p.k_per_split;
         const int kb1 = min(kb0 + p.k_per_split, p.k_blocks);
         const int acc = it & 1;
@@ -223,16 +258,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           const uint32_t sb = sa + Cfg::kABytes;
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
+            if (p.debug & 2) break;
             const uint64_t da = A_MN ? make_smem_desc(sa + k * 2048, BK * 128, 1024)
                                      : make_smem_desc(sa + k * 32, 16, 1024);
             const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, BK * 128, 1024)
                                      : make_smem_desc(sb + k * 32, 16, 1024);
-            umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (CTAS == 2) umma_f16_pair(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);
+          if (CTAS == 2) umma_commit_pair(&empty_bar[stage]);
+          else umma_commit(&empty_bar[stage]);
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[acc]);
+        if (CTAS == 2) umma_commit_pair(&tfull_bar[acc]);
+        else umma_commit(&tfull_bar[acc]);
       }
     }
   } else {
@@ -249,14 +288,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     const int nslot = two_out ? 2 : 4;
     const int slot_bytes = two_out ? 2 * SLAB_BYTES : SLAB_BYTES;
     const bool aux_in = p.has_aux_in != 0;
-    const int my_tiles = (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int my_tiles = (num_tiles - unit + units - 1) / units;
     const uint32_t total_slabs = (uint32_t)my_tiles * slabs_per_tile;
 
     auto issue_aux = [&](uint32_t sg) {  // leader only: TMA-load the epilogue input of slab sg
-      const int t = blockIdx.x + (sg / slabs_per_tile) * gridDim.x;
+      const int t = unit + (sg / slabs_per_tile) * units;
       const int mn = t % tiles_mn;
       const int col = (mn % p.n_blocks) * BN + (sg % slabs_per_tile) * SC;
-      const int row = (mn / p.n_blocks) * BM;
+      const int row = (mn / p.n_blocks) * (BM * CTAS) + rank * BM;
       const int slot = sg % nslot;
       mbar_expect_tx(&aux_bar[slot], SLAB_BYTES);
       tma_load_2d(smem_out + slot * slot_bytes, &tma_x, &aux_bar[slot], col, row);
@@ -264,15 +303,30 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     if (aux_in && leader)
       for (uint32_t sg = 0; sg + 1 < (uint32_t)nslot && sg < total_slabs; ++sg) issue_aux(sg);
 
-    int m_idx = 0, n_idx = 0, acc = 0;
+    // this warp has read its part of accumulator `a` out of TMEM: one arrival per warp on the
+    // (leader's) tempty barrier
+    auto release_acc = [&](int a) {
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (CTAS == 2) mbar_arrive_leader(&tempty_bar[a]);
+        else mbar_arrive(&tempty_bar[a]);
+      }
+    };
+    int m_idx = 0, n_idx = 0, acc = 0, zi = 0, zo = 0;
     float rs = 1.f;
     for (uint32_t sg = 0; sg < total_slabs; ++sg) {
       const int it = sg / slabs_per_tile;
       const int j = sg - it * slabs_per_tile;
       if (j == 0) {
-        const int tile = blockIdx.x + it * gridDim.x;
+        const int tile = unit + it * units;
         const int mn = tile % tiles_mn;
-        m_idx = (mn / p.n_blocks) * BM;
+        if (BATCH) {
+          const int z = tile / tiles_per_batch;
+          zi = z % p.batch_inner;
+          zo = z / p.batch_inner;
+        }
+        m_idx = (mn / p.n_blocks) * (BM * CTAS) + rank * BM;
         n_idx = (mn % p.n_blocks) * BN;
         acc = it & 1;
         mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
@@ -290,7 +344,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         uint32_t rr[32];
         tmem_ld32(taddr, rr);
         tmem_ld_wait();
-        if (j == slabs_per_tile - 1) { tc_fence_before(); mbar_arrive(&tempty_bar[acc]); }
+        if (j == slabs_per_tile - 1) release_acc(acc);
         float v[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(rr[i]);
@@ -327,7 +381,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         uint32_t rr[16];
         tmem_ld16(taddr, rr);
         tmem_ld_wait();
-        if (j == slabs_per_tile - 1) { tc_fence_before(); mbar_arrive(&tempty_bar[acc]); }
+        if (j == slabs_per_tile - 1) release_acc(acc);
         float v[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(rr[i]);
@@ -360,6 +414,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         } else if (two_out) {
           tma_store_2d(&tma_x, slab, c0, m_idx);
           tma_store_2d(&tma_d, slab + SLAB_BYTES, c0, m_idx);
+        } else if (BATCH) {
+          tma_store_4d(&tma_d, slab, c0, m_idx, zi, zo);
         } else {
           tma_store_2d(&tma_d, slab, c0, m_idx);
         }
@@ -370,9 +426,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   }
   tc_fence_before();
   __syncthreads();
+  if (CTAS == 2) cluster_sync_all();  // the peer may still read this CTA's smem / signal its barriers
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+    if (CTAS == 2) tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
+    else tmem_dealloc<Cfg::kTmemCols>(tmem_base);
   }
 }
 
@@ -425,6 +483,8 @@ static int num_sms() {
   return n;
 }
 
+static int pick_bn_batched(int64_t N) { return N <= 64 ? 64 : 128; }
+
 static int pick_bn(int64_t N) {
   if (N % 256 == 0) return 256;
   if (N % 192 == 0) return 192;
@@ -432,22 +492,23 @@ static int pick_bn(int64_t N) {
   return 128;
 }
 
-static int plan_split(const sav_gemm_args* a, int bn) {
+static int plan_split(const sav_gemm_args* a, int bn, int bm) {
   if (a->split_k > 0) return a->split_k;
   // auto (split_k == 0): only for fp32 outputs without epilogue, fill the machine
-  const int64_t tiles = ((a->M + BM - 1) / BM) * ((a->N + bn - 1) / bn);
+  const int64_t tiles = ((a->M + bm - 1) / bm) * ((a->N + bn - 1) / bn);
   const int64_t kb = (a->K + BK - 1) / BK;
-  if (!a->d_fp32 || tiles >= num_sms() || kb < 16) return 1;
-  int64_t s = num_sms() / tiles;
+  const int64_t units = num_sms() / (bm / BM);
+  if (!a->d_fp32 || tiles >= units || kb < 16) return 1;
+  int64_t s = units / tiles;
   if (s > kb / 8) s = kb / 8;
   return (int)(s < 1 ? 1 : s);
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int CTAS, bool BATCH = false>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
                        const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
-  using Cfg = GemmCfg<BN>;
-  auto kern = gemm_kernel<BN, A_MN, B_MN>;
+  using Cfg = GemmCfg<BN, B_MN, CTAS>;
+  auto kern = gemm_kernel<BN, A_MN, B_MN, CTAS, BATCH>;
   static bool attr_set = false;  // benign race: idempotent
   if (!attr_set) {
     cudaError_t e =
@@ -455,11 +516,38 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
     if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "gemm smem attr: %s", cudaGetErrorString(e));
     attr_set = true;
   }
-  const int tiles = p.m_blocks * p.n_blocks * p.split_k;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, kGemmThreads, Cfg::kSmem, st>>>(ta, tb, td, tx, p);
+  const int tiles = p.m_blocks * p.n_blocks * p.split_k * (BATCH ? p.nbatch : 1);
+  const int units = num_sms() / CTAS;
+  const int grid = (tiles < units ? tiles : units) * CTAS;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CTAS;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, td, tx, p);
+  if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "sav_gemm launch: %s", cudaGetErrorString(e));
   count_launch();
   return check_launch("sav_gemm");
+}
+
+// CTA pairs pay off when the pair tile (256 rows) is mostly full; SAV_GEMM_CTAS=1|2 overrides.
+static int pick_ctas(int64_t M) {
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("SAV_GEMM_CTAS");
+    forced = e ? atoi(e) : 0;
+  }
+  if (forced == 1 || forced == 2) return forced;
+  const int64_t pair_rows = ((M + 2 * BM - 1) / (2 * BM)) * (2 * BM);
+  const int64_t single_rows = ((M + BM - 1) / BM) * BM;
+  return pair_rows * 8 <= single_rows * 9 ? 2 : 1;  // <= 12.5 % extra padded rows
 }
 
 }  // namespace sav
@@ -483,7 +571,9 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
       !aligned16(a->col_scale))
     return set_error(SAV_ERR_ALIGN, "sav_gemm: pointers must be 16 B aligned");
   const int bn = pick_bn(a->N);
-  const int split = plan_split(a, bn);
+  const int ctas = pick_ctas(a->M);
+  const int bm = BM * ctas;
+  const int split = plan_split(a, bn, bm);
   const bool accum = a->accumulate || split > 1;
   const bool any_affine = a->bias || a->col_scale || a->row_scale;
   if (accum && (!a->d_fp32 || any_affine || a->act || a->aux_in || a->aux_out || a->residual))
@@ -499,7 +589,7 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
 
   GemmParams p;
   p.M = a->M; p.N = a->N; p.K = a->K;
-  p.m_blocks = (int)((a->M + BM - 1) / BM);
+  p.m_blocks = (int)((a->M + bm - 1) / bm);
   p.n_blocks = (int)((a->N + bn - 1) / bn);
   p.k_blocks = (int)((a->K + BK - 1) / BK);
   p.k_per_split = (p.k_blocks + split - 1) / split;
@@ -509,6 +599,12 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
   p.has_aux_in = (a->aux_in || a->residual) ? 1 : 0;
   p.bias = a->bias; p.col_scale = a->col_scale; p.row_scale = a->row_scale;
   p.rows_per_scale = a->rows_per_scale > 0 ? a->rows_per_scale : 1;
+  {
+    static int dbg = -1;
+    if (dbg < 0) { const char* e = getenv("SAV_GEMM_DEBUG"); dbg = e ? atoi(e) : 0; }
+    p.debug = dbg;
+  }
+  p.batch_inner = 1; p.nbatch = 1;
 
   CUtensorMap ta, tb, td, tx;
   int rc;
@@ -519,7 +615,7 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
     else          { dims[0] = a->M; dims[1] = a->K; box[0] = 64; box[1] = BK; }
     str[0] = 0; str[1] = (uint64_t)a->lda * 2;
     if ((rc = make_tmap_bf16(&ta, a->A, 2, dims, str, box))) return rc;
-    if (!a->b_mn) { dims[0] = a->K; dims[1] = a->N; box[0] = BK; box[1] = bn; }
+    if (!a->b_mn) { dims[0] = a->K; dims[1] = a->N; box[0] = BK; box[1] = bn / ctas; }
     else          { dims[0] = a->N; dims[1] = a->K; box[0] = 64; box[1] = BK; }
     str[1] = (uint64_t)a->ldb * 2;
     if ((rc = make_tmap_bf16(&tb, a->B, 2, dims, str, box))) return rc;
@@ -540,7 +636,8 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
   }
 #define SAV_GEMM_CASE(BNv, AM, BMj)                                                  \
   if (bn == BNv && (a->a_mn != 0) == AM && (a->b_mn != 0) == BMj)                     \
-    rc = launch_gemm<BNv, AM, BMj>(ta, tb, td, tx, p, st);
+    rc = ctas == 2 ? launch_gemm<BNv, AM, BMj, 2>(ta, tb, td, tx, p, st)              \
+                   : launch_gemm<BNv, AM, BMj, 1>(ta, tb, td, tx, p, st);
   rc = SAV_ERR_ARG;
   SAV_GEMM_CASE(128, false, false) SAV_GEMM_CASE(128, false, true)
   SAV_GEMM_CASE(128, true, false)  SAV_GEMM_CASE(128, true, true)
@@ -549,6 +646,57 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
   SAV_GEMM_CASE(256, false, false) SAV_GEMM_CASE(256, false, true)
   SAV_GEMM_CASE(256, true, false)  SAV_GEMM_CASE(256, true, true)
 #undef SAV_GEMM_CASE
+  return rc;
+}
+
+
+// ---- batched GEMM over (outer, inner) batch dims with independent strides: the materialised-
+// logits attention path (talking heads, class attention, 2-D relative logits, head dims != 64).
+extern "C" int sav_bgemm(const sav_bgemm_args* a, void* stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!a || a->M <= 0 || a->N <= 0 || a->K <= 0 || a->batch_outer <= 0 || a->batch_inner <= 0)
+    return set_error(SAV_ERR_SHAPE, "sav_bgemm: M,N,K and batch dims must be positive");
+  if (a->batch_outer * a->batch_inner > (1 << 22))
+    return set_error(SAV_ERR_SHAPE, "sav_bgemm: too many batches");
+  const int bn = pick_bn_batched(a->N);
+  GemmParams p = {};
+  p.M = a->M; p.N = a->N; p.K = a->K;
+  p.m_blocks = (int)((a->M + BM - 1) / BM);
+  p.n_blocks = (int)((a->N + bn - 1) / bn);
+  p.k_blocks = (int)((a->K + BK - 1) / BK);
+  p.k_per_split = p.k_blocks;
+  p.split_k = 1;
+  p.epi = a->d_fp32 ? EPI_F32 : EPI_PLAIN;
+  p.rows_per_scale = 1;
+  p.batch_inner = (int)a->batch_inner;
+  p.nbatch = (int)(a->batch_inner * a->batch_outer);
+  CUtensorMap ta, tb, td;
+  int rc;
+  uint64_t dims[4], str[4];
+  uint32_t box[4] = {0, 0, 1, 1};
+  dims[2] = a->batch_inner; dims[3] = a->batch_outer;
+  str[0] = 0;
+  if (!a->a_mn) { dims[0] = a->K; dims[1] = a->M; box[0] = BK; box[1] = BM; }
+  else          { dims[0] = a->M; dims[1] = a->K; box[0] = 64; box[1] = BK; }
+  str[1] = (uint64_t)a->lda * 2; str[2] = (uint64_t)a->a_stride_inner * 2; str[3] = (uint64_t)a->a_stride_outer * 2;
+  if ((rc = make_tmap_nd(&ta, a->A, 2, 4, dims, str, box))) return rc;
+  if (!a->b_mn) { dims[0] = a->K; dims[1] = a->N; box[0] = BK; box[1] = bn; }
+  else          { dims[0] = a->N; dims[1] = a->K; box[0] = 64; box[1] = BK; }
+  str[1] = (uint64_t)a->ldb * 2; str[2] = (uint64_t)a->b_stride_inner * 2; str[3] = (uint64_t)a->b_stride_outer * 2;
+  if ((rc = make_tmap_nd(&tb, a->B, 2, 4, dims, str, box))) return rc;
+  const int es = a->d_fp32 ? 4 : 2;
+  dims[0] = a->N; dims[1] = a->M; box[0] = 128 / es; box[1] = BM;
+  str[1] = (uint64_t)a->ldd * es; str[2] = (uint64_t)a->d_stride_inner * es; str[3] = (uint64_t)a->d_stride_outer * es;
+  if ((rc = make_tmap_nd(&td, a->D, es, 4, dims, str, box))) return rc;
+#define SAV_BGEMM_CASE(BNv, AM, BMj)                                  \
+  if (bn == BNv && (a->a_mn != 0) == AM && (a->b_mn != 0) == BMj)     \
+    rc = launch_gemm<BNv, AM, BMj, 1, true>(ta, tb, td, td, p, st);
+  rc = SAV_ERR_ARG;
+  SAV_BGEMM_CASE(64, false, false) SAV_BGEMM_CASE(64, false, true)
+  SAV_BGEMM_CASE(64, true, false)  SAV_BGEMM_CASE(64, true, true)
+  SAV_BGEMM_CASE(128, false, false) SAV_BGEMM_CASE(128, false, true)
+  SAV_BGEMM_CASE(128, true, false)  SAV_BGEMM_CASE(128, true, true)
+#undef SAV_BGEMM_CASE
   return rc;
 }
 

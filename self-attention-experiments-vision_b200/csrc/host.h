@@ -19,6 +19,10 @@ int check_launch(const char* what);
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                    const uint64_t* strides_bytes, const uint32_t* box);
 
+// Same for 2-byte (bf16) or 4-byte (fp32) elements.
+int make_tmap_nd(CUtensorMap* out, const void* base, int elem_bytes, int rank, const uint64_t* dims,
+                 const uint64_t* strides_bytes, const uint32_t* box);
+
 // 2-D row-major tensor [rows, cols] (elem_bytes 2 = bf16, 4 = fp32), row pitch ld elements,
 // box [box_rows, box_cols] with box_cols * elem_bytes == 128 (one swizzle row).
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, int64_t cols, int64_t rows,

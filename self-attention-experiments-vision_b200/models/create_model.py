@@ -5,6 +5,7 @@ Names and hyper-parameters are the reference's; `deit_ti_patch16` / `deit_s_patc
 `dtype` is accepted for signature compatibility; the compute path is always bf16 storage with fp32
 accumulation / statistics.
 """
+from models.cait import CaiT
 from models.vit import ViT
 
 _VIT = {
@@ -18,9 +19,29 @@ _VIT = {
 }
 
 
+_CAIT = {
+    # name: (num_layers, num_heads, embed_dim, stoch_depth_rate, layerscale_eps)  create_model.py:79-168
+    'cait_xxs_24': (24, 4, 192, 0.05, 1e-5),
+    'cait_xxs_36': (36, 4, 192, 0.1, 1e-6),
+    'cait_xs_24': (24, 6, 288, 0.05, 1e-5),
+    'cait_xs_36': (36, 6, 288, 0.1, 1e-6),
+    'cait_s_24': (24, 8, 384, 0.1, 1e-6),
+    'cait_s_36': (36, 8, 384, 0.2, 1e-6),
+    'cait_s_48': (48, 8, 384, 0.3, 1e-6),
+    'cait_m_24': (24, 16, 768, 0.2, 1e-5),
+    'cait_m_36': (36, 16, 768, 0.3, 1e-6),
+    'cait_m_48': (48, 16, 768, 0.4, 1e-6),
+}
+
+
 def create_model(model_name: str, num_classes: int = 1000, dtype=None):
     if model_name in _VIT:
         layers, heads, dim, p = _VIT[model_name]
         return ViT(num_classes=num_classes, num_layers=layers, num_heads=heads, embed_dim=dim,
                    patch_shape=(p, p), dtype=dtype)
+    if model_name in _CAIT:
+        layers, heads, dim, sd, eps = _CAIT[model_name]
+        return CaiT(num_classes=num_classes, num_layers=layers, num_layers_token_only=2,
+                    num_heads=heads, embed_dim=dim, patch_shape=(16, 16), stoch_depth_rate=sd,
+                    layerscale_eps=eps, dtype=dtype)
     raise NotImplementedError(f'{model_name} is not built yet (see DESIGN.md status table)')

@@ -1,4 +1,4 @@
-from models.layers.attentions import AttentionBlock, SelfAttentionBlock  # noqa: F401
+from models.layers.attentions import AttentionBlock, SelfAttentionBlock, TalkingHeadsBlock  # noqa: F401
 from models.layers.feedforwards import FFBlock  # noqa: F401
 from models.layers.normalizations import LayerScaleBlock  # noqa: F401
 from models.layers.position_embed import AddAbsPosEmbed  # noqa: F401

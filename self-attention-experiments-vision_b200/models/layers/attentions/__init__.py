@@ -1,1 +1,2 @@
+from models.layers.attentions.talking_heads import TalkingHeadsBlock  # noqa: F401
 from models.layers.attentions.attention import AttentionBlock, SelfAttentionBlock  # noqa: F401

@@ -10,6 +10,8 @@ from typing import Optional
 from sav import functional as F
 from sav import linen as nn
 
+from models.layers.attentions.talking_heads import TalkingHeadsBlock
+
 
 class AttentionBlock(nn.Module):
     num_heads: int
@@ -31,8 +33,6 @@ class AttentionBlock(nn.Module):
         out_ch = self.out_ch or in_ch
         if self.use_bias:
             raise NotImplementedError("AttentionBlock(use_bias=True)")
-        if self.talking_heads:
-            raise NotImplementedError("talking-heads attention (CaiT) is not built yet")
         if (self.attn_dropout_rate or self.out_dropout_rate) and is_training:
             raise NotImplementedError("attention dropout with rate > 0")
         (wq, wk, wv), w_qkv = self.fused_params(("queries", "keys", "values"), "kernel",
@@ -40,18 +40,27 @@ class AttentionBlock(nn.Module):
         scope = self._scope_path()
         w_out = self._param(scope + ("DenseGeneral_0", "kernel"),
                             nn.initializers.lecun_normal(in_axes=2), (H, d, out_ch))
+        mix = None
+        if self.talking_heads:                               # attention.py:44-46,50-52
+            mix = (TalkingHeadsBlock(num_heads=H)(), TalkingHeadsBlock(num_heads=H)())
+        # plain attention with d = 64 runs in the fused TMEM kernel; talking heads and other head
+        # dims go through the materialised-logits path (batched GEMMs + one row kernel)
+        fused = mix is None and d == 64
         if inputs_q is inputs_kv:
             qkv = F.linear(inputs_q, w_qkv)                  # attention.py:35-37, one GEMM
-            ctx = F.self_attention_core(qkv, H, d)           # attention.py:39-58
+            ctx = F.self_attention_core(qkv, H, d) if fused else \
+                F.mat_self_attention_core(qkv, H, d, mix)    # attention.py:39-58
         else:
             hd = H * d
             gq = w_qkv.gw[:, :hd] if w_qkv.gw is not None else None
             gkv = w_qkv.gw[:, hd:] if w_qkv.gw is not None else None
             q = F.linear(inputs_q, F.Weight(w_qkv.w[:, :hd], gq, [wq]))
             kv = F.linear(inputs_kv, F.Weight(w_qkv.w[:, hd:], gkv, [wk, wv]))
-            ctx = F.cross_attention_core(q, kv, H, d)
+            ctx = F.cross_attention_core(q, kv, H, d) if fused else \
+                F.mat_cross_attention_core(q, kv, H, d, mix)
         gw = w_out.grad.view(H * d, out_ch) if w_out.grad is not None else None
-        return F.linear(ctx, F.Weight(w_out.shadow.view(H * d, out_ch), gw, [w_out]))  # :60-63
+        return F.linear(ctx, F.Weight(w_out.shadow.view(H * d, out_ch), gw, [w_out],
+                                      wm=w_out.master.view(H * d, out_ch)))          # :60-63
 
 
 class SelfAttentionBlock(AttentionBlock):

@@ -59,6 +59,30 @@ class AttnBwdArgs(C.Structure):
     ]
 
 
+class BGemmArgs(C.Structure):
+    _fields_ = [
+        ("A", C.c_void_p), ("B", C.c_void_p), ("D", C.c_void_p),
+        ("M", C.c_int64), ("N", C.c_int64), ("K", C.c_int64),
+        ("batch_outer", C.c_int64), ("batch_inner", C.c_int64),
+        ("lda", C.c_int64), ("a_stride_inner", C.c_int64), ("a_stride_outer", C.c_int64),
+        ("ldb", C.c_int64), ("b_stride_inner", C.c_int64), ("b_stride_outer", C.c_int64),
+        ("ldd", C.c_int64), ("d_stride_inner", C.c_int64), ("d_stride_outer", C.c_int64),
+        ("a_mn", C.c_int32), ("b_mn", C.c_int32), ("d_fp32", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class ThSoftmaxArgs(C.Structure):
+    _fields_ = [
+        ("S", C.c_void_p), ("P", C.c_void_p), ("dP", C.c_void_p), ("dS", C.c_void_p),
+        ("mix_pre", C.c_void_p), ("mix_post", C.c_void_p),
+        ("dmix_pre", C.c_void_p), ("dmix_post", C.c_void_p),
+        ("rel", C.c_void_p), ("drel", C.c_void_p),
+        ("B", C.c_int64), ("H", C.c_int64), ("Nq", C.c_int64), ("Nk", C.c_int64),
+        ("ld", C.c_int64), ("ldr", C.c_int64),
+        ("rel_w", C.c_int32), ("rel_h", C.c_int32), ("scale", C.c_float), ("reserved", C.c_int32),
+    ]
+
+
 _P, _I64, _I32, _F = C.c_void_p, C.c_int64, C.c_int32, C.c_float
 
 # name -> (restype, argtypes); also the list the CPU test checks against include/sav_abi.h
@@ -69,6 +93,12 @@ SIGNATURES = {
     "sav_launch_count": (C.c_int64, []),
     "sav_gemm_workspace_bytes": (C.c_int64, [C.POINTER(GemmArgs)]),
     "sav_gemm": (C.c_int, [C.POINTER(GemmArgs), _P]),
+    "sav_bgemm": (C.c_int, [C.POINTER(BGemmArgs), _P]),
+    "sav_thsoftmax_fwd": (C.c_int, [C.POINTER(ThSoftmaxArgs), _P]),
+    "sav_thsoftmax_bwd": (C.c_int, [C.POINTER(ThSoftmaxArgs), _P]),
+    "sav_scale_rows_cols": (C.c_int, [_P, _I64, _P, _P, _I64, _P, _I64, _I64, _I64, _P]),
+    "sav_layerscale_grad": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P]),
+    "sav_copy2d_f32": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, _I32, _P]),
     "sav_colsum_bf16": (C.c_int, [_P, _I64, _I64, _I64, _P, _I32, _P]),
     "sav_layernorm_fwd": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _P, _P, _I64, _I64, _F, _P]),
     "sav_layernorm_bwd": (C.c_int, [_P, _I64, _P, _I64] + [_P] * 8 + [_I64, _I64, _P]),

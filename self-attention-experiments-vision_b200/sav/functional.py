@@ -30,10 +30,10 @@ def _meta(t):
 
 class Weight:
     """2-D bf16 weight view [K,N] (unit inner stride) + its fp32 gradient view + owning Params."""
-    __slots__ = ("w", "gw", "params")
+    __slots__ = ("w", "gw", "params", "wm")
 
-    def __init__(self, w, gw, params):
-        self.w, self.gw, self.params = w, gw, params
+    def __init__(self, w, gw, params, wm=None):
+        self.w, self.gw, self.params, self.wm = w, gw, params, wm
 
     def touch(self):
         for p in self.params:
@@ -53,6 +53,18 @@ def _grad16(var):
     out = torch.empty(g.shape, dtype=BF16, device=g.device)
     ops.cast_bf16(g.contiguous(), out)
     return out
+
+
+def _as2d(t, K):
+    """2-D [rows, K] view of an activation without copying: contiguous tensors reshape; [B,1,K]
+    row selections (class-token rows, cait.py:13) and 2-D strided views pass through."""
+    if t.is_contiguous():
+        return t.reshape(-1, K)
+    if t.dim() == 3 and t.shape[1] == 1:
+        return t[:, 0]
+    if t.dim() == 2:
+        return t
+    return t.contiguous().reshape(-1, K)
 
 
 class LazyLinear(Var):
@@ -98,7 +110,7 @@ class LazyLinear(Var):
         if xin.dtype != BF16:
             raise TypeError("linear: the input of a Dense must be a bf16 activation (apply LayerNorm "
                             "to the fp32 residual stream first)")
-        x2 = xin.reshape(-1, K) if xin.is_contiguous() else xin  # strided 2-D views pass through
+        x2 = _as2d(xin, K)
         M = x2.shape[0]
         out = torch.empty((M, N), dtype=F32 if stream else BF16, device=x2.device)
         pre = torch.empty((M, N), dtype=BF16, device=x2.device) if self.act else None
@@ -128,14 +140,22 @@ class LazyLinear(Var):
                 raise NotImplementedError("residual-stream Var with a second consumer before its "
                                           "LayerNorm backward")
             self.residual.g = self.g.view(self.residual.v.shape)
-        dy = _grad16(self)
+        scaled = self.col_scale is not None or self.row_scale is not None
+        if scaled:
+            # reverse mode of the LayerScale / drop-path epilogue: the branch gradient is the fp32
+            # stream gradient times both scales (one pass, bf16 out = the MMA operand)
+            if self.residual is None or self.g is None or self.g.dtype != F32:
+                raise NotImplementedError("LayerScale / drop-path epilogue without a residual add")
+            self.g16 = None
+            dy2 = ops.scale_rows_cols(self.g.reshape(-1, N),
+                                      self.col_scale.master if self.col_scale is not None else None,
+                                      self.row_scale, self.rows_per_scale)
+        else:
+            dy2 = _grad16(self).reshape(-1, N)
         self.g = None
-        dy2 = dy.reshape(-1, N)
-        if self.col_scale is not None or self.row_scale is not None:
-            raise NotImplementedError("backward through LayerScale / drop-path epilogue")
         if self.act and not self.g_is_pre:
             raise NotImplementedError("activated linear output must be consumed by a linear op")
-        x2 = x.v.reshape(-1, K) if x.v.is_contiguous() else x.v
+        x2 = _as2d(x.v, K)
         # dW[K,N] += X^T dY : both operands token-major (MN-major), split-K over tokens, TMA
         # reduce-add into the (zeroed) fp32 gradient arena
         W.touch()
@@ -143,10 +163,18 @@ class LazyLinear(Var):
         if self.bias is not None:
             self.bias.touch_grad()
             ops.colsum(dy2, out=self.bias.grad, accumulate=True)
+        if self.col_scale is not None:
+            # d layerscale from the finished dW / dbias (elementwise.cu), no saved activation
+            if W.wm is None:
+                raise NotImplementedError("LayerScale backward needs the fp32 master weight view")
+            self.col_scale.touch_grad()
+            ops.layerscale_grad(W.wm, W.gw, self.bias.master if self.bias is not None else None,
+                                self.bias.grad if self.bias is not None else None,
+                                self.col_scale.master, self.col_scale.grad)
         if x.requires_grad:
             # dX[M,K] = dY W^T (x gelu'(pre) when x is a fused-GELU output)
             dx = ops.gemm(dy2, W.w, b_mn=False, aux_in=x.pre_act)
-            _add_grad(x, dx.view(x.v.shape) if x.v.is_contiguous() else dx)
+            _add_grad(x, dx.view(x.v.shape) if x.v.is_contiguous() or dx.numel() == x.v.numel() else dx)
             x.g_is_pre = x.pre_act is not None
 
 
@@ -155,8 +183,13 @@ def _add_grad(var, g):
         var.g = g
     elif g.dtype == BF16 and var.g.dtype == BF16:
         var.g = ops.add(var.g.contiguous(), g.contiguous()).view(var.g.shape)
+    elif g.dtype == F32 and var.g.dtype == F32:
+        # fan-in of fp32 stream gradients (CaiT: the patch tokens feed every class-attention block)
+        C = g.shape[-1]
+        ops.copy2d_f32(g.reshape(-1, C), var.g.reshape(-1, C), accumulate=True)
+        var.g16 = None
     else:
-        raise NotImplementedError("fan-in of fp32 stream gradients outside LayerNorm backward")
+        raise NotImplementedError("gradient fan-in with mixed precisions")
 
 
 def linear(x, weight, bias=None, out_features_shape=None):
@@ -441,3 +474,204 @@ def softmax_cross_entropy(logits, labels, label_smoothing=0.0, world_size=1):
     B = lv.shape[0]
     dl, stats = ops.softmax_xent(lv.contiguous(), labels, label_smoothing, 1.0 / (B * world_size))
     return LossVar(logits, dl, stats, B)
+
+
+# ------------------------------------------------------------------ CaiT / BoTNet additions
+def tile_param_rows(param, B):
+    """jnp.tile(cls, [b,1,1]) (cait.py:157-160): fp32 parameter [1,1,C] -> stream Var [B,1,C]."""
+    C = param.master.shape[-1]
+    m = param.master.reshape(1, C)
+    if _meta(m):
+        return Var(torch.empty((B, 1, C), dtype=F32, device="meta"))
+    out = torch.empty((B, 1, C), dtype=F32, device=m.device)
+    ops.copy2d_f32(m.expand(B, C), out.view(B, C))
+    res = Var(out)
+
+    def bwd():
+        g = res.take_grad()
+        res.g16 = None
+        if g is None:
+            return
+        param.touch_grad()
+        g16 = torch.empty((B, C), dtype=BF16, device=g.device)
+        ops.cast_bf16(g.contiguous().view(B, C), g16)
+        ops.colsum(g16, out=param.grad.reshape(C), accumulate=True)
+    record(bwd)
+    return res
+
+
+def concat_tokens(cls_tok, x):
+    """jnp.concatenate([cls_token, x], axis=1) on the fp32 stream (cait.py:97,175)."""
+    tc, tx = cls_tok.v, x.v
+    B, N, C = tx.shape
+    if _meta(tx):
+        return Var(torch.empty((B, N + 1, C), dtype=F32, device="meta"))
+    if tc.dtype != F32 or tx.dtype != F32:
+        raise TypeError("concat_tokens: both inputs must be fp32 residual-stream tensors")
+    out = torch.empty((B, N + 1, C), dtype=F32, device=tx.device)
+    o2 = out.view(B, (N + 1) * C)
+    ops.copy2d_f32(tc.contiguous().view(B, C), o2[:, :C])
+    ops.copy2d_f32(tx.contiguous().view(B, N * C), o2[:, C:])
+    res = Var(out)
+
+    def bwd():
+        g = res.take_grad()
+        res.g16 = None
+        if g is None:
+            return
+        g2 = g.contiguous().view(B, (N + 1) * C)
+        for var, sl, shape in ((cls_tok, g2[:, :C], (B, 1, C)), (x, g2[:, C:], (B, N, C))):
+            if not var.requires_grad:
+                continue
+            if var.g is None:
+                fresh = torch.empty(shape, dtype=F32, device=g.device)
+                ops.copy2d_f32(sl, fresh.view(B, -1))
+                var.g, var.g16 = fresh, None
+            else:
+                ops.copy2d_f32(sl, var.g.view(B, -1), accumulate=True)
+                var.g16 = None
+    record(bwd)
+    return res
+
+
+def first_token_keepdim(x):
+    """inputs[:, 0:1, :] of a bf16 activation (cait.py:13) as a strided view -- no copy."""
+    t = x.v
+    B, N, C = t.shape
+    if _meta(t):
+        return Var(torch.empty((B, 1, C), dtype=t.dtype, device="meta"))
+    if t.dtype != BF16:
+        raise NotImplementedError("first_token_keepdim on the fp32 stream: apply LayerNorm first")
+    out = Var(t[:, 0:1])
+
+    def bwd():
+        g = out.take_grad()
+        if g is None:
+            return
+        full = torch.empty((B, N, C), dtype=BF16, device=t.device)
+        ops.fill(full.view(torch.float32), 0.0)
+        ops.copy2d(g.reshape(B, C), full[:, 0])
+        _add_grad(x, full)
+    record(bwd)
+    return out
+
+
+def _mat_attention(q4, k4, v4, scale, mix, rel_tab, rel_hw, out_shape, grads_cb):
+    """Materialised-logits attention (attn_mat.cu): S = q k^T (batched GEMM) -> mix / relative
+    logits / softmax / mix rows -> O = P v (batched GEMM).  q4/k4/v4: [B,N,H,D] bf16 views."""
+    B, Nq, H, D = q4.shape
+    mix_pre = mix[0].master if mix is not None else None
+    mix_post = mix[1].master if mix is not None else None
+    rel = None
+    if rel_tab is not None:
+        # per-query relative logits q . r for all 2W-1 + 2Hh-1 offsets: one skinny GEMM
+        # (botnet.py:96-111, the einsum 'b h H W d, r d -> b h H W r' for both axes at once)
+        rel = ops.gemm(q4.reshape(B * Nq * H, D), rel_tab.w, b_mn=False, out_fp32=True)
+        rel = rel.view(B, Nq, H, rel_tab.w.shape[0])
+    o, S, P = ops.attn_mat_fwd(q4, k4, v4, scale, mix_pre, mix_post, rel, rel_hw)
+    out = Var(o.view(out_shape))
+
+    def bwd():
+        d_o = out.take_grad()
+        if d_o is None:
+            return
+        dq4, dk4, dv4 = grads_cb()
+        dmix_pre = dmix_post = None
+        if mix is not None:
+            mix[0].touch_grad()
+            mix[1].touch_grad()
+            dmix_pre, dmix_post = mix[0].grad, mix[1].grad
+        drel = ops.attn_mat_bwd(q4, k4, v4, S, P, d_o.contiguous().view(B, Nq, H, D), dq4, dk4, dv4,
+                                scale, mix_pre, mix_post, dmix_pre, dmix_post, rel, rel_hw)
+        if drel is not None:
+            R = rel_tab.w.shape[0]
+            drel16 = torch.empty((B * Nq * H, R), dtype=BF16, device=drel.device)
+            ops.cast_bf16(drel.view(-1), drel16.view(-1))
+            # d table[R, D] += drel^T q ;  dq += drel table
+            rel_tab.touch()
+            ops.gemm(drel16, q4.reshape(B * Nq * H, D), a_mn=True, b_mn=True, out=rel_tab.gw,
+                     accumulate=True, split_k=0)
+            dq_rel = ops.gemm(drel16, rel_tab.w, b_mn=True)
+            dq_flat = dq4.reshape(-1)
+            return ops.add(dq_flat, dq_rel.view(-1))   # only the contiguous-q (cross) form has rel
+        return None
+    return out, bwd
+
+
+def mat_self_attention_core(qkv, num_heads, head_ch, mix=None):
+    """attention.py:39-58 with talking heads (attention.py:44-52) or a head dim other than 64, on a
+    fused QKV activation [B,N,3*H*d]."""
+    t = qkv.v
+    B, N, _ = t.shape
+    H, D = num_heads, head_ch
+    if _meta(t):
+        return Var(torch.empty((B, N, H * D), dtype=BF16, device="meta"))
+    t5 = t.view(B, N, 3, H, D)
+    hold = {}
+
+    def grads():
+        hold["dqkv"] = torch.empty_like(t5)
+        d = hold["dqkv"]
+        return d[:, :, 0], d[:, :, 1], d[:, :, 2]
+
+    out, bwd = _mat_attention(t5[:, :, 0], t5[:, :, 1], t5[:, :, 2], 1.0 / math.sqrt(D), mix, None,
+                              None, (B, N, H * D), grads)
+
+    def bwd2():
+        bwd()
+        if "dqkv" in hold:
+            _add_grad(qkv, hold.pop("dqkv").view(B, N, 3 * H * D))
+    record(bwd2)
+    return out
+
+
+def mat_cross_attention_core(q, kv, num_heads, head_ch, mix=None, rel_tab=None, rel_hw=None):
+    """q [B,Nq,H*d]; kv fused [B,Nk,2*H*d] -> [B,Nq,H*d] through the materialised path (class
+    attention cait.py:10-15; BoTNet MHSA with 2-D relative logits botnet.py:158-199)."""
+    tq, tkv = q.v, kv.v
+    B, Nq, _ = tq.shape
+    Nk = tkv.shape[1]
+    H, D = num_heads, head_ch
+    if _meta(tq):
+        return Var(torch.empty((B, Nq, H * D), dtype=BF16, device="meta"))
+    q4 = _as2d(tq, H * D).view(B, Nq, H, D) if not tq.is_contiguous() else tq.view(B, Nq, H, D)
+    if not q4.is_contiguous():
+        q4 = q4.contiguous()
+    kv5 = tkv.contiguous().view(B, Nk, 2, H, D)
+    hold = {}
+
+    def grads():
+        hold["dq"] = torch.empty((B, Nq, H, D), dtype=BF16, device=tq.device)
+        hold["dkv"] = torch.empty_like(kv5)
+        return hold["dq"], hold["dkv"][:, :, 0], hold["dkv"][:, :, 1]
+
+    out, bwd = _mat_attention(q4, kv5[:, :, 0], kv5[:, :, 1], 1.0 / math.sqrt(D), mix, rel_tab,
+                              rel_hw, (B, Nq, H * D), grads)
+
+    def bwd2():
+        dq_total = bwd()
+        if "dq" in hold:
+            dq = hold.pop("dq")
+            if dq_total is not None:
+                dq = dq_total.view(B, Nq, H, D)
+            _add_grad(q, dq.view(B, Nq, H * D))
+            _add_grad(kv, hold.pop("dkv").view(B, Nk, 2 * H * D))
+    record(bwd2)
+    return out
+
+
+def reshape(x, shape):
+    """View a contiguous activation under another shape (e.g. 'b H W c -> b (H W) c',
+    botnet.py:175-183); the gradient is viewed back."""
+    t = x.v
+    if _meta(t):
+        return Var(torch.empty(t.shape, dtype=t.dtype, device="meta").reshape(shape))
+    old = tuple(t.shape)
+    out = Var(t.contiguous().view(shape))
+
+    def bwd():
+        g = out.take_grad()
+        if g is not None:
+            _add_grad(x, g.contiguous().view(old))
+    record(bwd)
+    return out

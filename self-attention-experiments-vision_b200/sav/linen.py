@@ -152,7 +152,7 @@ class Module:
             return p
         raise AssertionError
 
-    def fused_params(self, names, leaf, init_fn, shape):
+    def fused_params(self, names, leaf, init_fn, shape, lead=()):
         """Allocate `len(names)` same-shaped kernels [K, *rest] as one [K, n, *rest] block so they
         can be used as a single GEMM weight; each stays visible as `<name>/<leaf>`."""
         run = _run()
@@ -180,13 +180,51 @@ class Module:
         shadow = master.to(torch.bfloat16) if not master.is_meta else master.to(torch.bfloat16)
         out = []
         for i, (p, v) in enumerate(zip(paths, vals)):
-            run.builder.add_leaf(p, shape, v, base=base, stride=stride, rel_offset=i * inner)
+            run.builder.add_leaf(p, tuple(lead) + tuple(shape), v.reshape(tuple(lead) + tuple(shape)),
+                                 base=base, stride=(0,) * len(lead) + stride, rel_offset=i * inner)
             tp = _TempParam(master[:, i].view((K,) + rest) if not rest == () else master[:, i],
                             shadow[:, i].view((K,) + rest))
             run.init_params[p] = tp
             out.append(tp)
         res = (out, F.Weight(shadow.view(K, n * inner), None, out))
         run.init_params[paths[0] + ("#fused",)] = res
+        return res
+
+    def stacked_params(self, names, rows, width, init_fn, pad_to=8):
+        """Allocate several [rows_i, width] tables back to back (row count padded to `pad_to` with
+        zero rows that receive zero gradients) so that they can be ONE K-major GEMM operand
+        [sum(rows) padded, width]; each stays visible as its own leaf (botnet.py:124-132)."""
+        run = _run()
+        base_path = self._scope_path()
+        paths = [base_path + (n,) for n in names]
+        total = sum(rows)
+        padded = (total + pad_to - 1) // pad_to * pad_to
+        if run.mode == "apply":
+            ps = [run.arena.params[p] for p in paths]
+            a, off = run.arena, ps[0].offset
+            w2 = torch.as_strided(a.shadow, (padded, width), (width, 1), off)
+            g2 = torch.as_strided(a.grad, (padded, width), (width, 1), off)
+            m2 = torch.as_strided(a.master, (padded, width), (width, 1), off)
+            return ps, F.Weight(w2, g2, ps, wm=m2)
+        key = paths[0] + ("#stacked",)
+        if key in run.init_params:
+            return run.init_params[key]
+        gen = self._gen("params")
+        vals = [init_fn(gen, (r, width)) for r in rows]
+        block = torch.zeros((padded, width))
+        block[:total] = torch.cat(vals, dim=0)
+        base = run.builder.alloc(padded * width)
+        master = self._to_dev(block, run)
+        shadow = master.to(torch.bfloat16)
+        out, r0 = [], 0
+        for p, v, r in zip(paths, vals, rows):
+            run.builder.add_leaf(p, (r, width), v, base=base, stride=(width, 1), rel_offset=r0 * width)
+            tp = _TempParam(master[r0:r0 + r], shadow[r0:r0 + r])
+            run.init_params[p] = tp
+            out.append(tp)
+            r0 += r
+        res = (out, F.Weight(shadow, None, out, wm=master))
+        run.init_params[key] = res
         return res
 
     def _to_dev(self, val, run):
@@ -298,7 +336,7 @@ class Dense(Module):
         kernel = self.param("kernel", self.kernel_init or initializers.lecun_normal(), (K, self.features))
         bias = self.param("bias", self.bias_init or initializers.zeros, (self.features,)) \
             if self.use_bias else None
-        return F.linear(inputs, F.Weight(kernel.shadow, kernel.grad, [kernel]), bias)
+        return F.linear(inputs, F.Weight(kernel.shadow, kernel.grad, [kernel], wm=kernel.master), bias)
 
 
 class LayerNorm(Module):

@@ -243,3 +243,110 @@ def copy2d(src, dst):
     rows, cols = src.shape
     assert dst.shape == src.shape and src.stride(1) == 1 and dst.stride(1) == 1
     check(lib().sav_copy2d_bf16(_p(src), src.stride(0), _p(dst), dst.stride(0), rows, cols, _stream()))
+
+
+# ------------------------------------------------------------------ materialised-logits attention
+def bgemm(A, B, D, M, N, K, a_mn=False, b_mn=False):
+    """Batched GEMM over 4-D views [outer, inner, rows, cols] (cols contiguous; any other strides).
+    A: rows = M (or K if a_mn), B: rows = N (or K if b_mn), D: [outer, inner, M, N] bf16 or fp32."""
+    from ._abi import BGemmArgs
+    for t in (A, B, D):
+        assert t.dim() == 4 and t.stride(3) == 1
+    a = BGemmArgs()
+    a.A, a.B, a.D = A.data_ptr(), B.data_ptr(), D.data_ptr()
+    a.M, a.N, a.K = M, N, K
+    a.batch_outer, a.batch_inner = A.shape[0], A.shape[1]
+    a.a_stride_outer, a.a_stride_inner, a.lda = A.stride(0), A.stride(1), A.stride(2)
+    a.b_stride_outer, a.b_stride_inner, a.ldb = B.stride(0), B.stride(1), B.stride(2)
+    a.d_stride_outer, a.d_stride_inner, a.ldd = D.stride(0), D.stride(1), D.stride(2)
+    a.a_mn, a.b_mn, a.d_fp32 = int(a_mn), int(b_mn), int(D.dtype == F32)
+    check(lib().sav_bgemm(C.byref(a), _stream()))
+    return D
+
+
+def _thsoftmax_args(S, Nk, scale, mix_pre, mix_post, rel, rel_hw):
+    from ._abi import ThSoftmaxArgs
+    B, H, Nq, ld = S.shape
+    a = ThSoftmaxArgs()
+    a.S = S.data_ptr()
+    a.B, a.H, a.Nq, a.Nk, a.ld = B, H, Nq, Nk, ld
+    a.scale = scale
+    if mix_pre is not None:
+        a.mix_pre, a.mix_post = mix_pre.data_ptr(), mix_post.data_ptr()
+    if rel is not None:
+        assert rel.is_contiguous() and rel.dtype == F32 and rel.dim() == 4
+        a.rel, a.ldr = rel.data_ptr(), rel.shape[3]
+        a.rel_h, a.rel_w = rel_hw
+    return a
+
+
+def attn_mat_fwd(q, k, v, scale, mix_pre=None, mix_post=None, rel=None, rel_hw=None):
+    """q [B,Nq,H,D], k/v [B,Nk,H,D] bf16 views -> (o [B,Nq,H,D], S fp32 [B,H,Nq,ld], P bf16).
+    Any D % 8 == 0; optional talking-heads transforms [H,H] fp32 and relative logits
+    rel fp32 [B,Nq,H,ldr] on an rel_hw = (Hh, W) key grid."""
+    B, Nq, H, D = q.shape
+    Nk = k.shape[1]
+    ld = (Nk + 7) // 8 * 8
+    S = torch.empty((B, H, Nq, ld), dtype=F32, device=q.device)
+    P = torch.empty((B, H, Nq, ld), dtype=BF16, device=q.device)
+    qv, kv, vv = q.permute(0, 2, 1, 3), k.permute(0, 2, 1, 3), v.permute(0, 2, 1, 3)
+    bgemm(qv, kv, S[..., :Nk], Nq, Nk, D)
+    a = _thsoftmax_args(S, Nk, scale, mix_pre, mix_post, rel, rel_hw)
+    a.P = P.data_ptr()
+    check(lib().sav_thsoftmax_fwd(C.byref(a), _stream()))
+    o = torch.empty((B, Nq, H, D), dtype=BF16, device=q.device)
+    bgemm(P[..., :Nk], vv, o.permute(0, 2, 1, 3), Nq, D, Nk, b_mn=True)
+    return o, S, P
+
+
+def attn_mat_bwd(q, k, v, S, P, d_o, dq, dk, dv, scale, mix_pre=None, mix_post=None,
+                 dmix_pre=None, dmix_post=None, rel=None, rel_hw=None):
+    """Reverse mode of attn_mat_fwd; writes dq/dk/dv (views like q/k/v), accumulates dmix_*,
+    returns drel (fp32, like rel) or None."""
+    B, Nq, H, D = q.shape
+    Nk = k.shape[1]
+    ld = S.shape[3]
+    qv, kv, vv = q.permute(0, 2, 1, 3), k.permute(0, 2, 1, 3), v.permute(0, 2, 1, 3)
+    dov = d_o.permute(0, 2, 1, 3)
+    Pv = P[..., :Nk]
+    bgemm(Pv, dov, dv.permute(0, 2, 1, 3), Nk, D, Nq, a_mn=True, b_mn=True)       # dV = P^T dO
+    dP = torch.empty((B, H, Nq, ld), dtype=F32, device=q.device)
+    bgemm(dov, vv, dP[..., :Nk], Nq, Nk, D)                                        # dP = dO V^T
+    dS = torch.empty((B, H, Nq, ld), dtype=BF16, device=q.device)
+    a = _thsoftmax_args(S, Nk, scale, mix_pre, mix_post, rel, rel_hw)
+    a.dP, a.dS = dP.data_ptr(), dS.data_ptr()
+    drel = None
+    if mix_pre is not None:
+        a.dmix_pre, a.dmix_post = dmix_pre.data_ptr(), dmix_post.data_ptr()
+    if rel is not None:
+        drel = torch.empty_like(rel)
+        a.drel = drel.data_ptr()
+    check(lib().sav_thsoftmax_bwd(C.byref(a), _stream()))
+    dSv = dS[..., :Nk]
+    bgemm(dSv, kv, dq.permute(0, 2, 1, 3), Nq, D, Nk, b_mn=True)                  # dQ = dS K
+    bgemm(dSv, qv, dk.permute(0, 2, 1, 3), Nk, D, Nq, a_mn=True, b_mn=True)       # dK = dS^T Q
+    return drel
+
+
+def scale_rows_cols(g, col_scale, row_scale, rows_per_scale, out=None):
+    """bf16(g * col_scale[n] * row_scale[m // rows_per_scale]) for fp32 g [rows, cols]."""
+    _req(g, F32, "g")
+    rows, cols = g.shape
+    if out is None:
+        out = torch.empty((rows, cols), dtype=BF16, device=g.device)
+    check(lib().sav_scale_rows_cols(_p(g), g.stride(0), _p(col_scale), _p(row_scale),
+                                    rows_per_scale, _p(out), out.stride(0), rows, cols, _stream()))
+    return out
+
+
+def layerscale_grad(W, dW, bias, dbias, col_scale, dcol_scale):
+    K, N = W.shape
+    check(lib().sav_layerscale_grad(_p(W), W.stride(0), _p(dW), dW.stride(0), K, N, _p(bias),
+                                    _p(dbias), _p(col_scale), _p(dcol_scale), _stream()))
+
+
+def copy2d_f32(src, dst, accumulate=False):
+    rows, cols = src.shape
+    assert dst.shape == src.shape and src.stride(1) == 1 and dst.stride(1) == 1
+    check(lib().sav_copy2d_f32(_p(src), src.stride(0), _p(dst), dst.stride(0), rows, cols,
+                               int(accumulate), _stream()))

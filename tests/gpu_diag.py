@@ -250,12 +250,17 @@ TIMING = {
     "t_fc2_dw": dict(M=1536, N=384, K=50432, mode="dw", a_mn=True),
     "t_qkv_dw": dict(M=384, N=1152, K=50432, mode="dw", a_mn=True),
     "t_out_dw": dict(M=384, N=384, K=50432, mode="dw", a_mn=True),
+    "t_sq_kk": dict(M=8192, N=8192, K=8192, mode="plain", b_mn=False),
+    "t_sq_km": dict(M=8192, N=8192, K=8192, mode="plain", b_mn=True),
 }
 
 
 def main():
     if "--time" in sys.argv:
+        only = os.environ.get("SAV_TIME_ONLY", "")
         for name, kw in TIMING.items():
+            if only and not any(o in name for o in only.split(",")):
+                continue
             try:
                 r = subprocess.run([sys.executable, __file__, "--timecase", name], capture_output=True,
                                    text=True, timeout=120)
