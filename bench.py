@@ -106,11 +106,11 @@ def run_reference(args):
     from oracle import vit_oracle as O
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
-    sample = 8
+    sample = 64
     cfg = O.vit_config(MODEL)
     params = O.synthetic_vit_params(cfg, 224, seed=42)
     images, labels = O.synthetic_batch(sample, 224, seed=0)
-    steps = max(1, min(args.steps, 5))
+    steps = max(1, min(args.steps, 8))
     warm = max(1, min(args.warmup, 1))
     for _ in range(warm):
         O.vit_loss_and_grads(params, images, labels, cfg, 0.1)
@@ -233,8 +233,9 @@ def main():
 
     for _ in range(W):
         loss = step()
-    with ClockSampler(local) as clk:
-        total_ms = timed(step, K)
+    clk = ClockSampler(local)
+    clk.__enter__()
+    total_ms = timed(step, K)
     loss_val = loss.item()
     value = B * world * K / (total_ms * 1e-3)
 
@@ -247,6 +248,7 @@ def main():
     for _ in range(2):
         e2e_step()
     e2e_ms = timed(e2e_step, K)
+    clk.__exit__()   # clocks / throttle reasons sampled across both timed regions
     e2e_value = B * world * K / (e2e_ms * 1e-3)
 
     pk = peaks()
@@ -269,17 +271,29 @@ def main():
         fl = 3 * 9.198e9 * B  # train FLOP/img = 3 x fwd
         out["step_tflops"] = fl / (total_ms / K * 1e-3) / 1e12
         out["step_frac_of_sustained_peak"] = out["step_tflops"] / pk["tf_sust"]
-        tf, ms = time_isolated_gemm(torch, ops, B * 197, cfg["embed_dim"], 4 * cfg["embed_dim"])
-        out["roofline"] = {"bound": "tensor", "kernel": "gemm_kernel<256> FC1 bias+GELU epilogue",
-                           "achieved": tf, "peak": pk["tf_burst"], "unit": "TFLOP/s",
-                           "frac": tf / pk["tf_burst"], "traffic": None, "ms": ms,
-                           "peak_source": pk["src"] + " (burst: kernel timed alone)"}
+        # dominant kernel = the FC1 GEMM (bias + GELU epilogue, saves the pre-activation): the most
+        # expensive single launch of the step.  K = 384 puts it past the ridge on the memory side:
+        # algorithmic bytes = X + W + bias in, pre-activation + activation out
+        # => 53 us at HBM peak vs 36 us at tensor peak, so the HBM roofline is the binding one.
+        M_, C_, H_ = B * 197, cfg["embed_dim"], 4 * cfg["embed_dim"]
+        tf, ms = time_isolated_gemm(torch, ops, M_, C_, H_)
+        alg_bytes = M_ * C_ * 2 + C_ * H_ * 2 + H_ * 4 + 2 * M_ * H_ * 2
+        gbs = alg_bytes / (ms * 1e-3) / 1e9
+        out["roofline"] = {"bound": "hbm", "kernel": "gemm_kernel<256,K,MN> FC1 bias+GELU epilogue (2 outputs)",
+                           "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s",
+                           "frac": gbs / pk["hbm"],
+                           # dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set
+                           # full capture profiles/r01c_ncu_full_fc1_fwd.txt (same shape)
+                           "traffic": 289.67e6, "algorithmic_bytes": alg_bytes, "ms": ms,
+                           "tensor_tflops": tf, "tensor_frac_of_burst_peak": tf / pk["tf_burst"],
+                           "peak_source": pk["src"] + " (copy bandwidth; kernel timed alone)"}
         if world == 1 and not args.no_cpu_baseline:
-            v, threads, dt = cpu_oracle_throughput(batch=8, reps=1)
+            v, threads, dt = cpu_oracle_throughput(batch=64, reps=5)
             out["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": threads, "kind": "port",
-                                   "sample": f"fwd+bwd of 8 images, DeiT-S/16 224^2, fp32 torch-CPU "
-                                             f"oracle, {dt:.1f} s; reference JAX CPU path not "
-                                             f"installable in this image"}
+                                   "sample": f"fwd+bwd of 64 images (of the 256-image step), best of 5 "
+                                             f"after 1 warm-up, DeiT-S/16 224^2, fp32 torch-CPU "
+                                             f"oracle, {dt:.1f} s per pass; reference JAX CPU path "
+                                             f"not installable in this image"}
         print(json.dumps(out), flush=True)
     if world > 1:
         # the captured step holds NCCL kernels; tearing the communicator down under a live CUDA graph

@@ -92,7 +92,7 @@ def cait_config(name):
 def _orthogonal(g, n, dtype):
     a = torch.randn((n, n), generator=g, dtype=torch.float64)
     q, r = torch.linalg.qr(a)
-    return (q * torch.sign(torch.diagonal(r))).to(dtype)
+    return (q * torch.sign(torch.diagonal(r))).to(dtype).contiguous()
 
 
 def synthetic_cait_params(cfg, img_size=224, seed=42, layerscale=None, dtype=torch.float32):
@@ -123,7 +123,7 @@ def synthetic_cait_params(cfg, img_size=224, seed=42, layerscale=None, dtype=tor
         if talking:
             for j in range(2):
                 p[f"TalkingHeadsBlock_{j}"] = {
-                    "talking_heads_transform": _orthogonal(g, H, dtype) + normal((H, H), 0.1)}
+                    "talking_heads_transform": (_orthogonal(g, H, dtype) + normal((H, H), 0.1)).contiguous()}
         return p
 
     def lscale():

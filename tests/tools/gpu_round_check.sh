@@ -1,13 +1,14 @@
+# One gpurun call: parity tests, bench (+ reference arm), launch list, variant timings, ncu captures.
 set -x
+T=${TAG:-r01d}
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/r01c_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r01c_pytest.log
-python tests/gpu_diag.py --time > gpurun_out/r01c_time.log 2>&1
-python bench.py --steps 10 --warmup 3 > gpurun_out/r01c_bench.json 2> gpurun_out/r01c_bench.err
-python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r01c_ref.json 2> gpurun_out/r01c_ref.err
+python -m pytest tests -m gpu -q --timeout 600 > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${T}_pytest.log
+python bench.py --steps 20 --warmup 5 > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err
+python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${T}_ref.json 2> gpurun_out/${T}_ref.err
+timeout 600 python tests/tools/variant_time.py > gpurun_out/${T}_variants.log 2>&1
+timeout 300 python tests/gpu_diag.py --time > gpurun_out/${T}_time.log 2>&1
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1400 --csv --log-file gpurun_out/${T}_launches_bench_nograph.csv python bench.py --steps 2 --warmup 1 --no-graph --no-cpu-baseline > gpurun_out/${T}_ncu_list.log 2>&1
 NCU="ncu --set full --clock-control none --import-source on"
-timeout 300 $NCU -k regex:gemm_kernel --launch-skip 3 -c 1 -f -o gpurun_out/r01c_fc1_fwd python tests/gpu_diag.py --timecase t_fc1_fwd > gpurun_out/ncu1.log 2>&1
-timeout 300 $NCU -k regex:attn_fwd --launch-skip 3 -c 1 -f -o gpurun_out/r01c_attn_fwd python tests/gpu_diag.py --timecase t_attn_fwd > gpurun_out/ncu2.log 2>&1
-timeout 300 $NCU -k regex:attn_bwd2 --launch-skip 3 -c 1 -f -o gpurun_out/r01c_attn_bwd python tests/gpu_diag.py --timecase t_attn_bwd > gpurun_out/ncu3.log 2>&1
-timeout 300 $NCU -k regex:gemm_kernel --launch-skip 3 -c 1 -f -o gpurun_out/r01c_fc2_fwd python tests/gpu_diag.py --timecase t_fc2_fwd > gpurun_out/ncu4.log 2>&1
-timeout 300 $NCU -k regex:gemm_kernel --launch-skip 3 -c 1 -f -o gpurun_out/r01c_fc1_dw python tests/gpu_diag.py --timecase t_fc1_dw > gpurun_out/ncu5.log 2>&1
-ls -la gpurun_out
+timeout 300 $NCU -k regex:thsoftmax_bwd --launch-skip 2 -c 1 -f -o gpurun_out/${T}_thsoftmax_bwd python tests/tools/variant_time.py cait > gpurun_out/ncu6.log 2>&1
+timeout 300 $NCU -k regex:ln_bwd --launch-skip 30 -c 1 -f -o gpurun_out/${T}_ln_bwd python bench.py --steps 1 --warmup 1 --no-graph --no-cpu-baseline > gpurun_out/ncu7.log 2>&1
+ls -la gpurun_out | tail -30
