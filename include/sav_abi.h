@@ -222,6 +222,33 @@ typedef struct {
 int sav_thsoftmax_fwd(const sav_thsoftmax_args* a, void* stream);
 int sav_thsoftmax_bwd(const sav_thsoftmax_args* a, void* stream);
 
+/* ---------------------------------------------------------------- CvT convolutional projection
+ * cvt_attention.py:12-40: depthwise 3x3 conv (stride 1|2, padding SAME, no bias) -> BatchNorm
+ * (batch statistics) -> 1x1 conv (a sav_gemm).  Channel-last tensors, C % 4 == 0.
+ *   x fp32 [B,H,W,C] (the fp32 residual stream -- CvT feeds the attention without a LayerNorm,
+ *   cvt.py:50-61); w fp32 [3,3,C] (flax depthwise kernel [3,3,1,C]); y bf16 [B,Ho,Wo,C] with
+ *   Ho = ceil(H/stride) (sav_dwconv3x3_out_hw).  sum / sumsq fp32 [C] receive the per-channel sum
+ *   and sum of squares of the conv output (zeroed by the callee) = the BatchNorm statistics. */
+int sav_dwconv3x3_out_hw(int64_t H, int64_t W, int32_t stride, int64_t* Ho, int64_t* Wo);
+int sav_dwconv3x3_fwd(const float* x, const float* w, void* y, float* sum, float* sumsq, int64_t B,
+                      int64_t H, int64_t W, int64_t C, int32_t stride, void* stream);
+/* dx fp32 [B,H,W,C] (+= if accumulate_dx: q, k and v projections read the same input);
+ * dw fp32 [3,3,C] ACCUMULATED. */
+int sav_dwconv3x3_bwd(const float* x, const float* w, const void* dy, float* dx, float* dw, int64_t B,
+                      int64_t H, int64_t W, int64_t C, int32_t stride, int32_t accumulate_dx,
+                      void* stream);
+/* flax nn.BatchNorm in training mode over rows = B*Ho*Wo: mean = sum/rows, var = sumsq/rows -
+ * mean^2 (biased), z = (y - mean) rsqrt(var + eps) gamma + beta; writes mean, rstd (saved for
+ * backward) and var (NULL to skip; for the caller's running averages).  y, z bf16 [rows, C]. */
+int sav_batchnorm_fwd(const void* y, const float* sum, const float* sumsq, const float* gamma,
+                      const float* beta, float eps, void* z, float* mean, float* rstd, float* var,
+                      int64_t rows, int64_t C, void* stream);
+/* dy = gamma rstd (dz - mean_rows(dz) - yhat mean_rows(dz yhat)); dgamma, dbeta ACCUMULATED;
+ * scratch fp32 [2C]. */
+int sav_batchnorm_bwd(const void* dz, const void* y, const float* mean, const float* rstd,
+                      const float* gamma, float* dgamma, float* dbeta, float* scratch, void* dy,
+                      int64_t rows, int64_t C, void* stream);
+
 /* ---------------------------------------------------------------- loss head (train.py:83-91)
  * one_hot -> smooth_labels(alpha) -> softmax_cross_entropy -> mean; writes dlogits = dloss/dlogits
  * (bf16 [B,classes]) and accumulates loss into loss_out[0] (zeroed by the callee), top1 count into

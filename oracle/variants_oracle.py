@@ -254,3 +254,76 @@ def synthetic_bot_params(C, num_heads, head_ch, H, W, seed=42, dtype=torch.float
         "RelativeLogits_0": {"rel_pos_emb_w": normal((2 * W - 1, head_ch), head_ch ** -0.5),
                              "rel_pos_emb_h": normal((2 * H - 1, head_ch), head_ch ** -0.5)},
     }
+
+
+# ----------------------------------------------------------------------------- CvT
+def same_pad_amounts(n, stride, k=3):
+    """jax / flax padding='SAME': out = ceil(n / stride); total = max((out-1)*stride + k - n, 0);
+    low = total // 2, high = total - low."""
+    out = -(-n // stride)
+    total = max((out - 1) * stride + k - n, 0)
+    return total // 2, total - total // 2
+
+
+def conv_projection(x, p, stride, eps=1e-5):
+    """ConvProjectionBlock.__call__ (cvt_attention.py:21-40), training mode: depthwise 3x3 nn.Conv
+    (feature_group_count = C, padding SAME, no bias; kernel [3,3,1,C]) -> nn.BatchNorm on batch
+    statistics (biased variance over B,H,W; epsilon 1e-5) -> 1x1 nn.Conv without bias
+    (kernel [1,1,C,out]).  x [B,H,W,C]."""
+    B, H, W, C = x.shape
+    pt, pb = same_pad_amounts(H, stride)
+    pl, pr = same_pad_amounts(W, stride)
+    xi = torch.nn.functional.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb))
+    wk = p["Conv_0"]["kernel"].permute(3, 2, 0, 1)                               # [C,1,3,3]
+    y = torch.nn.functional.conv2d(xi, wk, stride=stride, groups=C).permute(0, 2, 3, 1)
+    mean = y.mean(dim=(0, 1, 2))
+    var = (y * y).mean(dim=(0, 1, 2)) - mean * mean                              # flax: E[x^2]-E[x]^2
+    z = (y - mean) * torch.rsqrt(var + eps) * p["BatchNorm_0"]["scale"] + p["BatchNorm_0"]["bias"]
+    return z @ p["Conv_1"]["kernel"].reshape(C, -1)                              # 1x1 conv
+
+
+def cvt_attention(x, p, num_heads, strides=(1, 2, 2)):
+    """CvTAttentionBlock.__call__ (cvt_attention.py:58-113) with inputs_q = inputs_kv = x
+    [B,H,W,C] (CvTSelfAttentionBlock, :116-120)."""
+    B = x.shape[0]
+    q, k, v = (conv_projection(x, p[f"ConvProjectionBlock_{i}"], s) for i, s in enumerate(strides))
+    hd = q.shape[-1]
+    d = hd // num_heads
+    q, k, v = (t.reshape(B, -1, num_heads, d) for t in (q, k, v))                # :81-83
+    q = q / math.sqrt(d)                                                         # :85
+    w = softmax_last(torch.einsum("bqhd,bkhd->bhqk", q, k))                      # :87-94
+    o = torch.einsum("bhqk,bkhd->bqhd", w, v)                                    # :103-104
+    return torch.einsum("bqhd,hdc->bqc", o, p["DenseGeneral_0"]["kernel"])       # :106-109
+
+
+def cvt_stage_block(tokens, p, num_heads):
+    """StageBlock.__call__ (cvt.py:50-68) incl. zero_pad_and_reshape (cvt.py:10-16)."""
+    B, L, C = tokens.shape
+    S = int(math.ceil(math.sqrt(L)))
+    padded = torch.cat([tokens, tokens.new_zeros(B, S * S - L, C)], dim=1)       # cvt.py:14
+    grid = padded.reshape(B, S, S, C)                                            # cvt.py:15
+    x = cvt_attention(grid, p["CvTSelfAttentionBlock_0"], num_heads) + padded    # cvt.py:53-61
+    y = layer_norm(x, p["LayerNorm_0"]["scale"], p["LayerNorm_0"]["bias"])       # cvt.py:63
+    return x + ff_block(y, p["FFBlock_0"])                                       # cvt.py:64-67
+
+
+def synthetic_cvt_stage_params(C, num_heads, seed=42, dtype=torch.float32):
+    g = torch.Generator().manual_seed(seed)
+
+    def normal(shape, std):
+        return (torch.randn(shape, generator=g, dtype=torch.float64) * std).to(dtype)
+    d = C // num_heads
+    hid = 4 * C
+
+    def proj():
+        return {"Conv_0": {"kernel": normal((3, 3, 1, C), 1.0 / 3.0)},
+                "BatchNorm_0": {"scale": 1.0 + normal((C,), 0.1), "bias": normal((C,), 0.1)},
+                "Conv_1": {"kernel": normal((1, 1, C, C), 1.0 / math.sqrt(C))}}
+    return {
+        "CvTSelfAttentionBlock_0": {"ConvProjectionBlock_0": proj(), "ConvProjectionBlock_1": proj(),
+                                    "ConvProjectionBlock_2": proj(),
+                                    "DenseGeneral_0": {"kernel": normal((num_heads, d, C), 1.0 / math.sqrt(C))}},
+        "LayerNorm_0": {"scale": 1.0 + normal((C,), 0.02), "bias": normal((C,), 0.02)},
+        "FFBlock_0": {"Dense_0": {"kernel": normal((C, hid), 1.0 / math.sqrt(C)), "bias": normal((hid,), 0.02)},
+                      "Dense_1": {"kernel": normal((hid, C), 1.0 / math.sqrt(hid)), "bias": normal((C,), 0.02)}},
+    }

@@ -1,4 +1,5 @@
 from models.layers.attentions import AttentionBlock, SelfAttentionBlock, TalkingHeadsBlock  # noqa: F401
+from models.layers.attentions import CvTAttentionBlock, CvTSelfAttentionBlock  # noqa: F401
 from models.layers.feedforwards import FFBlock  # noqa: F401
 from models.layers.normalizations import LayerScaleBlock  # noqa: F401
 from models.layers.position_embed import AddAbsPosEmbed  # noqa: F401

@@ -99,6 +99,11 @@ SIGNATURES = {
     "sav_scale_rows_cols": (C.c_int, [_P, _I64, _P, _P, _I64, _P, _I64, _I64, _I64, _P]),
     "sav_layerscale_grad": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P]),
     "sav_copy2d_f32": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, _I32, _P]),
+    "sav_dwconv3x3_out_hw": (C.c_int, [_I64, _I64, _I32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "sav_dwconv3x3_fwd": (C.c_int, [_P, _P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _P]),
+    "sav_dwconv3x3_bwd": (C.c_int, [_P, _P, _P, _P, _P, _I64, _I64, _I64, _I64, _I32, _I32, _P]),
+    "sav_batchnorm_fwd": (C.c_int, [_P, _P, _P, _P, _P, _F, _P, _P, _P, _P, _I64, _I64, _P]),
+    "sav_batchnorm_bwd": (C.c_int, [_P] * 9 + [_I64, _I64, _P]),
     "sav_colsum_bf16": (C.c_int, [_P, _I64, _I64, _I64, _P, _I32, _P]),
     "sav_layernorm_fwd": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _P, _P, _I64, _I64, _F, _P]),
     "sav_layernorm_bwd": (C.c_int, [_P, _I64, _P, _I64] + [_P] * 8 + [_I64, _I64, _P]),

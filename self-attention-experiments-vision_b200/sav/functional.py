@@ -675,3 +675,112 @@ def reshape(x, shape):
             _add_grad(x, g.contiguous().view(old))
     record(bwd)
     return out
+
+
+# ------------------------------------------------------------------ CvT additions
+def dwconv_bn(x, w, gamma, beta, stride, eps):
+    """Depthwise 3x3 conv (SAME, no bias) + BatchNorm with batch statistics on the fp32 stream
+    [B,H,W,C] -> bf16 [B,Ho,Wo,C] (cvt_attention.py:25-36)."""
+    t = x.v
+    B, H, W, C = t.shape
+    if _meta(t):
+        ho, wo = -(-H // stride), -(-W // stride)
+        return Var(torch.empty((B, ho, wo, C), dtype=BF16, device="meta"))
+    if t.dtype != F32:
+        raise TypeError("dwconv_bn: input must be the fp32 residual stream")
+    tc = t.contiguous()
+    w9 = w.master.reshape(9, C)
+    y, stats = ops.dwconv3x3_fwd(tc, w9, stride)
+    z, mrv = ops.batchnorm_fwd(y, stats, gamma.master, beta.master, eps)
+    out = Var(z)
+
+    def bwd():
+        dz = out.take_grad()
+        if dz is None:
+            return
+        for p in (w, gamma, beta):
+            p.touch_grad()
+        dy = ops.batchnorm_bwd(dz.contiguous(), y, mrv, gamma.master, gamma.grad, beta.grad)
+        if x.requires_grad:
+            fresh = x.g is None
+            if fresh:
+                x.g = torch.empty_like(tc)
+            dx = x.g if x.g.is_contiguous() else None
+            if dx is None:
+                raise NotImplementedError("dwconv backward into a strided stream gradient")
+            ops.dwconv3x3_bwd(tc, w9, dy, dx, w.grad.reshape(9, C), stride, not fresh)
+            x.g16 = None
+        else:
+            scratch = torch.empty_like(tc)
+            ops.dwconv3x3_bwd(tc, w9, dy, scratch, w.grad.reshape(9, C), stride, False)
+    record(bwd)
+    return out
+
+
+def attention3(q, k, v, num_heads, head_ch):
+    """attention.py:39-58 / cvt_attention.py:85-104 on three separate projections q [B,Nq,H*d],
+    k, v [B,Nk,H*d] (Nq != Nk when the key / value projections are strided)."""
+    tq, tk, tv = q.v, k.v, v.v
+    B, Nq, _ = tq.shape
+    Nk = tk.shape[1]
+    H, D = num_heads, head_ch
+    if _meta(tq):
+        return Var(torch.empty((B, Nq, H * D), dtype=BF16, device="meta"))
+    q4, k4, v4 = (t.contiguous().view(B, -1, H, D) for t in (tq, tk, tv))
+    scale = 1.0 / math.sqrt(D)
+    fused = D == 64
+    if fused:
+        o, lse = ops.attn_fwd(q4, k4, v4, scale)
+        out = Var(o[0].view(B, Nq, H * D))
+    else:
+        o, S, P = ops.attn_mat_fwd(q4, k4, v4, scale)
+        out = Var(o.view(B, Nq, H * D))
+
+    def bwd():
+        d_o = out.take_grad()
+        if d_o is None:
+            return
+        dq, dk, dv = torch.empty_like(q4), torch.empty_like(k4), torch.empty_like(v4)
+        d4 = d_o.contiguous().view(B, Nq, H, D)
+        if fused:
+            ops.attn_bwd(q4, k4, v4, o, d4, lse, dq, dk, dv, scale)
+        else:
+            ops.attn_mat_bwd(q4, k4, v4, S, P, d4, dq, dk, dv, scale)
+        _add_grad(q, dq.view(B, Nq, H * D))
+        _add_grad(k, dk.view(B, Nk, H * D))
+        _add_grad(v, dv.view(B, Nk, H * D))
+    record(bwd)
+    return out
+
+
+def pad_tokens_to_square(x):
+    """cvt.py:10-16 zero_pad_and_reshape on the fp32 stream: [B,L,C] -> ([B,S*S,C], S) with
+    S = ceil(sqrt(L)), zero tokens appended."""
+    t = x.v
+    B, L, C = t.shape
+    S = int(math.ceil(math.sqrt(L)))
+    if S * S == L:
+        return x, S
+    if _meta(t):
+        return Var(torch.empty((B, S * S, C), dtype=t.dtype, device="meta")), S
+    if t.dtype != F32:
+        raise TypeError("pad_tokens_to_square: fp32 residual stream expected")
+    out = torch.empty((B, S * S, C), dtype=F32, device=t.device)
+    ops.fill(out, 0.0)
+    ops.copy2d_f32(t.contiguous().view(B, L * C), out.view(B, S * S * C)[:, :L * C])
+    res = Var(out)
+
+    def bwd():
+        g = res.take_grad()
+        res.g16 = None
+        if g is None or not x.requires_grad:
+            return
+        sl = g.contiguous().view(B, S * S * C)[:, :L * C]
+        if x.g is None:
+            x.g = torch.empty((B, L, C), dtype=F32, device=g.device)
+            ops.copy2d_f32(sl, x.g.view(B, L * C))
+        else:
+            ops.copy2d_f32(sl, x.g.view(B, L * C), accumulate=True)
+        x.g16 = None
+    record(bwd)
+    return res, S

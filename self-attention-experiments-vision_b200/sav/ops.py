@@ -350,3 +350,49 @@ def copy2d_f32(src, dst, accumulate=False):
     assert dst.shape == src.shape and src.stride(1) == 1 and dst.stride(1) == 1
     check(lib().sav_copy2d_f32(_p(src), src.stride(0), _p(dst), dst.stride(0), rows, cols,
                                int(accumulate), _stream()))
+
+
+# ------------------------------------------------------------------ CvT convolutional projection
+def dwconv_out_hw(H, W, stride):
+    ho, wo = C.c_int64(0), C.c_int64(0)
+    check(lib().sav_dwconv3x3_out_hw(H, W, stride, C.byref(ho), C.byref(wo)))
+    return int(ho.value), int(wo.value)
+
+
+def dwconv3x3_fwd(x, w, stride):
+    """x fp32 [B,H,W,C], w fp32 [3,3,C] -> (y bf16 [B,Ho,Wo,C], sum [C], sumsq [C])."""
+    _req(x, F32, "x")
+    B, H, W, Cc = x.shape
+    Ho, Wo = dwconv_out_hw(H, W, stride)
+    y = torch.empty((B, Ho, Wo, Cc), dtype=BF16, device=x.device)
+    stats = torch.empty((2, Cc), dtype=F32, device=x.device)
+    check(lib().sav_dwconv3x3_fwd(_p(x), _p(w), _p(y), _p(stats[0]), _p(stats[1]), B, H, W, Cc, stride,
+                                  _stream()))
+    return y, stats
+
+
+def dwconv3x3_bwd(x, w, dy, dx, dw, stride, accumulate_dx):
+    B, H, W, Cc = x.shape
+    check(lib().sav_dwconv3x3_bwd(_p(x), _p(w), _p(dy), _p(dx), _p(dw), B, H, W, Cc, stride,
+                                  int(accumulate_dx), _stream()))
+
+
+def batchnorm_fwd(y, stats, gamma, beta, eps):
+    """y bf16 [..., C] + (sum, sumsq) -> (z bf16, mean, rstd, var)."""
+    Cc = y.shape[-1]
+    rows = y.numel() // Cc
+    z = torch.empty_like(y)
+    mrv = torch.empty((3, Cc), dtype=F32, device=y.device)
+    check(lib().sav_batchnorm_fwd(_p(y), _p(stats[0]), _p(stats[1]), _p(gamma), _p(beta), eps, _p(z),
+                                  _p(mrv[0]), _p(mrv[1]), _p(mrv[2]), rows, Cc, _stream()))
+    return z, mrv
+
+
+def batchnorm_bwd(dz, y, mrv, gamma, dgamma, dbeta):
+    Cc = y.shape[-1]
+    rows = y.numel() // Cc
+    dy = torch.empty_like(y)
+    scratch = torch.empty(2 * Cc, dtype=F32, device=y.device)
+    check(lib().sav_batchnorm_bwd(_p(dz), _p(y), _p(mrv[0]), _p(mrv[1]), _p(gamma), _p(dgamma),
+                                  _p(dbeta), _p(scratch), _p(dy), rows, Cc, _stream()))
+    return dy

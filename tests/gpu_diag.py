@@ -196,6 +196,42 @@ CASES["gemm_accum"] = (case_gemm, dict(a_mn=True, b_mn=True, N=384, epi="accum",
 CASES["gemm_fp32"] = (case_gemm, dict(a_mn=True, b_mn=True, N=384, epi="fp32", M=192, K=3000))
 CASES["gemm_splitk"] = (case_gemm, dict(a_mn=True, b_mn=True, N=384, epi="fp32", M=192, K=3000, split_k=5))
 CASES["gemm_big"] = (case_gemm, dict(a_mn=False, b_mn=True, N=1152, M=4000, K=384))
+CASES["gemm_pair_oob"] = (case_gemm, dict(a_mn=False, b_mn=True, N=192, M=1568, K=192))
+CASES["gemm_pair_oob2"] = (case_gemm, dict(a_mn=False, b_mn=False, N=192, M=1568, K=192))
+
+
+def case_conv(B=2, H=28, W=28, C=192, stride=2):
+    import torch
+    from sav import ops
+    torch.manual_seed(0)
+    x = torch.randn(B, H, W, C, device="cuda")
+    w = torch.randn(3, 3, C, device="cuda") / 3
+    y, stats = ops.dwconv3x3_fwd(x, w.reshape(9, C), stride)
+    Ho, Wo = y.shape[1], y.shape[2]
+    pt = max((Ho - 1) * stride + 3 - H, 0)
+    pl = max((Wo - 1) * stride + 3 - W, 0)
+    xi = torch.nn.functional.pad(x.permute(0, 3, 1, 2), (pl // 2, pl - pl // 2, pt // 2, pt - pt // 2))
+    xi.requires_grad_(True)
+    wk = w.permute(2, 0, 1)[:, None].contiguous().requires_grad_(True)
+    ref = torch.nn.functional.conv2d(xi, wk, stride=stride, groups=C).permute(0, 2, 3, 1)
+    errs = {"y": rel_err(y, ref), "sum": rel_err(stats[0], ref.sum((0, 1, 2))),
+            "sumsq": rel_err(stats[1], (ref * ref).sum((0, 1, 2)))}
+    dy = torch.randn_like(ref).bfloat16()
+    (ref * dy.float()).sum().backward()
+    dx = torch.empty_like(x)
+    dw = torch.zeros(9, C, device="cuda")
+    ops.dwconv3x3_bwd(x, w.reshape(9, C), dy.contiguous(), dx, dw, stride, False)
+    gx = xi.grad[:, :, pt // 2:pt // 2 + H, pl // 2:pl // 2 + W].permute(0, 2, 3, 1)
+    errs["dx"] = rel_err(dx, gx)
+    errs["dw"] = rel_err(dw, wk.grad[:, 0].permute(1, 2, 0).reshape(9, C))
+    torch.cuda.synchronize()
+    return errs
+
+
+CASES["conv_192_s2"] = (case_conv, {})
+CASES["conv_192_s1"] = (case_conv, dict(stride=1))
+CASES["conv_64_s2"] = (case_conv, dict(B=1, H=56, W=56, C=64))
+CASES["conv_384_odd"] = (case_conv, dict(B=2, H=15, W=15, C=384))
 CASES["ln"] = (case_ln, {})
 CASES["ln_strided"] = (case_ln, dict(strided=True))
 CASES["stem"] = (case_stem, {})
@@ -204,6 +240,11 @@ CASES["attn_fwd_64"] = (case_attn, dict(Nq=64, Nk=64, bwd=False))
 CASES["attn_197"] = (case_attn, {})
 CASES["attn_577"] = (case_attn, dict(B=1, H=2, Nq=577, Nk=577))
 CASES["attn_cross"] = (case_attn, dict(B=2, H=2, Nq=225, Nk=64))
+CASES["attn_cvt2_fwd"] = (case_attn, dict(B=2, H=3, Nq=784, Nk=196, bwd=False))
+CASES["attn_cvt2"] = (case_attn, dict(B=2, H=3, Nq=784, Nk=196))
+CASES["attn_cvt1_fwd"] = (case_attn, dict(B=1, H=1, Nq=3136, Nk=784, bwd=False))
+CASES["attn_cvt1"] = (case_attn, dict(B=1, H=1, Nq=3136, Nk=784))
+CASES["attn_q300_k100"] = (case_attn, dict(B=1, H=1, Nq=300, Nk=100))
 
 
 def case_attn_time(B=256, H=6, N=197, bwd=False, reps=20):
@@ -290,7 +331,7 @@ def main():
             continue
         try:
             r = subprocess.run([sys.executable, __file__, "--case", name], capture_output=True,
-                               text=True, timeout=90)
+                               text=True, timeout=45)
             line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")]
             if r.returncode == 0 and line:
                 errs = json.loads(line[-1][7:])

@@ -212,3 +212,55 @@ def test_cait_reference_layerscale_init():
     # the reference's LayerScale init 1e-5 (cait_test.py:18): branches nearly vanish in the stream
     _cait_case("cait_xxs4_ls1e-5", num_layers=4, heads=4, dim=192, batch=8, img=224, layerscale=None,
                drop_rate=0.0)
+
+
+# ------------------------------------------------------------------------------ CvT stage block
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,L,C,heads", [
+    (4, 197, 384, 6),     # CvT stage 3: 197 tokens -> 15 x 15 map, keys on 8 x 8 (odd SAME padding)
+    (2, 784, 192, 3),     # stage 2: 28 x 28 queries, 14 x 14 keys
+    (1, 3136, 64, 1),     # stage 1: 56 x 56 queries, 28 x 28 keys, one head
+])
+def test_cvt_stage_block(B, L, C, heads):
+    import sav
+    from models import StageBlock
+    from sav.tape import Var
+    g = torch.Generator().manual_seed(L)
+    x = torch.randn((B, L, C), generator=g)
+    params = V.synthetic_cvt_stage_params(C, heads, seed=42)
+    pr = O.tree_map(lambda t: t.detach().clone().requires_grad_(True), params)
+    xr = x.clone().requires_grad_(True)
+    out_ref = V.cvt_stage_block(xr, pr, heads)
+    cot = torch.randn(out_ref.shape, generator=g)
+    (out_ref * cot).sum().backward()
+
+    model = StageBlock(num_heads=heads, embed_dim=C)
+    variables = sav.load_params(model, params, Var(x.cuda()), is_training=True)
+    holder = {}
+
+    class Cot:
+        def __init__(self, out):
+            self.out = out
+
+        def seed(self):
+            self.out.g = cot.cuda()
+
+    def fn(p, xv):
+        holder["out"] = model.apply({"params": p}, xv, is_training=True)
+        return Cot(holder["out"])
+    xv = Var(x.cuda())
+    _, grads = sav.value_and_grad(fn)(variables["params"], xv)
+    torch.cuda.synchronize()
+    errs = {"out": _rel(holder["out"].v, out_ref), "dx": _rel(xv.g, xr.grad)}
+    ours = dict(O.tree_leaves(grads))
+    for path, t in O.tree_leaves(pr):
+        errs[path] = _rel(ours[path], t.grad)
+    # a constant added to every key shifts all logits of a query equally: the softmax -- hence the
+    # loss -- does not depend on the key projection's BatchNorm bias, its true gradient is 0
+    kb = "CvTSelfAttentionBlock_0/ConvProjectionBlock_1/BatchNorm_0/bias"
+    ref_kb = dict(O.tree_leaves(pr))[kb].grad
+    scale_ref = dict(O.tree_leaves(pr))["CvTSelfAttentionBlock_0/ConvProjectionBlock_2/BatchNorm_0/bias"].grad
+    assert float(ref_kb.abs().max()) < 1e-4 * float(scale_ref.abs().max())
+    assert float(ours[kb].float().abs().max().cpu()) < 2e-2 * float(scale_ref.abs().max())
+    del errs[kb]
+    _check(f"cvt_stage_B{B}L{L}C{C}", errs)

@@ -122,6 +122,41 @@ def test_class_attention_uses_only_row_zero_as_query():
     assert out.shape == (2, 1, 16)
 
 
+def test_cvt_same_padding_matches_jax_convention():
+    # even input, stride 2: the single padded row / column is on the HIGH side; odd input: both
+    assert V.same_pad_amounts(56, 2) == (0, 1)
+    assert V.same_pad_amounts(15, 2) == (1, 1)
+    assert V.same_pad_amounts(14, 1) == (1, 1)
+
+
+def test_cvt_stage_block_oracle_shapes_and_finite_differences():
+    C, h = 16, 2
+    params = V.synthetic_cvt_stage_params(C, h, dtype=torch.float64)
+    # 10 tokens -> padded to 16 (4x4 map); keys/values on the 2x2 strided map
+    x = torch.randn(3, 10, C, dtype=torch.float64, generator=torch.Generator().manual_seed(0))
+    out = V.cvt_stage_block(x, params, h)
+    assert out.shape == (3, 16, C)
+    cot = torch.randn(3, 16, C, dtype=torch.float64, generator=torch.Generator().manual_seed(1))
+
+    def fn(p):
+        return (V.cvt_stage_block(x, p, h) * cot).sum()
+    assert _fd_check(fn, params, n_probe=4, eps=1e-5) < 1e-4   # key-BN bias: exact-zero gradient vs FD noise
+
+
+def test_cvt_stage_block_shape_and_param_names():
+    """models/cvt_test.py only asserts logits shape; here: the stage block pads 197 tokens to a
+    15 x 15 map (cvt.py:10-16) and the parameter tree matches the oracle's."""
+    from models import StageBlock
+    from sav.tape import Var
+    m = StageBlock(num_heads=6, embed_dim=384)
+    x = Var(torch.empty((2, 197, 384), device="meta", dtype=torch.float32))
+    out, variables = m.init_with_output({"params": 0}, x, is_training=True)
+    assert tuple(out.shape) == (2, 225, 384)
+    ours = {k: tuple(v.shape) for k, v in O.tree_leaves(variables["params"])}
+    ref = {k: tuple(v.shape) for k, v in O.tree_leaves(V.synthetic_cvt_stage_params(384, 6))}
+    assert ours == ref
+
+
 # ------------------------------------------------------------------------- module surface (meta)
 @pytest.mark.parametrize("name,heads,dim", [("cait_xxs_24", 4, 192), ("cait_xs_24", 6, 288),
                                             ("cait_s_24", 8, 384)])
