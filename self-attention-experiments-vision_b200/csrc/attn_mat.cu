@@ -326,6 +326,221 @@ thsoftmax_bwd_kernel(const SoftArgs a) {
   }
 }
 
+// ---- register / shared-memory resident variants for Nk <= 32 * KPL (CaiT: 196 / 197 keys).
+// The row's mixed logits are computed ONCE: forward keeps exp(t - m) for the lane's keys in
+// registers between the statistics and the output pass; backward parks p and dp in shared memory
+// (conflict-free [slot][lane] layout) so that S is read twice and dP once, instead of 4x / 2x.
+constexpr int kKPL = 7;
+
+template <int H>
+__global__ void __launch_bounds__(kRowWarps * 32)
+thsoftmax_fwd_res_kernel(const SoftArgs a) {
+  __shared__ float t1[H * H], t2[H * H];
+  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
+    t1[i] = a.mix_pre[i];
+    t2[i] = a.mix_post[i];
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int64_t rows = (int64_t)a.B * a.Nq;
+  const int64_t hs = (int64_t)a.Nq * a.ld;
+  const float sc = a.scale * kLog2e;
+  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + (threadIdx.x >> 5); row < rows;
+       row += (int64_t)gridDim.x * kRowWarps) {
+    const int q = (int)(row % a.Nq);
+    const int64_t b = row / a.Nq;
+    const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
+    const float* s0 = a.S + off;
+    bf16* p0 = a.P + off;
+    float e[kKPL][H], m[H], inv[H];
+#pragma unroll
+    for (int i = 0; i < H; ++i) m[i] = -INFINITY;
+#pragma unroll
+    for (int kk = 0; kk < kKPL; ++kk) {
+      const int k = lane + 32 * kk;
+      if (k < a.Nk) {
+        float s[H];
+        th_logits<H>(a, s0, hs, k, t1, sc, s, e[kk]);
+#pragma unroll
+        for (int i = 0; i < H; ++i) m[i] = fmaxf(m[i], e[kk][i]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < H; ++i) e[kk][i] = -INFINITY;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < H; ++i) { m[i] = warp_max(m[i]); inv[i] = 0.f; }
+#pragma unroll
+    for (int kk = 0; kk < kKPL; ++kk)
+#pragma unroll
+      for (int i = 0; i < H; ++i) {
+        e[kk][i] = ex2_fast(e[kk][i] - m[i]);   // exp2(-inf) = 0 for the padded keys
+        inv[i] += e[kk][i];
+      }
+#pragma unroll
+    for (int i = 0; i < H; ++i) inv[i] = 1.f / warp_sum(inv[i]);
+#pragma unroll
+    for (int kk = 0; kk < kKPL; ++kk) {
+      const int k = lane + 32 * kk;
+      if (k < a.ld) {
+#pragma unroll
+        for (int j = 0; j < H; ++j) {
+          float acc = 0.f;
+#pragma unroll
+          for (int i = 0; i < H; ++i) acc = fmaf(t2[i * H + j], e[kk][i] * inv[i], acc);
+          p0[j * hs + k] = __float2bfloat16(acc);
+        }
+      }
+    }
+  }
+}
+
+template <int H>
+__global__ void __launch_bounds__(kRowWarps * 32)
+thsoftmax_bwd_res_kernel(const SoftArgs a) {
+  extern __shared__ float park[];   // [kRowWarps][2][kKPL * H][32]
+  __shared__ float t1[H * H], t2[H * H];
+  __shared__ float red1[H * H], red2[H * H];
+  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
+    t1[i] = a.mix_pre[i];
+    t2[i] = a.mix_post[i];
+    red1[i] = 0.f;
+    red2[i] = 0.f;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* pp = park + (size_t)warp * 2 * kKPL * H * 32 + lane;   // p  at pp[(kk*H+i)*32]
+  float* dd = pp + kKPL * H * 32;                               // dp at dd[(kk*H+i)*32]
+  const int64_t rows = (int64_t)a.B * a.Nq;
+  const int64_t hs = (int64_t)a.Nq * a.ld;
+  const float sc = a.scale * kLog2e;
+  float g1[H * H], g2[H * H];
+#pragma unroll
+  for (int i = 0; i < H * H; ++i) { g1[i] = 0.f; g2[i] = 0.f; }
+  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + warp; row < rows;
+       row += (int64_t)gridDim.x * kRowWarps) {
+    const int q = (int)(row % a.Nq);
+    const int64_t b = row / a.Nq;
+    const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
+    const float* s0 = a.S + off;
+    const float* d0 = a.dP + off;
+    bf16* ds0 = a.dS + off;
+    float m[H], inv[H], delta[H];
+#pragma unroll
+    for (int i = 0; i < H; ++i) m[i] = -INFINITY;
+    // pass 1: mixed logits -> park, running max
+#pragma unroll
+    for (int kk = 0; kk < kKPL; ++kk) {
+      const int k = lane + 32 * kk;
+      float s[H], t[H];
+      if (k < a.Nk) {
+        th_logits<H>(a, s0, hs, k, t1, sc, s, t);
+      } else {
+#pragma unroll
+        for (int i = 0; i < H; ++i) t[i] = -INFINITY;
+      }
+#pragma unroll
+      for (int i = 0; i < H; ++i) {
+        m[i] = fmaxf(m[i], t[i]);
+        pp[(kk * H + i) * 32] = t[i];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < H; ++i) { m[i] = warp_max(m[i]); inv[i] = 0.f; }
+#pragma unroll
+    for (int kk = 0; kk < kKPL; ++kk)
+#pragma unroll
+      for (int i = 0; i < H; ++i) {
+        const float ev = ex2_fast(pp[(kk * H + i) * 32] - m[i]);
+        pp[(kk * H + i) * 32] = ev;
+        inv[i] += ev;
+      }
+#pragma unroll
+    for (int i = 0; i < H; ++i) { inv[i] = 1.f / warp_sum(inv[i]); delta[i] = 0.f; }
+    // pass 2: p, dp = T2 dP', delta, d mix_post
+#pragma unroll
+    for (int kk = 0; kk < kKPL; ++kk) {
+      const int k = lane + 32 * kk;
+      if (k < a.Nk) {
+        float dpo[H];
+#pragma unroll
+        for (int j = 0; j < H; ++j) dpo[j] = d0[j * hs + k];
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+          const float pi = pp[(kk * H + i) * 32] * inv[i];
+          pp[(kk * H + i) * 32] = pi;
+          float dpi = 0.f;
+#pragma unroll
+          for (int j = 0; j < H; ++j) {
+            dpi = fmaf(t2[i * H + j], dpo[j], dpi);
+            g2[i * H + j] = fmaf(pi, dpo[j], g2[i * H + j]);
+          }
+          dd[(kk * H + i) * 32] = dpi;
+          delta[i] = fmaf(pi, dpi, delta[i]);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < H; ++i) delta[i] = warp_sum(delta[i]);
+    // pass 3: d logits, dS = T1 dt, d mix_pre (raw S re-read: L1 / L2 resident)
+#pragma unroll
+    for (int kk = 0; kk < kKPL; ++kk) {
+      const int k = lane + 32 * kk;
+      if (k < a.ld) {
+        float dt[H], s[H];
+        if (k < a.Nk) {
+#pragma unroll
+          for (int i = 0; i < H; ++i) {
+            dt[i] = pp[(kk * H + i) * 32] * (dd[(kk * H + i) * 32] - delta[i]) * a.scale;
+            s[i] = s0[i * hs + k];
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < H; ++i) { dt[i] = 0.f; s[i] = 0.f; }
+        }
+#pragma unroll
+        for (int h = 0; h < H; ++h) {
+          float acc = 0.f;
+#pragma unroll
+          for (int i = 0; i < H; ++i) {
+            acc = fmaf(t1[h * H + i], dt[i], acc);
+            g1[h * H + i] = fmaf(s[h], dt[i], g1[h * H + i]);
+          }
+          ds0[h * hs + k] = __float2bfloat16(acc);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < H * H; ++i) {
+    const float v1 = warp_sum(g1[i]);
+    const float v2 = warp_sum(g2[i]);
+    if (lane == 0) {
+      atomicAdd(&red1[i], v1);
+      atomicAdd(&red2[i], v2);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
+    atomicAdd(a.dmix_pre + i, red1[i]);
+    atomicAdd(a.dmix_post + i, red2[i]);
+  }
+}
+
+template <int H>
+static int launch_th_bwd_res(const SoftArgs& a, int grid, cudaStream_t st) {
+  const size_t sm = (size_t)kRowWarps * 2 * kKPL * H * 32 * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set && sm > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(thsoftmax_bwd_res_kernel<H>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "thsoftmax smem attr: %s", cudaGetErrorString(e));
+    attr_set = true;
+  }
+  thsoftmax_bwd_res_kernel<H><<<grid, kRowWarps * 32, sm, st>>>(a);
+  return SAV_OK;
+}
+
 static int soft_grid(int64_t rows) {
   int64_t blocks = (rows + kRowWarps - 1) / kRowWarps;
   const int64_t cap = 148 * 8;
@@ -367,8 +582,13 @@ extern "C" int sav_thsoftmax_fwd(const sav_thsoftmax_args* x, void* stream) {
     softmax_rows_fwd_kernel<<<soft_grid((int64_t)a.B * a.H * a.Nq), kRowWarps * 32, 0, st>>>(a);
   } else {
     const int grid = soft_grid((int64_t)a.B * a.Nq);
+    const bool res = a.ld <= 32 * kKPL;   // the row fits the register-resident variant
     switch (a.H) {
-#define SAV_TH_CASE(Hv) case Hv: thsoftmax_fwd_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a); break;
+#define SAV_TH_CASE(Hv)                                                              \
+  case Hv:                                                                           \
+    if (res) thsoftmax_fwd_res_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a);       \
+    else thsoftmax_fwd_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a);               \
+    break;
       SAV_TH_CASE(2) SAV_TH_CASE(3) SAV_TH_CASE(4) SAV_TH_CASE(6) SAV_TH_CASE(8)
 #undef SAV_TH_CASE
       default:
@@ -396,8 +616,13 @@ extern "C" int sav_thsoftmax_bwd(const sav_thsoftmax_args* x, void* stream) {
     // few, fat blocks: every block ends with H*H atomics per transform
     int64_t blocks = ((int64_t)a.B * a.Nq + kRowWarps - 1) / kRowWarps;
     const int grid = (int)(blocks < 148 * 4 ? blocks : 148 * 4);
+    const bool res = a.ld <= 32 * kKPL;
     switch (a.H) {
-#define SAV_TH_CASE(Hv) case Hv: thsoftmax_bwd_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a); break;
+#define SAV_TH_CASE(Hv)                                                              \
+  case Hv:                                                                           \
+    if (res) { if ((rc = launch_th_bwd_res<Hv>(a, grid, st))) return rc; }           \
+    else thsoftmax_bwd_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a);               \
+    break;
       SAV_TH_CASE(2) SAV_TH_CASE(3) SAV_TH_CASE(4) SAV_TH_CASE(6) SAV_TH_CASE(8)
 #undef SAV_TH_CASE
       default:

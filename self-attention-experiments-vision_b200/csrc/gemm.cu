@@ -435,28 +435,50 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
 }
 
 // ---- column sums of a bf16 [M,N] matrix (bias gradients; ff.py:24,27 reverse-mode).
-// grid = (N/64 col-groups, row-splits); each thread owns 2 adjacent columns, 8 row-lanes per
-// block, smem reduce, one red.add per column per block (out is an accumulator).
-__global__ void colsum_kernel(const bf16* __restrict__ X, int64_t M, int64_t N, int64_t ldx,
-                              float* __restrict__ out) {
-  __shared__ float2 red[8][32];
+// grid = (N/256 column groups, row splits); a lane owns 8 adjacent columns (one 16-byte load per
+// row, a warp reads 512 contiguous bytes), 8 row-lanes per block, smem reduce, one red.add per
+// column per block (out is an accumulator).
+__global__ void __launch_bounds__(256)
+colsum_kernel(const bf16* __restrict__ X, int64_t M, int64_t N, int64_t ldx, float* __restrict__ out) {
+  __shared__ float red[8][32][8];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int64_t col = (int64_t)blockIdx.x * 64 + tx * 2;
-  float2 acc = make_float2(0.f, 0.f);
+  const int64_t col = (int64_t)blockIdx.x * 256 + tx * 8;
+  float acc[8] = {};
   if (col < N) {
-    for (int64_t r = (int64_t)blockIdx.y * 8 + ty; r < M; r += (int64_t)gridDim.y * 8) {
-      const uint32_t u = *reinterpret_cast<const uint32_t*>(X + r * ldx + col);
-      const float2 f = unpack_bf16(u);
-      acc.x += f.x;
-      acc.y += f.y;
+    const int64_t step = (int64_t)gridDim.y * 8;
+    int64_t r = (int64_t)blockIdx.y * 8 + ty;
+    // two independent loads in flight per thread
+    for (; r + step < M; r += 2 * step) {
+      const uint4 u0 = *reinterpret_cast<const uint4*>(X + r * ldx + col);
+      const uint4 u1 = *reinterpret_cast<const uint4*>(X + (r + step) * ldx + col);
+      const uint32_t w0[4] = {u0.x, u0.y, u0.z, u0.w}, w1[4] = {u1.x, u1.y, u1.z, u1.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 a = unpack_bf16(w0[j]), b = unpack_bf16(w1[j]);
+        acc[2 * j] += a.x + b.x;
+        acc[2 * j + 1] += a.y + b.y;
+      }
+    }
+    if (r < M) {
+      const uint4 u0 = *reinterpret_cast<const uint4*>(X + r * ldx + col);
+      const uint32_t w0[4] = {u0.x, u0.y, u0.z, u0.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 a = unpack_bf16(w0[j]);
+        acc[2 * j] += a.x;
+        acc[2 * j + 1] += a.y;
+      }
     }
   }
-  red[ty][tx] = acc;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[ty][tx][j] = acc[j];
   __syncthreads();
-  if (ty == 0 && col < N) {
-    for (int j = 1; j < 8; ++j) { acc.x += red[j][tx].x; acc.y += red[j][tx].y; }
-    atomicAdd(out + col, acc.x);
-    atomicAdd(out + col + 1, acc.y);
+  // thread (ty, tx) finishes column tx*8 + ty
+  if (col < N) {
+    float v = 0.f;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) v += red[y][tx][ty];
+    atomicAdd(out + col + ty, v);
   }
 }
 
@@ -712,13 +734,14 @@ extern "C" int sav_fill_f32(float* ptr, float v, int64_t n, void* stream) {
 extern "C" int sav_colsum_bf16(const void* X, int64_t M, int64_t N, int64_t ldx, float* out,
                                int32_t accumulate, void* stream) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (M <= 0 || N <= 0 || N % 2 || ldx % 2) return set_error(SAV_ERR_SHAPE, "sav_colsum: bad shape");
+  if (M <= 0 || N <= 0 || N % 8 || ldx % 8 || !aligned16(X))
+    return set_error(SAV_ERR_SHAPE, "sav_colsum: need N, ldx multiples of 8 and a 16 B aligned base");
   if (!accumulate) {
     int rc = sav_fill_f32(out, 0.f, N, stream);
     if (rc) return rc;
   }
-  dim3 grid((unsigned)((N + 63) / 64), 1);
-  int64_t want = (num_sms() * 4 + grid.x - 1) / grid.x;
+  dim3 grid((unsigned)((N + 255) / 256), 1);
+  int64_t want = (num_sms() * 8 + grid.x - 1) / grid.x;
   int64_t maxy = (M + 7) / 8;
   grid.y = (unsigned)(want < maxy ? (want < 1 ? 1 : want) : maxy);
   colsum_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const bf16*>(X), M, N, ldx, out);
