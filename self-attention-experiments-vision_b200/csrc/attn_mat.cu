@@ -332,6 +332,15 @@ thsoftmax_bwd_kernel(const SoftArgs a) {
 // (conflict-free [slot][lane] layout) so that S is read twice and dP once, instead of 4x / 2x.
 constexpr int kKPL = 7;
 
+// 4-byte asynchronous global -> shared copy: the whole row (H x Nk logits and their gradients) is
+// requested up front without holding a register per element, so one warp keeps ~14 KB in flight
+__device__ __forceinline__ void cp_async4(float* dst, const float* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.wait_all;" ::: "memory");
+}
+
 template <int H>
 __global__ void __launch_bounds__(kRowWarps * 32)
 thsoftmax_fwd_res_kernel(const SoftArgs a) {
@@ -428,13 +437,35 @@ thsoftmax_bwd_res_kernel(const SoftArgs a) {
     float m[H], inv[H], delta[H];
 #pragma unroll
     for (int i = 0; i < H; ++i) m[i] = -INFINITY;
-    // pass 1: mixed logits -> park, running max
+    // pass 0: request the row -- raw logits into the p slots, dP into the dp slots
 #pragma unroll
     for (int kk = 0; kk < kKPL; ++kk) {
       const int k = lane + 32 * kk;
-      float s[H], t[H];
       if (k < a.Nk) {
-        th_logits<H>(a, s0, hs, k, t1, sc, s, t);
+#pragma unroll
+        for (int h = 0; h < H; ++h) {
+          cp_async4(&pp[(kk * H + h) * 32], s0 + h * hs + k);
+          cp_async4(&dd[(kk * H + h) * 32], d0 + h * hs + k);
+        }
+      }
+    }
+    cp_async_wait_all();
+    // pass 1: mixed logits (in place), running max
+#pragma unroll
+    for (int kk = 0; kk < kKPL; ++kk) {
+      const int k = lane + 32 * kk;
+      float t[H];
+      if (k < a.Nk) {
+        float s[H];
+#pragma unroll
+        for (int h = 0; h < H; ++h) s[h] = pp[(kk * H + h) * 32];
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+          float acc = 0.f;
+#pragma unroll
+          for (int h = 0; h < H; ++h) acc = fmaf(t1[h * H + i], s[h], acc);
+          t[i] = acc * sc;
+        }
       } else {
 #pragma unroll
         for (int i = 0; i < H; ++i) t[i] = -INFINITY;
@@ -464,7 +495,7 @@ thsoftmax_bwd_res_kernel(const SoftArgs a) {
       if (k < a.Nk) {
         float dpo[H];
 #pragma unroll
-        for (int j = 0; j < H; ++j) dpo[j] = d0[j * hs + k];
+        for (int j = 0; j < H; ++j) dpo[j] = dd[(kk * H + j) * 32];
 #pragma unroll
         for (int i = 0; i < H; ++i) {
           const float pi = pp[(kk * H + i) * 32] * inv[i];
