@@ -342,8 +342,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       const int col = n_idx + j * SC + half * (SC / 2);
       if (!f32) {
         uint32_t rr[32];
-        tmem_ld32(taddr, rr);
-        tmem_ld_wait();
+        if (p.debug & 8) {   // development: no TMEM read
+#pragma unroll
+          for (int i = 0; i < 32; ++i) rr[i] = 0x3f800000u;
+        } else {
+          tmem_ld32(taddr, rr);
+          tmem_ld_wait();
+        }
         if (j == slabs_per_tile - 1) release_acc(acc);
         float v[32];
 #pragma unroll
@@ -366,8 +371,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           epi_affine<32>(p, v, col, rs);
           if (two_out) {
             st_bf16x32(slab, r, half * 4, v);  // pre-activation (saved for backward)
+            if (!(p.debug & 4)) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = gelu_fast(v[i]);
+              for (int i = 0; i < 32; ++i) v[i] = gelu_fast(v[i]);
+            }
             st_bf16x32(slab + SLAB_BYTES, r, half * 4, v);
           } else {
             if (p.act == 1) {
@@ -411,6 +418,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         const int c0 = n_idx + j * SC;
         if (p.epi == EPI_ACCUM) {
           tma_reduce_add_2d(&tma_d, slab, c0, m_idx);
+        } else if (p.debug & 16) {   // development: no global stores
         } else if (two_out) {
           tma_store_2d(&tma_x, slab, c0, m_idx);
           tma_store_2d(&tma_d, slab + SLAB_BYTES, c0, m_idx);
