@@ -257,6 +257,13 @@ int sav_softmax_xent(const void* logits, int64_t ld, const int32_t* labels, int6
                      int64_t classes, float label_smoothing, float grad_scale, void* dlogits,
                      float* loss_out, void* stream);
 
+/* utils.py:20-31 topk_correct (train.py:98-99): out[i*B + b] = 1.0 if the label of example b is
+ * among the k_i highest logits (argsort tie order: larger class index ranks higher), else 0.0;
+ * 1 <= nk <= 4.  logits bf16 [B, classes] ld; out fp32 [nk, B]. */
+int sav_topk_correct(const void* logits, int64_t ld, const int32_t* labels, int64_t B,
+                     int64_t classes, int32_t nk, int32_t k0, int32_t k1, int32_t k2, int32_t k3,
+                     float* out, void* stream);
+
 /* ---------------------------------------------------------------- parameters / optimizer
  * fp32 -> bf16 shadow copy of the flat parameter arena */
 int sav_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);

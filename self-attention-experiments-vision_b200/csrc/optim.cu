@@ -121,6 +121,31 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g,
   }
 }
 
+// utils.py:20-31 topk_correct: jnp.argsort is ascending and stable, the top-k are the last k
+// indices, so among equal logits the larger class index ranks higher.  rank = number of classes
+// ranked above the label; correct_k = rank < k.  Warp per example.
+__global__ void __launch_bounds__(128)
+topk_kernel(const bf16* __restrict__ logits, int64_t ld, const int32_t* __restrict__ labels, int B,
+            int classes, int nk, int4 ks, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (b >= B) return;
+  const bf16* row = logits + (int64_t)b * ld;
+  const int lab = labels[b];
+  const float l_lab = __bfloat162float(row[lab]);
+  int above = 0;
+  for (int c = lane; c < classes; c += 32) {
+    const float l = __bfloat162float(row[c]);
+    above += (l > l_lab || (l == l_lab && c > lab)) ? 1 : 0;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) above += __shfl_xor_sync(0xffffffffu, above, o);
+  if (lane == 0) {
+    const int kk[4] = {ks.x, ks.y, ks.z, ks.w};
+    for (int i = 0; i < nk; ++i) out[(int64_t)i * B + b] = above < kk[i] ? 1.f : 0.f;
+  }
+}
+
 __global__ void add_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b,
                            bf16* __restrict__ y, int64_t n8) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n8;
@@ -170,6 +195,18 @@ extern "C" int sav_softmax_xent(const void* logits, int64_t ld, const int32_t* l
       grad_scale, reinterpret_cast<bf16*>(dlogits), loss_out);
   count_launch();
   return check_launch("sav_softmax_xent");
+}
+
+extern "C" int sav_topk_correct(const void* logits, int64_t ld, const int32_t* labels, int64_t B,
+                                int64_t classes, int32_t nk, int32_t k0, int32_t k1, int32_t k2,
+                                int32_t k3, float* out, void* stream) {
+  if (B <= 0 || classes <= 0 || nk < 1 || nk > 4)
+    return set_error(SAV_ERR_SHAPE, "sav_topk_correct: bad shape (1 <= nk <= 4)");
+  topk_kernel<<<(int)((B + 3) / 4), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const bf16*>(logits), ld, labels, (int)B, (int)classes, nk,
+      make_int4(k0, k1, k2, k3), out);
+  count_launch();
+  return check_launch("sav_topk_correct");
 }
 
 extern "C" int sav_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {

@@ -137,6 +137,28 @@ class ParamArena:
     def tree(self):
         return self._tree("master")
 
+    def _tree_of(self, flat):
+        """Tree of views into another flat buffer with the arena's layout (Adam moments)."""
+        root = ParamTree()
+        root.arena = self
+        for path, p in self.params.items():
+            d = root
+            for k in path[:-1]:
+                d = d.setdefault(k, {})
+            d[path[-1]] = p._view(flat)
+        return root
+
+    def load_tree_into(self, flat, tree):
+        """Copy a nested dict with the parameter tree's names / shapes into `flat` (arena layout)."""
+        def walk(d, prefix):
+            for k, v in d.items():
+                if isinstance(v, dict):
+                    walk(v, prefix + (k,))
+                else:
+                    p = self.params[prefix + (k,)]
+                    p._view(flat).copy_(v.to(device=self.device, dtype=torch.float32))
+        walk(tree, ())
+
     def grad_tree(self):
         return self._tree("grad")
 
