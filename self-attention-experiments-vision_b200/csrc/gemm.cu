@@ -42,6 +42,7 @@ struct GemmParams {
   int64_t rows_per_scale;
   int batch_inner;  // batched (BATCH=true) only: size of the inner batch dim (heads)
   int nbatch;       // total batches (1 when not batched)
+  long long* dbg;   // development only: timeline buffer (tests/tools/gemm_timeline.py) or null
   int debug;        // development only (SAV_GEMM_DEBUG): 1 = skip TMA loads, 2 = skip MMAs
 };
 
@@ -134,6 +135,18 @@ __device__ __forceinline__ void st_bf16x32(uint8_t* slab, int r, int cb, const f
                    pack_bf16(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16(v[g * 8 + 6], v[g * 8 + 7]));
 }
 
+// development timeline: (event, clock64) pairs of CTA 0, 256 slots per role
+#define GEMM_STAMP(role, ev)                                         \
+  do {                                                               \
+    if (p.dbg && blockIdx.x == 0 && dbg_n < 255 && STAMP_LANE) {     \
+      p.dbg[(role) * 512 + 2 * dbg_n] = (ev);                        \
+      p.dbg[(role) * 512 + 2 * dbg_n + 1] = clock64();               \
+      ++dbg_n;                                                       \
+    }                                                                \
+  } while (0)
+
+#define STAMP_LANE true
+
 template <int BN, bool A_MN, bool B_MN, int CTAS, bool BATCH>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -151,7 +164,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   uint64_t* aux_bar = tempty_bar + 2;  // [4]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + 4);
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle so that the compiler knows the role branches are warp-uniform
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -192,7 +206,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      int dbg_n = 0;
       for (int tile = unit; tile < num_tiles; tile += units) {
+        GEMM_STAMP(0, 1);
         const int z = BATCH ? tile / tiles_per_batch : 0;
         const int zi = BATCH ? z % p.batch_inner : 0, zo = BATCH ? z / p.batch_inner : 0;
         const int tl = tile - z * tiles_per_batch;
@@ -203,7 +219,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         const int kb0 = split * p.k_per_split;
         const int kb1 = min(kb0 + p.k_per_split, p.k_blocks);
         for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (!(p.debug & 512)) mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
           // the leader's full barrier collects the bytes of both CTAs' loads
@@ -237,12 +253,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && rank == 0) {
+    // The whole warp walks the loop (every lane polls the barriers) and one elected lane issues:
+    // with warp-uniform control flow and operands ptxas keeps the descriptors in uniform registers.
+    // Issuing from an `if (lane == 0)` region instead wraps every UTCHMMA in a vote / R2UR
+    // waterfall loop that costs ~150 cycles per MMA -- more than a 128x192x16 MMA takes.
+    if (rank == 0) {
+#undef STAMP_LANE
+#define STAMP_LANE (lane == 0)
       constexpr uint32_t idesc = make_idesc_bf16(BM * CTAS, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+      int dbg_n = 0;
       for (int tile = unit; tile < num_tiles; tile += units, ++it) {
+        GEMM_STAMP(1, 10);
         const int split = (tile % tiles_per_batch) / tiles_mn;
         const int kb0 = split * p.k_per_split;
         const int kb1 = min(kb0 + p.k_per_split, p.k_blocks);
@@ -250,29 +274,54 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         const uint32_t acc_phase = (it >> 1) & 1;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
+        GEMM_STAMP(1, 11);
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
+          // debug bits 256 / 512 (with bit 1 only): free-running issue without the full-barrier
+          // wait / without the per-k-block commit, to separate hand-shake cost from MMA pacing
+          if (!(p.debug & 256)) mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
+          if (kb == kb0) GEMM_STAMP(1, 12);
           const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
           const uint32_t sb = sa + Cfg::kABytes;
+          // descriptors as (low, high) words: within a stage only the 14-bit start-address field
+          // moves (K-major +32 B, MN-major +2048 B per 16-deep step)
+          const uint64_t da0 = A_MN ? make_smem_desc(sa, BK * 128, 1024) : make_smem_desc(sa, 16, 1024);
+          const uint64_t db0 = B_MN ? make_smem_desc(sb, BK * 128, 1024) : make_smem_desc(sb, 16, 1024);
+          const uint32_t a_lo = (uint32_t)da0, a_hi = (uint32_t)(da0 >> 32);
+          const uint32_t b_lo = (uint32_t)db0, b_hi = (uint32_t)(db0 >> 32);
+          constexpr uint32_t a_step = A_MN ? (2048 >> 4) : (32 >> 4);
+          constexpr uint32_t b_step = B_MN ? (2048 >> 4) : (32 >> 4);
+          if (elect_one()) {
+            // debug bit 128: issue every MMA twice (timing experiment: per-MMA vs per-k-block cost)
+            for (int rep = 0; rep < ((p.debug & 128) ? 2 : 1); ++rep)
+              if (!(p.debug & 2)) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            if (p.debug & 2) break;
-            const uint64_t da = A_MN ? make_smem_desc(sa + k * 2048, BK * 128, 1024)
-                                     : make_smem_desc(sa + k * 32, 16, 1024);
-            const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, BK * 128, 1024)
-                                     : make_smem_desc(sb + k * 32, 16, 1024);
-            if (CTAS == 2) umma_f16_pair(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-            else umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                for (int k = 0; k < BK / 16; ++k) {
+                  const uint32_t acc_flag = (kb > kb0 || k > 0 || rep > 0) ? 1u : 0u;
+                  if (CTAS == 2)
+                    umma_f16_pair_lh(d_tmem, a_lo + k * a_step, a_hi, b_lo + k * b_step, b_hi, idesc, acc_flag);
+                  else
+                    umma_f16_lh(d_tmem, a_lo + k * a_step, a_hi, b_lo + k * b_step, b_hi, idesc, acc_flag);
+                }
+              }
+            if (!(p.debug & 512)) {
+              if (CTAS == 2) umma_commit_pair(&empty_bar[stage]);
+              else umma_commit(&empty_bar[stage]);
+            }
           }
-          if (CTAS == 2) umma_commit_pair(&empty_bar[stage]);
-          else umma_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
-        if (CTAS == 2) umma_commit_pair(&tfull_bar[acc]);
-        else umma_commit(&tfull_bar[acc]);
+        if (elect_one()) {
+          if (CTAS == 2) umma_commit_pair(&tfull_bar[acc]);
+          else umma_commit(&tfull_bar[acc]);
+        }
+        __syncwarp();
+        GEMM_STAMP(1, 13);
       }
+#undef STAMP_LANE
+#define STAMP_LANE true
     }
   } else {
     // ------------------------------------------------------------------ epilogue (warps 2..9)
@@ -315,6 +364,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     };
     int m_idx = 0, n_idx = 0, acc = 0, zi = 0, zo = 0;
     float rs = 1.f;
+    int dbg_n = leader ? 0 : 1000;
     for (uint32_t sg = 0; sg < total_slabs; ++sg) {
       const int it = sg / slabs_per_tile;
       const int j = sg - it * slabs_per_tile;
@@ -329,8 +379,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         m_idx = (mn / p.n_blocks) * (BM * CTAS) + rank * BM;
         n_idx = (mn % p.n_blocks) * BN;
         acc = it & 1;
+        GEMM_STAMP(2, 20);
         mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
         tc_fence_after();
+        GEMM_STAMP(2, 21);
         if (p.row_scale) {
           const int64_t row = (int64_t)m_idx + r;
           rs = row < p.M ? p.row_scale[row / p.rows_per_scale] : 0.f;
@@ -406,14 +458,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           *reinterpret_cast<float4*>(slab + slab_off(r, half * 4 + g)) =
               make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
       }
-      fence_proxy_async_smem();
+      if (!(p.debug & 32)) fence_proxy_async_smem();
       if (leader) {
         // every earlier store has finished READING its slab => the slot of slab sg-1 (which
         // slab sg+nslot-1 reuses; at sg == 0 that slot has never been used) is free
         tma_store_wait_read<0>();
         if (aux_in && sg + nslot - 1 < total_slabs) issue_aux(sg + nslot - 1);
       }
-      named_bar_sync(1, kEpiThreads);
+      if (!(p.debug & 64)) named_bar_sync(1, kEpiThreads);
       if (leader) {
         const int c0 = n_idx + j * SC;
         if (p.epi == EPI_ACCUM) {
@@ -428,6 +480,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           tma_store_2d(&tma_d, slab, c0, m_idx);
         }
         tma_store_commit();
+        if (j == slabs_per_tile - 1) GEMM_STAMP(2, 22);
       }
     }
     if (leader) tma_store_wait<0>();
@@ -516,6 +569,12 @@ static int num_sms() {
 static int pick_bn_batched(int64_t N) { return N <= 64 ? 64 : 128; }
 
 static int pick_bn(int64_t N) {
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("SAV_GEMM_BN");
+    forced = e ? atoi(e) : 0;
+  }
+  if (forced == 128 || forced == 192 || forced == 256) return forced;
   if (N % 256 == 0) return 256;
   if (N % 192 == 0) return 192;
   if (N > 128 && N % 128 != 0 && N <= 192) return 192;
@@ -635,6 +694,7 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
     p.debug = dbg;
   }
   p.batch_inner = 1; p.nbatch = 1;
+  p.dbg = reinterpret_cast<long long*>(sav_debug_buffer());
 
   CUtensorMap ta, tb, td, tx;
   int rc;
@@ -698,6 +758,7 @@ extern "C" int sav_bgemm(const sav_bgemm_args* a, void* stream) {
   p.split_k = 1;
   p.epi = a->d_fp32 ? EPI_F32 : EPI_PLAIN;
   p.rows_per_scale = 1;
+  p.dbg = nullptr;
   p.batch_inner = (int)a->batch_inner;
   p.nbatch = (int)(a->batch_inner * a->batch_outer);
   CUtensorMap ta, tb, td;
