@@ -63,7 +63,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
   uint64_t* mma_done = bars + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
 
-  const int tid = threadIdx.x, warp = tid >> 5;
+  // warp index through a shuffle: `warp == 0` branches are then provably warp-uniform
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int nq_blk = (p.Nq + AT - 1) / AT;
 
@@ -109,28 +110,34 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
       s_lse[tid] = (q < p.Nq) ? p.lse[si] * LOG2E : INFINITY;
       s_delta[tid] = (q < p.Nq) ? p.delta[si] : 0.f;
     }
-    if (tid == 0) {
-      if (i + 1 < nq_blk) {
+    // warp 0 waits as a whole and one elected lane issues: uniform control flow keeps the MMA
+    // descriptors in uniform registers (no per-instruction vote / R2UR waterfall)
+    if (warp == 0) {
+      if (i + 1 < nq_blk && elect_one()) {
         const int nb = (i + 1) & 1;
         mbar_expect_tx(&qdo_full[nb], 2 * TILE_B);
         tma_load_3d(sQ + nb * TILE_B, &tq, &qdo_full[nb], h * AD, (i + 1) * AT, b);
         tma_load_3d(sdO + nb * TILE_B, &tdo, &qdo_full[nb], h * AD, (i + 1) * AT, b);
       }
+      __syncwarp();
       if (i == 0) mbar_wait(kv_full, 0);
       mbar_wait(&qdo_full[buf], (i >> 1) & 1);
       tc_fence_after();
       const uint32_t idesc = make_idesc_bf16(AT, nq_cur, false, false);
       const uint32_t ak = smem_u32(sK), av = smem_u32(sV);
       const uint32_t bq = smem_u32(sQ + buf * TILE_B), bdo = smem_u32(sdO + buf * TILE_B);
+      if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < AD / 16; ++k)
-        umma_f16(tSt, make_smem_desc(ak + k * 32, 16, 1024), make_smem_desc(bq + k * 32, 16, 1024),
-                 idesc, k > 0);
+        for (int k = 0; k < AD / 16; ++k)
+          umma_f16(tSt, make_smem_desc(ak + k * 32, 16, 1024), make_smem_desc(bq + k * 32, 16, 1024),
+                   idesc, k > 0);
 #pragma unroll
-      for (int k = 0; k < AD / 16; ++k)
-        umma_f16(tdPt, make_smem_desc(av + k * 32, 16, 1024),
-                 make_smem_desc(bdo + k * 32, 16, 1024), idesc, k > 0);
-      umma_commit(s_full);
+        for (int k = 0; k < AD / 16; ++k)
+          umma_f16(tdPt, make_smem_desc(av + k * 32, 16, 1024),
+                   make_smem_desc(bdo + k * 32, 16, 1024), idesc, k > 0);
+        umma_commit(s_full);
+      }
+      __syncwarp();
     }
     __syncthreads();  // s_lse / s_delta visible; also reconverges warp 0
     mbar_wait(s_full, i & 1);
@@ -164,7 +171,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
     fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
-    if (tid == 0) {
+    if (warp == 0) {
       tc_fence_after();
       const uint32_t apt = smem_u32(sPt), ads = smem_u32(sdSt);
       const uint32_t bq = smem_u32(sQ + buf * TILE_B), bdo = smem_u32(sdO + buf * TILE_B);
@@ -172,18 +179,20 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
       const uint32_t id_kmn = make_idesc_bf16(AT, AD, false, true);  // A K-major, B MN-major
       const uint32_t id_mnmn = make_idesc_bf16(AT, AD, true, true);  // A MN-major, B MN-major
       const int ksteps = nq_cur / 16;
-      // dV[keys,d] += P^T[keys,q] dO[q,d] ; dK[keys,d] += dS^T[keys,q] Q[q,d]   (K = queries)
-      for (int ks = 0; ks < ksteps; ++ks)
-        umma_f16(tdV, make_smem_desc(apt + (ks >> 2) * TILE_B + (ks & 3) * 32, 16, 1024),
-                 make_smem_desc(bdo + ks * 2048, TILE_B, 1024), id_kmn, (i > 0 || ks > 0));
-      for (int ks = 0; ks < ksteps; ++ks)
-        umma_f16(tdK, make_smem_desc(ads + (ks >> 2) * TILE_B + (ks & 3) * 32, 16, 1024),
-                 make_smem_desc(bq + ks * 2048, TILE_B, 1024), id_kmn, (i > 0 || ks > 0));
-      // dQ[q,d] = dS[q,keys] K[keys,d]   (K = keys; A = dS^T buffer read MN-major)
-      for (int ks = 0; ks < AT / 16; ++ks)
-        umma_f16(tdQ, make_smem_desc(ads + ks * 2048, TILE_B, 1024),
-                 make_smem_desc(bk + ks * 2048, TILE_B, 1024), id_mnmn, ks > 0);
-      umma_commit(mma_done);
+      if (elect_one()) {
+        // dV[keys,d] += P^T[keys,q] dO[q,d] ; dK[keys,d] += dS^T[keys,q] Q[q,d]   (K = queries)
+        for (int ks = 0; ks < ksteps; ++ks)
+          umma_f16(tdV, make_smem_desc(apt + (ks >> 2) * TILE_B + (ks & 3) * 32, 16, 1024),
+                   make_smem_desc(bdo + ks * 2048, TILE_B, 1024), id_kmn, (i > 0 || ks > 0));
+        for (int ks = 0; ks < ksteps; ++ks)
+          umma_f16(tdK, make_smem_desc(ads + (ks >> 2) * TILE_B + (ks & 3) * 32, 16, 1024),
+                   make_smem_desc(bq + ks * 2048, TILE_B, 1024), id_kmn, (i > 0 || ks > 0));
+        // dQ[q,d] = dS[q,keys] K[keys,d]   (K = keys; A = dS^T buffer read MN-major)
+        for (int ks = 0; ks < AT / 16; ++ks)
+          umma_f16(tdQ, make_smem_desc(ads + ks * 2048, TILE_B, 1024),
+                   make_smem_desc(bk + ks * 2048, TILE_B, 1024), id_mnmn, ks > 0);
+        umma_commit(mma_done);
+      }
     }
     __syncwarp();
     mbar_wait(mma_done, i & 1);

@@ -90,7 +90,8 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   uint64_t* dq_free = bars + 15;    // 256 arrivals
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // warp index through a shuffle: the role branches are then provably warp-uniform for ptxas
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int ppi = p.nkt * p.nqt;  // (key tile, query tile) pairs per item
   const int my_items = (p.n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   const int total_pairs = my_items * ppi;
@@ -144,7 +145,9 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // whole warp walks the loop, one elected lane issues: warp-uniform control flow keeps the
+    // descriptors in uniform registers (no per-MMA vote / R2UR waterfall)
+    {
       const uint64_t dQ0 = make_smem_desc(smem_u32(sQ), 16, 1024);            // K-major B of S^T
       const uint64_t ddO0 = make_smem_desc(smem_u32(sdO), 16, 1024);          // K-major B of dP^T
       const uint64_t dQm0 = make_smem_desc(smem_u32(sQ), BT_BYTES, 1024);     // MN-major B of dK
@@ -158,7 +161,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       constexpr uint32_t id_kmn = make_idesc_bf16(BT, BD, false, true);
       constexpr uint32_t id_mnmn = make_idesc_bf16(BT, BD, true, true);
       constexpr uint32_t TILE16 = BT_BYTES >> 4;  // descriptor address units (16 B)
-      int dbg_n = 0;
+      int dbg_n = lane == 0 ? 0 : 1000;
 
       auto lo = [](uint64_t d) { return (uint32_t)d; };
       auto hi = [](uint64_t d) { return (uint32_t)(d >> 32); };
@@ -178,13 +181,16 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         const uint32_t id_s = make_idesc_bf16(BT, nq_cur, false, false);
         const uint32_t a_k = lo(dK0) + st * 2 * TILE16, a_v = lo(dV0) + st * 2 * TILE16;
         const uint32_t b_q = lo(dQ0) + i * TILE16, b_do = lo(ddO0) + i * TILE16;
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < BD / 16; ++k)
-          umma_f16_lh(tSt, a_k + k * 2, hi(dK0), b_q + k * 2, hi(dQ0), id_s, k > 0);
+          for (int k = 0; k < BD / 16; ++k)
+            umma_f16_lh(tSt, a_k + k * 2, hi(dK0), b_q + k * 2, hi(dQ0), id_s, k > 0);
 #pragma unroll
-        for (int k = 0; k < BD / 16; ++k)
-          umma_f16_lh(tdPt, a_v + k * 2, hi(dV0), b_do + k * 2, hi(ddO0), id_s, k > 0);
-        umma_commit(st_full);
+          for (int k = 0; k < BD / 16; ++k)
+            umma_f16_lh(tdPt, a_v + k * 2, hi(dV0), b_do + k * 2, hi(ddO0), id_s, k > 0);
+          umma_commit(st_full);
+        }
+        __syncwarp();
         SAV_RECB(1, 42);
       };
       auto issue_grads = [&](int q) {
@@ -201,15 +207,18 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         const uint32_t b_k = lo(dKm0) + st * 2 * TILE16;
         const uint32_t acc_j = j > 0;
         // dQ_i[q,d] += dS[q,keys] K_j[keys,d]   (K = keys; A = the dS^T buffer read MN-major)
+        if (elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          if (ks < nk_steps)
-            umma_f16_lh(tdQ + i * BD, lo(ddSm0) + ks * 128, hi(ddSm0), b_k + ks * 128, hi(dKm0),
-                        id_mnmn, ks > 0 ? 1u : acc_j);
-        umma_commit(pds_free);
-        if (i == p.nqt - 1) umma_commit(&kv_empty[st]);
-        if (j == p.nkt - 1) umma_commit(&qdo_empty[i]);
-        if (rem == ppi - 1) umma_commit(dq_full);
+          for (int ks = 0; ks < 8; ++ks)
+            if (ks < nk_steps)
+              umma_f16_lh(tdQ + i * BD, lo(ddSm0) + ks * 128, hi(ddSm0), b_k + ks * 128, hi(dKm0),
+                          id_mnmn, ks > 0 ? 1u : acc_j);
+          umma_commit(pds_free);
+          if (i == p.nqt - 1) umma_commit(&kv_empty[st]);
+          if (j == p.nkt - 1) umma_commit(&qdo_empty[i]);
+          if (rem == ppi - 1) umma_commit(dq_full);
+        }
+        __syncwarp();
         SAV_RECB(1, 45);
       };
       if (total_pairs > 0) issue_sdp(0);
@@ -226,9 +235,8 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   }
   else if (warp == 2) {
     // ------------------------------------------------------------------ second MMA issuer: dV, dK
-    // (tcgen05.mma dispatch from one thread is latency-bound at ~90 cycles per instruction for
-    //  these N = 64 shapes, so the gradient MMAs are split over two issuing warps)
-    if (lane == 0) {
+    // (two issuing warps: the waits of one chain overlap the issue of the other)
+    {
       const uint64_t dQm0 = make_smem_desc(smem_u32(sQ), BT_BYTES, 1024);     // MN-major B of dK
       const uint64_t ddOm0 = make_smem_desc(smem_u32(sdO), BT_BYTES, 1024);   // MN-major B of dV
       const uint64_t dPt0 = make_smem_desc(smem_u32(sPt), 16, 1024);          // K-major A of dV
@@ -248,19 +256,22 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         const uint32_t b_do = lo(ddOm0) + i * TILE16, b_q = lo(dQm0) + i * TILE16;
         const uint32_t acc_i = i > 0;
         // dV[keys,d] += P^T[keys,q] dO_i[q,d];  dK[keys,d] += dS^T[keys,q] Q_i[q,d]   (K = queries)
+        if (elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          if (ks < nq_steps)
-            umma_f16_lh(tdV, lo(dPt0) + (ks >> 2) * TILE16 + (ks & 3) * 2, hi(dPt0), b_do + ks * 128,
-                        hi(ddOm0), id_kmn, ks > 0 ? 1u : acc_i);
+          for (int ks = 0; ks < 8; ++ks)
+            if (ks < nq_steps)
+              umma_f16_lh(tdV, lo(dPt0) + (ks >> 2) * TILE16 + (ks & 3) * 2, hi(dPt0), b_do + ks * 128,
+                          hi(ddOm0), id_kmn, ks > 0 ? 1u : acc_i);
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          if (ks < nq_steps)
-            umma_f16_lh(tdK, lo(ddSt0) + (ks >> 2) * TILE16 + (ks & 3) * 2, hi(ddSt0), b_q + ks * 128,
-                        hi(dQm0), id_kmn, ks > 0 ? 1u : acc_i);
-        umma_commit(pds_free);
-        if (i == p.nqt - 1) umma_commit(dkv_full);
-        if (j == p.nkt - 1) umma_commit(&qdo_empty[i]);
+          for (int ks = 0; ks < 8; ++ks)
+            if (ks < nq_steps)
+              umma_f16_lh(tdK, lo(ddSt0) + (ks >> 2) * TILE16 + (ks & 3) * 2, hi(ddSt0), b_q + ks * 128,
+                          hi(dQm0), id_kmn, ks > 0 ? 1u : acc_i);
+          umma_commit(pds_free);
+          if (i == p.nqt - 1) umma_commit(dkv_full);
+          if (j == p.nkt - 1) umma_commit(&qdo_empty[i]);
+        }
+        __syncwarp();
       }
     }
   }

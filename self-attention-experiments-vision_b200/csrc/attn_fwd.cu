@@ -182,7 +182,8 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   uint64_t* s_free = bars + 18;   // [g]  (128 arrivals)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // warp index through a shuffle: the role branches are then provably warp-uniform for ptxas
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int q_tiles = (p.Nq + FQ - 1) / FQ;
 
   if (tid == 0) {
@@ -240,9 +241,12 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     }
   } else if (warp == 1 || warp == 2) {
     // ------------------------------------------------------------------ MMA issuer of group w
-    if (lane == 0) {
+    // All 32 lanes walk the loop and poll the barriers; one elected lane issues.  With warp-uniform
+    // control flow the descriptors live in uniform registers; issuing from `if (lane == 0)` wraps
+    // every UTCHMMA in a vote / R2UR waterfall (~150 cycles per MMA, several times its run time).
+    {
       const int w = warp - 1;
-      int dbg_n = 0;
+      int dbg_n = lane == 0 ? 0 : 1000;
       const uint32_t region = tmem + w * 256;
       uint32_t uq = 0, g = 0, c = 0;  // Q tiles used, kv blocks seen, blocks processed by this group
       // descriptors are built once; per MMA only the 14-bit start-address field advances
@@ -266,7 +270,11 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           SAV_REC(1 + w, 10);
           mbar_wait_sleep(&kv_full[st], (g >> 1) & 1);
           SAV_REC(1 + w, 11);
-          if (!active) { mbar_arrive(&kv_empty[st]); continue; }
+          if (!active) {
+            if (elect_one()) mbar_arrive(&kv_empty[st]);
+            __syncwarp();
+            continue;
+          }
           if (j == 0) mbar_wait_sleep(&q_full[qb], q_phase);
           mbar_wait_sleep(&s_free[w], (c & 1) ^ 1);
           SAV_REC(1 + w, 12);
@@ -276,24 +284,30 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           const uint64_t dk = dk0 + (uint64_t)(st * ((2 * FKV_BYTES) >> 4));
           const uint64_t dv = dv0 + (uint64_t)(st * ((2 * FKV_BYTES) >> 4));
           const uint32_t id_s = make_idesc_bf16(FQ, n_cur, false, false);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < FD / 16; ++k)  // +32 B per 16-element K step
-            umma_f16_lh(region, (uint32_t)dq + k * 2, (uint32_t)(dq >> 32), (uint32_t)dk + k * 2,
-                        (uint32_t)(dk >> 32), id_s, k > 0);
-          umma_commit(&s_full[w]);
-          if (j == p.nkb - 1) umma_commit(&q_empty[qb]);
+            for (int k = 0; k < FD / 16; ++k)  // +32 B per 16-element K step
+              umma_f16_lh(region, (uint32_t)dq + k * 2, (uint32_t)(dq >> 32), (uint32_t)dk + k * 2,
+                          (uint32_t)(dk >> 32), id_s, k > 0);
+            umma_commit(&s_full[w]);
+            if (j == p.nkb - 1) umma_commit(&q_empty[qb]);
+          }
+          __syncwarp();
           SAV_REC(1 + w, 13);
           mbar_wait_sleep(&p_full[w], c & 1);
           SAV_REC(1 + w, 14);
           tc_fence_after();
           const int ksteps = n_cur >> 4;
+          if (elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < FK / 16; ++ks)  // +8 TMEM columns of P, +2048 B of V per 16 keys
-            if (ks < ksteps)
-              umma_f16_ts_lh(region + 128, region + ks * 8, (uint32_t)dv + ks * 128, (uint32_t)(dv >> 32),
-                             id_pv, ks > 0);
-          umma_commit(&o_full[w]);
-          umma_commit(&kv_empty[st]);
+            for (int ks = 0; ks < FK / 16; ++ks)  // +8 TMEM columns of P, +2048 B of V per 16 keys
+              if (ks < ksteps)
+                umma_f16_ts_lh(region + 128, region + ks * 8, (uint32_t)dv + ks * 128, (uint32_t)(dv >> 32),
+                               id_pv, ks > 0);
+            umma_commit(&o_full[w]);
+            umma_commit(&kv_empty[st]);
+          }
+          __syncwarp();
           SAV_REC(1 + w, 15);
           ++c;
         }

@@ -203,7 +203,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   const int num_tiles = tiles_per_batch * (BATCH ? p.nbatch : 1);
 
   if (warp == 0) {
-    if (lane == 0) {
+    // TMA producer: whole warp walks the loop, one elected lane issues (see the MMA warp)
+    {
+#undef STAMP_LANE
+#define STAMP_LANE (lane == 0)
       int stage = 0;
       uint32_t phase = 0;
       int dbg_n = 0;
@@ -224,12 +227,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           uint8_t* sb = sa + Cfg::kABytes;
           // the leader's full barrier collects the bytes of both CTAs' loads
           if (p.debug & 1) {  // MMA-only rate: operands are whatever the smem holds
-            if (rank == 0) mbar_arrive(&full_bar[stage]);
+            if (rank == 0 && elect_one()) mbar_arrive(&full_bar[stage]);
+            __syncwarp();
             if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
             continue;
           }
-          if (rank == 0) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * CTAS);
           const int k_idx = kb * BK;
+          if (elect_one()) {
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes * CTAS);
           auto load = [&](void* dst, const CUtensorMap* m, int c0, int c1) {
             if (BATCH) tma_load_4d(dst, m, &full_bar[stage], c0, c1, zi, zo);
             else if (CTAS == 2) tma_load_2d_pair(dst, m, &full_bar[stage], c0, c1);
@@ -248,9 +253,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
             for (int j = 0; j < Cfg::kBBoxes; ++j)
               load(sb + j * (BK * 128), &tma_b, n_idx + j * 64, k_idx);
           }
+          }
+          __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
+#undef STAMP_LANE
+#define STAMP_LANE true
     }
   } else if (warp == 1) {
     // The whole warp walks the loop (every lane polls the barriers) and one elected lane issues:
@@ -349,7 +358,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       mbar_expect_tx(&aux_bar[slot], SLAB_BYTES);
       tma_load_2d(smem_out + slot * slot_bytes, &tma_x, &aux_bar[slot], col, row);
     };
-    if (aux_in && leader)
+    if (aux_in && ew == 0 && elect_one())
       for (uint32_t sg = 0; sg + 1 < (uint32_t)nslot && sg < total_slabs; ++sg) issue_aux(sg);
 
     // this warp has read its part of accumulator `a` out of TMEM: one arrival per warp on the
@@ -459,14 +468,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
               make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
       }
       if (!(p.debug & 32)) fence_proxy_async_smem();
-      if (leader) {
-        // every earlier store has finished READING its slab => the slot of slab sg-1 (which
-        // slab sg+nslot-1 reuses; at sg == 0 that slot has never been used) is free
-        tma_store_wait_read<0>();
+      // slot reuse: the writes of slab sg+1 (after this step's barrier) overwrite the slot of slab
+      // sg+1-nslot, so at most nslot-2 earlier stores may still be reading.  With an epilogue
+      // input the prefetch of slab sg+nslot-1 lands in slab sg-1's slot: everything must be read.
+      __syncwarp();
+      if (ew == 0 && elect_one()) {
+        if (!aux_in && !two_out) tma_store_wait_read<2>();
+        else tma_store_wait_read<0>();
         if (aux_in && sg + nslot - 1 < total_slabs) issue_aux(sg + nslot - 1);
       }
       if (!(p.debug & 64)) named_bar_sync(1, kEpiThreads);
-      if (leader) {
+      if (ew == 0 && elect_one()) {
         const int c0 = n_idx + j * SC;
         if (p.epi == EPI_ACCUM) {
           tma_reduce_add_2d(&tma_d, slab, c0, m_idx);
