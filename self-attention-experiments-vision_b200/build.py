@@ -31,12 +31,22 @@ def build(force=False, verbose=False):
     os.makedirs(objdir, exist_ok=True)
     jobs = []
     objs = []
+    # SAV_GEMM_DEV=1: compile the GEMM's development instrumentation in (SAV_GEMM_DEBUG switches and
+    # the role timeline used by tests/tools/gemm_*.sh); the default build carries none of it
+    dev = os.environ.get("SAV_GEMM_DEV", "0") == "1"
+    marker = os.path.join(objdir, ".gemm_dev")
+    was_dev = os.path.exists(marker)
     for s in SOURCES:
         src = os.path.join(CSRC, s)
         obj = os.path.join(objdir, s.replace(".cu", ".o"))
         objs.append(obj)
-        if force or _newer([src] + headers, obj):
-            jobs.append([NVCC] + FLAGS + ["-c", src, "-o", obj])
+        extra = ["-DSAV_GEMM_DEV"] if (dev and s == "gemm.cu") else []
+        if force or _newer([src] + headers, obj) or (s == "gemm.cu" and dev != was_dev):
+            jobs.append([NVCC] + FLAGS + extra + ["-c", src, "-o", obj])
+    if dev:
+        open(marker, "w").close()
+    elif was_dev:
+        os.remove(marker)
 
     def run(cmd):
         if verbose:

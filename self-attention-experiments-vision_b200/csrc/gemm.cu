@@ -24,7 +24,8 @@ constexpr int BM = 128;  // UMMA M
 constexpr int BK = 64;   // 64 bf16 = one 128-byte swizzle row
 constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kGemmThreads = 64 + kEpiThreads;
+constexpr int kStoreWarp = 2 + kEpiWarps;          // issues the epilogue's TMA stores / input loads
+constexpr int kGemmThreads = 64 + kEpiThreads + 32;
 constexpr int SLAB_BYTES = BM * 128;        // 128 rows x 128 B
 constexpr int kOutBytes = 4 * SLAB_BYTES;   // epilogue slab ring: 4 x 16 KB (or 2 x 32 KB)
 
@@ -64,6 +65,9 @@ struct GemmCfg {
   static_assert(kStages >= 3, "too few stages");
 };
 
+__device__ __forceinline__ void named_bar_arrive(int id, int count) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
 __device__ __forceinline__ void named_bar_sync(int id, int count) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
@@ -89,15 +93,49 @@ __device__ __forceinline__ float dgelu_fast(float x) {
   const float du = 0.7978845608028654f + 0.10703222440890037f * x2;
   return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
 }
+// The same two functions on element pairs through the packed fp32x2 pipe: the epilogue of the MLP
+// GEMMs is FP32-issue bound (two warps per scheduler), so halving the instruction count is what
+// shortens it.  Agrees with the scalar versions to fp32 rounding (results are rounded to bf16).
+__device__ __forceinline__ void gelu_fast2(float& a, float& b) {
+  const uint64_t c0 = f2_pack(0.7978845608028654f, 0.7978845608028654f);
+  const uint64_t c1 = f2_pack(0.035677408136300125f, 0.035677408136300125f);
+  const uint64_t hf = f2_pack(0.5f, 0.5f);
+  const uint64_t x = f2_pack(a, b);
+  const uint64_t u = f2_mul(x, f2_fma(c1, f2_mul(x, x), c0));
+  float ua, ub;
+  f2_unpack(u, ua, ub);
+  const uint64_t hx = f2_mul(hf, x);
+  f2_unpack(f2_fma(hx, f2_pack(tanh_fast(ua), tanh_fast(ub)), hx), a, b);
+}
+// (va, vb) *= gelu'(xa, xb)
+__device__ __forceinline__ void dgelu_mul2(float& va, float& vb, float xa, float xb) {
+  const uint64_t c0 = f2_pack(0.7978845608028654f, 0.7978845608028654f);
+  const uint64_t c1 = f2_pack(0.035677408136300125f, 0.035677408136300125f);
+  const uint64_t c2 = f2_pack(0.10703222440890037f, 0.10703222440890037f);
+  const uint64_t hf = f2_pack(0.5f, 0.5f), one = f2_pack(1.f, 1.f), neg1 = f2_pack(-1.f, -1.f);
+  const uint64_t x = f2_pack(xa, xb);
+  const uint64_t x2 = f2_mul(x, x);
+  const uint64_t u = f2_mul(x, f2_fma(c1, x2, c0));
+  float ua, ub;
+  f2_unpack(u, ua, ub);
+  const uint64_t t = f2_pack(tanh_fast(ua), tanh_fast(ub));
+  const uint64_t du = f2_fma(c2, x2, c0);
+  const uint64_t sech2 = f2_fma(f2_mul(neg1, t), t, one);              // 1 - t^2
+  const uint64_t lhs = f2_fma(hf, t, hf);                              // 0.5 (1 + t)
+  const uint64_t g = f2_fma(f2_mul(f2_mul(hf, x), sech2), du, lhs);
+  f2_unpack(f2_mul(f2_pack(va, vb), g), va, vb);
+}
 
 // bias / LayerScale / drop-path on NV consecutive columns starting at `col`
 template <int NV>
-__device__ __forceinline__ void epi_affine(const GemmParams& p, float (&v)[NV], int col, float rs) {
+__device__ __forceinline__ void epi_affine(const GemmParams& p, float (&v)[NV], int col, float rs,
+                                           const float4* bias_pre = nullptr) {
   if (col + NV <= p.N) {
     if (p.bias) {
 #pragma unroll
       for (int j = 0; j < NV; j += 4) {
-        const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
+        const float4 b = bias_pre ? bias_pre[j / 4]
+                                  : __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
         v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
       }
     }
@@ -135,7 +173,12 @@ __device__ __forceinline__ void st_bf16x32(uint8_t* slab, int r, int cb, const f
                    pack_bf16(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16(v[g * 8 + 6], v[g * 8 + 7]));
 }
 
-// development timeline: (event, clock64) pairs of CTA 0, 256 slots per role
+// Development instrumentation, compiled in only with -DSAV_GEMM_DEV (SAV_GEMM_DEV=1 python build.py):
+//  * SAV_GEMM_DEBUG bits switch parts of the kernel off (see launch_gemm) for limit experiments;
+//  * the timeline writes (event, clock64) pairs of CTA 0, 256 slots per role.
+// The production build carries neither: the epilogue is instruction-issue bound.
+#ifdef SAV_GEMM_DEV
+#define GEMM_DBG(bits) (p.debug & (bits))
 #define GEMM_STAMP(role, ev)                                         \
   do {                                                               \
     if (p.dbg && blockIdx.x == 0 && dbg_n < 255 && STAMP_LANE) {     \
@@ -144,6 +187,10 @@ __device__ __forceinline__ void st_bf16x32(uint8_t* slab, int r, int cb, const f
       ++dbg_n;                                                       \
     }                                                                \
   } while (0)
+#else
+#define GEMM_DBG(bits) false
+#define GEMM_STAMP(role, ev) do { (void)dbg_n; } while (0)
+#endif
 
 #define STAMP_LANE true
 
@@ -162,7 +209,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint64_t* aux_bar = tempty_bar + 2;  // [4]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + 4);
+  uint64_t* slot_free = aux_bar + 4;  // [4] slab slot has been read by its TMA store
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(slot_free + 4);
 
   // warp index through a shuffle so that the compiler knows the role branches are warp-uniform
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
@@ -181,7 +229,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], kEpiWarps * CTAS);  // one arrival per epilogue warp (both CTAs)
     }
-    for (int s = 0; s < 4; ++s) mbar_init(&aux_bar[s], 1);
+    for (int s = 0; s < 4; ++s) { mbar_init(&aux_bar[s], 1); mbar_init(&slot_free[s], 1); }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -222,11 +270,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         const int kb0 = split * p.k_per_split;
         const int kb1 = min(kb0 + p.k_per_split, p.k_blocks);
         for (int kb = kb0; kb < kb1; ++kb) {
-          if (!(p.debug & 512)) mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (!(GEMM_DBG(512))) mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
           // the leader's full barrier collects the bytes of both CTAs' loads
-          if (p.debug & 1) {  // MMA-only rate: operands are whatever the smem holds
+          if (GEMM_DBG(1)) {  // MMA-only rate: operands are whatever the smem holds
             if (rank == 0 && elect_one()) mbar_arrive(&full_bar[stage]);
             __syncwarp();
             if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
@@ -288,7 +336,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         for (int kb = kb0; kb < kb1; ++kb) {
           // debug bits 256 / 512 (with bit 1 only): free-running issue without the full-barrier
           // wait / without the per-k-block commit, to separate hand-shake cost from MMA pacing
-          if (!(p.debug & 256)) mbar_wait(&full_bar[stage], phase);
+          if (!(GEMM_DBG(256))) mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           if (kb == kb0) GEMM_STAMP(1, 12);
           const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
@@ -303,8 +351,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           constexpr uint32_t b_step = B_MN ? (2048 >> 4) : (32 >> 4);
           if (elect_one()) {
             // debug bit 128: issue every MMA twice (timing experiment: per-MMA vs per-k-block cost)
-            for (int rep = 0; rep < ((p.debug & 128) ? 2 : 1); ++rep)
-              if (!(p.debug & 2)) {
+            for (int rep = 0; rep < ((GEMM_DBG(128)) ? 2 : 1); ++rep)
+              if (!(GEMM_DBG(2))) {
 #pragma unroll
                 for (int k = 0; k < BK / 16; ++k) {
                   const uint32_t acc_flag = (kb > kb0 || k > 0 || rep > 0) ? 1u : 0u;
@@ -314,7 +362,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                     umma_f16_lh(d_tmem, a_lo + k * a_step, a_hi, b_lo + k * b_step, b_hi, idesc, acc_flag);
                 }
               }
-            if (!(p.debug & 512)) {
+            if (!(GEMM_DBG(512))) {
               if (CTAS == 2) umma_commit_pair(&empty_bar[stage]);
               else umma_commit(&empty_bar[stage]);
             }
@@ -334,9 +382,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     }
   } else {
     // ------------------------------------------------------------------ epilogue (warps 2..9)
+    // and its store warp (warp 10).  The eight epilogue warps turn accumulator slabs into output
+    // slabs in shared memory and only ARRIVE on the slab's named barrier; the store warp waits
+    // there, issues the TMA store, and hands the slot back (slot_free mbarrier, or the arrival of
+    // the next epilogue input loaded into it) once the store has read it.  No epilogue warp ever
+    // waits for a TMA issue or for the other warps.
     const int ew = warp - 2;
     const int sub = warp & 3;                 // TMEM sub-partition this warp may read
-    const int half = ew >> 2;                 // which half of the slab's columns
+    const int half = (ew >> 2) & 1;           // which half of the slab's columns
     const int r = sub * 32 + lane;            // row inside the tile (TMEM lane)
     const bool leader = (ew == 0 && lane == 0);
     const bool f32 = (p.epi == EPI_F32 || p.epi == EPI_ACCUM);
@@ -348,18 +401,81 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     const bool aux_in = p.has_aux_in != 0;
     const int my_tiles = (num_tiles - unit + units - 1) / units;
     const uint32_t total_slabs = (uint32_t)my_tiles * slabs_per_tile;
+    constexpr int kSlabBarThreads = kEpiThreads + 32;
 
-    auto issue_aux = [&](uint32_t sg) {  // leader only: TMA-load the epilogue input of slab sg
-      const int t = unit + (sg / slabs_per_tile) * units;
-      const int mn = t % tiles_mn;
-      const int col = (mn % p.n_blocks) * BN + (sg % slabs_per_tile) * SC;
-      const int row = (mn / p.n_blocks) * (BM * CTAS) + rank * BM;
-      const int slot = sg % nslot;
-      mbar_expect_tx(&aux_bar[slot], SLAB_BYTES);
-      tma_load_2d(smem_out + slot * slot_bytes, &tma_x, &aux_bar[slot], col, row);
-    };
-    if (aux_in && ew == 0 && elect_one())
-      for (uint32_t sg = 0; sg + 1 < (uint32_t)nslot && sg < total_slabs; ++sg) issue_aux(sg);
+    if (warp == kStoreWarp) {
+#undef STAMP_LANE
+#define STAMP_LANE (lane == 0)
+      int dbg_n = 0;
+      // global coordinates of slab sg of this CTA
+      auto slab_coords = [&](uint32_t sg, int& c0, int& row, int& zi, int& zo) {
+        const int tile = unit + (int)(sg / slabs_per_tile) * units;
+        const int mn = tile % tiles_mn;
+        c0 = (mn % p.n_blocks) * BN + (int)(sg % slabs_per_tile) * SC;
+        row = (mn / p.n_blocks) * (BM * CTAS) + rank * BM;
+        const int z = BATCH ? tile / tiles_per_batch : 0;
+        zi = BATCH ? z % p.batch_inner : 0;
+        zo = BATCH ? z / p.batch_inner : 0;
+      };
+      auto issue_aux = [&](uint32_t sg) {  // elected lane: TMA-load the epilogue input of slab sg
+        int c0, row, zi, zo;
+        slab_coords(sg, c0, row, zi, zo);
+        const int slot = sg % nslot;
+        mbar_expect_tx(&aux_bar[slot], SLAB_BYTES);
+        tma_load_2d(smem_out + slot * slot_bytes, &tma_x, &aux_bar[slot], c0, row);
+      };
+      // hand the slot of slab t back: either directly, or by loading the next input into it
+      auto recycle = [&](uint32_t t) {
+        if (aux_in) {
+          if (t + nslot < total_slabs) issue_aux(t + nslot);
+        } else {
+          mbar_arrive(&slot_free[t % nslot]);
+        }
+      };
+      if (aux_in && elect_one())
+        for (uint32_t sg = 0; sg < (uint32_t)nslot && sg < total_slabs; ++sg) issue_aux(sg);
+      __syncwarp();
+      // stores allowed to be still reading when the next one is issued
+      const uint32_t lag = nslot == 4 ? 1 : 0;
+      for (uint32_t sg = 0; sg < total_slabs; ++sg) {
+        const int slot = sg % nslot;
+        named_bar_sync(1 + slot, kSlabBarThreads);
+        GEMM_STAMP(3, 26);
+        if (elect_one()) {
+          int c0, row, zi, zo;
+          slab_coords(sg, c0, row, zi, zo);
+          uint8_t* slab = smem_out + slot * slot_bytes;
+          if (p.epi == EPI_ACCUM) {
+            tma_reduce_add_2d(&tma_d, slab, c0, row);
+          } else if (GEMM_DBG(16)) {   // development: no global stores
+          } else if (two_out) {
+            tma_store_2d(&tma_x, slab, c0, row);
+            tma_store_2d(&tma_d, slab + SLAB_BYTES, c0, row);
+          } else if (BATCH) {
+            tma_store_4d(&tma_d, slab, c0, row, zi, zo);
+          } else {
+            tma_store_2d(&tma_d, slab, c0, row);
+          }
+          tma_store_commit();
+          GEMM_STAMP(3, 28);
+          if (lag == 0) {
+            tma_store_wait_read<0>();
+            recycle(sg);
+          } else {
+            tma_store_wait_read<1>();
+            if (sg >= 1) recycle(sg - 1);
+          }
+          GEMM_STAMP(3, 27);
+        }
+        __syncwarp();
+      }
+      if (elect_one()) {
+        tma_store_wait<0>();
+      }
+      __syncwarp();
+#undef STAMP_LANE
+#define STAMP_LANE true
+    } else {
 
     // this warp has read its part of accumulator `a` out of TMEM: one arrival per warp on the
     // (leader's) tempty barrier
@@ -374,9 +490,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     int m_idx = 0, n_idx = 0, acc = 0, zi = 0, zo = 0;
     float rs = 1.f;
     int dbg_n = leader ? 0 : 1000;
+    // bias of the NEXT slab is fetched while this one is stored, so the (L2-latency) loads never
+    // sit between the TMEM read and the shared-memory writes
+    float4 bias_pre[8];
+    auto tile_col0 = [&](int it_) { return (((unit + it_ * units) % tiles_mn) % p.n_blocks) * BN; };
+    auto prefetch_bias = [&](int it_n, int j_n, int n_idx_n) {  // slab (it_n, j_n) of this CTA
+      if (f32 || !p.bias || it_n >= my_tiles) return;
+      const int col_n = n_idx_n + j_n * SC + half * (SC / 2);
+      if (col_n + 32 <= p.N) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          bias_pre[q] = __ldg(reinterpret_cast<const float4*>(p.bias + col_n + 4 * q));
+      }
+    };
+    prefetch_bias(0, 0, tile_col0(0));
+    int it = 0, j = -1, slot = -1;
+    uint32_t slot_phase = 1;          // parity of the slot ring's current round, inverted
     for (uint32_t sg = 0; sg < total_slabs; ++sg) {
-      const int it = sg / slabs_per_tile;
-      const int j = sg - it * slabs_per_tile;
+      if (++j == slabs_per_tile) { j = 0; ++it; }
+      if (++slot == nslot) { slot = 0; slot_phase ^= 1; }
       if (j == 0) {
         const int tile = unit + it * units;
         const int mn = tile % tiles_mn;
@@ -397,25 +529,27 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           rs = row < p.M ? p.row_scale[row / p.rows_per_scale] : 0.f;
         }
       }
-      const int slot = sg % nslot;
       uint8_t* slab = smem_out + slot * slot_bytes;
       const uint32_t taddr = tmem_base + ((uint32_t)(sub * 32) << 16) + acc * BN + j * SC + half * (SC / 2);
       const int col = n_idx + j * SC + half * (SC / 2);
+      // the slot's previous store has read it (with an epilogue input, its arrival implies that)
+      if (!aux_in) mbar_wait(&slot_free[slot], slot_phase);
       if (!f32) {
         uint32_t rr[32];
-        if (p.debug & 8) {   // development: no TMEM read
+        if (GEMM_DBG(8)) {   // development: no TMEM read
 #pragma unroll
           for (int i = 0; i < 32; ++i) rr[i] = 0x3f800000u;
         } else {
           tmem_ld32(taddr, rr);
           tmem_ld_wait();
         }
+        GEMM_STAMP(2, 23);
         if (j == slabs_per_tile - 1) release_acc(acc);
         float v[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(rr[i]);
         if (p.epi == EPI_DGELU) {
-          mbar_wait(&aux_bar[slot], (sg / nslot) & 1);
+          mbar_wait(&aux_bar[slot], slot_phase ^ 1);
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const uint4 a = *reinterpret_cast<const uint4*>(slab + slab_off(r, half * 4 + g));
@@ -423,24 +557,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               const float2 h = unpack_bf16(w[q]);
-              v[g * 8 + 2 * q] *= dgelu_fast(h.x);
-              v[g * 8 + 2 * q + 1] *= dgelu_fast(h.y);
+              dgelu_mul2(v[g * 8 + 2 * q], v[g * 8 + 2 * q + 1], h.x, h.y);
             }
           }
           st_bf16x32(slab, r, half * 4, v);
         } else {
-          epi_affine<32>(p, v, col, rs);
+          epi_affine<32>(p, v, col, rs, bias_pre);
+          if (j + 1 < slabs_per_tile) prefetch_bias(it, j + 1, n_idx);
+          else prefetch_bias(it + 1, 0, tile_col0(it + 1));
           if (two_out) {
             st_bf16x32(slab, r, half * 4, v);  // pre-activation (saved for backward)
-            if (!(p.debug & 4)) {
+            if (!(GEMM_DBG(4))) {
 #pragma unroll
-              for (int i = 0; i < 32; ++i) v[i] = gelu_fast(v[i]);
+              for (int i = 0; i < 32; i += 2) gelu_fast2(v[i], v[i + 1]);
             }
             st_bf16x32(slab + SLAB_BYTES, r, half * 4, v);
           } else {
             if (p.act == 1) {
 #pragma unroll
-              for (int i = 0; i < 32; ++i) v[i] = gelu_fast(v[i]);
+              for (int i = 0; i < 32; i += 2) gelu_fast2(v[i], v[i + 1]);
             }
             st_bf16x32(slab, r, half * 4, v);
           }
@@ -455,7 +590,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(rr[i]);
         if (p.epi == EPI_F32) epi_affine<16>(p, v, col, rs);
         if (aux_in) {
-          mbar_wait(&aux_bar[slot], (sg / nslot) & 1);
+          mbar_wait(&aux_bar[slot], slot_phase ^ 1);
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const float4 a = *reinterpret_cast<const float4*>(slab + slab_off(r, half * 4 + g));
@@ -467,35 +602,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           *reinterpret_cast<float4*>(slab + slab_off(r, half * 4 + g)) =
               make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
       }
-      if (!(p.debug & 32)) fence_proxy_async_smem();
-      // slot reuse: the writes of slab sg+1 (after this step's barrier) overwrite the slot of slab
-      // sg+1-nslot, so at most nslot-2 earlier stores may still be reading.  With an epilogue
-      // input the prefetch of slab sg+nslot-1 lands in slab sg-1's slot: everything must be read.
-      __syncwarp();
-      if (ew == 0 && elect_one()) {
-        if (!aux_in && !two_out) tma_store_wait_read<2>();
-        else tma_store_wait_read<0>();
-        if (aux_in && sg + nslot - 1 < total_slabs) issue_aux(sg + nslot - 1);
-      }
-      if (!(p.debug & 64)) named_bar_sync(1, kEpiThreads);
-      if (ew == 0 && elect_one()) {
-        const int c0 = n_idx + j * SC;
-        if (p.epi == EPI_ACCUM) {
-          tma_reduce_add_2d(&tma_d, slab, c0, m_idx);
-        } else if (p.debug & 16) {   // development: no global stores
-        } else if (two_out) {
-          tma_store_2d(&tma_x, slab, c0, m_idx);
-          tma_store_2d(&tma_d, slab + SLAB_BYTES, c0, m_idx);
-        } else if (BATCH) {
-          tma_store_4d(&tma_d, slab, c0, m_idx, zi, zo);
-        } else {
-          tma_store_2d(&tma_d, slab, c0, m_idx);
-        }
-        tma_store_commit();
-        if (j == slabs_per_tile - 1) GEMM_STAMP(2, 22);
-      }
+      GEMM_STAMP(2, 24);
+      if (!(GEMM_DBG(32))) fence_proxy_async_smem();
+      GEMM_STAMP(2, 25);
+      named_bar_arrive(1 + slot, kSlabBarThreads);   // never blocks: the store warp does the waiting
     }
-    if (leader) tma_store_wait<0>();
+    }
   }
   tc_fence_before();
   __syncthreads();

@@ -1,3 +1,4 @@
+# Needs a dev build: SAV_GEMM_DEV=1 python self-attention-experiments-vision_b200/build.py
 export SAV_TIME_ONLY=t_sq,t_fc1_dw,t_fc2_dw,t_fc1_dx,t_fc1_fwd
 for c in 1 2; do for d in 0 1 2; do echo "== ctas=$c debug=$d"; SAV_GEMM_CTAS=$c SAV_GEMM_DEBUG=$d timeout 200 python tests/gpu_diag.py --time; done; done
 python - <<'PY'

@@ -1,3 +1,4 @@
+# Needs a dev build: SAV_GEMM_DEV=1 python self-attention-experiments-vision_b200/build.py
 # MMA-only cost per tile (24 k-blocks = 96 MMAs) by accumulator width and CTA-pair mode:
 # loads, TMEM reads and stores disabled (bits 1+8+16), so the tile period is pure issue pacing.
 #  +128 issues every MMA twice; +256 no full-barrier wait; +512 no per-k-block commit / empty wait

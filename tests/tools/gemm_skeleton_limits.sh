@@ -1,3 +1,4 @@
+# Needs a dev build: SAV_GEMM_DEV=1 python self-attention-experiments-vision_b200/build.py
 # Which part of the empty GEMM skeleton costs time?  (development; bits 32 = no proxy fence,
 # 64 = no per-slab named barrier -- timing only, results are garbage)
 export SAV_TIME_ONLY=t_fc1_fwd,t_qkv_fwd,t_fc1_dx
