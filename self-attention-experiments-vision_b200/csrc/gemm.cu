@@ -22,7 +22,8 @@ namespace sav {
 
 constexpr int BM = 128;  // UMMA M
 constexpr int BK = 64;   // 64 bf16 = one 128-byte swizzle row
-constexpr int kEpiWarps = 8;
+constexpr int kEpiWarps = 16;                        // four per TMEM sub-partition / scheduler
+constexpr int kColParts = kEpiWarps / 4;             // column parts of a slab (one per warp of a sub-partition)
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kStoreWarp = 2 + kEpiWarps;          // issues the epilogue's TMA stores / input loads
 constexpr int kGemmThreads = 64 + kEpiThreads + 32;
@@ -165,9 +166,10 @@ __device__ __forceinline__ void epi_affine(const GemmParams& p, float (&v)[NV], 
 __device__ __forceinline__ uint32_t slab_off(int r, int c) {
   return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4));
 }
-__device__ __forceinline__ void st_bf16x32(uint8_t* slab, int r, int cb, const float (&v)[32]) {
+template <int NV>
+__device__ __forceinline__ void st_bf16(uint8_t* slab, int r, int cb, const float (&v)[NV]) {
 #pragma unroll
-  for (int g = 0; g < 4; ++g)
+  for (int g = 0; g < NV / 8; ++g)
     *reinterpret_cast<uint4*>(slab + slab_off(r, cb + g)) =
         make_uint4(pack_bf16(v[g * 8 + 0], v[g * 8 + 1]), pack_bf16(v[g * 8 + 2], v[g * 8 + 3]),
                    pack_bf16(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16(v[g * 8 + 6], v[g * 8 + 7]));
@@ -389,7 +391,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     // waits for a TMA issue or for the other warps.
     const int ew = warp - 2;
     const int sub = warp & 3;                 // TMEM sub-partition this warp may read
-    const int half = (ew >> 2) & 1;           // which half of the slab's columns
+    const int part = (ew >> 2) & (kColParts - 1);   // which column part of the slab
     const int r = sub * 32 + lane;            // row inside the tile (TMEM lane)
     const bool leader = (ew == 0 && lane == 0);
     const bool f32 = (p.epi == EPI_F32 || p.epi == EPI_ACCUM);
@@ -492,14 +494,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     int dbg_n = leader ? 0 : 1000;
     // bias of the NEXT slab is fetched while this one is stored, so the (L2-latency) loads never
     // sit between the TMEM read and the shared-memory writes
-    float4 bias_pre[8];
+    constexpr int CB = 64 / kColParts;   // columns per thread, bf16 slabs (64 accumulator columns)
+    constexpr int CF = 32 / kColParts;   // columns per thread, fp32 slabs (32 accumulator columns)
+    float4 bias_pre[CB / 4];
     auto tile_col0 = [&](int it_) { return (((unit + it_ * units) % tiles_mn) % p.n_blocks) * BN; };
     auto prefetch_bias = [&](int it_n, int j_n, int n_idx_n) {  // slab (it_n, j_n) of this CTA
       if (f32 || !p.bias || it_n >= my_tiles) return;
-      const int col_n = n_idx_n + j_n * SC + half * (SC / 2);
-      if (col_n + 32 <= p.N) {
+      const int col_n = n_idx_n + j_n * SC + part * CB;
+      if (col_n + CB <= p.N) {
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
+        for (int q = 0; q < CB / 4; ++q)
           bias_pre[q] = __ldg(reinterpret_cast<const float4*>(p.bias + col_n + 4 * q));
       }
     };
@@ -530,29 +534,31 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         }
       }
       uint8_t* slab = smem_out + slot * slot_bytes;
-      const uint32_t taddr = tmem_base + ((uint32_t)(sub * 32) << 16) + acc * BN + j * SC + half * (SC / 2);
-      const int col = n_idx + j * SC + half * (SC / 2);
+      const uint32_t taddr = tmem_base + ((uint32_t)(sub * 32) << 16) + acc * BN + j * SC + part * (SC / kColParts);
+      const int col = n_idx + j * SC + part * (SC / kColParts);
       // the slot's previous store has read it (with an epilogue input, its arrival implies that)
       if (!aux_in) mbar_wait(&slot_free[slot], slot_phase);
+      constexpr int CH = 2;   // 16-byte chunks per thread and slab row (CB bf16 or CF floats = 32 B)
+      static_assert(CB * 2 == CH * 16 && CF * 4 == CH * 16, "epilogue warp layout");
       if (!f32) {
-        uint32_t rr[32];
+        uint32_t rr[CB];
         if (GEMM_DBG(8)) {   // development: no TMEM read
 #pragma unroll
-          for (int i = 0; i < 32; ++i) rr[i] = 0x3f800000u;
+          for (int i = 0; i < CB; ++i) rr[i] = 0x3f800000u;
         } else {
-          tmem_ld32(taddr, rr);
+          tmem_ld16(taddr, rr);
           tmem_ld_wait();
         }
         GEMM_STAMP(2, 23);
         if (j == slabs_per_tile - 1) release_acc(acc);
-        float v[32];
+        float v[CB];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(rr[i]);
+        for (int i = 0; i < CB; ++i) v[i] = __uint_as_float(rr[i]);
         if (p.epi == EPI_DGELU) {
           mbar_wait(&aux_bar[slot], slot_phase ^ 1);
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const uint4 a = *reinterpret_cast<const uint4*>(slab + slab_off(r, half * 4 + g));
+          for (int g = 0; g < CH; ++g) {
+            const uint4 a = *reinterpret_cast<const uint4*>(slab + slab_off(r, part * CH + g));
             const uint32_t w[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -560,46 +566,46 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
               dgelu_mul2(v[g * 8 + 2 * q], v[g * 8 + 2 * q + 1], h.x, h.y);
             }
           }
-          st_bf16x32(slab, r, half * 4, v);
+          st_bf16<CB>(slab, r, part * CH, v);
         } else {
-          epi_affine<32>(p, v, col, rs, bias_pre);
+          epi_affine<CB>(p, v, col, rs, bias_pre);
           if (j + 1 < slabs_per_tile) prefetch_bias(it, j + 1, n_idx);
           else prefetch_bias(it + 1, 0, tile_col0(it + 1));
           if (two_out) {
-            st_bf16x32(slab, r, half * 4, v);  // pre-activation (saved for backward)
+            st_bf16<CB>(slab, r, part * CH, v);  // pre-activation (saved for backward)
             if (!(GEMM_DBG(4))) {
 #pragma unroll
-              for (int i = 0; i < 32; i += 2) gelu_fast2(v[i], v[i + 1]);
+              for (int i = 0; i < CB; i += 2) gelu_fast2(v[i], v[i + 1]);
             }
-            st_bf16x32(slab + SLAB_BYTES, r, half * 4, v);
+            st_bf16<CB>(slab + SLAB_BYTES, r, part * CH, v);
           } else {
             if (p.act == 1) {
 #pragma unroll
-              for (int i = 0; i < 32; i += 2) gelu_fast2(v[i], v[i + 1]);
+              for (int i = 0; i < CB; i += 2) gelu_fast2(v[i], v[i + 1]);
             }
-            st_bf16x32(slab, r, half * 4, v);
+            st_bf16<CB>(slab, r, part * CH, v);
           }
         }
       } else {
-        uint32_t rr[16];
-        tmem_ld16(taddr, rr);
+        uint32_t rr[CF];
+        tmem_ld8(taddr, rr);
         tmem_ld_wait();
         if (j == slabs_per_tile - 1) release_acc(acc);
-        float v[16];
+        float v[CF];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(rr[i]);
-        if (p.epi == EPI_F32) epi_affine<16>(p, v, col, rs);
+        for (int i = 0; i < CF; ++i) v[i] = __uint_as_float(rr[i]);
+        if (p.epi == EPI_F32) epi_affine<CF>(p, v, col, rs);
         if (aux_in) {
           mbar_wait(&aux_bar[slot], slot_phase ^ 1);
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const float4 a = *reinterpret_cast<const float4*>(slab + slab_off(r, half * 4 + g));
+          for (int g = 0; g < CH; ++g) {
+            const float4 a = *reinterpret_cast<const float4*>(slab + slab_off(r, part * CH + g));
             v[g * 4] += a.x; v[g * 4 + 1] += a.y; v[g * 4 + 2] += a.z; v[g * 4 + 3] += a.w;
           }
         }
 #pragma unroll
-        for (int g = 0; g < 4; ++g)
-          *reinterpret_cast<float4*>(slab + slab_off(r, half * 4 + g)) =
+        for (int g = 0; g < CH; ++g)
+          *reinterpret_cast<float4*>(slab + slab_off(r, part * CH + g)) =
               make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
       }
       GEMM_STAMP(2, 24);
