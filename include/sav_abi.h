@@ -110,6 +110,12 @@ int sav_bgemm(const sav_bgemm_args* a, void* stream);
 /* column sums: out[n] (+)= sum_m X[m,n]   (bias gradients; ff.py:24,27 reverse-mode) */
 int sav_colsum_bf16(const void* X, int64_t M, int64_t N, int64_t ldx, float* out,
                     int32_t accumulate, void* stream);
+/* Same result without same-address atomics: row-split partial sums go to `workspace` (device,
+ * >= sav_colsum_workspace_bytes(M, N) bytes, 16 B aligned, contents don't matter), a second small
+ * kernel folds them into out.  Deterministic summation order. */
+int64_t sav_colsum_workspace_bytes(int64_t M, int64_t N);
+int sav_colsum_bf16_ws(const void* X, int64_t M, int64_t N, int64_t ldx, float* out,
+                       int32_t accumulate, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------- LayerNorm (vit.py:19,26,57)
  * Flax nn.LayerNorm: fp32 stats, var = E[x^2]-E[x]^2, eps inside rsqrt, y = xhat*scale + bias.

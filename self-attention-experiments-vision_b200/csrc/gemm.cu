@@ -673,6 +673,92 @@ colsum_kernel(const bf16* __restrict__ X, int64_t M, int64_t N, int64_t ldx, flo
   }
 }
 
+// ---- two-pass column sums.  The one-kernel version above ends in one red.add per column and
+// block: with ~600 row splits that is ~600 same-address atomics per column, serialised in L2
+// (N = 384: 56 us for 39 MB).  Here every block stores its partial row; a second kernel folds them.
+// A block reads whole rows of a column group (width chosen so that lanes x rows-per-pass fills
+// the 256 threads: N = 384 -> one group, 5 rows per pass; 1536 -> three groups of 512, 4 rows), so
+// each pass is one contiguous chunk of memory and the blocks of the grid sweep the matrix like a
+// grid-stride copy; 8 independent 16-byte loads in flight per thread.
+__global__ void __launch_bounds__(256)
+colsum_partial_kernel(const bf16* __restrict__ X, int64_t M, int64_t N, int64_t ldx,
+                      float* __restrict__ part, int W) {
+  __shared__ float red[256 * 8];
+  const int64_t c0 = (int64_t)blockIdx.x * W;   // column group of W <= 2048 columns
+  const int width = (int)((N - c0) < W ? (N - c0) : W);
+  const int lanes = width / 8;          // threads per row
+  const int rpp = 256 / lanes;          // rows per pass
+  const int rl = threadIdx.x / lanes, cl = threadIdx.x - rl * lanes;
+  float acc[8] = {};
+  if (rl < rpp) {
+    const bf16* px = X + c0 + cl * 8;
+    const int64_t step = (int64_t)gridDim.y * rpp;
+    int64_t r = (int64_t)blockIdx.y * rpp + rl;
+    auto add = [&](const uint4& u) {
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 a = unpack_bf16(w[j]);
+        acc[2 * j] += a.x;
+        acc[2 * j + 1] += a.y;
+      }
+    };
+    // batches of 8 loads, all issued before the first add (volatile asm keeps ptxas from
+    // interleaving them with the adds, which left two or three in flight); rows past the end are
+    // predicated off and contribute zeros, so there is no serial tail
+    for (; r < M; r += 8 * step) {
+      uint4 u[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int64_t ri = r + i * step;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+            "mov.u32 %0, 0;\n\tmov.u32 %1, 0;\n\tmov.u32 %2, 0;\n\tmov.u32 %3, 0;\n\t"
+            "@p ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}\n"
+            : "=&r"(u[i].x), "=&r"(u[i].y), "=&r"(u[i].z), "=&r"(u[i].w)
+            : "l"(px + ri * ldx), "r"((int)(ri < M)));
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) add(u[i]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.x * 8 + j] = acc[j];   // [rl][cl*8 + j], row pitch lanes*8
+  __syncthreads();
+  for (int c = threadIdx.x; c < width; c += 256) {
+    float v = 0.f;
+    for (int y = 0; y < rpp; ++y) v += red[y * lanes * 8 + c];
+    part[(int64_t)blockIdx.y * N + c0 + c] = v;
+  }
+}
+// out[n] (+)= sum_y part[y][n];  block = 32 columns x 32 row lanes, four loads in flight per thread
+// (the grid is only N/32 blocks, so the partials must be walked wide, not deep)
+__global__ void __launch_bounds__(1024)
+colsum_finish_kernel(const float* __restrict__ part, int64_t Y, int64_t N, float* __restrict__ out,
+                     int accumulate) {
+  __shared__ float red[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t n = (int64_t)blockIdx.x * 32 + tx;
+  float a[4] = {};
+  if (n < N) {
+    for (int64_t y = ty; y < Y; y += 128) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int64_t yi = y + 32 * i;
+        a[i] += yi < Y ? part[yi * N + n] : 0.f;
+      }
+    }
+  }
+  red[ty][tx] = (a[0] + a[1]) + (a[2] + a[3]);
+  __syncthreads();
+  if (ty == 0 && n < N) {
+    float v = accumulate ? out[n] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v += red[j][tx];
+    out[n] = v;
+  }
+}
+
 __global__ void fill_kernel(float* p, float v, int64_t n) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
        i += (int64_t)gridDim.x * blockDim.x)
@@ -928,6 +1014,67 @@ extern "C" int sav_fill_f32(float* ptr, float v, int64_t n, void* stream) {
   fill_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(ptr, v, n);
   count_launch();
   return check_launch("sav_fill_f32");
+}
+
+// column groups: N = gx * W with W % 8 == 0 when possible (else 2048-wide groups with a narrower
+// last one), gx picked to keep the most threads busy.  Power-of-two widths are avoided: blocks of
+// the same rows then start 256 B / 512 B / 1 KB apart and camp on the same HBM channels (measured,
+// N = 1536: W = 512 / 256 / 128 -> 42-45 us, W = 384 / 192 -> 33 us; profiles/r01j_colsum_w.log).
+static void colsum_plan(int64_t N, int64_t* gx_out, int64_t* W_out) {
+  const int64_t g0 = (N + 2047) / 2048;
+  int64_t best_g = g0, best_w = N < 2048 ? N : 2048, best_active = 0;
+  for (int64_t g = g0; g < g0 + 8; ++g) {
+    if (N % (g * 8) != 0) continue;
+    const int64_t w = N / g;
+    if ((w & (w - 1)) == 0) continue;
+    const int64_t lanes = w / 8, active = lanes * (256 / lanes);
+    if (active > best_active) { best_active = active; best_g = g; best_w = w; }
+  }
+  static int forced = -1;   // development override: SAV_COLSUM_W=<group width>
+  if (forced < 0) {
+    const char* e = getenv("SAV_COLSUM_W");
+    forced = e ? atoi(e) : 0;
+  }
+  if (forced >= 8 && forced <= 2048 && forced % 8 == 0 && N % forced == 0) {
+    best_g = N / forced;
+    best_w = forced;
+  }
+  *gx_out = best_g;
+  *W_out = best_w;
+}
+static int64_t colsum_splits(int64_t M, int64_t N) {
+  int64_t gx, W;
+  colsum_plan(N, &gx, &W);
+  int64_t want = (num_sms() * 8 + gx - 1) / gx;
+  const int64_t rpp = 256 / (W / 8);
+  const int64_t maxy = (M + rpp * 16 - 1) / (rpp * 16);   // at least two full load batches per thread
+  if (want > maxy) want = maxy;
+  return want < 1 ? 1 : want;
+}
+extern "C" int64_t sav_colsum_workspace_bytes(int64_t M, int64_t N) {
+  if (M <= 0 || N <= 0) return 0;
+  return colsum_splits(M, N) * N * (int64_t)sizeof(float);
+}
+extern "C" int sav_colsum_bf16_ws(const void* X, int64_t M, int64_t N, int64_t ldx, float* out,
+                                  int32_t accumulate, void* workspace, int64_t workspace_bytes,
+                                  void* stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (M <= 0 || N <= 0 || N % 8 || ldx % 8 || !aligned16(X))
+    return set_error(SAV_ERR_SHAPE, "sav_colsum: need N, ldx multiples of 8 and a 16 B aligned base");
+  if (!workspace || !aligned16(workspace) || workspace_bytes < sav_colsum_workspace_bytes(M, N))
+    return set_error(SAV_ERR_ARG, "sav_colsum_bf16_ws: workspace missing, misaligned or too small");
+  const int64_t Y = colsum_splits(M, N);
+  int64_t gx, W;
+  colsum_plan(N, &gx, &W);
+  dim3 grid((unsigned)gx, (unsigned)Y);
+  float* part = reinterpret_cast<float*>(workspace);
+  colsum_partial_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const bf16*>(X), M, N, ldx, part, (int)W);
+  count_launch();
+  int rc = check_launch("sav_colsum_bf16_ws");
+  if (rc) return rc;
+  colsum_finish_kernel<<<(unsigned)((N + 31) / 32), 1024, 0, st>>>(part, Y, N, out, accumulate);
+  count_launch();
+  return check_launch("sav_colsum_bf16_ws");
 }
 
 extern "C" int sav_colsum_bf16(const void* X, int64_t M, int64_t N, int64_t ldx, float* out,

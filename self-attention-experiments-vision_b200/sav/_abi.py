@@ -105,6 +105,8 @@ SIGNATURES = {
     "sav_batchnorm_fwd": (C.c_int, [_P, _P, _P, _P, _P, _F, _P, _P, _P, _P, _I64, _I64, _P]),
     "sav_batchnorm_bwd": (C.c_int, [_P] * 9 + [_I64, _I64, _P]),
     "sav_colsum_bf16": (C.c_int, [_P, _I64, _I64, _I64, _P, _I32, _P]),
+    "sav_colsum_workspace_bytes": (C.c_int64, [_I64, _I64]),
+    "sav_colsum_bf16_ws": (C.c_int, [_P, _I64, _I64, _I64, _P, _I32, _P, _I64, _P]),
     "sav_layernorm_fwd": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _P, _P, _I64, _I64, _F, _P]),
     "sav_layernorm_bwd": (C.c_int, [_P, _I64, _P, _I64] + [_P] * 8 + [_I64, _I64, _P]),
     "sav_patchify": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _I64, _I64, _I32, _P]),

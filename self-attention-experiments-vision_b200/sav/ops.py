@@ -85,12 +85,23 @@ def gemm(A, B, *, a_mn=False, b_mn=False, out=None, out_fp32=False, bias=None, a
     return out
 
 
+_COLSUM_WS = {}
+
+
 def colsum(X, out=None, accumulate=False):
+    """out[n] (+)= sum_m X[m,n] through the two-pass entry point (row-split partials in a cached
+    per-device workspace, no same-address atomics)."""
     _req(X, BF16, "X")
     M, N = X.shape
     if out is None:
         out = torch.empty(N, dtype=F32, device=X.device)
-    check(lib().sav_colsum_bf16(_p(X), M, N, X.stride(0), _p(out), int(accumulate), _stream()))
+    need = int(lib().sav_colsum_workspace_bytes(M, N))
+    ws = _COLSUM_WS.get(X.device)
+    if ws is None or ws.numel() < need:
+        # allocated outside CUDA-graph capture by the eager warm-up step; the stream orders its reuse
+        ws = _COLSUM_WS[X.device] = torch.empty(max(need, 16 << 20), dtype=torch.uint8, device=X.device)
+    check(lib().sav_colsum_bf16_ws(_p(X), M, N, X.stride(0), _p(out), int(accumulate), _p(ws),
+                                   ws.numel(), _stream()))
     return out
 
 
