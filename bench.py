@@ -283,8 +283,12 @@ def main():
                            "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s",
                            "frac": gbs / pk["hbm"],
                            # dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set
-                           # full capture profiles/r01c_ncu_full_fc1_fwd.txt (same shape)
-                           "traffic": 289.67e6, "algorithmic_bytes": alg_bytes, "ms": ms,
+                           # full capture profiles/r01j_ncu_full_fc1_fwd.txt (same shape): 40.0 MB read
+                           # + 249.4 MB written (the tail of the 310 MB output is still in L2)
+                           "traffic": 289.36e6, "algorithmic_bytes": alg_bytes, "ms": ms,
+                           # 89 % of the bytes are writes; write-only HBM peak on this pool is
+                           # 3.76-3.9 TB/s (tests/tools/hbm_write_peak.py) against 6.5 TB/s for a copy
+                           "write_bytes": 2 * M_ * H_ * 2,
                            "tensor_tflops": tf, "tensor_frac_of_burst_peak": tf / pk["tf_burst"],
                            "peak_source": pk["src"] + " (copy bandwidth; kernel timed alone)"}
         if world == 1 and not args.no_cpu_baseline:
