@@ -1,15 +1,18 @@
 // Persistent warp-specialised bf16 GEMM for sm_100a: TMA -> 128B-swizzled smem ring -> tcgen05.mma
 // (accumulators double-buffered in TMEM) -> fused epilogue -> swizzled smem slab -> TMA store.
-// One CTA per SM, 320 threads:
-//   warp 0     TMA producer (one elected lane)
-//   warp 1     MMA issuer (one lane) + TMEM allocator
-//   warps 2-9  epilogue: every 128-row x 128-byte output slab is produced by all 8 warps (two warps
-//              per TMEM sub-partition, half of the slab's columns each): tcgen05.ld -> bias / GELU /
-//              dGELU / LayerScale / drop-path / residual -> smem slab -> one TMA store (coalesced,
-//              clipped at the M/N edges).  Epilogue *inputs* (fp32 residual stream, saved GELU
-//              pre-activation) are TMA-loaded into the very slab buffer they are combined in, a few
-//              slabs ahead, so the K=384 GEMMs of the block -- which sit on the HBM/tensor ridge --
-//              stream their epilogue traffic at full width.
+// One CTA (or a cta_group::2 pair on 256-row tiles) per SM, 608 threads:
+//   warp 0       TMA producer   } whole warp walks the loop, one elect.sync lane issues: warp-uniform
+//   warp 1       MMA issuer     } control flow keeps descriptors in uniform registers (no per-MMA
+//                               } vote / R2UR waterfall); warp 1 also owns the TMEM allocation
+//   warps 2-17   epilogue: every 128-row x 128-byte output slab is produced by all 16 warps (four per
+//                TMEM sub-partition, a quarter of the slab's columns each): tcgen05.ld -> bias / GELU /
+//                dGELU / LayerScale / drop-path / residual -> smem slab -> fence.proxy.async ->
+//                bar.arrive on the slot's named barrier.  They never wait for a store or each other.
+//   warp 18      store warp: bar.sync on the slot's barrier -> one TMA store (coalesced, clipped at
+//                the M/N edges) -> wait_group.read -> slot handed back (slot_free mbarrier, or the
+//                TMA load of the next epilogue input into it).  Epilogue *inputs* (fp32 residual
+//                stream, saved GELU pre-activation) land in the very slab buffer they are combined
+//                in, four slabs ahead.
 // Operands may be K-major or MN-major (selected by the smem + instruction descriptors), so
 // forward (X W), dX (dY W^T) and dW (X^T dY) all run here without any transposed copies.  dW is
 // split over K (tokens) and the partial tiles are combined with TMA reduce-add (fp32) in L2.
