@@ -183,7 +183,9 @@ def main():
     if world > 1:
         from sav.dp import DataParallel
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        dp = DataParallel()
+        # development knobs for the exchange: bucket size (MB) and overlap with backward
+        dp = DataParallel(bucket_mb=float(os.environ.get("SAV_DP_BUCKET_MB", "16")),
+                          overlap=os.environ.get("SAV_DP_OVERLAP", "1") == "1")
     W = max(3, args.warmup)
     K = args.steps
     B = args.batch
