@@ -1,0 +1,70 @@
+"""Bias-gradient column sums (reverse mode of the bias adds in ff.py:24,27 and attention.py:29-37,
+60-63) through the C ABI: the two-pass entry point `sav_colsum_bf16_ws` and the workspace-free
+`sav_colsum_bf16`, against an fp64 CPU sum of the same bf16 values.
+
+Tolerance: the kernels add bf16 values in fp32; with M rows the rounding error of a column sum is
+bounded by M * 2^-24 * sum|x|, so the test asserts |d| <= 1e-5 * sum|x| + 1e-6 per column."""
+import ctypes
+
+import pytest
+import torch
+
+SHAPES = [(1, 8), (7, 24), (256, 1000), (1576, 192), (50432, 384), (1576, 3072), (333, 2056),
+          (12608, 768), (5000, 1152), (4097, 1536)]
+
+
+def _ref(x):
+    xd = x.detach().cpu().double()
+    return xd.sum(0), xd.abs().sum(0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N", SHAPES)
+def test_colsum_two_pass_matches_fp64_sum(M, N):
+    from sav import ops
+    g = torch.Generator().manual_seed(M * 131 + N)
+    x = torch.randn((M, N), generator=g).bfloat16().cuda()
+    ref, mag = _ref(x)
+    out = ops.colsum(x)
+    assert out.dtype == torch.float32 and out.shape == (N,)
+    err = (out.cpu().double() - ref).abs()
+    assert bool((err <= 1e-5 * mag + 1e-6).all()), float((err / (mag + 1e-6)).max())
+    # accumulate=True adds to what is there (gradient arena semantics)
+    base = torch.randn((N,), generator=g).cuda()
+    out2 = ops.colsum(x, out=base.clone(), accumulate=True)
+    err2 = (out2.cpu().double() - (ref + base.cpu().double())).abs()
+    assert bool((err2 <= 1e-5 * mag + 1e-5).all())
+
+
+@pytest.mark.gpu
+def test_colsum_strided_view_and_legacy_entry_point():
+    from sav import _abi, ops
+    g = torch.Generator().manual_seed(5)
+    wide = torch.randn((3000, 1152 + 16), generator=g).bfloat16().cuda()
+    x = wide[:, 8:8 + 1152]                       # row pitch 1168, 16-byte aligned start
+    ref, mag = _ref(x)
+    out = ops.colsum(x)
+    assert bool(((out.cpu().double() - ref).abs() <= 1e-5 * mag + 1e-6).all())
+    # the workspace-free entry point must agree
+    lib = _abi.lib()
+    legacy = torch.zeros(1152, device="cuda")
+    rc = lib.sav_colsum_bf16(ctypes.c_void_p(x.data_ptr()), 3000, 1152, x.stride(0),
+                             ctypes.c_void_p(legacy.data_ptr()), 0,
+                             ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    assert bool(((legacy.cpu().double() - ref).abs() <= 1e-5 * mag + 1e-6).all())
+
+
+@pytest.mark.gpu
+def test_colsum_rejects_small_workspace():
+    from sav import _abi
+    lib = _abi.lib()
+    x = torch.zeros((64, 64), dtype=torch.bfloat16, device="cuda")
+    out = torch.zeros(64, device="cuda")
+    ws = torch.zeros(16, dtype=torch.uint8, device="cuda")
+    need = lib.sav_colsum_workspace_bytes(64, 64)
+    assert need > 16
+    rc = lib.sav_colsum_bf16_ws(ctypes.c_void_p(x.data_ptr()), 64, 64, 64, ctypes.c_void_p(out.data_ptr()), 0,
+                                ctypes.c_void_p(ws.data_ptr()), 16,
+                                ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc != 0
