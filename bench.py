@@ -241,15 +241,30 @@ def main():
     loss_val = loss.item()
     value = B * world * K / (total_ms * 1e-3)
 
-    # e2e: every step copies its inputs from pinned host memory and reads the loss back
-    def e2e_step():
-        images.copy_(images_host, non_blocking=True)
-        labels.copy_(labels_host, non_blocking=True)
-        l = step()
-        return l.item()
-    for _ in range(2):
-        e2e_step()
-    e2e_ms = timed(e2e_step, K)
+    # e2e: every step copies its inputs from pinned host memory and reads the loss back.  Through
+    # the graphed step's host-fed API the copy of batch i+1 is issued right after step i is
+    # launched (double-buffered staging, sav/train.py), so K host->device copies happen inside
+    # the timed region and only the first one is exposed.
+    if args.no_graph:
+        def e2e_step():
+            images.copy_(images_host, non_blocking=True)
+            labels.copy_(labels_host, non_blocking=True)
+            l = step()
+            return l.item()
+
+        def e2e_loop(n):
+            for _ in range(n):
+                e2e_step()
+    else:
+        def e2e_loop(n):
+            step.prefetch(images_host, labels_host)
+            for i in range(n):
+                l = step.step_prefetched()
+                if i + 1 < n:
+                    step.prefetch(images_host, labels_host)
+                l.item()
+    e2e_loop(2)
+    e2e_ms = timed(lambda: e2e_loop(K), 1)
     clk.__exit__()   # clocks / throttle reasons sampled across both timed regions
     e2e_value = B * world * K / (e2e_ms * 1e-3)
 
