@@ -204,7 +204,7 @@ int sav_attn_bwd(const sav_attn_bwd_args* a, void* stream);
  *                                                       (botnet.py:78-141; q = qy*W+qx, k = ky*W+kx)
  *   p = softmax_k(logits)                                             (attention.py:48)
  *   P[b,j,q,k] = sum_i mix_post[i,j] * p[b,i,q,k]   -> bf16 [B,H,Nq,ld], columns >= Nk zeroed
- * mix_pre/mix_post [H,H] fp32 (both or neither; NULL = identity; H in {2,3,4,6,8} when given);
+ * mix_pre/mix_post [H,H] fp32 (both or neither; NULL = identity; H in {2,3,4,6,8,12,16} when given);
  * rel fp32 [B,Nq,H,ldr] = unscaled q.r^W (first 2W-1 columns) | q.r^H (next 2Hh-1), or NULL.
  * Backward takes dP = dO v^T (fp32, same layout), recomputes p from S, and writes dS (bf16, the
  * gradient of the raw q.k products, scale folded in), drel (fp32 [B,Nq,H,ldr], overwritten) and

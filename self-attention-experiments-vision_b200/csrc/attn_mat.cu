@@ -326,6 +326,113 @@ thsoftmax_bwd_kernel(const SoftArgs a) {
   }
 }
 
+// ---- many heads (H = 12, 16: CaiT-M).  The H x H gradient accumulators of the kernel above do not
+// fit in registers (2 * 256 floats per lane), so the backward runs H / HS times, each launch
+// accumulating the HS columns [I0, I0 + HS) of d mix_pre and the matching rows of d mix_post;
+// the launch with I0 == 0 also writes dS.  Everything else is recomputed per launch -- this path
+// is about coverage of the 16-head constructors, not speed.
+template <int H, int HS, int I0>
+__global__ void __launch_bounds__(kRowWarps * 32)
+thsoftmax_bwd_slice_kernel(const SoftArgs a) {
+  __shared__ float t1[H * H], t2[H * H];
+  __shared__ float red1[H * HS], red2[HS * H];
+  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
+    t1[i] = a.mix_pre[i];
+    t2[i] = a.mix_post[i];
+  }
+  for (int i = threadIdx.x; i < H * HS; i += blockDim.x) { red1[i] = 0.f; red2[i] = 0.f; }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int64_t rows = (int64_t)a.B * a.Nq;
+  const int64_t hs = (int64_t)a.Nq * a.ld;
+  const float sc = a.scale * kLog2e;
+  float g1[H * HS], g2[HS * H];   // d mix_pre[h, I0+ii], d mix_post[I0+ii, j]
+#pragma unroll
+  for (int i = 0; i < H * HS; ++i) { g1[i] = 0.f; g2[i] = 0.f; }
+  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + (threadIdx.x >> 5); row < rows;
+       row += (int64_t)gridDim.x * kRowWarps) {
+    const int q = (int)(row % a.Nq);
+    const int64_t b = row / a.Nq;
+    const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
+    const float* s0 = a.S + off;
+    const float* d0 = a.dP + off;
+    bf16* ds0 = a.dS + off;
+    float m[H], inv[H], delta[H];
+    th_stats<H>(a, s0, hs, lane, t1, sc, m, inv);
+#pragma unroll
+    for (int i = 0; i < H; ++i) delta[i] = 0.f;
+    for (int k = lane; k < a.Nk; k += 32) {
+      float s[H], t[H], dpo[H];
+      th_logits<H>(a, s0, hs, k, t1, sc, s, t);
+#pragma unroll
+      for (int j = 0; j < H; ++j) dpo[j] = d0[j * hs + k];
+#pragma unroll
+      for (int i = 0; i < H; ++i) {
+        const float pi = ex2_fast(t[i] - m[i]) * inv[i];
+        float dpi = 0.f;
+#pragma unroll
+        for (int j = 0; j < H; ++j) {
+          dpi = fmaf(t2[i * H + j], dpo[j], dpi);
+          if (i >= I0 && i < I0 + HS) g2[(i - I0) * H + j] = fmaf(pi, dpo[j], g2[(i - I0) * H + j]);
+        }
+        delta[i] = fmaf(pi, dpi, delta[i]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < H; ++i) delta[i] = warp_sum(delta[i]);
+    for (int k = lane; k < (I0 == 0 ? a.ld : a.Nk); k += 32) {
+      float dt[H], s[H], t[H];
+      if (k < a.Nk) {
+        float dpo[H];
+        th_logits<H>(a, s0, hs, k, t1, sc, s, t);
+#pragma unroll
+        for (int j = 0; j < H; ++j) dpo[j] = d0[j * hs + k];
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+          const float pi = ex2_fast(t[i] - m[i]) * inv[i];
+          float dpi = 0.f;
+#pragma unroll
+          for (int j = 0; j < H; ++j) dpi = fmaf(t2[i * H + j], dpo[j], dpi);
+          dt[i] = pi * (dpi - delta[i]) * a.scale;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < H; ++i) { dt[i] = 0.f; s[i] = 0.f; }
+      }
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        float acc = 0.f;
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+          acc = fmaf(t1[h * H + i], dt[i], acc);
+          if (i >= I0 && i < I0 + HS) g1[h * HS + (i - I0)] = fmaf(s[h], dt[i], g1[h * HS + (i - I0)]);
+        }
+        if (I0 == 0) ds0[h * hs + k] = __float2bfloat16(acc);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < H * HS; ++i) {
+    const float v1 = warp_sum(g1[i]);
+    const float v2 = warp_sum(g2[i]);
+    if (lane == 0) {
+      atomicAdd(&red1[i], v1);
+      atomicAdd(&red2[i], v2);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < H * HS; i += blockDim.x) {
+    atomicAdd(a.dmix_pre + (i / HS) * H + I0 + (i % HS), red1[i]);     // [h][I0 + ii]
+    atomicAdd(a.dmix_post + (I0 + i / H) * H + (i % H), red2[i]);      // [I0 + ii][j]
+  }
+}
+template <int H, int HS, int I0>
+static void launch_th_bwd_slices(const SoftArgs& a, int grid, cudaStream_t st) {
+  thsoftmax_bwd_slice_kernel<H, HS, I0><<<grid, kRowWarps * 32, 0, st>>>(a);
+  count_launch();
+  if constexpr (I0 + HS < H) launch_th_bwd_slices<H, HS, I0 + HS>(a, grid, st);
+}
+
 // ---- register / shared-memory resident variants for Nk <= 32 * KPL (CaiT: 196 / 197 keys).
 // The row's mixed logits are computed ONCE: forward keeps exp(t - m) for the lane's keys in
 // registers between the statistics and the output pass; backward parks p and dp in shared memory
@@ -622,8 +729,10 @@ extern "C" int sav_thsoftmax_fwd(const sav_thsoftmax_args* x, void* stream) {
     break;
       SAV_TH_CASE(2) SAV_TH_CASE(3) SAV_TH_CASE(4) SAV_TH_CASE(6) SAV_TH_CASE(8)
 #undef SAV_TH_CASE
+      case 12: thsoftmax_fwd_kernel<12><<<grid, kRowWarps * 32, 0, st>>>(a); break;
+      case 16: thsoftmax_fwd_kernel<16><<<grid, kRowWarps * 32, 0, st>>>(a); break;
       default:
-        return set_error(SAV_ERR_SHAPE, "sav_thsoftmax_fwd: talking heads built for H in {2,3,4,6,8}");
+        return set_error(SAV_ERR_SHAPE, "sav_thsoftmax_fwd: talking heads built for H in {2,3,4,6,8,12,16}");
     }
   }
   count_launch();
@@ -656,8 +765,10 @@ extern "C" int sav_thsoftmax_bwd(const sav_thsoftmax_args* x, void* stream) {
     break;
       SAV_TH_CASE(2) SAV_TH_CASE(3) SAV_TH_CASE(4) SAV_TH_CASE(6) SAV_TH_CASE(8)
 #undef SAV_TH_CASE
+      case 12: launch_th_bwd_slices<12, 3, 0>(a, grid, st); break;
+      case 16: launch_th_bwd_slices<16, 2, 0>(a, grid, st); break;
       default:
-        return set_error(SAV_ERR_SHAPE, "sav_thsoftmax_bwd: talking heads built for H in {2,3,4,6,8}");
+        return set_error(SAV_ERR_SHAPE, "sav_thsoftmax_bwd: talking heads built for H in {2,3,4,6,8,12,16}");
     }
   }
   count_launch();

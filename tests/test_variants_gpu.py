@@ -67,6 +67,8 @@ def _attn_ref(q, k, v, scale, t1=None, t2=None):
     (3, 4, 196, 196, 48, True),      # CaiT-XXS self-attention layer
     (2, 8, 196, 196, 48, True),      # CaiT-S
     (2, 6, 50, 50, 48, True),        # ragged (not a tile multiple), 6 heads
+    (2, 16, 70, 70, 48, True),       # CaiT-M head count (sliced backward), ragged
+    (1, 12, 197, 197, 64, True),     # 12 heads, 197 keys
     (5, 4, 1, 197, 48, False),       # class attention: one query row
     (2, 3, 70, 33, 32, False),       # Nq != Nk, small head dim
     (2, 4, 196, 196, 128, False),    # BoTNet head dim without the relative term
@@ -205,6 +207,13 @@ def test_cait_s_width_drop_path_all_grads():
     # CaiT-S width (8 heads x 48), drop-path 0.1 with shared masks, layerscale 0.1
     _cait_case("cait_s3_ls0p1_dp", num_layers=3, heads=8, dim=384, batch=8, img=224, layerscale=0.1,
                drop_rate=0.1)
+
+
+@pytest.mark.gpu
+def test_cait_m_width_16_heads_all_grads():
+    # CaiT-M width (16 heads x 48 = 768): the many-head talking-heads path (sliced backward)
+    _cait_case("cait_m2_ls0p1", num_layers=2, heads=16, dim=768, batch=4, img=224, layerscale=0.1,
+               drop_rate=0.0)
 
 
 @pytest.mark.gpu
