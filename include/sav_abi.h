@@ -134,6 +134,14 @@ int sav_layernorm_bwd(const void* dy, int64_t ldy, const float* x, int64_t ldx, 
                       const float* mean, const float* rstd, const float* dx_add, float* dx,
                       void* dx_bf16, float* dscale, float* dbias, int64_t rows, int64_t C,
                       void* stream);
+/* Same, and additionally dx_bf16_colsum[c] += sum_rows dx_bf16[row, c] when non-NULL: dx_bf16 is the
+ * dY of the Linear that wrote this residual stream (out-proj / FC2, vit.py:24,31), so this is that
+ * Linear's bias gradient (attention.py:60-63, ff.py:27 reverse mode) without a pass over dY. */
+int sav_layernorm_bwd_colsum(const void* dy, int64_t ldy, const float* x, int64_t ldx,
+                             const float* scale, const float* mean, const float* rstd,
+                             const float* dx_add, float* dx, void* dx_bf16, float* dscale,
+                             float* dbias, float* dx_bf16_colsum, int64_t rows, int64_t C,
+                             void* stream);
 
 /* ---------------------------------------------------------------- patch embedding stem
  * train.py:80-81 + patch_embed.py:19-22: images fp32 [H,W,C,N] (reference batch layout) ->

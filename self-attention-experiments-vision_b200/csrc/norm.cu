@@ -98,18 +98,19 @@ ln_fwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict_
 // dscale / dbias: per-warp register partials -> shared-memory reduce -> one red.add per column
 // per block into the (zero-initialised or accumulating) gradient arena.
 template <int CHUNKS>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, CHUNKS <= 2 ? 2 : 1)
 ln_bwd_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __restrict__ x, int64_t ldx,
               const float* __restrict__ scale, const float* __restrict__ mean_in,
               const float* __restrict__ rstd_in, const float* __restrict__ dx_add,
               float* __restrict__ dx, bf16* __restrict__ dx16, float* __restrict__ dscale,
-              float* __restrict__ dbias, int64_t rows, int C) {
-  extern __shared__ float sacc[];  // [2][C]
+              float* __restrict__ dbias, float* __restrict__ dsum, int64_t rows, int C) {
+  extern __shared__ float sacc[];  // [2][C] (+ [C] column sums of the bf16 dx copy when dsum)
   const int lane = threadIdx.x & 31;
   const int64_t warp_global = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int64_t warps_total = (int64_t)gridDim.x * 8;
   const int nchunk = C / 8;
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sacc[i] = 0.f;
+  const int nacc = dsum ? 3 * C : 2 * C;
+  for (int i = threadIdx.x; i < nacc; i += blockDim.x) sacc[i] = 0.f;
   __syncthreads();
   float ds[CHUNKS][8], db[CHUNKS][8], g[CHUNKS][8];
 #pragma unroll
@@ -167,6 +168,13 @@ ln_bwd_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __restrict_
         }
         store8(dx + row * ldx + ch * 8, o);
         if (dx16) store8(dx16 + row * ldx + ch * 8, o);
+        if (dsum) {
+          // column sums of the bf16 copy = bias gradient of the Linear that produced this stream
+          // (its dY is exactly dx16): shared-memory adds, the accumulator registers are spoken for
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            atomicAdd(&sacc[2 * C + ch * 8 + j], __bfloat162float(__float2bfloat16(o[j])));
+        }
       }
     }
   }
@@ -182,8 +190,8 @@ ln_bwd_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __restrict_
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) {
-    float* out = (i < C) ? (dscale + i) : (dbias + (i - C));
+  for (int i = threadIdx.x; i < nacc; i += blockDim.x) {
+    float* out = (i < C) ? (dscale + i) : (i < 2 * C ? dbias + (i - C) : dsum + (i - 2 * C));
     atomicAdd(out, sacc[i]);
   }
 }
@@ -222,10 +230,13 @@ extern "C" int sav_layernorm_fwd(const float* x, int64_t ldx, const float* scale
   return check_launch("sav_layernorm_fwd");
 }
 
-extern "C" int sav_layernorm_bwd(const void* dy, int64_t ldy, const float* x, int64_t ldx,
-                                 const float* scale, const float* mean, const float* rstd,
-                                 const float* dx_add, float* dx, void* dx_bf16, float* dscale,
-                                 float* dbias, int64_t rows, int64_t C, void* stream) {
+extern "C" int sav_layernorm_bwd_colsum(const void* dy, int64_t ldy, const float* x, int64_t ldx,
+                                        const float* scale, const float* mean, const float* rstd,
+                                        const float* dx_add, float* dx, void* dx_bf16,
+                                        float* dscale, float* dbias, float* dx_bf16_colsum,
+                                        int64_t rows, int64_t C, void* stream) {
+  if (dx_bf16_colsum && !dx_bf16)
+    return set_error(SAV_ERR_ARG, "sav_layernorm_bwd_colsum: column sums need the bf16 copy");
   if (rows <= 0 || C <= 0 || C % 8 || C > 32 * LN_MAX_CHUNKS * 8 || ldx % 8 || ldy % 8)
     return set_error(SAV_ERR_SHAPE, "sav_layernorm_bwd: need C %% 8 == 0 and C <= 1024");
   if (!aligned16(dy) || !aligned16(x) || !aligned16(dx) || !aligned16(dx_add) || !aligned16(dx_bf16))
@@ -233,11 +244,12 @@ extern "C" int sav_layernorm_bwd(const void* dy, int64_t ldy, const float* x, in
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int grid = ln_grid(rows);
   const int chunks = (int)((C / 8 + 31) / 32);
-  const size_t sm = 2 * C * sizeof(float);
+  float* dsum = dx_bf16_colsum;
+  const size_t sm = (dsum ? 3 : 2) * C * sizeof(float);
 #define LN_BWD(CH)                                                                            \
   ln_bwd_kernel<CH><<<grid, 256, sm, st>>>(reinterpret_cast<const bf16*>(dy), ldy, x, ldx, scale, \
                                             mean, rstd, dx_add, dx,                            \
-                                            reinterpret_cast<bf16*>(dx_bf16), dscale, dbias, rows, (int)C)
+                                            reinterpret_cast<bf16*>(dx_bf16), dscale, dbias, dsum, rows, (int)C)
   switch (chunks) {
     case 1: LN_BWD(1); break;
     case 2: LN_BWD(2); break;
@@ -247,4 +259,12 @@ extern "C" int sav_layernorm_bwd(const void* dy, int64_t ldy, const float* x, in
 #undef LN_BWD
   count_launch();
   return check_launch("sav_layernorm_bwd");
+}
+
+extern "C" int sav_layernorm_bwd(const void* dy, int64_t ldy, const float* x, int64_t ldx,
+                                 const float* scale, const float* mean, const float* rstd,
+                                 const float* dx_add, float* dx, void* dx_bf16, float* dscale,
+                                 float* dbias, int64_t rows, int64_t C, void* stream) {
+  return sav_layernorm_bwd_colsum(dy, ldy, x, ldx, scale, mean, rstd, dx_add, dx, dx_bf16, dscale,
+                                  dbias, nullptr, rows, C, stream);
 }

@@ -15,6 +15,8 @@ is no CPU compute.
 """
 import math
 
+import os
+
 import torch
 
 from . import ops
@@ -38,6 +40,13 @@ class Weight:
     def touch(self):
         for p in self.params:
             p.touch_grad()
+
+
+# SAV_FUSE_BIAS_COLSUM=1 folds the out-proj / FC2 bias gradients into LayerNorm backward
+# (sav_layernorm_bwd_colsum).  Off by default: measured on one box it costs 0.35 ms per DeiT-S step
+# (14.38 vs 14.02 ms, profiles/r01n_ab_fuse.log) -- the 384 shared-memory adds per row slow the
+# bytes-in-flight-bound LayerNorm kernel by more than the two 14 us column-sum passes it removes.
+_FUSE_BIAS_COLSUM = os.environ.get("SAV_FUSE_BIAS_COLSUM", "0") == "1"
 
 
 def _grad16(var):
@@ -68,7 +77,7 @@ def _as2d(t, K):
 
 
 class LazyLinear(Var):
-    __slots__ = ("x", "weight", "bias", "act", "col_scale", "row_scale", "rows_per_scale",
+    __slots__ = ("bias_grad_from", "x", "weight", "bias", "act", "col_scale", "row_scale", "rows_per_scale",
                  "residual", "out_shape", "_done")
 
     def __init__(self, x, weight, bias, out_shape):
@@ -161,8 +170,11 @@ class LazyLinear(Var):
         W.touch()
         ops.gemm(x2, dy2, a_mn=True, b_mn=True, out=W.gw, accumulate=True, split_k=0)
         if self.bias is not None:
-            self.bias.touch_grad()
-            ops.colsum(dy2, out=self.bias.grad, accumulate=True)
+            done = getattr(self, "bias_grad_from", None)
+            self.bias_grad_from = None
+            if scaled or done is None or done.data_ptr() != dy2.data_ptr() or done.numel() != dy2.numel():
+                self.bias.touch_grad()
+                ops.colsum(dy2, out=self.bias.grad, accumulate=True)
         if self.col_scale is not None:
             # d layerscale from the finished dW / dbias (elementwise.cu), no saved activation
             if W.wm is None:
@@ -287,11 +299,21 @@ class LazyLayerNorm(Var):
             bias.touch_grad()
             prev = x.take_grad() if x.requires_grad else None
             x.g16 = None
+            # When the stream was written by a residual-fused Linear (out-proj / FC2), the bf16 copy
+            # produced here IS that Linear's dY, so its bias gradient (column sums of dY) is
+            # accumulated by this kernel instead of a separate pass over dY.
+            fuse = (_FUSE_BIAS_COLSUM and x.requires_grad and isinstance(x, LazyLinear) and x.bias is not None
+                    and x.col_scale is None and x.row_scale is None and x.v.is_contiguous())
+            if fuse:
+                x.bias.touch_grad()
             dx, dx16 = ops.layernorm_bwd(dy.contiguous().view(-1, C), x2, scale.master, mean, rstd,
                                          scale.grad, bias.grad,
-                                         dx_add=prev.contiguous().view(-1, C) if prev is not None else None)
+                                         dx_add=prev.contiguous().view(-1, C) if prev is not None else None,
+                                         dx16_colsum=x.bias.grad.reshape(C) if fuse else None)
             if x.requires_grad:
                 x.g, x.g16 = dx.view(xc.shape), dx16.view(xc.shape)
+                if fuse:
+                    x.bias_grad_from = dx16
         record(bwd)
 
     def first_token(self):

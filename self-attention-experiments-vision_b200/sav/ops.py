@@ -118,7 +118,8 @@ def layernorm_fwd(x, scale, bias, eps=1e-6):
     return y, mean, rstd
 
 
-def layernorm_bwd(dy, x, scale, mean, rstd, dscale, dbias, dx_add=None, dx=None, dx16=None):
+def layernorm_bwd(dy, x, scale, mean, rstd, dscale, dbias, dx_add=None, dx=None, dx16=None,
+                  dx16_colsum=None):
     """dy bf16 [rows,C]; x fp32 [rows,C] view; returns (dx fp32, dx16 bf16) with x's row pitch.
     dscale / dbias are accumulated."""
     _req(dy, BF16, "dy"); _req(x, F32, "x")
@@ -130,9 +131,13 @@ def layernorm_bwd(dy, x, scale, mean, rstd, dscale, dbias, dx_add=None, dx=None,
         dx16 = torch.empty((rows, C_), dtype=BF16, device=x.device)
     assert dx.stride(0) == x.stride(0) and (dx16 is None or dx16.stride(0) == x.stride(0))
     assert dx_add is None or (dx_add.dtype == F32 and dx_add.stride(0) == x.stride(0))
-    check(lib().sav_layernorm_bwd(_p(dy), dy.stride(0), _p(x), x.stride(0), _p(scale), _p(mean),
-                                  _p(rstd), _p(dx_add), _p(dx), _p(dx16), _p(dscale), _p(dbias),
-                                  rows, C_, _stream()))
+    if dx16_colsum is not None:
+        # accumulates the column sums of dx16 (the bias gradient of the Linear that wrote x)
+        _req(dx16_colsum, F32, "dx16_colsum")
+        assert dx16_colsum.numel() == C_ and dx16 is not None
+    check(lib().sav_layernorm_bwd_colsum(_p(dy), dy.stride(0), _p(x), x.stride(0), _p(scale), _p(mean),
+                                         _p(rstd), _p(dx_add), _p(dx), _p(dx16), _p(dscale), _p(dbias),
+                                         _p(dx16_colsum), rows, C_, _stream()))
     return dx, dx16
 
 
