@@ -271,6 +271,14 @@ int sav_softmax_xent(const void* logits, int64_t ld, const int32_t* labels, int6
                      int64_t classes, float label_smoothing, float grad_scale, void* dlogits,
                      float* loss_out, void* stream);
 
+/* Same with the mixup / cutmix branch of train.py:84-87: y = ratio[b]*one_hot(labels[b]) +
+ * (1-ratio[b])*one_hot(mix_labels[b]) before smooth_labels.  mix_labels (int32 [B]) and ratio
+ * (fp32 [B]) are both NULL (plain labels) or both given. */
+int sav_softmax_xent_mix(const void* logits, int64_t ld, const int32_t* labels,
+                         const int32_t* mix_labels, const float* ratio, int64_t B, int64_t classes,
+                         float label_smoothing, float grad_scale, void* dlogits, float* loss_out,
+                         void* stream);
+
 /* utils.py:20-31 topk_correct (train.py:98-99): out[i*B + b] = 1.0 if the label of example b is
  * among the k_i highest logits (argsort tie order: larger class index ranks higher), else 0.0;
  * 1 <= nk <= 4.  logits bf16 [B, classes] ld; out fp32 [nk, B]. */
@@ -291,6 +299,22 @@ int sav_sumsq(const float* g, int64_t n, float* out, void* stream);
 int sav_adam_step(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n,
                   const float* sumsq, float max_norm, float lr, float b1, float b2, float eps,
                   float wd, int64_t t, const float* hyper, void* stream);
+/* optax.scale_by_schedule + the Adam bias corrections as a device-resident counter (train.py:25-27,
+ * 214-220): step[0] (device int64, the optax `count`) is read, incremented, and hyper (device
+ * fp32[3]) is set to {lr(count), 1-b1^(count+1), 1-b2^(count+1)} for the sav_adam_step enqueued
+ * after it, so a captured CUDA graph advances the schedule by itself on every replay.
+ * mode 0: lr = peak_value (constant; simple_train.py:27);  mode 1:
+ * optax.warmup_cosine_decay_schedule(init_value, peak_value, warmup_steps, decay_steps, end_value);
+ * mode 2: hyper[0] is left as the host wrote it (arbitrary Python schedule). */
+int sav_schedule_step(int64_t* step, float* hyper, int32_t mode, float init_value, float peak_value,
+                      int64_t warmup_steps, int64_t decay_steps, float end_value, float b1, float b2,
+                      void* stream);
+/* stochastic_depth.py:16-27 mask source: out[b] = floor(keep + U[b]) / keep with U from
+ * Philox4x32-10 keyed by seed, counter (b, call_index, step); the step comes from step_dev (device
+ * int64, e.g. the counter of sav_schedule_step) when non-NULL so graph replays resample, else from
+ * step_host.  out fp32 [B]. */
+int sav_drop_path_factors(uint64_t seed, const int64_t* step_dev, int64_t step_host,
+                          int64_t call_index, int64_t B, float keep, float* out, void* stream);
 
 /* elementwise helpers (bf16): y = a + b ; used only where no GEMM epilogue can absorb the add */
 int sav_add_bf16(const void* a, const void* b, void* y, int64_t n, void* stream);

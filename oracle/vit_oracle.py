@@ -106,14 +106,39 @@ def vit_forward(params, images_nhwc, num_layers, num_heads, patch_shape):
 
 
 # ----------------------------------------------------------------------------- train step pieces
-def loss_fn(logits, labels, num_classes, label_smoothing=0.0, device_count=1):
-    """train.py:83-91: one_hot -> optax.smooth_labels -> optax.softmax_cross_entropy -> mean
-    (-> / device_count, kept as a switch; SURVEY D7 uses the plain mean)."""
+def loss_fn(logits, labels, num_classes, label_smoothing=0.0, device_count=1, mix_labels=None, ratio=None):
+    """train.py:83-91: one_hot -> (mixup: ratio*y + (1-ratio)*y1, train.py:84-87) ->
+    optax.smooth_labels -> optax.softmax_cross_entropy -> mean (-> / device_count, kept as a
+    switch; SURVEY D7 uses the plain mean)."""
     y = torch.nn.functional.one_hot(labels.long(), num_classes).to(logits.dtype)  # train.py:83
+    if mix_labels is not None:                                                 # train.py:84-87
+        y1 = torch.nn.functional.one_hot(mix_labels.long(), num_classes).to(logits.dtype)
+        y = ratio[:, None] * y + (1.0 - ratio[:, None]) * y1
     y = (1.0 - label_smoothing) * y + label_smoothing / num_classes            # train.py:88
     logp = logits - torch.logsumexp(logits, dim=-1, keepdim=True)
     loss = -(y * logp).sum(-1).mean()                                          # train.py:89-90
     return loss / device_count                                                 # train.py:91
+
+
+def warmup_cosine_decay_schedule(init_value, peak_value, warmup_steps, decay_steps, end_value=0.0):
+    """optax.warmup_cosine_decay_schedule as called in train.py:215-220, restated from optax's
+    published source: join_schedules([linear_schedule(init, peak, warmup),
+    cosine_decay_schedule(peak, decay - warmup, alpha=end/peak)], [warmup])."""
+    def linear(count):
+        count = min(max(count, 0), warmup_steps)
+        frac = 1.0 - count / warmup_steps
+        return (init_value - peak_value) * frac + peak_value
+
+    def cosine(count):
+        D = decay_steps - warmup_steps
+        count = min(count, D)
+        cosine_decay = 0.5 * (1.0 + math.cos(math.pi * count / D))
+        alpha = end_value / peak_value
+        return peak_value * ((1.0 - alpha) * cosine_decay + alpha)
+
+    def schedule(count):
+        return linear(count) if count < warmup_steps else cosine(count - warmup_steps)
+    return schedule
 
 
 def hwcn_to_nhwc(images_hwcn):

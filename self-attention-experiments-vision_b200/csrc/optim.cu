@@ -20,6 +20,7 @@ __device__ __forceinline__ float wmax(float v) {
 // loss_b = -sum target*log_softmax;  dlogits = (softmax - target) * grad_scale.
 __global__ void __launch_bounds__(128)
 xent_kernel(const bf16* __restrict__ logits, int64_t ld, const int32_t* __restrict__ labels,
+            const int32_t* __restrict__ mix_labels, const float* __restrict__ ratio,
             int B, int classes, float alpha, float grad_scale, bf16* __restrict__ dlogits,
             float* __restrict__ loss_out) {
   const int lane = threadIdx.x & 31;
@@ -44,12 +45,17 @@ xent_kernel(const bf16* __restrict__ logits, int64_t ld, const int32_t* __restri
   const float lse = mx + logf(se);
   const int lab = labels[b];
   const float l_lab = __bfloat162float(row[lab]);
-  // -sum_c t_c (l_c - lse) = lse - (1-a) l_lab - a/classes * sum_c l_c
-  const float loss = lse - (1.f - alpha) * l_lab - alpha / classes * sl;
+  // mixup / cutmix targets (train.py:84-87): y = r*onehot(lab) + (1-r)*onehot(lab2)
+  const int lab2 = mix_labels ? mix_labels[b] : lab;
+  const float r = mix_labels ? ratio[b] : 1.f;
+  const float l_lab2 = __bfloat162float(row[lab2]);
+  const float w1 = (1.f - alpha) * r, w2 = (1.f - alpha) * (1.f - r);
+  // -sum_c t_c (l_c - lse) = lse - w1 l_lab - w2 l_lab2 - a/classes * sum_c l_c
+  const float loss = lse - w1 * l_lab - w2 * l_lab2 - alpha / classes * sl;
   const float inv = 1.f / se;
   for (int c = lane; c < classes; c += 32) {
     const float l = __bfloat162float(row[c]);
-    const float t = (c == lab ? (1.f - alpha) : 0.f) + alpha / classes;
+    const float t = (c == lab ? w1 : 0.f) + (c == lab2 ? w2 : 0.f) + alpha / classes;
     dlogits[(int64_t)b * ld + c] = __float2bfloat16((__expf(l - mx) * inv - t) * grad_scale);
   }
   if (lane == 0) {
@@ -174,6 +180,69 @@ __global__ void copy2d_kernel(const bf16* __restrict__ src, int64_t lds, bf16* _
   }
 }
 
+// optax.warmup_cosine_decay_schedule (train.py:215-220) evaluated at `count`.
+__device__ __forceinline__ float warmup_cosine(float init_v, float peak, int64_t warm, int64_t decay,
+                                               float end_v, int64_t count) {
+  if (count < warm) {
+    // linear_schedule(init, peak, warm)
+    const float frac = 1.f - (float)count / (float)warm;
+    return (init_v - peak) * frac + peak;
+  }
+  // cosine_decay_schedule(peak, decay - warm, alpha = end / peak) at count - warm
+  const int64_t D = decay - warm > 0 ? decay - warm : 1;
+  int64_t c = count - warm;
+  if (c > D) c = D;
+  const float cosv = 0.5f * (1.f + cospif((float)c / (float)D));
+  const float alpha = peak != 0.f ? end_v / peak : 0.f;
+  return peak * ((1.f - alpha) * cosv + alpha);
+}
+
+// One thread: advances the device-resident step counter and writes {lr, 1-b1^t, 1-b2^t} for the
+// Adam kernel that follows it IN THE SAME (possibly graph-replayed) stream, so no host value is
+// read at execution time.  optax.scale_by_schedule evaluates the schedule at the count BEFORE the
+// increment (first update uses schedule(0)); scale_by_adam bias-corrects with count + 1.
+__global__ void schedule_kernel(int64_t* __restrict__ step, float* __restrict__ hyper, int mode,
+                                float init_v, float peak, int64_t warm, int64_t decay, float end_v,
+                                float b1, float b2) {
+  if (threadIdx.x || blockIdx.x) return;
+  const int64_t count = step[0];
+  const int64_t t = count + 1;
+  step[0] = t;
+  if (mode == 0) hyper[0] = peak;
+  else if (mode == 1) hyper[0] = warmup_cosine(init_v, peak, warm, decay, end_v, count);
+  // mode 2: hyper[0] was written by the host (arbitrary Python schedule)
+  hyper[1] = 1.f - powf(b1, (float)t);
+  hyper[2] = 1.f - powf(b2, (float)t);
+}
+
+// Philox4x32-10 counter-based generator: key = seed, counter = (sample, call index, step lo, hi).
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+
+// stochastic_depth.py:16-27: factor[b] = floor(keep + U[b]) / keep, U uniform in [0,1).
+// The step is read from the device counter (if given) so that graph replays resample.
+__global__ void drop_path_kernel(uint64_t seed, const int64_t* __restrict__ step_dev,
+                                 int64_t step_host, int64_t call, int B, float keep,
+                                 float* __restrict__ out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const int64_t step = step_dev ? step_dev[0] : step_host;
+  const uint4 r = philox4x32_10(make_uint4((uint32_t)b, (uint32_t)call, (uint32_t)step,
+                                           (uint32_t)((uint64_t)step >> 32)),
+                                make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+  const float u = (float)(r.x >> 8) * (1.f / 16777216.f);
+  out[b] = floorf(keep + u) / keep;
+}
+
 static int grid_for(int64_t work, int threads) {
   int64_t b = (work + threads - 1) / threads;
   const int64_t cap = 148 * 8;
@@ -184,17 +253,50 @@ static int grid_for(int64_t work, int threads) {
 
 using namespace sav;
 
-extern "C" int sav_softmax_xent(const void* logits, int64_t ld, const int32_t* labels, int64_t B,
-                                int64_t classes, float label_smoothing, float grad_scale,
-                                void* dlogits, float* loss_out, void* stream) {
+extern "C" int sav_softmax_xent_mix(const void* logits, int64_t ld, const int32_t* labels,
+                                    const int32_t* mix_labels, const float* ratio, int64_t B,
+                                    int64_t classes, float label_smoothing, float grad_scale,
+                                    void* dlogits, float* loss_out, void* stream) {
   if (B <= 0 || classes <= 0) return set_error(SAV_ERR_SHAPE, "sav_softmax_xent: bad shape");
+  if ((mix_labels == nullptr) != (ratio == nullptr))
+    return set_error(SAV_ERR_ARG, "sav_softmax_xent_mix: mix_labels and ratio go together");
   int rc = sav_fill_f32(loss_out, 0.f, 2, stream);
   if (rc) return rc;
   xent_kernel<<<(int)((B + 3) / 4), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const bf16*>(logits), ld, labels, (int)B, (int)classes, label_smoothing,
-      grad_scale, reinterpret_cast<bf16*>(dlogits), loss_out);
+      reinterpret_cast<const bf16*>(logits), ld, labels, mix_labels, ratio, (int)B, (int)classes,
+      label_smoothing, grad_scale, reinterpret_cast<bf16*>(dlogits), loss_out);
   count_launch();
   return check_launch("sav_softmax_xent");
+}
+
+extern "C" int sav_softmax_xent(const void* logits, int64_t ld, const int32_t* labels, int64_t B,
+                                int64_t classes, float label_smoothing, float grad_scale,
+                                void* dlogits, float* loss_out, void* stream) {
+  return sav_softmax_xent_mix(logits, ld, labels, nullptr, nullptr, B, classes, label_smoothing,
+                              grad_scale, dlogits, loss_out, stream);
+}
+
+extern "C" int sav_schedule_step(int64_t* step, float* hyper, int32_t mode, float init_value,
+                                 float peak_value, int64_t warmup_steps, int64_t decay_steps,
+                                 float end_value, float b1, float b2, void* stream) {
+  if (!step || !hyper) return set_error(SAV_ERR_ARG, "sav_schedule_step: null step / hyper");
+  if (mode < 0 || mode > 2) return set_error(SAV_ERR_ARG, "sav_schedule_step: mode in {0,1,2}");
+  if (mode == 1 && warmup_steps < 0) return set_error(SAV_ERR_ARG, "sav_schedule_step: warmup < 0");
+  schedule_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      step, hyper, mode, init_value, peak_value, warmup_steps, decay_steps, end_value, b1, b2);
+  count_launch();
+  return check_launch("sav_schedule_step");
+}
+
+extern "C" int sav_drop_path_factors(uint64_t seed, const int64_t* step_dev, int64_t step_host,
+                                     int64_t call_index, int64_t B, float keep, float* out,
+                                     void* stream) {
+  if (B <= 0) return SAV_OK;
+  if (!(keep > 0.f && keep <= 1.f)) return set_error(SAV_ERR_ARG, "sav_drop_path_factors: keep in (0,1]");
+  drop_path_kernel<<<(int)((B + 127) / 128), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      seed, step_dev, step_host, call_index, (int)B, keep, out);
+  count_launch();
+  return check_launch("sav_drop_path_factors");
 }
 
 extern "C" int sav_topk_correct(const void* logits, int64_t ld, const int32_t* labels, int64_t B,

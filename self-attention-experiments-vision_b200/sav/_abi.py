@@ -116,6 +116,9 @@ SIGNATURES = {
     "sav_attn_fwd": (C.c_int, [C.POINTER(AttnFwdArgs), _P]),
     "sav_attn_bwd": (C.c_int, [C.POINTER(AttnBwdArgs), _P]),
     "sav_softmax_xent": (C.c_int, [_P, _I64, _P, _I64, _I64, _F, _F, _P, _P, _P]),
+    "sav_softmax_xent_mix": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _I64, _F, _F, _P, _P, _P]),
+    "sav_schedule_step": (C.c_int, [_P, _P, _I32, _F, _F, _I64, _I64, _F, _F, _F, _P]),
+    "sav_drop_path_factors": (C.c_int, [C.c_uint64, _P, _I64, _I64, _I64, _F, _P, _P]),
     "sav_topk_correct": (C.c_int, [_P, _I64, _P, _I64, _I64, _I32, _I32, _I32, _I32, _I32, _P, _P]),
     "sav_cast_f32_bf16": (C.c_int, [_P, _P, _I64, _P]),
     "sav_sumsq": (C.c_int, [_P, _I64, _P, _P]),

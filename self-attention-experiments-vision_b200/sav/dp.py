@@ -55,7 +55,7 @@ def _leaf_span(p):
 class DataParallel:
     """Gradient hook for sav.tape.value_and_grad: begin() / wrote(path) / after_node(i) / finish()."""
 
-    def __init__(self, bucket_mb=16.0, group=None, overlap=True):
+    def __init__(self, bucket_mb=16.0, group=None, overlap=True, reference_double_scale=False):
         if not dist.is_initialized():
             raise RuntimeError("DataParallel needs an initialised torch.distributed process group")
         self.group = group
@@ -63,6 +63,11 @@ class DataParallel:
         self.rank = dist.get_rank(group)
         self.bucket_elems = int(bucket_mb * (1 << 20) / 4)
         self.overlap = overlap
+        # train.py:91 divides the loss by device_count and train.py:96 pmean's the gradients on top
+        # (net 1/world^2).  Default: the true global mean (1/world).  The switch
+        # reproduces the reference's scaling -- it matters under clip_by_global_norm, whose
+        # threshold then sees gradients `world` times smaller.
+        self.reference_double_scale = bool(reference_double_scale)
         self.buckets = None       # [(lo, hi, paths)]
         self.fire_after = None    # node index -> [bucket ids]; None until learned
         self._last_writer = {}

@@ -490,11 +490,13 @@ class LossVar:
         return float(self.stats[1].item())
 
 
-def softmax_cross_entropy(logits, labels, label_smoothing=0.0, world_size=1):
-    """train.py:83-91 (plain mean over the global batch)."""
+def softmax_cross_entropy(logits, labels, label_smoothing=0.0, world_size=1, mix_labels=None, ratio=None):
+    """train.py:83-91 (plain mean over the global batch); mix_labels / ratio are the
+    optional mixup keys of the batch (train.py:84-87)."""
     lv = logits.v
     B = lv.shape[0]
-    dl, stats = ops.softmax_xent(lv.contiguous(), labels, label_smoothing, 1.0 / (B * world_size))
+    dl, stats = ops.softmax_xent(lv.contiguous(), labels, label_smoothing, 1.0 / (B * world_size),
+                                 mix_labels, ratio)
     return LossVar(logits, dl, stats, B)
 
 

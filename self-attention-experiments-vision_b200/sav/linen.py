@@ -177,7 +177,7 @@ class Module:
         base = run.builder.alloc(block.numel())
         stride = (n * inner,) + tuple(_contig(rest))
         master = self._to_dev(block, run)
-        shadow = master.to(torch.bfloat16) if not master.is_meta else master.to(torch.bfloat16)
+        shadow = _shadow_of(master)
         out = []
         for i, (p, v) in enumerate(zip(paths, vals)):
             run.builder.add_leaf(p, tuple(lead) + tuple(shape), v.reshape(tuple(lead) + tuple(shape)),
@@ -215,7 +215,7 @@ class Module:
         block[:total] = torch.cat(vals, dim=0)
         base = run.builder.alloc(padded * width)
         master = self._to_dev(block, run)
-        shadow = master.to(torch.bfloat16)
+        shadow = _shadow_of(master)
         out, r0 = [], 0
         for p, v, r in zip(paths, vals, rows):
             run.builder.add_leaf(p, (r, width), v, base=base, stride=(width, 1), rel_offset=r0 * width)
@@ -234,7 +234,7 @@ class Module:
 
     def _temp(self, val, run):
         m = self._to_dev(val, run)
-        return _TempParam(m, m.to(torch.bfloat16))
+        return _TempParam(m, _shadow_of(m))
 
     def _gen(self, stream):
         run = _run()
@@ -249,6 +249,22 @@ class Module:
 
     def make_rng(self, stream):
         return self._gen(stream)
+
+    def make_device_rng(self, stream):
+        """Device-side stream (sav/rng.py): rngs[stream] is an int seed or a rng.DeviceRng carrying
+        the training step's device counter; one instance per apply() so call indices restart."""
+        from .rng import DeviceRng
+        run = _run()
+        key = ("device", stream)
+        if key not in run.gens:
+            seed = run.rngs.get(stream)
+            if seed is None:
+                raise KeyError(f"{type(self).__name__} needs an rng named '{stream}'")
+            if isinstance(seed, DeviceRng):
+                run.gens[key] = DeviceRng(seed.seed, seed.step_dev, seed.step)
+            else:
+                run.gens[key] = DeviceRng(int(seed) if not torch.is_tensor(seed) else int(seed.flatten()[0]))
+        return run.gens[key]
 
     # ---- init / apply -------------------------------------------------------------------------
     def _execute(self, run, args, kw):
@@ -283,6 +299,17 @@ class Module:
         run = _Run("apply", arena=params.arena, rngs=rngs or {}, device=params.arena.device)
         args = tuple(_to_run_device(a, params.arena.device) for a in args)
         return self._execute(run, args, kw)
+
+
+def _shadow_of(master):
+    """bf16 copy of an init-mode fp32 tensor through the library's own cast kernel (no torch op)."""
+    if not master.is_cuda:
+        return master.to(torch.bfloat16)     # meta (shape-only) path
+    from . import ops
+    out = torch.empty(master.shape, dtype=torch.bfloat16, device=master.device)
+    if master.numel():
+        ops.cast_bf16(master.contiguous().view(-1), out.view(-1))
+    return out
 
 
 def _contig(shape):

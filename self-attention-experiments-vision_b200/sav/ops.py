@@ -220,15 +220,40 @@ def attn_bwd(q, k, v, o2, d_o, lse, dq, dk, dv, scale=None):
     check(lib().sav_attn_bwd(C.byref(a), _stream()))
 
 
-def softmax_xent(logits, labels, label_smoothing=0.0, grad_scale=1.0):
-    """logits bf16 [B,classes], labels int32 [B] -> (dlogits bf16, stats fp32 [loss_sum, top1])."""
+def softmax_xent(logits, labels, label_smoothing=0.0, grad_scale=1.0, mix_labels=None, ratio=None):
+    """logits bf16 [B,classes], labels int32 [B] (+ optional mixup partner labels int32 [B] and
+    ratio fp32 [B], train.py:84-87) -> (dlogits bf16, stats fp32 [loss_sum, top1])."""
     _req(logits, BF16, "logits")
     B, classes = logits.shape
+    if labels.dtype != torch.int32 or (mix_labels is not None and mix_labels.dtype != torch.int32):
+        raise _abi.SavError("softmax_xent: labels must be int32")
+    if (mix_labels is None) != (ratio is None):
+        raise _abi.SavError("softmax_xent: mix_labels and ratio go together")
+    if ratio is not None:
+        _req(ratio, F32, "ratio")
     dl = torch.empty_like(logits)
     stats = torch.empty(2, dtype=F32, device=logits.device)
-    check(lib().sav_softmax_xent(_p(logits), logits.stride(0), _p(labels), B, classes,
-                                 label_smoothing, grad_scale, _p(dl), _p(stats), _stream()))
+    check(lib().sav_softmax_xent_mix(_p(logits), logits.stride(0), _p(labels), _p(mix_labels), _p(ratio),
+                                     B, classes, label_smoothing, grad_scale, _p(dl), _p(stats), _stream()))
     return dl, stats
+
+
+def schedule_step(step_dev, hyper, mode, init_value, peak_value, warmup_steps, decay_steps, end_value,
+                  b1, b2):
+    """Advance the device step counter (int64 [1]) and write {lr, 1-b1^t, 1-b2^t} into hyper."""
+    assert step_dev.dtype == torch.int64 and hyper.dtype == F32 and hyper.numel() >= 3
+    check(lib().sav_schedule_step(_p(step_dev), _p(hyper), int(mode), float(init_value), float(peak_value),
+                                  int(warmup_steps), int(decay_steps), float(end_value), float(b1),
+                                  float(b2), _stream()))
+
+
+def drop_path_factors(seed, step_dev, step_host, call_index, B, keep, out=None, device=None):
+    """floor(keep + U)/keep per sample from the device Philox stream (stochastic_depth.py:16-27)."""
+    if out is None:
+        out = torch.empty(B, dtype=F32, device=device)
+    check(lib().sav_drop_path_factors(int(seed) & 0xFFFFFFFFFFFFFFFF, _p(step_dev), int(step_host),
+                                      int(call_index), B, float(keep), _p(out), _stream()))
+    return out
 
 
 def cast_bf16(src, dst):

@@ -55,10 +55,10 @@ def test_checkpoint_roundtrip_through_train_state(tmp_path):
     state.arena.master.add_(1.0)
     state.arena.m.zero_()
     state.arena.v.zero_()
-    state.step = 0
+    state.set_step(0)
     sd = C.restore_checkpoint(path, state)
     torch.cuda.synchronize()
-    assert state.step == 2 and sd["step"] == 2
+    assert state.step == 2 and int(sd["step"]) == 2 and int(state.step_dev.item()) == 2
     # every parameter leaf and moment is restored bit-exactly (fp32 -> bytes -> fp32)
     for path_, p in state.arena.params.items():
         for name, flat in (("p", state.arena.master), ("m", state.arena.m), ("v", state.arena.v)):
@@ -66,4 +66,6 @@ def test_checkpoint_roundtrip_through_train_state(tmp_path):
     # the bf16 shadow was refreshed from the restored master
     k = next(iter(state.arena.params.values()))
     assert torch.equal(k.shadow.float(), k.master.bfloat16().float())
-    assert "Encoder_0" in sd["params"] and "mu" in sd["opt_state"]
+    # the reference TrainState nesting: whole variables under params, optax.chain states by index
+    assert "Encoder_0" in sd["params"]["params"] and set(sd["opt_state"]) == {"0", "1", "2", "3"}
+    assert "Encoder_0" in sd["opt_state"]["1"]["mu"]["params"] and int(sd["opt_state"]["3"]["count"]) == 2

@@ -164,12 +164,13 @@ def _cait_case(tag, num_layers, heads, dim, batch, img, layerscale, drop_rate, s
     factors = None
     sd_seed = 1234
     if drop_rate > 0:
-        # the module draws torch.rand((b,)) from the 'stochastic_depth' stream once per
-        # StochasticDepthBlock call, in execution order (stochastic_depth.py:17-21)
-        gen = torch.Generator().manual_seed(sd_seed)
-        keep = 1.0 - drop_rate
-        factors = [torch.floor(keep + torch.rand((batch,), generator=gen)) / keep
-                   for _ in range(2 * (num_layers + 2))]
+        # the module draws its per-sample factors from the device Philox stream keyed by
+        # (seed, step, call index) once per StochasticDepthBlock call, in execution order
+        # (stochastic_depth.py:17-21); the oracle is fed the same factors
+        from sav.rng import drop_path_factors
+        factors = [f.cpu() for f in drop_path_factors(sd_seed, 0, 2 * (num_layers + 2), batch,
+                                                      1.0 - drop_rate, "cuda")]
+        assert any(float(f.min()) == 0.0 for f in factors) and all(float(f.max()) > 1.0 for f in factors)
     loss_ref, logits_ref, grads_ref = V.cait_loss_and_grads(params, images, labels, cfg, 0.1, factors)
 
     model = CaiT(num_classes=1000, num_layers=num_layers, num_layers_token_only=2, num_heads=heads,
