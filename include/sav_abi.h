@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define SAV_ABI_VERSION 2
+#define SAV_ABI_VERSION 3
 
 enum sav_status {
   SAV_OK = 0,
@@ -295,9 +295,10 @@ int sav_sumsq(const float* g, int64_t n, float* out, void* stream);
  * g *= min(1, max_norm/||g||) (sumsq[0] holds ||g||^2; max_norm<=0 disables) -> Adam(b1,b2,eps,
  * bias-corrected with step t) -> + wd*p -> * (-lr) -> p += update; also refreshes bf16 shadow.
  * hyper (optional, device fp32[3] = {lr, 1-b1^t, 1-b2^t}) overrides lr/t so that the step can be
- * replayed from a CUDA graph while the schedule advances. */
+ * replayed from a CUDA graph while the schedule advances.  b1 / b2 are doubles so that
+ * (1 - decay) is formed as optax forms it: in double from the Python float, then rounded. */
 int sav_adam_step(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n,
-                  const float* sumsq, float max_norm, float lr, float b1, float b2, float eps,
+                  const float* sumsq, float max_norm, float lr, double b1, double b2, float eps,
                   float wd, int64_t t, const float* hyper, void* stream);
 /* optax.scale_by_schedule + the Adam bias corrections as a device-resident counter (train.py:25-27,
  * 214-220): step[0] (device int64, the optax `count`) is read, incremented, and hyper (device
@@ -307,7 +308,7 @@ int sav_adam_step(float* p, const float* g, float* m, float* v, void* p_bf16, in
  * optax.warmup_cosine_decay_schedule(init_value, peak_value, warmup_steps, decay_steps, end_value);
  * mode 2: hyper[0] is left as the host wrote it (arbitrary Python schedule). */
 int sav_schedule_step(int64_t* step, float* hyper, int32_t mode, float init_value, float peak_value,
-                      int64_t warmup_steps, int64_t decay_steps, float end_value, float b1, float b2,
+                      int64_t warmup_steps, int64_t decay_steps, float end_value, double b1, double b2,
                       void* stream);
 /* stochastic_depth.py:16-27 mask source: out[b] = floor(keep + U[b]) / keep with U from
  * Philox4x32-10 keyed by seed, counter (b, call_index, step); the step comes from step_dev (device

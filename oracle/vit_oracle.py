@@ -171,10 +171,16 @@ def adam_chain_step(p, g, m, v, t, lr, max_norm=None, b1=0.9, b2=0.999, eps=1e-8
         gn = torch.sqrt((g * g).sum())
         if gn >= max_norm:
             g = g * (max_norm / gn)
-    m = b1 * m + (1 - b1) * g
-    v = b2 * v + (1 - b2) * g * g
-    mhat = m / (1 - b1 ** t)
-    vhat = v / (1 - b2 ** t)
+    # optax.scale_by_adam arithmetic is float32 throughout: (1 - decay) is a Python double rounded to
+    # fp32 by weak typing, the bias correction 1 - decay**count is evaluated in fp32
+    f32 = torch.float32
+    omb1, omb2 = torch.tensor(1 - b1, dtype=f32), torch.tensor(1 - b2, dtype=f32)
+    b1t, b2t = torch.tensor(b1, dtype=f32), torch.tensor(b2, dtype=f32)
+    m = omb1 * g + b1t * m
+    v = omb2 * (g * g) + b2t * v
+    tt = torch.tensor(float(t), dtype=f32)
+    mhat = m / (1 - torch.pow(b1t, tt))
+    vhat = v / (1 - torch.pow(b2t, tt))
     upd = mhat / (torch.sqrt(vhat) + eps) + wd * p
     return p - lr * upd, m, v
 

@@ -196,6 +196,114 @@ ln_bwd_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __restrict_
   }
 }
 
+// Lean backward for C <= 512 (every DeiT / CaiT / CvT width): a lane owns 16-byte pieces (4
+// columns) lane, lane+32, ...; C = 384 is exactly three pieces per lane.  dy stays packed (bf16x4 in
+// two registers) across the row reduction and g = dy*scale is recomputed after it, which keeps
+// the kernel at <= 85 registers = three 256-thread blocks per SM: the kernel is bound by bytes in
+// flight (one row = 3.8 KB per warp), not by arithmetic.
+// DSUM: also accumulate the column sums of the bf16 copy dx16 -- the bias gradient of the Linear
+// that wrote this stream (its dY IS dx16) -- in REGISTER accumulators (the shared-memory version
+// of round 1 cost more than the separate 14 us column-sum pass it removed).
+template <int PIECES, bool DSUM>
+__global__ void __launch_bounds__(256, (PIECES <= 3 && !DSUM) ? 3 : 2)
+ln_bwd_pieces_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __restrict__ x,
+                     int64_t ldx, const float* __restrict__ scale, const float* __restrict__ mean_in,
+                     const float* __restrict__ rstd_in, const float* __restrict__ dx_add,
+                     float* __restrict__ dx, bf16* __restrict__ dx16, float* __restrict__ dscale,
+                     float* __restrict__ dbias, float* __restrict__ dsum, int64_t rows, int C) {
+  extern __shared__ float sacc[];  // [2 or 3][C]
+  const int lane = threadIdx.x & 31;
+  const int64_t warp_global = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int64_t warps_total = (int64_t)gridDim.x * 8;
+  const int npiece = C / 4;
+  const int nacc = (DSUM ? 3 : 2) * C;
+  for (int i = threadIdx.x; i < nacc; i += blockDim.x) sacc[i] = 0.f;
+  __syncthreads();
+  float4 ds[PIECES], db[PIECES], g[PIECES], dc[DSUM ? PIECES : 1];
+#pragma unroll
+  for (int i = 0; i < PIECES; ++i) {
+    const int pc = lane + i * 32;
+    ds[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    db[i] = ds[i];
+    if (DSUM) dc[i] = ds[i];
+    g[i] = pc < npiece ? *reinterpret_cast<const float4*>(scale + pc * 4) : ds[i];
+  }
+  for (int64_t row = warp_global; row < rows; row += warps_total) {
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float4 xh[PIECES], add[PIECES];
+    uint2 dvp[PIECES];
+    // all global loads of the row are issued before the first reduction (one latency per row)
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) {
+      const int pc = lane + i * 32;
+      if (pc < npiece) {
+        if (dx_add) add[i] = *reinterpret_cast<const float4*>(dx_add + row * ldx + pc * 4);
+        xh[i] = *reinterpret_cast<const float4*>(x + row * ldx + pc * 4);
+        dvp[i] = *reinterpret_cast<const uint2*>(dy + row * ldy + pc * 4);
+      }
+    }
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) {
+      const int pc = lane + i * 32;
+      if (pc < npiece) {
+        const float2 d01 = unpack_bf16(dvp[i].x), d23 = unpack_bf16(dvp[i].y);
+        xh[i].x = (xh[i].x - mean) * rstd; xh[i].y = (xh[i].y - mean) * rstd;
+        xh[i].z = (xh[i].z - mean) * rstd; xh[i].w = (xh[i].w - mean) * rstd;
+        const float g0 = d01.x * g[i].x, g1 = d01.y * g[i].y, g2 = d23.x * g[i].z, g3 = d23.y * g[i].w;
+        s1 += (g0 + g1) + (g2 + g3);
+        s2 += (g0 * xh[i].x + g1 * xh[i].y) + (g2 * xh[i].z + g3 * xh[i].w);
+        ds[i].x += d01.x * xh[i].x; ds[i].y += d01.y * xh[i].y;
+        ds[i].z += d23.x * xh[i].z; ds[i].w += d23.y * xh[i].w;
+        db[i].x += d01.x; db[i].y += d01.y; db[i].z += d23.x; db[i].w += d23.y;
+      }
+    }
+    s1 = warp_sum(s1) / (float)C;
+    s2 = warp_sum(s2) / (float)C;
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) {
+      const int pc = lane + i * 32;
+      if (pc < npiece) {
+        const float2 d01 = unpack_bf16(dvp[i].x), d23 = unpack_bf16(dvp[i].y);
+        float4 o;
+        o.x = rstd * (d01.x * g[i].x - s1 - xh[i].x * s2);
+        o.y = rstd * (d01.y * g[i].y - s1 - xh[i].y * s2);
+        o.z = rstd * (d23.x * g[i].z - s1 - xh[i].z * s2);
+        o.w = rstd * (d23.y * g[i].w - s1 - xh[i].w * s2);
+        if (dx_add) { o.x += add[i].x; o.y += add[i].y; o.z += add[i].z; o.w += add[i].w; }
+        *reinterpret_cast<float4*>(dx + row * ldx + pc * 4) = o;
+        if (dx16) {
+          const uint32_t p01 = pack_bf16(o.x, o.y), p23 = pack_bf16(o.z, o.w);
+          *reinterpret_cast<uint2*>(dx16 + row * ldx + pc * 4) = make_uint2(p01, p23);
+          if (DSUM) {
+            const float2 r01 = unpack_bf16(p01), r23 = unpack_bf16(p23);
+            dc[i].x += r01.x; dc[i].y += r01.y; dc[i].z += r23.x; dc[i].w += r23.y;
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < PIECES; ++i) {
+    const int pc = lane + i * 32;
+    if (pc < npiece) {
+      float* a = sacc + pc * 4;
+      atomicAdd(a, ds[i].x); atomicAdd(a + 1, ds[i].y); atomicAdd(a + 2, ds[i].z); atomicAdd(a + 3, ds[i].w);
+      a += C;
+      atomicAdd(a, db[i].x); atomicAdd(a + 1, db[i].y); atomicAdd(a + 2, db[i].z); atomicAdd(a + 3, db[i].w);
+      if (DSUM) {
+        a += C;
+        atomicAdd(a, dc[i].x); atomicAdd(a + 1, dc[i].y); atomicAdd(a + 2, dc[i].z); atomicAdd(a + 3, dc[i].w);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < nacc; i += blockDim.x) {
+    float* out = (i < C) ? (dscale + i) : (i < 2 * C ? dbias + (i - C) : dsum + (i - 2 * C));
+    atomicAdd(out, sacc[i]);
+  }
+}
+
 static int ln_grid(int64_t rows) {
   int64_t g = (rows + 7) / 8;
   const int64_t cap = 148 * 4;
@@ -246,6 +354,31 @@ extern "C" int sav_layernorm_bwd_colsum(const void* dy, int64_t ldy, const float
   const int chunks = (int)((C / 8 + 31) / 32);
   float* dsum = dx_bf16_colsum;
   const size_t sm = (dsum ? 3 : 2) * C * sizeof(float);
+  if (C <= 512 && dx_bf16) {
+    const int pieces = (int)((C / 4 + 31) / 32);
+    const int grid_p = (int)((rows + 7) / 8 < 148 * 6 ? ((rows + 7) / 8 < 1 ? 1 : (rows + 7) / 8) : 148 * 6);
+#define LN_BWDP(PC, DS)                                                                          \
+  ln_bwd_pieces_kernel<PC, DS><<<grid_p, 256, sm, st>>>(reinterpret_cast<const bf16*>(dy), ldy, x, ldx, \
+      scale, mean, rstd, dx_add, dx, reinterpret_cast<bf16*>(dx_bf16), dscale, dbias, dsum, rows, (int)C)
+    if (dsum) {
+      switch (pieces) {
+        case 1: LN_BWDP(1, true); break;
+        case 2: LN_BWDP(2, true); break;
+        case 3: LN_BWDP(3, true); break;
+        default: LN_BWDP(4, true); break;
+      }
+    } else {
+      switch (pieces) {
+        case 1: LN_BWDP(1, false); break;
+        case 2: LN_BWDP(2, false); break;
+        case 3: LN_BWDP(3, false); break;
+        default: LN_BWDP(4, false); break;
+      }
+    }
+#undef LN_BWDP
+    count_launch();
+    return check_launch("sav_layernorm_bwd");
+  }
 #define LN_BWD(CH)                                                                            \
   ln_bwd_kernel<CH><<<grid, 256, sm, st>>>(reinterpret_cast<const bf16*>(dy), ldy, x, ldx, scale, \
                                             mean, rstd, dx_add, dx,                            \

@@ -104,8 +104,8 @@ __global__ void sumsq_kernel(const float* __restrict__ g, int64_t n, float* __re
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g,
                             float* __restrict__ m, float* __restrict__ v, bf16* __restrict__ pb,
                             int64_t n, const float* __restrict__ sumsq, float max_norm, float lr,
-                            float b1, float b2, float eps, float wd, float bc1, float bc2,
-                            const float* __restrict__ hyper) {
+                            float b1, float b2, float omb1, float omb2, float eps, float wd,
+                            float bc1, float bc2, const float* __restrict__ hyper) {
   if (hyper) { lr = hyper[0]; bc1 = hyper[1]; bc2 = hyper[2]; }
   float clip = 1.f;
   if (max_norm > 0.f && sumsq) {
@@ -115,8 +115,10 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g,
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
        i += (int64_t)gridDim.x * blockDim.x) {
     const float gi = g[i] * clip;
-    const float mi = b1 * m[i] + (1.f - b1) * gi;
-    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    // optax update_moment: (1 - decay) * g^order + decay * moment, with (1 - decay) formed in
+    // double from the Python float and THEN rounded (omb = fp32(1 - decay), not 1.f - fp32(decay))
+    const float mi = omb1 * gi + b1 * m[i];
+    const float vi = omb2 * (gi * gi) + b2 * v[i];
     m[i] = mi;
     v[i] = vi;
     const float pi = p[i];
@@ -278,12 +280,13 @@ extern "C" int sav_softmax_xent(const void* logits, int64_t ld, const int32_t* l
 
 extern "C" int sav_schedule_step(int64_t* step, float* hyper, int32_t mode, float init_value,
                                  float peak_value, int64_t warmup_steps, int64_t decay_steps,
-                                 float end_value, float b1, float b2, void* stream) {
+                                 float end_value, double b1, double b2, void* stream) {
   if (!step || !hyper) return set_error(SAV_ERR_ARG, "sav_schedule_step: null step / hyper");
   if (mode < 0 || mode > 2) return set_error(SAV_ERR_ARG, "sav_schedule_step: mode in {0,1,2}");
   if (mode == 1 && warmup_steps < 0) return set_error(SAV_ERR_ARG, "sav_schedule_step: warmup < 0");
   schedule_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      step, hyper, mode, init_value, peak_value, warmup_steps, decay_steps, end_value, b1, b2);
+      step, hyper, mode, init_value, peak_value, warmup_steps, decay_steps, end_value, (float)b1,
+      (float)b2);
   count_launch();
   return check_launch("sav_schedule_step");
 }
@@ -330,15 +333,17 @@ extern "C" int sav_sumsq(const float* g, int64_t n, float* out, void* stream) {
 }
 
 extern "C" int sav_adam_step(float* p, const float* g, float* m, float* v, void* p_bf16,
-                             int64_t n, const float* sumsq, float max_norm, float lr, float b1,
-                             float b2, float eps, float wd, int64_t t, const float* hyper,
+                             int64_t n, const float* sumsq, float max_norm, float lr, double b1d,
+                             double b2d, float eps, float wd, int64_t t, const float* hyper,
                              void* stream) {
+  const float b1 = (float)b1d, b2 = (float)b2d;
+  const float omb1 = (float)(1.0 - b1d), omb2 = (float)(1.0 - b2d);
   if (n <= 0) return SAV_OK;
   if (t < 1 && !hyper) return set_error(SAV_ERR_ARG, "sav_adam_step: step count t starts at 1");
   const float bc1 = 1.f - powf(b1, (float)t), bc2 = 1.f - powf(b2, (float)t);
   adam_kernel<<<grid_for(n, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      p, g, m, v, reinterpret_cast<bf16*>(p_bf16), n, sumsq, max_norm, lr, b1, b2, eps, wd, bc1, bc2,
-      hyper);
+      p, g, m, v, reinterpret_cast<bf16*>(p_bf16), n, sumsq, max_norm, lr, b1, b2, omb1, omb2, eps, wd,
+      bc1, bc2, hyper);
   count_launch();
   return check_launch("sav_adam_step");
 }

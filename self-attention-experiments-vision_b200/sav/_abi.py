@@ -83,7 +83,7 @@ class ThSoftmaxArgs(C.Structure):
     ]
 
 
-_P, _I64, _I32, _F = C.c_void_p, C.c_int64, C.c_int32, C.c_float
+_P, _I64, _I32, _F, _D = C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_double
 
 # name -> (restype, argtypes); also the list the CPU test checks against include/sav_abi.h
 SIGNATURES = {
@@ -117,12 +117,12 @@ SIGNATURES = {
     "sav_attn_bwd": (C.c_int, [C.POINTER(AttnBwdArgs), _P]),
     "sav_softmax_xent": (C.c_int, [_P, _I64, _P, _I64, _I64, _F, _F, _P, _P, _P]),
     "sav_softmax_xent_mix": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _I64, _F, _F, _P, _P, _P]),
-    "sav_schedule_step": (C.c_int, [_P, _P, _I32, _F, _F, _I64, _I64, _F, _F, _F, _P]),
+    "sav_schedule_step": (C.c_int, [_P, _P, _I32, _F, _F, _I64, _I64, _F, _D, _D, _P]),
     "sav_drop_path_factors": (C.c_int, [C.c_uint64, _P, _I64, _I64, _I64, _F, _P, _P]),
     "sav_topk_correct": (C.c_int, [_P, _I64, _P, _I64, _I64, _I32, _I32, _I32, _I32, _I32, _P, _P]),
     "sav_cast_f32_bf16": (C.c_int, [_P, _P, _I64, _P]),
     "sav_sumsq": (C.c_int, [_P, _I64, _P, _P]),
-    "sav_adam_step": (C.c_int, [_P, _P, _P, _P, _P, _I64, _P, _F, _F, _F, _F, _F, _F, _I64, _P, _P]),
+    "sav_adam_step": (C.c_int, [_P, _P, _P, _P, _P, _I64, _P, _F, _F, _D, _D, _F, _F, _I64, _P, _P]),
     "sav_add_bf16": (C.c_int, [_P, _P, _P, _I64, _P]),
     "sav_fill_f32": (C.c_int, [_P, _F, _I64, _P]),
     "sav_copy2d_bf16": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, _P]),
@@ -142,7 +142,7 @@ def lib():
             fn = getattr(l, name)
             fn.restype = res
             fn.argtypes = args
-        if l.sav_abi_version() != 2:
+        if l.sav_abi_version() != 3:
             raise SavError("libsav_b200.so ABI version mismatch")
         _lib = l
     return _lib

@@ -42,11 +42,11 @@ class Weight:
             p.touch_grad()
 
 
-# SAV_FUSE_BIAS_COLSUM=1 folds the out-proj / FC2 bias gradients into LayerNorm backward
-# (sav_layernorm_bwd_colsum).  Off by default: measured on one box it costs 0.35 ms per DeiT-S step
-# (14.38 vs 14.02 ms, profiles/r01n_ab_fuse.log) -- the 384 shared-memory adds per row slow the
-# bytes-in-flight-bound LayerNorm kernel by more than the two 14 us column-sum passes it removes.
-_FUSE_BIAS_COLSUM = os.environ.get("SAV_FUSE_BIAS_COLSUM", "0") == "1"
+# The out-proj / FC2 bias gradients (column sums of the bf16 stream-gradient copy) are accumulated
+# by LayerNorm backward itself in register accumulators: +1.6 us on the 60 us kernel against a
+# separate 14.4 us column-sum pass (profiles/r02d_membound.log; 13.29 -> 13.18 ms per DeiT-S step).
+# SAV_FUSE_BIAS_COLSUM=0 restores the separate pass (A/B switch).
+_FUSE_BIAS_COLSUM = os.environ.get("SAV_FUSE_BIAS_COLSUM", "1") == "1"
 
 
 def _grad16(var):

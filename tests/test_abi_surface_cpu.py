@@ -40,7 +40,7 @@ def test_library_exports_every_declared_symbol(built_lib):
     lib = ctypes.CDLL(built_lib.LIB_PATH)
     for name in _declared_functions():
         assert hasattr(lib, name), f"{name} declared in include/sav_abi.h but not exported"
-    assert built_lib.lib().sav_abi_version() == 2
+    assert built_lib.lib().sav_abi_version() == 3
 
 
 def test_ctypes_table_matches_header(built_lib):

@@ -67,7 +67,10 @@ def test_device_schedule_matches_optax_restatement():
         assert abs(float(h[0]) - ref(count)) <= 2e-6 * peak + 1e-12, (count, float(h[0]), ref(count))
         assert abs(host(count) - ref(count)) <= 1e-12
         assert abs(float(h[1]) - (1 - b1 ** (count + 1))) <= 1e-6
-        assert abs(float(h[2]) - (1 - b2 ** (count + 1))) <= 1e-6 * max(1 - b2 ** (count + 1), 1e-3) + 1e-7
+        # fp32 like optax (1 - decay**count in float32): two ulps of the power
+        import numpy as np
+        bc2 = np.float32(1) - np.power(np.float32(b2), np.float32(count + 1))
+        assert abs(float(h[2]) - float(bc2)) <= 2.4e-7
     assert ref(0) == 0.0 and abs(ref(warm) - peak) < 1e-12 and abs(ref(10 ** 6) - end) < 1e-12
 
 
@@ -98,9 +101,14 @@ def test_unsynchronised_graphed_steps_equal_eager_synchronised_steps(lr_kind):
     assert s1.step == s2.step == N + 2
     assert int(s1.step_dev.item()) == int(s2.step_dev.item()) == N + 2
     a, b = s1.arena.master, s2.arena.master
-    # dW split-K partials are combined by fp32 reduce-adds in arrival order: fp32 rounding, not bits
-    err = float((a - b).abs().max() / a.abs().max())
-    assert err <= 2e-4, err
+    # Two separately built states: dW split-K partials are combined by fp32 reduce-adds in arrival
+    # order, and Adam's m / sqrt(v) turns last-bit gradient differences of near-zero gradients into
+    # O(lr) parameter differences on a few elements -- so compare in relative L2.  A schedule that
+    # is stale by ONE step moves every parameter by sum_t |lr_t - lr_{t+1}| ~ 3e-3 against an rms
+    # parameter of ~0.07: relative L2 >= 4e-2.
+    l2 = float((a - b).norm() / a.norm())
+    print("unsynchronised vs eager: relative L2", l2, "max", float((a - b).abs().max()))
+    assert l2 <= 4e-3, l2
     assert float((s1.hyper - s2.hyper).abs().max()) <= 1e-7 * 3e-3 + 1e-9
 
 

@@ -68,6 +68,12 @@ def main():
     warm = timeit([lambda: ops.layernorm_bwd(dy[0], x[0], scale, mean, rstd, dscale, dbias, dx_add=g[0],
                                              dx=dx[0], dx16=dx16[0])] * 4)
     report("ln_bwd (+stream grad)", cold, warm, M * C * 16)
+    dsum = torch.zeros(C, device=dev)
+    cold = timeit([(lambda i=i: ops.layernorm_bwd(dy[i], x[i], scale, mean, rstd, dscale, dbias, dx_add=g[i],
+                                                  dx=dx[i], dx16=dx16[i], dx16_colsum=dsum)) for i in range(nbuf)])
+    warm = timeit([lambda: ops.layernorm_bwd(dy[0], x[0], scale, mean, rstd, dscale, dbias, dx_add=g[0],
+                                             dx=dx[0], dx16=dx16[0], dx16_colsum=dsum)] * 4)
+    report("ln_bwd + bias colsum", cold, warm, M * C * 16)
 
 
 if __name__ == "__main__":
