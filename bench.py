@@ -132,25 +132,90 @@ def run_reference(args):
     }), flush=True)
 
 
-def time_isolated_gemm(torch, ops, M, C, hid, reps=20):
-    """Dominant kernel (FC1: [M,C]x[C,4C] + bias + GELU epilogue) timed alone with CUDA events."""
-    x = torch.randn(M, C, device="cuda").bfloat16()
-    w = (torch.randn(C, hid, device="cuda") / C ** 0.5).bfloat16()
-    b = torch.randn(hid, device="cuda")
-    out = torch.empty(M, hid, device="cuda", dtype=torch.bfloat16)
-    pre = torch.empty_like(out)
-    for _ in range(3):
-        ops.gemm(x, w, b_mn=True, out=out, bias=b, act=1, aux_out=pre)
+def _event_time(torch, fn, reps=20, warm=3):
+    """Average device time (ms) of fn() with CUDA events on the launching stream."""
+    for _ in range(warm):
+        fn()
     st = torch.cuda.current_stream()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     e0.record(st)
     for _ in range(reps):
-        ops.gemm(x, w, b_mn=True, out=out, bias=b, act=1, aux_out=pre)
+        fn()
     e1.record(st)
     torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / reps
-    return 2.0 * M * C * hid / (ms * 1e-3) / 1e12, ms
+    return e0.elapsed_time(e1) / reps
+
+
+def kernel_rooflines(torch, ops, B, cfg, pk, launches_per_step_ms):
+    """The step's heaviest kernels timed ALONE (CUDA events, every launch streams > L2 of fresh
+    bytes) against both roofs on SURVEY 8(d)'s accounting: algorithmic FLOPs (1 MAC = 2, backward
+    without recomputation) and algorithmic bytes (every bf16 operand / result once).  The entry
+    with the largest share of the step (duration x launches per step / step time) comes first."""
+    N, C, H = 197, cfg["embed_dim"], cfg["num_heads"]
+    d, hid, M, L = C // H, 4 * C, B * 197, cfg["num_layers"]
+    dev = "cuda"
+    ents = []
+
+    def entry(name, what, ms, flops, alg_bytes, launches, note=None):
+        t_tensor = flops / (pk["tf_burst"] * 1e12) * 1e3
+        t_hbm = alg_bytes / (pk["hbm"] * 1e9) * 1e3
+        bound = "tensor" if t_tensor >= t_hbm else "hbm"
+        e = {"kernel": name, "replaces": what, "ms": ms, "launches_per_step": launches,
+             "share_of_step": ms * launches / launches_per_step_ms,
+             "flops": flops, "algorithmic_bytes": alg_bytes,
+             "tflops": flops / (ms * 1e-3) / 1e12, "gbs": alg_bytes / (ms * 1e-3) / 1e9,
+             "tensor_floor_ms": t_tensor, "hbm_floor_ms": t_hbm, "bound": bound,
+             "frac_of_tensor_peak": flops / (ms * 1e-3) / 1e12 / pk["tf_burst"],
+             "frac_of_hbm_peak": alg_bytes / (ms * 1e-3) / 1e9 / pk["hbm"]}
+        e["frac"] = e["frac_of_tensor_peak"] if bound == "tensor" else e["frac_of_hbm_peak"]
+        if note:
+            e["note"] = note
+        ents.append(e)
+
+    # ---- fused attention (attention.py:39-58 and its reverse mode), one encoder layer
+    qkv = torch.randn(B, N, 3, H, d, device=dev).bfloat16()
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    o2, lse = ops.attn_fwd(q, k, v)
+    d_o = torch.randn(B, N, H, d, device=dev).bfloat16()
+    dqkv = torch.empty_like(qkv)
+    tok = B * N * H * d * 2           # bytes of one bf16 [B,N,H,d] tensor
+    ms = _event_time(torch, lambda: ops.attn_fwd(q, k, v))
+    entry("attn_fwd2_kernel", "attention.py:39-58", ms, 4.0 * N * N * d * B * H, 4 * tok, L,
+          "q,k,v in, o out; the kernel also writes o_lo (bf16 remainder of O) and lse")
+    ms = _event_time(torch, lambda: ops.attn_bwd(q, k, v, o2, d_o, lse, dqkv[:, :, 0], dqkv[:, :, 1],
+                                                 dqkv[:, :, 2]))
+    entry("attn_bwd3_kernel", "reverse mode of attention.py:39-58", ms, 8.0 * N * N * d * B * H, 8 * tok, L,
+          "q,k,v,o,dO in, dq,dk,dv out (10 N^2 d executed with S recomputed; also reads o_lo)")
+    del qkv, o2, d_o, dqkv
+    # ---- FC1 GEMM, bias + GELU epilogue (ff.py:24-25)
+    x = torch.randn(M, C, device=dev).bfloat16()
+    w = (torch.randn(C, hid, device=dev) / C ** 0.5).bfloat16()
+    b = torch.randn(hid, device=dev)
+    out = torch.empty(M, hid, device=dev, dtype=torch.bfloat16)
+    pre = torch.empty_like(out)
+    ms = _event_time(torch, lambda: ops.gemm(x, w, b_mn=True, out=out, bias=b, act=1, aux_out=pre))
+    entry("gemm_kernel<256,K,MN,pair> FC1", "ff.py:24-25", ms, 2.0 * M * C * hid,
+          M * C * 2 + C * hid * 2 + hid * 4 + M * hid * 2, L,
+          "8(d) accounting: ONE bf16 output; the kernel writes two (pre-activation saved for the "
+          "backward + activation): actual bytes %d" % (M * C * 2 + C * hid * 2 + hid * 4 + 2 * M * hid * 2))
+    del out, pre, w, b
+    # ---- LayerNorm backward (+ stream-gradient fan-in, bf16 copy, bias column sums)
+    xs = torch.randn(M, C, device=dev)
+    dy = torch.randn(M, C, device=dev).bfloat16()
+    g_in = torch.randn(M, C, device=dev)
+    dx = torch.empty(M, C, device=dev)
+    dx16 = torch.empty(M, C, device=dev, dtype=torch.bfloat16)
+    sc, bi = torch.ones(C, device=dev), torch.zeros(C, device=dev)
+    dsc, dbi = torch.zeros(C, device=dev), torch.zeros(C, device=dev)
+    _y, mean, rstd = ops.layernorm_fwd(xs, sc, bi)
+    ms = _event_time(torch, lambda: ops.layernorm_bwd(dy, xs, sc, mean, rstd, dsc, dbi, dx_add=g_in, dx=dx,
+                                                      dx16=dx16))
+    entry("ln_bwd_pieces_kernel", "reverse mode of nn.LayerNorm (vit.py:19,26,57)", ms, 0.0, 3 * M * C * 2,
+          2 * L + 1, "8(d): 3 x bf16 per element; the kernel moves 16 B per element (fp32 x, fp32 stream "
+                     "gradient in and out, bf16 dy, bf16 copy): actual bytes %d" % (16 * M * C))
+    ents.sort(key=lambda e: -e["share_of_step"])
+    return ents
 
 
 def main():
@@ -288,26 +353,37 @@ def main():
         fl = 3 * 9.198e9 * B  # train FLOP/img = 3 x fwd
         out["step_tflops"] = fl / (total_ms / K * 1e-3) / 1e12
         out["step_frac_of_sustained_peak"] = out["step_tflops"] / pk["tf_sust"]
-        # dominant kernel = the FC1 GEMM (bias + GELU epilogue, saves the pre-activation): the most
-        # expensive single launch of the step.  K = 384 puts it past the ridge on the memory side:
-        # algorithmic bytes = X + W + bias in, pre-activation + activation out
-        # => 53 us at HBM peak vs 36 us at tensor peak, so the HBM roofline is the binding one.
-        M_, C_, H_ = B * 197, cfg["embed_dim"], 4 * cfg["embed_dim"]
-        tf, ms = time_isolated_gemm(torch, ops, M_, C_, H_)
-        alg_bytes = M_ * C_ * 2 + C_ * H_ * 2 + H_ * 4 + 2 * M_ * H_ * 2
-        gbs = alg_bytes / (ms * 1e-3) / 1e9
-        out["roofline"] = {"bound": "hbm", "kernel": "gemm_kernel<256,K,MN> FC1 bias+GELU epilogue (2 outputs)",
-                           "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s",
-                           "frac": gbs / pk["hbm"],
-                           # dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set
-                           # full capture profiles/r01j_ncu_full_fc1_fwd.txt (same shape): 40.0 MB read
-                           # + 249.4 MB written (the tail of the 310 MB output is still in L2)
-                           "traffic": 289.36e6, "algorithmic_bytes": alg_bytes, "ms": ms,
-                           # 89 % of the bytes are writes; write-only HBM peak on this pool is
-                           # 3.76-3.9 TB/s (tests/tools/hbm_write_peak.py) against 6.5 TB/s for a copy
-                           "write_bytes": 2 * M_ * H_ * 2,
-                           "tensor_tflops": tf, "tensor_frac_of_burst_peak": tf / pk["tf_burst"],
-                           "peak_source": pk["src"] + " (copy bandwidth; kernel timed alone)"}
+        # Roofline block: the heaviest kernels of the step timed alone; `roofline` is the one with
+        # the largest share of the step, `kernels` lists all of them with both roofs.  BASELINE's
+        # metric names "attn TC-pipe % of peak": attention_tc_pipe carries FLOP/time against the
+        # measured dense-bf16 burst peak for both attention kernels and the ncu tensor-pipe counter
+        # of the same shapes (profiles/, captured under ncu, not in this run).
+        ents = kernel_rooflines(torch, ops, B, cfg, pk, total_ms / K)
+        top = ents[0]
+        traffic = {"attn_bwd3_kernel": None, "attn_fwd2_kernel": None}
+        try:
+            with open(os.path.join(ROOT, "profiles", "r02_ncu_counters.json")) as f:
+                ncu = json.load(f)
+        except Exception:
+            ncu = {}
+        for e in ents:
+            c = ncu.get(e["kernel"].split("<")[0].split(" ")[0], {})
+            e["traffic"] = c.get("dram_bytes")
+            if "tensor_pipe_pct" in c:
+                e["ncu_tensor_pipe_pct"] = c["tensor_pipe_pct"]
+        out["roofline"] = {"bound": top["bound"], "kernel": top["kernel"],
+                           "achieved": top["gbs"] if top["bound"] == "hbm" else top["tflops"],
+                           "peak": pk["hbm"] if top["bound"] == "hbm" else pk["tf_burst"],
+                           "unit": "GB/s" if top["bound"] == "hbm" else "TFLOP/s",
+                           "frac": top["frac"], "traffic": top.get("traffic"),
+                           "algorithmic_bytes": top["algorithmic_bytes"], "flops": top["flops"],
+                           "ms": top["ms"], "share_of_step": top["share_of_step"],
+                           "peak_source": pk["src"] + " (burst / copy figures; kernel timed alone)"}
+        out["kernels"] = ents
+        att = {e["kernel"]: e for e in ents if e["kernel"].startswith("attn")}
+        out["attention_tc_pipe"] = {
+            k: {"tflops": e["tflops"], "pct_of_dense_bf16_peak": 100.0 * e["frac_of_tensor_peak"],
+                "ncu_tensor_pipe_pct": e.get("ncu_tensor_pipe_pct")} for k, e in att.items()}
         if world == 1 and not args.no_cpu_baseline:
             v, threads, dt = cpu_oracle_throughput(batch=64, reps=5)
             out["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": threads, "kind": "port",

@@ -263,6 +263,64 @@ int sav_batchnorm_bwd(const void* dz, const void* y, const float* mean, const fl
                       const float* gamma, float* dgamma, float* dbeta, float* scratch, void* dy,
                       int64_t rows, int64_t C, void* stream);
 
+/* LayerNorm INTO the fp32 residual stream (the LayerNorm that closes the CvT conv token embedding,
+ * cvt.py:34): fp32 in, fp32 out; reverse mode with an fp32 upstream gradient; otherwise as
+ * sav_layernorm_fwd / sav_layernorm_bwd. */
+int sav_layernorm_fwd_f32(const float* x, int64_t ldx, const float* scale, const float* bias, float* y,
+                          int64_t ldy, float* mean, float* rstd, int64_t rows, int64_t C, float eps,
+                          void* stream);
+int sav_layernorm_bwd_f32(const float* dy, int64_t ldy, const float* x, int64_t ldx, const float* scale,
+                          const float* mean, const float* rstd, const float* dx_add, float* dx,
+                          void* dx_bf16, float* dscale, float* dbias, int64_t rows, int64_t C,
+                          void* stream);
+/* dst fp32 [rows, cols] ldd (+)= src bf16 [rows, cols] lds */
+int sav_cast2d_bf16_f32(const void* src, int64_t lds, float* dst, int64_t ldd, int64_t rows,
+                        int64_t cols, int32_t accumulate, void* stream);
+
+/* ---------------------------------------------------------------- dense convolutions (im2col + GEMM)
+ * nn.Conv of the CvT token embedding (cvt.py:27-31: 7x7 / 3x3, stride 4 / 2, SAME, bias) and of the
+ * BoTNet ResNet stem / bottleneck convs (botnet.py:47-64,291-305): the patch matrix is built by
+ * sav_im2col, the contraction is sav_gemm (forward [M,K]x[K,Cout]; dW = cols^T dY; dcols = dY W^T),
+ * and sav_col2im folds dcols back onto the input (gather form, no atomics).
+ * x is addressed through element strides, so both [B,H,W,C] and the loader's [H,W,C,N] work. */
+typedef struct sav_conv2d_geom {
+  int64_t B, H, W, C;            /* input */
+  int64_t Ho, Wo;                /* output spatial size */
+  int32_t kh, kw, sh, sw;        /* kernel, strides */
+  int32_t pad_top, pad_left;     /* low-side zero padding (high side implied by Ho / Wo) */
+  int64_t xs_b, xs_h, xs_w, xs_c; /* element strides of x */
+  int64_t ld;                    /* row pitch of the patch matrix: >= kh*kw*C, multiple of 8 */
+} sav_conv2d_geom;
+/* flax / XLA padding='SAME': out = ceil(in / stride), total pad = max((out-1)*stride + k - in, 0),
+ * low side = total / 2. */
+int sav_conv_same_geom(int64_t in, int32_t k, int32_t stride, int64_t* out, int32_t* pad_lo);
+/* cols bf16 [B*Ho*Wo, ld], feature order (kh, kw, cin); columns >= kh*kw*C are zero */
+int sav_im2col(const void* x, int32_t x_is_fp32, void* cols, const sav_conv2d_geom* g, void* stream);
+/* dx [B,H,W,C] contiguous (fp32 or bf16) (+)= fold(dcols) */
+int sav_col2im(const void* dcols, void* dx, int32_t dx_is_fp32, int32_t accumulate,
+               const sav_conv2d_geom* g, void* stream);
+/* BatchNorm pieces beyond sav_batchnorm_fwd/bwd: batch sums of a bf16 [rows,C] tensor (callee
+ * zero-fills sum / sumsq), the running-average update ra = momentum*ra + (1-momentum)*stat
+ * (flax nn.BatchNorm, cvt_attention.py:33-36), and the eval-mode apply from running averages. */
+int sav_bn_stats(const void* y, int64_t rows, int64_t C, float* sum, float* sumsq, void* stream);
+int sav_bn_update_running(const float* mean, const float* var, float* ra_mean, float* ra_var,
+                          float momentum, int64_t C, void* stream);
+int sav_batchnorm_eval(const void* y, const float* ra_mean, const float* ra_var, const float* gamma,
+                       const float* beta, float eps, void* z, int64_t rows, int64_t C, void* stream);
+
+/* ---------------------------------------------------------------- rotary helpers
+ * models/layers/position_embed.py:8-45 (unused by every reference model and unfinished there:
+ * parity unpinned; the intended RoFormer rotation with the reference's literal float32 frequency
+ * table inv_freq[i] = 1 / (10e4^(2i) / dim), position_embed.py:29).
+ * sav_rotary: x, y [outer, n, inner, d] contiguous (bf16, or fp32 when is_fp32), rotation of the
+ * (2i, 2i+1) pairs of the last axis by t * inv_freq[i], t = index on the n axis
+ * (apply_rotary_pos_emb + rotate_every_two, position_embed.py:8-20); inverse != 0 rotates back
+ * (the reverse mode).  sav_rotary_table: FixedPositionalEmbedding (position_embed.py:23-34),
+ * emb fp32 [n, dim] = concat(freqs, freqs). */
+int sav_rotary(const void* x, void* y, int64_t outer, int64_t n, int64_t inner, int64_t d,
+               int32_t is_fp32, int32_t inverse, void* stream);
+int sav_rotary_table(float* emb, int64_t n, int64_t dim, void* stream);
+
 /* ---------------------------------------------------------------- loss head (train.py:83-91)
  * one_hot -> smooth_labels(alpha) -> softmax_cross_entropy -> mean; writes dlogits = dloss/dlogits
  * (bf16 [B,classes]) and accumulates loss into loss_out[0] (zeroed by the callee), top1 count into

@@ -327,3 +327,149 @@ def synthetic_cvt_stage_params(C, num_heads, seed=42, dtype=torch.float32):
         "FFBlock_0": {"Dense_0": {"kernel": normal((C, hid), 1.0 / math.sqrt(C)), "bias": normal((hid,), 0.02)},
                       "Dense_1": {"kernel": normal((hid, C), 1.0 / math.sqrt(hid)), "bias": normal((C,), 0.02)}},
     }
+
+
+def conv_projection_eval(x, p, stride, ra_mean, ra_var, eps=1e-5):
+    """ConvProjectionBlock with use_running_average=True (is_training=False, cvt_attention.py:33):
+    the BatchNorm normalises with the running averages."""
+    B, H, W, C = x.shape
+    pt, pb = same_pad_amounts(H, stride)
+    pl, pr = same_pad_amounts(W, stride)
+    xi = torch.nn.functional.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb))
+    wk = p["Conv_0"]["kernel"].permute(3, 2, 0, 1)
+    y = torch.nn.functional.conv2d(xi, wk, stride=stride, groups=C).permute(0, 2, 3, 1)
+    z = (y - ra_mean) * torch.rsqrt(ra_var + eps) * p["BatchNorm_0"]["scale"] + p["BatchNorm_0"]["bias"]
+    return z @ p["Conv_1"]["kernel"].reshape(C, -1)
+
+
+def conv_projection_batch_stats(x, p, stride):
+    """(mean, biased var) over B,H,W of the depthwise conv output -- what flax nn.BatchNorm folds into
+    its running averages: ra <- momentum * ra + (1 - momentum) * stat."""
+    B, H, W, C = x.shape
+    pt, pb = same_pad_amounts(H, stride)
+    pl, pr = same_pad_amounts(W, stride)
+    xi = torch.nn.functional.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb))
+    wk = p["Conv_0"]["kernel"].permute(3, 2, 0, 1)
+    y = torch.nn.functional.conv2d(xi, wk, stride=stride, groups=C).permute(0, 2, 3, 1)
+    mean = y.mean(dim=(0, 1, 2))
+    return mean, (y * y).mean(dim=(0, 1, 2)) - mean * mean
+
+
+def conv2d_same(x, kernel, bias, stride):
+    """nn.Conv(features, (k,k), strides=(s,s), padding='SAME') on [B,H,W,Cin] with a Flax kernel
+    [kh,kw,cin,cout] (cvt.py:27-31)."""
+    k = kernel.shape[0]
+    B, H, W, C = x.shape
+    pt, pb = same_pad_amounts(H, stride, k)
+    pl, pr = same_pad_amounts(W, stride, k)
+    xi = torch.nn.functional.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb))
+    y = torch.nn.functional.conv2d(xi, kernel.permute(3, 2, 0, 1), bias=bias, stride=stride)
+    return y.permute(0, 2, 3, 1)
+
+
+def conv_token_embed(x, p, stride):
+    """ConvTokenEmbedBlock.__call__ (cvt.py:25-35): conv -> 'b H W c -> b (H W) c' -> LayerNorm."""
+    y = conv2d_same(x, p["Conv_0"]["kernel"], p["Conv_0"]["bias"], stride)      # cvt.py:27-31
+    y = y.reshape(y.shape[0], -1, y.shape[-1])                                   # cvt.py:32
+    return layer_norm(y, p["LayerNorm_0"]["scale"], p["LayerNorm_0"]["bias"])    # cvt.py:34
+
+
+def cvt_forward(params, images_nhwc, cfg):
+    """CvT.__call__ (cvt.py:131-171) + Stage.__call__ (cvt.py:86-113), training mode."""
+    x = images_nhwc
+    n = len(cfg["stage_sizes"])
+    for i in range(n):
+        sp = params[f"Stage_{i}"]
+        x = conv_token_embed(x, sp["ConvTokenEmbedBlock_0"], cfg["embed_strides"][i])   # cvt.py:88-91
+        if i == n - 1:                                                           # insert_cls, cvt.py:93-98
+            x = torch.cat([sp["cls"].expand(x.shape[0], -1, -1), x], dim=1)
+        for j in range(cfg["stage_sizes"][i]):                                   # cvt.py:100-110
+            x = cvt_stage_block(x, sp[f"StageBlock_{j}"], cfg["num_heads"][i])
+        if i < n - 1:
+            S = int(math.sqrt(x.shape[1]))                                       # cvt.py:147-149
+            x = x.reshape(x.shape[0], S, S, x.shape[-1])
+    cls_token = x[:, 0]                                                          # cvt.py:165
+    return cls_token @ params["Dense_0"]["kernel"] + params["Dense_0"]["bias"]   # cvt.py:166-170
+
+
+def cvt_config(name):
+    cfgs = {
+        "cvt-13": dict(stage_sizes=(1, 2, 10), num_heads=(1, 3, 6), embed_dim=(64, 192, 384)),
+        "cvt-21": dict(stage_sizes=(1, 4, 16), num_heads=(1, 3, 6), embed_dim=(64, 192, 384)),
+        "cvt-w24": dict(stage_sizes=(2, 2, 20), num_heads=(3, 12, 16), embed_dim=(192, 768, 1024)),
+    }
+    c = dict(cfgs[name])
+    c.update(embed_kernel_size=(7, 3, 3), embed_strides=(4, 2, 2), num_classes=1000)
+    return c
+
+
+def synthetic_cvt_params(cfg, seed=42, dtype=torch.float32):
+    """SURVEY 8d synthetic init with the Flax auto-names of cvt.py."""
+    g = torch.Generator().manual_seed(seed)
+
+    def normal(shape, std):
+        return (torch.randn(shape, generator=g, dtype=torch.float64) * std).to(dtype)
+    params = {}
+    cin = 3
+    n = len(cfg["stage_sizes"])
+    for i in range(n):
+        C, k = cfg["embed_dim"][i], cfg["embed_kernel_size"][i]
+        sp = {"ConvTokenEmbedBlock_0": {
+            "Conv_0": {"kernel": normal((k, k, cin, C), 1.0 / math.sqrt(k * k * cin)), "bias": normal((C,), 0.02)},
+            "LayerNorm_0": {"scale": 1.0 + normal((C,), 0.02), "bias": normal((C,), 0.02)}}}
+        if i == n - 1:
+            sp["cls"] = normal((1, 1, C), 0.02)
+        for j in range(cfg["stage_sizes"][i]):
+            sp[f"StageBlock_{j}"] = synthetic_cvt_stage_params(C, cfg["num_heads"][i],
+                                                               seed=seed + 100 * i + j + 1, dtype=dtype)
+        params[f"Stage_{i}"] = sp
+        cin = C
+    nc = cfg["num_classes"]
+    params["Dense_0"] = {"kernel": normal((cin, nc), 0.02), "bias": normal((nc,), 0.02)}
+    return params
+
+
+def cvt_loss_and_grads(params, images_hwcn, labels, cfg, label_smoothing=0.0):
+    from .vit_oracle import hwcn_to_nhwc, loss_fn
+    p = tree_map(lambda t: t.detach().clone().requires_grad_(True), params)
+    logits = cvt_forward(p, hwcn_to_nhwc(images_hwcn), cfg)
+    loss = loss_fn(logits, labels, cfg["num_classes"], label_smoothing)
+    loss.backward()
+    grads = tree_map(lambda t: t.grad if t.grad is not None else torch.zeros_like(t), p)
+    return loss.detach(), logits.detach(), grads
+
+
+# ----------------------------------------------------------------------------- rotary helpers
+def rotate_every_two(x):
+    """position_embed.py:8-14 literally: x1 = x[:, :, ::2], x2 = x[:, :, 1::2],
+    stack((-x2, x1), -1) -> '... d j -> ... (d j)'."""
+    x1 = x[..., ::2]
+    x2 = x[..., 1::2]
+    return torch.stack((-x2, x1), dim=-1).reshape(x.shape)
+
+
+def fixed_positional_embedding(n, dim, dtype=torch.float32):
+    """FixedPositionalEmbedding.__call__ (position_embed.py:26-34) literally, in float32 (the
+    RotaryPositionalEmbedding dtype, position_embed.py:38): intervals = arange(0, dim, 2);
+    inv_freq = 1 / (10e4**intervals / dim)  -- the power overflows to inf from 10e4**8 on, so those
+    frequencies are exactly 0; freqs = einsum('i,j->ij', arange(n), inv_freq);
+    emb = concatenate([freqs, freqs], -1)."""
+    intervals = torch.arange(0, dim, 2, dtype=dtype)
+    inv_freq = 1.0 / (torch.pow(torch.tensor(10e4, dtype=dtype), intervals) / dim)
+    t = torch.arange(n, dtype=dtype)
+    freqs = torch.einsum("i,j->ij", t, inv_freq)
+    return torch.cat([freqs, freqs], dim=-1)
+
+
+def apply_rotary_pos_emb(x, n_axis=0):
+    """apply_rotary_pos_emb (position_embed.py:17-20) under the intended reading (the reference
+    unpacks (sin, cos) from the single tensor FixedPositionalEmbedding returns, which cannot run):
+    sin, cos = sin / cos of the [n, dim/2] frequencies, each repeated 'b n -> b (n j)', j=2 and
+    broadcast over the axes between the sequence axis and the last; x cos + rotate_every_two(x) sin."""
+    n, dim = x.shape[n_axis], x.shape[-1]
+    freqs = fixed_positional_embedding(n, dim)[:, :dim // 2].to(x.dtype)
+    sin = torch.repeat_interleave(torch.sin(freqs), 2, dim=-1)
+    cos = torch.repeat_interleave(torch.cos(freqs), 2, dim=-1)
+    shape = [1] * x.dim()
+    shape[n_axis], shape[-1] = n, dim
+    return x * cos.view(shape) + rotate_every_two(x) * sin.view(shape)

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libsav_b200.so")
 SOURCES = ["host.cu", "gemm.cu", "attn.cu", "attn_fwd.cu", "attn_bwd.cu", "norm.cu", "stem.cu", "optim.cu",
-           "attn_mat.cu", "elementwise.cu", "conv.cu"]
+           "attn_mat.cu", "elementwise.cu", "conv.cu", "conv2d.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
@@ -36,13 +36,24 @@ def build(force=False, verbose=False):
     dev = os.environ.get("SAV_GEMM_DEV", "0") == "1"
     marker = os.path.join(objdir, ".gemm_dev")
     was_dev = os.path.exists(marker)
+    # SAV_ATTN_DEV=1: role timeline of the attention backward (tests/tools/attn_timeline.py --bwd)
+    adev = os.environ.get("SAV_ATTN_DEV", "0") == "1"
+    amarker = os.path.join(objdir, ".attn_dev")
+    was_adev = os.path.exists(amarker)
     for s in SOURCES:
         src = os.path.join(CSRC, s)
         obj = os.path.join(objdir, s.replace(".cu", ".o"))
         objs.append(obj)
         extra = ["-DSAV_GEMM_DEV"] if (dev and s == "gemm.cu") else []
-        if force or _newer([src] + headers, obj) or (s == "gemm.cu" and dev != was_dev):
+        if adev and s == "attn_bwd.cu":
+            extra = ["-DSAV_ATTN_DEV"]
+        if force or _newer([src] + headers, obj) or (s == "gemm.cu" and dev != was_dev) or \
+                (s == "attn_bwd.cu" and adev != was_adev):
             jobs.append([NVCC] + FLAGS + extra + ["-c", src, "-o", obj])
+    if adev:
+        open(amarker, "w").close()
+    elif was_adev:
+        os.remove(amarker)
     if dev:
         open(marker, "w").close()
     elif was_dev:

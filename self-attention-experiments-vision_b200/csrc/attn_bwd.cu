@@ -11,7 +11,7 @@
 // S^T / dP^T chunks are double-buffered in TMEM, so the tensor pipe works on chunk n+1 / n+2 while
 // the math warps are on chunk n, and nothing ever waits for an epilogue.
 //
-// 512 threads, one CTA per SM, every role free-running behind mbarriers:
+// 640 threads, one CTA per SM, every role free-running behind mbarriers:
 //   warp 0       TMA producer (Q_i, dO_i per item; K_j, V_j ring)
 //   warp 1       MMA issuer A: S^T and dP^T chunks (runs up to two chunks ahead of the math)
 //   warp 2       MMA issuer B: dV, dK per chunk, dQ per query tile -- every gradient MMA is issued
@@ -23,6 +23,11 @@
 //                128B-swizzled shared memory
 //   warps 12-15  epilogue: dV_j / dK_j after each key tile, dQ_0 / dQ_1 after each item, out of
 //                TMEM -> bf16 -> own staging buffers -> TMA store.  The math warps never drain.
+//   warps 16-19  delta = rowsum(dO o (O + O_lo)) of the NEXT item (no separate kernel, no second
+//                pass over dO): straight from global, one item ahead, handed to warp 3 through the
+//                global workspace.  Registers are redistributed with setmaxnreg: 56 for the
+//                producer / issuer / statistics warpgroup, 80 for the epilogue and delta warpgroups,
+//                128 for the two math warpgroups (640 x 96 at launch).
 // TMEM (512 columns): S^T[2] 64+64 | dP^T[2] 64+64 | dV 64 | dK 64 | dQ_0 64 | dQ_1 64.
 // The softmax scale of dK / dQ is applied once at read-out.
 #include "common.cuh"
@@ -34,12 +39,16 @@ constexpr int BT = 128;                 // tile edge (keys per tile, queries per
 constexpr int BD = 64;                  // head dim
 constexpr int BC = 64;                  // query columns per chunk
 constexpr int BT_BYTES = BT * BD * 2;   // 16 KB: one [128 x 64] bf16 tile, 128-byte rows
-constexpr int kBwdThreads = 512;
+constexpr int kBwdThreads = 640;
 constexpr float B_LOG2E = 1.4426950408889634f;
 
 struct AttnBwd2Params {
   const float* lse;
-  const float* delta;
+  float* delta;            // workspace [B, H, Nq]: rows -> columns hand-over inside warp 3
+  const bf16* o;           // forward output, its bf16 rounding remainder (may be NULL) and dO:
+  const bf16* o_lo;        //   [B, Nq, H, 64] views, element strides o_bs / o_rs
+  const bf16* d_o;
+  long long o_bs, o_rs;
   int B, H, Nq, Nk;
   int n_items;   // B * H
   int nkt;       // key tiles (1 or 2)
@@ -47,6 +56,21 @@ struct AttnBwd2Params {
   float scale, scale_log2;
   long long* dbg;
 };
+
+// Development timeline (compiled in only with -DSAV_ATTN_DEV: SAV_ATTN_DEV=1 python build.py):
+// (event, clock64) pairs of CTA 0, 256 slots per role, read by tests/tools/attn_timeline.py --bwd.
+#ifdef SAV_ATTN_DEV
+#define BWD_STAMP(role, ev)                                                       \
+  do {                                                                            \
+    if (p.dbg && blockIdx.x == 0 && dbg_on && dbg_n < 255) {                      \
+      p.dbg[(role) * 512 + 2 * dbg_n] = (ev);                                     \
+      p.dbg[(role) * 512 + 2 * dbg_n + 1] = clock64();                            \
+      ++dbg_n;                                                                    \
+    }                                                                             \
+  } while (0)
+#else
+#define BWD_STAMP(role, ev) do { } while (0)
+#endif
 
 // byte offset of 16-byte group `g16` (0..7) of row `r` inside a [rows x 128 B] SW128 tile
 __device__ __forceinline__ uint32_t bsw128(int r, int g16) {
@@ -63,7 +87,7 @@ constexpr int kOffdSt = 10 * BT_BYTES;          // dS^T [cc] 2 x [128 keys x 64 
 constexpr int kOffStage = 12 * BT_BYTES;        // epilogue staging, 2 x 16 KB
 constexpr int kOffStats = 14 * BT_BYTES;        // float[256] -lse*log2e | float[256] -delta
 constexpr int kOffBars = kOffStats + 2 * 256 * 4;
-constexpr int kNumBars = 28;
+constexpr int kNumBars = 28;   // 25 used
 constexpr int kBwd2Smem = kOffBars + kNumBars * 8 + 16;
 static_assert(kBwd2Smem <= 232448, "attention backward exceeds the 227 KB shared-memory limit");
 
@@ -120,11 +144,17 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   uint64_t* dq_free = bars + 18;      //          4 epilogue warps
   uint64_t* st_full = bars + 19;      //          32 lanes of warp 3: statistics of the item
   uint64_t* st_empty = bars + 20;     //          8 math warps
+  uint64_t* dl_ready = bars + 21;     // [item&1] 128 delta threads: delta of the item is in global
+  uint64_t* dl_free = bars + 23;      // [item&1] warp 3 has taken it (bounds the delta warps' run-ahead)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kNumBars);
 
   // warp index through a shuffle: the role branches are then provably warp-uniform for ptxas
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int my_items = (p.n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+#ifdef SAV_ATTN_DEV
+  int dbg_n = 0;
+  const bool dbg_on = (lane == 0);
+#endif
 
   if (tid == 0) {
     if (smem_u32(smem) & 1023u) __trap();   // SW128 tiles need a 1024-byte aligned base
@@ -140,6 +170,8 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     mbar_init(dkv_full, 1); mbar_init(dkv_free, 4);
     mbar_init(dq_full, 1); mbar_init(dq_free, 4);
     mbar_init(st_full, 32); mbar_init(st_empty, 8);
+    mbar_init(&dl_ready[0], 128); mbar_init(&dl_ready[1], 128);
+    mbar_init(&dl_free[0], 1); mbar_init(&dl_free[1], 1);
     fence_barrier_init();
   }
   if (warp == 3) tmem_alloc<512>(tmem_slot);
@@ -152,6 +184,14 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   auto lo = [](uint64_t d) { return (uint32_t)d; };
   auto hi = [](uint64_t d) { return (uint32_t)(d >> 32); };
 
+  // Register budget: the CTA's pool is what it was launched with, 640 threads x 96 = 61 440.
+  // Warpgroup limits after redistribution: 56 (producer / issuers / statistics) + 2 x 128 (math) +
+  // 80 (epilogue) + 80 (delta) = 472 x 128 threads = 60 416 <= pool, so both setmaxnreg.inc can be
+  // satisfied (a sum above the pool deadlocks the second one).  The code of a role has to be
+  // DOMINATED by its warpgroup's setmaxnreg for ptxas to allocate against the new limit (a
+  // setmaxnreg.dec that merely precedes the role dispatch caps the whole kernel), hence the nesting.
+  if (warp < 4) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
@@ -160,14 +200,18 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         const int item = blockIdx.x + itl * gridDim.x;
         const int h = item % p.H, b = item / p.H;
         auto load_qdo = [&](int i) {
+          BWD_STAMP(0, 1);
           mbar_wait_sleep(&qdo_empty[i], (itl & 1) ^ 1);
+          BWD_STAMP(0, 2);
           mbar_expect_tx(&qdo_full[i], 2 * BT_BYTES);
           tma_load_3d(sQ + i * BT_BYTES, &tq, &qdo_full[i], h * BD, i * BT, b);
           tma_load_3d(sdO + i * BT_BYTES, &tdo, &qdo_full[i], h * BD, i * BT, b);
         };
         auto load_kv = [&](int j) {
           const int st = gk & 1;
+          BWD_STAMP(0, 3);
           mbar_wait_sleep(&kv_empty[st], ((gk >> 1) & 1) ^ 1);
+          BWD_STAMP(0, 4);
           mbar_expect_tx(&kv_full[st], 2 * BT_BYTES);
           tma_load_3d(sKV + st * 2 * BT_BYTES, &tk, &kv_full[st], h * BD, j * BT, b);
           tma_load_3d(sKV + st * 2 * BT_BYTES + BT_BYTES, &tv, &kv_full[st], h * BD, j * BT, b);
@@ -191,16 +235,20 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     for (int itl = 0; itl < my_items; ++itl) {
       for (int j = 0; j < p.nkt; ++j, ++gk) {
         const int st = gk & 1;
+        BWD_STAMP(1, 10);
         mbar_wait_sleep(&kv_full[st], (gk >> 1) & 1);
+        BWD_STAMP(1, 11);
         const uint32_t a_k = lo(dK0) + st * 2 * TILE16, a_v = lo(dV0) + st * 2 * TILE16;
         for (int i = 0; i < p.nqt; ++i) {
-          if (j == 0) mbar_wait_sleep(&qdo_full[i], itl & 1);
+          if (j == 0) { BWD_STAMP(1, 14); mbar_wait_sleep(&qdo_full[i], itl & 1); BWD_STAMP(1, 15); }
           const int nq_cur = round16(min(BT, p.Nq - i * BT));
           const int nch = (nq_cur + BC - 1) / BC;
           for (int cc = 0; cc < nch; ++cc, ++n) {
             const int ncols = min(BC, nq_cur - cc * BC);
             const uint32_t buf = n & 1, use = n >> 1;
+            BWD_STAMP(1, 12);
             if (use > 0) mbar_wait_sleep(&s_free[buf], (use - 1) & 1);
+            BWD_STAMP(1, 13);
             tc_fence_after();
             const uint32_t id_s = make_idesc_bf16(BT, ncols, false, false);
             // rows [cc*64, cc*64 + ncols) of the K-major Q_i / dO_i tiles: 64 rows = 8 KB
@@ -243,12 +291,15 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           const int nch = (nq_cur + BC - 1) / BC;
           for (int cc = 0; cc < nch; ++cc) {
             const int ksteps = min(BC, nq_cur - cc * BC) >> 4;
+            BWD_STAMP(2, 20);
             mbar_wait_sleep(&pds_full[cc], use_cc[cc] & 1);
+            BWD_STAMP(2, 21);
             ++use_cc[cc];
             const bool first_of_keytile = (i == 0 && cc == 0);
             const bool last_of_tile = (cc == nch - 1);
             if (first_of_keytile && gk > 0) mbar_wait_sleep(dkv_free, (gk - 1) & 1);
             if (last_of_tile && j == 0 && i == 0 && itl > 0) mbar_wait_sleep(dq_free, (itl - 1) & 1);
+            BWD_STAMP(2, 22);
             tc_fence_after();
             // dV[keys,d] += P^T[keys,q] dO_i[q,d];  dK[keys,d] += dS^T[keys,q] Q_i[q,d]  (K = q)
             const uint32_t a_p = lo(dPt0) + cc * TILE16, a_ds = lo(ddSt0) + cc * TILE16;
@@ -289,27 +340,38 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     }
   } else if (warp == 3) {
     // ------------------------------------------------------------------ per-item statistics
-    // 8 query columns per lane: the global loads of item itl are issued before waiting for the
-    // math warps to release the buffer, so only a shared-memory store sits on the critical path
+    // 8 query columns per lane.  delta comes from the delta warps through the global workspace;
+    // the loads of item itl are issued before waiting for the math warps to release the buffer,
+    // so only a shared-memory store sits on the critical path.
     for (int itl = 0; itl < my_items; ++itl) {
       const int item = blockIdx.x + itl * gridDim.x;
       const int64_t base = (int64_t)item * p.Nq;   // lse / delta are [B, H, Nq]
       float nl[8], nd[8];
+      BWD_STAMP(6, 50);
+      mbar_wait_sleep(&dl_ready[itl & 1], (itl >> 1) & 1);
+      BWD_STAMP(6, 51);
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         const int c = lane * 8 + e;
         nl[e] = (c < p.Nq) ? -p.lse[base + c] * B_LOG2E : -INFINITY;
-        nd[e] = (c < p.Nq) ? -p.delta[base + c] : 0.f;
+        nd[e] = (c < p.Nq) ? -__ldcg(p.delta + base + c) : 0.f;
       }
+      // (the values are consumed by the stores below, i.e. the loads have completed by then)
+      BWD_STAMP(6, 52);
       if (itl > 0) mbar_wait_sleep(st_empty, (itl - 1) & 1);
+      BWD_STAMP(6, 53);
 #pragma unroll
       for (int e = 0; e < 8; e += 4) {
         *reinterpret_cast<float4*>(s_nl2 + lane * 8 + e) = make_float4(nl[e], nl[e + 1], nl[e + 2], nl[e + 3]);
         *reinterpret_cast<float4*>(s_nd + lane * 8 + e) = make_float4(nd[e], nd[e + 1], nd[e + 2], nd[e + 3]);
       }
       mbar_arrive(st_full);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&dl_free[itl & 1]);
     }
+  }
   } else if (warp < 12) {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
     // ------------------------------------------------------------------ math warps
     const int sub = warp & 3;              // TMEM sub-partition
     const int hf = (warp - 4) >> 2;        // which 32 of the chunk's 64 query columns
@@ -317,8 +379,13 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     const uint32_t lane_off = (uint32_t)(sub * 32) << 16;
     const uint64_t sc2 = f2_pack(p.scale_log2, p.scale_log2);
     uint32_t n = 0, tiles = 0;
+#ifdef SAV_ATTN_DEV
+    const int mrole = (warp == 4) ? 3 : (warp == 8 ? 4 : 7);
+#endif
     for (int itl = 0; itl < my_items; ++itl) {
+      BWD_STAMP(mrole, 35);
       mbar_wait(st_full, itl & 1);
+      BWD_STAMP(mrole, 36);
       for (int j = 0; j < p.nkt; ++j) {
         // key rows at or beyond the (16-rounded) key count of this tile are never read: as K of
         // the dQ MMAs they are cut by nk_steps, as M rows of dV / dK they are clipped by the store
@@ -331,7 +398,9 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
             const uint32_t buf = n & 1, use = n >> 1;
             const bool live = rows_live && hf * 32 < ncols;
             uint32_t pk_p[16], pk_ds[16];
+            BWD_STAMP(mrole, 30);
             mbar_wait(&s_full[buf], use & 1);
+            BWD_STAMP(mrole, 31);
             tc_fence_after();
             if (live) {
               uint32_t rs[32], rp[32];
@@ -366,7 +435,9 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
             }
             // the first chunk of a query tile reuses buffers the previous tile's dV / dK / dQ MMAs
             // read: wait for issuer B's commit behind that tile's dQ
+            BWD_STAMP(mrole, 32);
             if (cc == 0 && tiles > 0) mbar_wait(pds_free, (tiles - 1) & 1);
+            BWD_STAMP(mrole, 33);
             if (live) {
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
@@ -380,6 +451,7 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(&pds_full[cc]);
+            BWD_STAMP(mrole, 34);
           }
         }
       }
@@ -387,7 +459,8 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       __syncwarp();
       if (lane == 0) mbar_arrive(st_empty);
     }
-  } else {
+  } else if (warp < 16) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
     // ------------------------------------------------------------------ epilogue warps (12..15)
     const int sub = warp & 3;
     const int r = sub * 32 + lane;         // key row (dV / dK) or query row (dQ) of the tile
@@ -414,31 +487,91 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       const int item = blockIdx.x + itl * gridDim.x;
       const int h = item % p.H, b = item / p.H;
       for (int j = 0; j < p.nkt; ++j, ++gk) {
-        uint32_t pv[32], pkk[32];
+        uint32_t pk[32];
+        BWD_STAMP(5, 42);
         mbar_wait(dkv_full, gk & 1);
+        BWD_STAMP(5, 43);
         tc_fence_after();
-        tmem_row64_to_bf16(tdV + lane_off, 1.f, pv);
-        tmem_row64_to_bf16(tdK + lane_off, p.scale, pkk);
+        tmem_row64_to_bf16(tdV + lane_off, 1.f, pk);
+        store_tile(&tdv, pk, h * BD, j * BT, b);     // key rows >= Nk are clipped by the map
+        tmem_row64_to_bf16(tdK + lane_off, p.scale, pk);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(dkv_free);        // next key tile may overwrite dV / dK
-        store_tile(&tdv, pv, h * BD, j * BT, b);     // key rows >= Nk are clipped by the map
-        store_tile(&tdk, pkk, h * BD, j * BT, b);
+        store_tile(&tdk, pk, h * BD, j * BT, b);
+        BWD_STAMP(5, 44);
       }
+      BWD_STAMP(5, 45);
       mbar_wait(dq_full, itl & 1);
+      BWD_STAMP(5, 46);
       tc_fence_after();
       {
-        uint32_t q0[32], q1[32];
-        tmem_row64_to_bf16(tdQ + lane_off, p.scale, q0);
-        if (p.nqt > 1) tmem_row64_to_bf16(tdQ + BD + lane_off, p.scale, q1);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(dq_free);         // next item may overwrite dQ
-        store_tile(&tdq, q0, h * BD, 0, b);          // rows >= Nq clipped
-        if (p.nqt > 1) store_tile(&tdq, q1, h * BD, BT, b);
+        uint32_t pk[32];
+        tmem_row64_to_bf16(tdQ + lane_off, p.scale, pk);
+        if (p.nqt == 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(dq_free);       // next item may overwrite dQ
+        }
+        store_tile(&tdq, pk, h * BD, 0, b);          // rows >= Nq clipped
+        if (p.nqt > 1) {
+          tmem_row64_to_bf16(tdQ + BD + lane_off, p.scale, pk);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(dq_free);
+          store_tile(&tdq, pk, h * BD, BT, b);
+        }
       }
     }
     if (leader) tma_store_wait<0>();
+  } else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+    // ------------------------------------------------------------------ delta warps (16..19)
+    // delta[q] = sum_d dO[q,d] (O + O_lo)[q,d] of the item AFTER the one the math warps are on:
+    // 8 lanes per 128-byte row, 16 rows per pass of the 128 threads, the loads of 6 passes in
+    // flight.  Nothing waits for these warps except the statistics hand-over of the next item.
+    const int dt = tid - 512;
+    const int part = dt & 7, row0 = dt >> 3;
+    for (int itl = 0; itl < my_items; ++itl) {
+      const int item = blockIdx.x + itl * gridDim.x;
+      const int h = item % p.H, b = item / p.H;
+      const int64_t base = (int64_t)b * p.o_bs + h * BD + part * 8;
+      float* dout = p.delta + (int64_t)item * p.Nq;
+      if (itl >= 2) mbar_wait_sleep(&dl_free[itl & 1], ((itl - 2) >> 1) & 1);
+      constexpr int PB = 4;
+      for (int q0 = 0; q0 < p.Nq; q0 += 16 * PB) {
+        uint4 a[PB], l[PB], g[PB];
+#pragma unroll
+        for (int u = 0; u < PB; ++u) {
+          const int q = q0 + u * 16 + row0;
+          if (q < p.Nq) {
+            const int64_t off = base + (int64_t)q * p.o_rs;
+            a[u] = __ldcg(reinterpret_cast<const uint4*>(p.o + off));
+            g[u] = __ldcg(reinterpret_cast<const uint4*>(p.d_o + off));
+            l[u] = p.o_lo ? __ldcg(reinterpret_cast<const uint4*>(p.o_lo + off)) : make_uint4(0, 0, 0, 0);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < PB; ++u) {
+          const int q = q0 + u * 16 + row0;
+          float sum = 0.f;
+          if (q < p.Nq) {
+            const uint32_t aw[4] = {a[u].x, a[u].y, a[u].z, a[u].w}, gw[4] = {g[u].x, g[u].y, g[u].z, g[u].w};
+            const uint32_t lw[4] = {l[u].x, l[u].y, l[u].z, l[u].w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const float2 af = unpack_bf16(aw[k]), gf = unpack_bf16(gw[k]), lf = unpack_bf16(lw[k]);
+              sum += (af.x + lf.x) * gf.x + (af.y + lf.y) * gf.y;
+            }
+          }
+          sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+          sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+          sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+          if (q < p.Nq && part == 0) dout[q] = sum;
+        }
+      }
+      mbar_arrive(&dl_ready[itl & 1]);   // release: this thread's global stores are ordered before
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -447,43 +580,6 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     tmem_dealloc<512>(tmem);
   }
 }
-
-// delta[b,h,q] = sum_d dO[b,q,h,d] * (O + O_lo)[b,q,h,d]: 8 lanes per (b,q,h) row, 16-byte loads
-__global__ void attn_delta2_kernel(const bf16* __restrict__ o, const bf16* __restrict__ o_lo,
-                                   const bf16* __restrict__ d_o, float* __restrict__ delta, int B,
-                                   int H, int Nq, int64_t o_bs, int64_t o_rs) {
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t rowh = t >> 3;  // (b, q, h) index, h fastest
-  const int part = (int)(t & 7);
-  const bool ok = rowh < (int64_t)B * Nq * H;
-  float s = 0.f;
-  if (ok) {
-    const int hh = (int)(rowh % H);
-    const int q = (int)((rowh / H) % Nq);
-    const int b = (int)(rowh / ((int64_t)H * Nq));
-    const int64_t off = (int64_t)b * o_bs + (int64_t)q * o_rs + hh * BD + part * 8;
-    const uint4 a = *reinterpret_cast<const uint4*>(o + off);
-    const uint4 g = *reinterpret_cast<const uint4*>(d_o + off);
-    uint4 l = make_uint4(0, 0, 0, 0);
-    if (o_lo) l = *reinterpret_cast<const uint4*>(o_lo + off);
-    const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w}, lw[4] = {l.x, l.y, l.z, l.w};
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float2 af = unpack_bf16(aw[k]), gf = unpack_bf16(gw[k]), lf = unpack_bf16(lw[k]);
-      s += (af.x + lf.x) * gf.x + (af.y + lf.y) * gf.y;
-    }
-  }
-  s += __shfl_xor_sync(0xffffffffu, s, 1);
-  s += __shfl_xor_sync(0xffffffffu, s, 2);
-  s += __shfl_xor_sync(0xffffffffu, s, 4);
-  if (ok && part == 0) {
-    const int hh = (int)(rowh % H);
-    const int q = (int)((rowh / H) % Nq);
-    const int b = (int)(rowh / ((int64_t)H * Nq));
-    delta[((int64_t)b * H + hh) * Nq + q] = s;
-  }
-}
-
 
 static int make_bnhd_map128(CUtensorMap* m, const void* base, int64_t H, int64_t N, int64_t B,
                             int64_t bs, int64_t rs) {
@@ -510,14 +606,11 @@ int launch_attn_bwd2(const sav_attn_bwd_args* a, cudaStream_t st) {
     if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "attn bwd2 smem attr: %s", cudaGetErrorString(e));
     attr = true;
   }
-  const int64_t rows8 = a->B * a->Nq * a->H * 8;
-  attn_delta2_kernel<<<(unsigned)((rows8 + 255) / 256), 256, 0, st>>>(
-      reinterpret_cast<const bf16*>(a->o), reinterpret_cast<const bf16*>(a->o_lo),
-      reinterpret_cast<const bf16*>(a->d_o), a->delta, (int)a->B, (int)a->H, (int)a->Nq,
-      a->o_batch_stride, a->o_row_stride);
-  count_launch();
   AttnBwd2Params p;
   p.lse = a->lse; p.delta = a->delta;
+  p.o = reinterpret_cast<const bf16*>(a->o); p.o_lo = reinterpret_cast<const bf16*>(a->o_lo);
+  p.d_o = reinterpret_cast<const bf16*>(a->d_o);
+  p.o_bs = a->o_batch_stride; p.o_rs = a->o_row_stride;
   p.B = (int)a->B; p.H = (int)a->H; p.Nq = (int)a->Nq; p.Nk = (int)a->Nk;
   p.n_items = p.B * p.H;
   p.nkt = (p.Nk + BT - 1) / BT;

@@ -73,6 +73,74 @@ __global__ void copy2d_f32_kernel(const float* __restrict__ src, int64_t lds, fl
   }
 }
 
+// ---- rotary position embedding (position_embed.py:8-45).  The reference's frequency table is
+// inv_freq[i] = 1 / (10e4^(2i) / dim) evaluated in float32 (position_embed.py:29: 10e4 = 1e5, the
+// power overflows to inf for 2i >= 8, so those frequencies are exactly 0);  theta[t,i] = t inv_freq[i];
+//   y[2i]   = x[2i] cos(theta) - x[2i+1] sin(theta)
+//   y[2i+1] = x[2i+1] cos(theta) + x[2i] sin(theta)          (x cos + rotate_every_two(x) sin)
+// `inverse` rotates by -theta: the reverse mode (the rotation is orthogonal).
+__device__ __forceinline__ float rotary_inv_freq(int i, int dim) {
+  const float pw = powf(1e5f, (float)(2 * i));
+  return 1.f / (pw / (float)dim);
+}
+
+template <typename T>
+__global__ void rotary_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t outer, int64_t n,
+                              int64_t inner, int d, float sign) {
+  const int half = d / 2;
+  const int64_t total = outer * n * inner * half;
+  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int i = (int)(idx % half);
+    const int64_t row = idx / half;              // (outer, t, inner)
+    const int64_t t = (row / inner) % n;
+    float sn, cs;
+    sincosf((float)t * rotary_inv_freq(i, d), &sn, &cs);
+    sn *= sign;
+    float a, b;
+    if (sizeof(T) == 2) {
+      const float2 v = unpack_bf16(reinterpret_cast<const uint32_t*>(x)[idx]);
+      a = v.x; b = v.y;
+      reinterpret_cast<uint32_t*>(y)[idx] = pack_bf16(a * cs - b * sn, b * cs + a * sn);
+    } else {
+      const float2 v = reinterpret_cast<const float2*>(x)[idx];
+      a = v.x; b = v.y;
+      reinterpret_cast<float2*>(y)[idx] = make_float2(a * cs - b * sn, b * cs + a * sn);
+    }
+  }
+}
+
+// FixedPositionalEmbedding (position_embed.py:23-34): emb[t, :] = concat(freqs[t], freqs[t]),
+// freqs[t, i] = t * inv_freq[i]; fp32 [n, dim].
+__global__ void rotary_table_kernel(float* __restrict__ emb, int64_t n, int dim) {
+  const int half = dim / 2;
+  const int64_t total = n * half;
+  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int i = (int)(idx % half);
+    const int64_t t = idx / half;
+    const float f = (float)t * rotary_inv_freq(i, dim);
+    emb[t * dim + i] = f;
+    emb[t * dim + half + i] = f;
+  }
+}
+
+// dst fp32 [rows, cols] (row pitch ldd) (+)= src bf16 [rows, cols] (row pitch lds): the bf16 gradient of
+// a row selection handed back to the fp32 stream (x[:, 0] of cvt.py:165)
+__global__ void cast2d_bf16_f32_kernel(const bf16* __restrict__ src, int64_t lds, float* __restrict__ dst,
+                                       int64_t ldd, int64_t rows, int64_t cols2, int accumulate) {
+  const int64_t total = rows * cols2;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / cols2;
+    const int64_t c = (i - r * cols2) * 2;
+    float2 v = unpack_bf16(*reinterpret_cast<const uint32_t*>(src + r * lds + c));
+    float2* d = reinterpret_cast<float2*>(dst + r * ldd + c);
+    if (accumulate) { const float2 o = *d; v.x += o.x; v.y += o.y; }
+    *d = v;
+  }
+}
+
 static int ew_grid(int64_t work, int threads) {
   int64_t b = (work + threads - 1) / threads;
   const int64_t cap = 148 * 8;
@@ -120,4 +188,45 @@ extern "C" int sav_copy2d_f32(const float* src, int64_t lds, float* dst, int64_t
                                                                 accumulate);
   count_launch();
   return check_launch("sav_copy2d_f32");
+}
+
+extern "C" int sav_rotary(const void* x, void* y, int64_t outer, int64_t n, int64_t inner, int64_t d,
+                          int32_t is_fp32, int32_t inverse, void* stream) {
+  if (outer <= 0 || n <= 0 || inner <= 0 || d <= 0) return SAV_OK;
+  if (d % 2) return set_error(SAV_ERR_SHAPE, "sav_rotary: the rotated dimension must be even");
+  if ((reinterpret_cast<uintptr_t>(x) & 7) || (reinterpret_cast<uintptr_t>(y) & 7))
+    return set_error(SAV_ERR_ALIGN, "sav_rotary: 8 B alignment required");
+  const int64_t work = outer * n * inner * (d / 2);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const float sign = inverse ? -1.f : 1.f;
+  if (is_fp32)
+    rotary_kernel<float><<<ew_grid(work, 256), 256, 0, st>>>(
+        reinterpret_cast<const float*>(x), reinterpret_cast<float*>(y), outer, n, inner, (int)d, sign);
+  else
+    rotary_kernel<bf16><<<ew_grid(work, 256), 256, 0, st>>>(
+        reinterpret_cast<const bf16*>(x), reinterpret_cast<bf16*>(y), outer, n, inner, (int)d, sign);
+  count_launch();
+  return check_launch("sav_rotary");
+}
+
+extern "C" int sav_rotary_table(float* emb, int64_t n, int64_t dim, void* stream) {
+  if (n <= 0 || dim <= 0) return SAV_OK;
+  if (dim % 2) return set_error(SAV_ERR_SHAPE, "sav_rotary_table: dim must be even");
+  rotary_table_kernel<<<ew_grid(n * (dim / 2), 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      emb, n, (int)dim);
+  count_launch();
+  return check_launch("sav_rotary_table");
+}
+
+extern "C" int sav_cast2d_bf16_f32(const void* src, int64_t lds, float* dst, int64_t ldd, int64_t rows,
+                                   int64_t cols, int32_t accumulate, void* stream) {
+  if (rows <= 0 || cols <= 0) return SAV_OK;
+  if (cols % 2 || lds % 2 || ldd % 2 || (reinterpret_cast<uintptr_t>(src) & 3) ||
+      (reinterpret_cast<uintptr_t>(dst) & 7))
+    return set_error(SAV_ERR_ALIGN, "sav_cast2d_bf16_f32: cols/ld %% 2 and 4/8 B alignment required");
+  cast2d_bf16_f32_kernel<<<ew_grid(rows * (cols / 2), 256), 256, 0,
+                           reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const bf16*>(src), lds, dst, ldd, rows, cols / 2, accumulate);
+  count_launch();
+  return check_launch("sav_cast2d_bf16_f32");
 }

@@ -44,10 +44,10 @@ __device__ __forceinline__ void store8(float* p, const float (&f)[8]) {
   *reinterpret_cast<float4*>(p + 4) = make_float4(f[4], f[5], f[6], f[7]);
 }
 
-template <int CHUNKS>
+template <int CHUNKS, typename TY>
 __global__ void __launch_bounds__(256)
 ln_fwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ scale,
-              const float* __restrict__ bias, bf16* __restrict__ y, int64_t ldy,
+              const float* __restrict__ bias, TY* __restrict__ y, int64_t ldy,
               float* __restrict__ mean_out, float* __restrict__ rstd_out, int64_t rows, int C,
               float eps) {
   const int lane = threadIdx.x & 31;
@@ -94,12 +94,86 @@ ln_fwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict_
   }
 }
 
+// Forward for C <= 512 with balanced 16-byte pieces (4 columns per lane per piece: C = 384 is three
+// pieces per lane, where 8-column chunks leave half the lanes with one chunk and half with two).
+// Two rows per warp iteration keep twice the bytes in flight.
+template <int PIECES>
+__global__ void __launch_bounds__(256, 4)
+ln_fwd_pieces_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ scale,
+                     const float* __restrict__ bias, bf16* __restrict__ y, int64_t ldy,
+                     float* __restrict__ mean_out, float* __restrict__ rstd_out, int64_t rows, int C,
+                     float eps) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp_global = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int64_t warps_total = (int64_t)gridDim.x * 8;
+  const int npiece = C / 4;
+  float4 g[PIECES], b[PIECES];
+#pragma unroll
+  for (int i = 0; i < PIECES; ++i) {
+    const int pc = lane + i * 32;
+    g[i] = b[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (pc < npiece) {
+      g[i] = *reinterpret_cast<const float4*>(scale + pc * 4);
+      b[i] = *reinterpret_cast<const float4*>(bias + pc * 4);
+    }
+  }
+  const float invC = 1.f / (float)C;
+  for (int64_t row = warp_global * 2; row < rows; row += warps_total * 2) {
+    const bool two = row + 1 < rows;
+    float4 v0[PIECES], v1[PIECES];
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) {
+      const int pc = lane + i * 32;
+      v0[i] = v1[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (pc < npiece) {
+        v0[i] = *reinterpret_cast<const float4*>(x + row * ldx + pc * 4);
+        if (two) v1[i] = *reinterpret_cast<const float4*>(x + (row + 1) * ldx + pc * 4);
+      }
+    }
+    float s0 = 0.f, q0 = 0.f, s1 = 0.f, q1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) {
+      s0 += (v0[i].x + v0[i].y) + (v0[i].z + v0[i].w);
+      q0 += (v0[i].x * v0[i].x + v0[i].y * v0[i].y) + (v0[i].z * v0[i].z + v0[i].w * v0[i].w);
+      s1 += (v1[i].x + v1[i].y) + (v1[i].z + v1[i].w);
+      q1 += (v1[i].x * v1[i].x + v1[i].y * v1[i].y) + (v1[i].z * v1[i].z + v1[i].w * v1[i].w);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+      q0 += __shfl_xor_sync(0xffffffffu, q0, o);
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      q1 += __shfl_xor_sync(0xffffffffu, q1, o);
+    }
+    const float m0 = s0 * invC, m1 = s1 * invC;
+    const float r0 = rsqrtf(fmaxf(q0 * invC - m0 * m0, 0.f) + eps);
+    const float r1 = rsqrtf(fmaxf(q1 * invC - m1 * m1, 0.f) + eps);
+    if (lane == 0) {
+      mean_out[row] = m0; rstd_out[row] = r0;
+      if (two) { mean_out[row + 1] = m1; rstd_out[row + 1] = r1; }
+    }
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) {
+      const int pc = lane + i * 32;
+      if (pc < npiece) {
+        *reinterpret_cast<uint2*>(y + row * ldy + pc * 4) = make_uint2(
+            pack_bf16((v0[i].x - m0) * r0 * g[i].x + b[i].x, (v0[i].y - m0) * r0 * g[i].y + b[i].y),
+            pack_bf16((v0[i].z - m0) * r0 * g[i].z + b[i].z, (v0[i].w - m0) * r0 * g[i].w + b[i].w));
+        if (two)
+          *reinterpret_cast<uint2*>(y + (row + 1) * ldy + pc * 4) = make_uint2(
+              pack_bf16((v1[i].x - m1) * r1 * g[i].x + b[i].x, (v1[i].y - m1) * r1 * g[i].y + b[i].y),
+              pack_bf16((v1[i].z - m1) * r1 * g[i].z + b[i].z, (v1[i].w - m1) * r1 * g[i].w + b[i].w));
+      }
+    }
+  }
+}
+
 // dx = rstd * (g - mean_c(g) - xhat * mean_c(g * xhat)),  g = dy * scale   (+ dx_add)
 // dscale / dbias: per-warp register partials -> shared-memory reduce -> one red.add per column
 // per block into the (zero-initialised or accumulating) gradient arena.
-template <int CHUNKS>
+template <int CHUNKS, typename TDY>
 __global__ void __launch_bounds__(256, CHUNKS <= 2 ? 2 : 1)
-ln_bwd_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __restrict__ x, int64_t ldx,
+ln_bwd_kernel(const TDY* __restrict__ dy, int64_t ldy, const float* __restrict__ x, int64_t ldx,
               const float* __restrict__ scale, const float* __restrict__ mean_in,
               const float* __restrict__ rstd_in, const float* __restrict__ dx_add,
               float* __restrict__ dx, bf16* __restrict__ dx16, float* __restrict__ dscale,
@@ -324,9 +398,26 @@ extern "C" int sav_layernorm_fwd(const float* x, int64_t ldx, const float* scale
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int grid = ln_grid(rows);
   const int chunks = (int)((C / 8 + 31) / 32);
+  if (C <= 512 && rows >= 1024) {
+    const int pieces = (int)((C / 4 + 31) / 32);
+    const int64_t want = (rows + 15) / 16;
+    const int grid_p = (int)(want < 148 * 8 ? want : 148 * 8);
+#define LN_FWDP(PC)                                                                              \
+  ln_fwd_pieces_kernel<PC><<<grid_p, 256, 0, st>>>(x, ldx, scale, bias, reinterpret_cast<bf16*>(y), \
+                                                    ldy, mean, rstd, rows, (int)C, eps)
+    switch (pieces) {
+      case 1: LN_FWDP(1); break;
+      case 2: LN_FWDP(2); break;
+      case 3: LN_FWDP(3); break;
+      default: LN_FWDP(4); break;
+    }
+#undef LN_FWDP
+    count_launch();
+    return check_launch("sav_layernorm_fwd");
+  }
 #define LN_FWD(CH)                                                                          \
-  ln_fwd_kernel<CH><<<grid, 256, 0, st>>>(x, ldx, scale, bias, reinterpret_cast<bf16*>(y), ldy, \
-                                           mean, rstd, rows, (int)C, eps)
+  ln_fwd_kernel<CH, bf16><<<grid, 256, 0, st>>>(x, ldx, scale, bias, reinterpret_cast<bf16*>(y), ldy, \
+                                                 mean, rstd, rows, (int)C, eps)
   switch (chunks) {
     case 1: LN_FWD(1); break;
     case 2: LN_FWD(2); break;
@@ -380,9 +471,9 @@ extern "C" int sav_layernorm_bwd_colsum(const void* dy, int64_t ldy, const float
     return check_launch("sav_layernorm_bwd");
   }
 #define LN_BWD(CH)                                                                            \
-  ln_bwd_kernel<CH><<<grid, 256, sm, st>>>(reinterpret_cast<const bf16*>(dy), ldy, x, ldx, scale, \
-                                            mean, rstd, dx_add, dx,                            \
-                                            reinterpret_cast<bf16*>(dx_bf16), dscale, dbias, dsum, rows, (int)C)
+  ln_bwd_kernel<CH, bf16><<<grid, 256, sm, st>>>(reinterpret_cast<const bf16*>(dy), ldy, x, ldx, scale, \
+                                                  mean, rstd, dx_add, dx,                            \
+                                                  reinterpret_cast<bf16*>(dx_bf16), dscale, dbias, dsum, rows, (int)C)
   switch (chunks) {
     case 1: LN_BWD(1); break;
     case 2: LN_BWD(2); break;
@@ -400,4 +491,56 @@ extern "C" int sav_layernorm_bwd(const void* dy, int64_t ldy, const float* x, in
                                  float* dbias, int64_t rows, int64_t C, void* stream) {
   return sav_layernorm_bwd_colsum(dy, ldy, x, ldx, scale, mean, rstd, dx_add, dx, dx_bf16, dscale,
                                   dbias, nullptr, rows, C, stream);
+}
+
+// ---- fp32-in / fp32-out flavour: the LayerNorm that closes the CvT conv token embedding
+// (cvt.py:34) normalises INTO the residual stream, so its output and the gradient coming back are
+// the fp32 stream, not a bf16 GEMM operand.  Three launches per CvT step: the generic kernels.
+extern "C" int sav_layernorm_fwd_f32(const float* x, int64_t ldx, const float* scale,
+                                     const float* bias, float* y, int64_t ldy, float* mean,
+                                     float* rstd, int64_t rows, int64_t C, float eps, void* stream) {
+  if (rows <= 0 || C <= 0 || C % 8 || C > 32 * LN_MAX_CHUNKS * 8 || ldx % 4 || ldy % 4)
+    return set_error(SAV_ERR_SHAPE, "sav_layernorm_fwd_f32: need C %% 8 == 0 and C <= 1024");
+  if (!aligned16(x) || !aligned16(y) || !aligned16(scale) || !aligned16(bias))
+    return set_error(SAV_ERR_ALIGN, "sav_layernorm_fwd_f32: pointers must be 16 B aligned");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = ln_grid(rows);
+  const int chunks = (int)((C / 8 + 31) / 32);
+#define LN_FWD32(CH) \
+  ln_fwd_kernel<CH, float><<<grid, 256, 0, st>>>(x, ldx, scale, bias, y, ldy, mean, rstd, rows, (int)C, eps)
+  switch (chunks) {
+    case 1: LN_FWD32(1); break;
+    case 2: LN_FWD32(2); break;
+    case 3: LN_FWD32(3); break;
+    default: LN_FWD32(4); break;
+  }
+#undef LN_FWD32
+  count_launch();
+  return check_launch("sav_layernorm_fwd_f32");
+}
+
+extern "C" int sav_layernorm_bwd_f32(const float* dy, int64_t ldy, const float* x, int64_t ldx,
+                                     const float* scale, const float* mean, const float* rstd,
+                                     const float* dx_add, float* dx, void* dx_bf16, float* dscale,
+                                     float* dbias, int64_t rows, int64_t C, void* stream) {
+  if (rows <= 0 || C <= 0 || C % 8 || C > 32 * LN_MAX_CHUNKS * 8 || ldx % 8 || ldy % 4)
+    return set_error(SAV_ERR_SHAPE, "sav_layernorm_bwd_f32: need C %% 8 == 0 and C <= 1024");
+  if (!aligned16(dy) || !aligned16(x) || !aligned16(dx) || !aligned16(dx_add) || !aligned16(dx_bf16))
+    return set_error(SAV_ERR_ALIGN, "sav_layernorm_bwd_f32: pointers must be 16 B aligned");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = ln_grid(rows);
+  const int chunks = (int)((C / 8 + 31) / 32);
+  const size_t sm = 2 * C * sizeof(float);
+#define LN_BWD32(CH)                                                                           \
+  ln_bwd_kernel<CH, float><<<grid, 256, sm, st>>>(dy, ldy, x, ldx, scale, mean, rstd, dx_add, dx, \
+                                                   reinterpret_cast<bf16*>(dx_bf16), dscale, dbias, nullptr, rows, (int)C)
+  switch (chunks) {
+    case 1: LN_BWD32(1); break;
+    case 2: LN_BWD32(2); break;
+    case 3: LN_BWD32(3); break;
+    default: LN_BWD32(4); break;
+  }
+#undef LN_BWD32
+  count_launch();
+  return check_launch("sav_layernorm_bwd_f32");
 }

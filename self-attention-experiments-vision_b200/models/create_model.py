@@ -6,6 +6,7 @@ Names and hyper-parameters are the reference's; `deit_ti_patch16` / `deit_s_patc
 accumulation / statistics.
 """
 from models.cait import CaiT
+from models.cvt import CvT
 from models.vit import ViT
 
 _VIT = {
@@ -34,6 +35,16 @@ _CAIT = {
 }
 
 
+_CVT = {
+    # name: (stage_sizes, num_heads, embed_dim)                  create_model.py:169-183
+    # the reference writes embed_dim (64, 192, 368) for cvt-13 / cvt-21; 368 % 6 heads != 0 trips its
+    # own assert (cvt_attention.py:65), cvt_test.py:14-15 and the CvT paper use 384
+    'cvt-13': ((1, 2, 10), (1, 3, 6), (64, 192, 384)),
+    'cvt-21': ((1, 4, 16), (1, 3, 6), (64, 192, 384)),
+    'cvt-w24': ((2, 2, 20), (3, 12, 16), (192, 768, 1024)),
+}
+
+
 def create_model(model_name: str, num_classes: int = 1000, dtype=None):
     if model_name in _VIT:
         layers, heads, dim, p = _VIT[model_name]
@@ -44,4 +55,7 @@ def create_model(model_name: str, num_classes: int = 1000, dtype=None):
         return CaiT(num_classes=num_classes, num_layers=layers, num_layers_token_only=2,
                     num_heads=heads, embed_dim=dim, patch_shape=(16, 16), stoch_depth_rate=sd,
                     layerscale_eps=eps, dtype=dtype)
+    if model_name in _CVT:
+        sizes, heads, dims = _CVT[model_name]
+        return CvT(num_classes=num_classes, stage_sizes=sizes, num_heads=heads, embed_dim=dims)
     raise NotImplementedError(f'{model_name} is not built yet (see DESIGN.md status table)')

@@ -7,10 +7,13 @@ elementwise pass producing the bf16 GEMM operand, the 1x1 conv is the tcgen05 GE
 attention core is the fused TMEM kernel with independent Nq / Nk (head dim 64 at every CvT stage).
 
 Parameter names follow Flax auto-naming: ConvProjectionBlock_{0,1,2}/{Conv_0/kernel [3,3,1,C],
-BatchNorm_0/{scale,bias}, Conv_1/kernel [1,1,C,h*d]}, DenseGeneral_0/kernel [h,d,C].  BatchNorm
-runs on batch statistics (is_training=True, the training step); running averages
-('batch_stats', momentum 0.9) are host-side state the reference's train.py never threads through
-apply_fn and are not kept here -- is_training=False raises.
+BatchNorm_0/{scale,bias}, Conv_1/kernel [1,1,C,h*d] (+ Conv_1/bias with use_bias)},
+DenseGeneral_0/kernel [h,d,C].  BatchNorm follows flax: batch statistics when is_training, running
+averages otherwise (use_running_average=not is_training, cvt_attention.py:33-36); the running
+averages live in the 'batch_stats' collection ({...BatchNorm_0: {mean, var}}), are created by init()
+and updated in place (momentum 0.9) when apply() is called with mutable=['batch_stats'].  The
+reference's train.py never passes mutable, where flax would raise; here the update is
+then skipped so that its apply_fn(params, images, is_training=True) call shape keeps working.
 """
 from typing import Optional, Tuple
 
@@ -33,11 +36,6 @@ class ConvProjectionBlock(nn.Module):
         in_ch = inputs.shape[-1]
         if self.kernel_size != 3:
             raise NotImplementedError("ConvProjectionBlock: only the 3x3 depthwise kernel is built")
-        if self.use_bias:
-            raise NotImplementedError("ConvProjectionBlock(use_bias=True)")
-        if not is_training:
-            raise NotImplementedError("BatchNorm with running averages (eval mode): batch_stats are "
-                                      "not kept, see module docstring")
         scope = self._scope_path()
         w_dw = self._param(scope + ("Conv_0", "kernel"), nn.initializers.lecun_normal(in_axes=3),
                            (3, 3, 1, in_ch))                               # cvt_attention.py:25-30
@@ -45,10 +43,32 @@ class ConvProjectionBlock(nn.Module):
         beta = self._param(scope + ("BatchNorm_0", "bias"), nn.initializers.zeros, (in_ch,))
         w_pw = self._param(scope + ("Conv_1", "kernel"), nn.initializers.lecun_normal(in_axes=3),
                            (1, 1, in_ch, self.out_ch))                     # cvt_attention.py:37-39
-        z = F.dwconv_bn(inputs, w_dw, gamma, beta, self.strides, self.bn_epsilon)
+        b_pw = self._param(scope + ("Conv_1", "bias"), nn.initializers.zeros, (self.out_ch,)) \
+            if self.use_bias else None                                   # cvt_attention.py:39
+        ra = self._batch_stats(scope + ("BatchNorm_0",), in_ch)
+        z = F.dwconv_bn(inputs, w_dw, gamma, beta, self.strides, self.bn_epsilon, running=ra,
+                        momentum=self.bn_momentum, training=is_training,
+                        update=self.is_mutable_collection("batch_stats"))
         gw = w_pw.grad.view(in_ch, self.out_ch) if w_pw.grad is not None else None
         return F.linear(z, F.Weight(w_pw.shadow.view(in_ch, self.out_ch), gw, [w_pw],
-                                    wm=w_pw.master.view(in_ch, self.out_ch)))
+                                    wm=w_pw.master.view(in_ch, self.out_ch)), b_pw)
+
+    def _batch_stats(self, path, C):
+        """flax nn.BatchNorm state: batch_stats/<...>/BatchNorm_0/{mean (zeros), var (ones)}."""
+        import torch
+        from sav import linen
+        run = linen._run()
+        out = []
+        for name, fill in (("mean", 0.0), ("var", 1.0)):
+            p = path + (name,)
+            if p not in run.batch_stats:
+                if run.mode == "apply":
+                    if not run.batch_stats:
+                        return None      # apply() without the collection: training-mode statistics only
+                    raise KeyError(f"batch_stats/{'/'.join(p)} not found in variables")
+                run.batch_stats[p] = torch.full((C,), fill, dtype=torch.float32, device=run.device)
+            out.append(run.batch_stats[p])
+        return tuple(out)
 
 
 class CvTAttentionBlock(nn.Module):

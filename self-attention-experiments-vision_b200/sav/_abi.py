@@ -71,6 +71,17 @@ class BGemmArgs(C.Structure):
     ]
 
 
+class Conv2dGeom(C.Structure):
+    _fields_ = [
+        ("B", C.c_int64), ("H", C.c_int64), ("W", C.c_int64), ("C", C.c_int64),
+        ("Ho", C.c_int64), ("Wo", C.c_int64),
+        ("kh", C.c_int32), ("kw", C.c_int32), ("sh", C.c_int32), ("sw", C.c_int32),
+        ("pad_top", C.c_int32), ("pad_left", C.c_int32),
+        ("xs_b", C.c_int64), ("xs_h", C.c_int64), ("xs_w", C.c_int64), ("xs_c", C.c_int64),
+        ("ld", C.c_int64),
+    ]
+
+
 class ThSoftmaxArgs(C.Structure):
     _fields_ = [
         ("S", C.c_void_p), ("P", C.c_void_p), ("dP", C.c_void_p), ("dS", C.c_void_p),
@@ -119,6 +130,17 @@ SIGNATURES = {
     "sav_softmax_xent_mix": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _I64, _F, _F, _P, _P, _P]),
     "sav_schedule_step": (C.c_int, [_P, _P, _I32, _F, _F, _I64, _I64, _F, _D, _D, _P]),
     "sav_drop_path_factors": (C.c_int, [C.c_uint64, _P, _I64, _I64, _I64, _F, _P, _P]),
+    "sav_layernorm_fwd_f32": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _P, _P, _I64, _I64, _F, _P]),
+    "sav_layernorm_bwd_f32": (C.c_int, [_P, _I64, _P, _I64] + [_P] * 8 + [_I64, _I64, _P]),
+    "sav_cast2d_bf16_f32": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, _I32, _P]),
+    "sav_conv_same_geom": (C.c_int, [_I64, _I32, _I32, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
+    "sav_im2col": (C.c_int, [_P, _I32, _P, C.POINTER(Conv2dGeom), _P]),
+    "sav_col2im": (C.c_int, [_P, _P, _I32, _I32, C.POINTER(Conv2dGeom), _P]),
+    "sav_bn_stats": (C.c_int, [_P, _I64, _I64, _P, _P, _P]),
+    "sav_bn_update_running": (C.c_int, [_P, _P, _P, _P, _F, _I64, _P]),
+    "sav_batchnorm_eval": (C.c_int, [_P, _P, _P, _P, _P, _F, _P, _I64, _I64, _P]),
+    "sav_rotary": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _I32, _I32, _P]),
+    "sav_rotary_table": (C.c_int, [_P, _I64, _I64, _P]),
     "sav_topk_correct": (C.c_int, [_P, _I64, _P, _I64, _I64, _I32, _I32, _I32, _I32, _I32, _P, _P]),
     "sav_cast_f32_bf16": (C.c_int, [_P, _P, _I64, _P]),
     "sav_sumsq": (C.c_int, [_P, _I64, _P, _P]),

@@ -702,9 +702,11 @@ def reshape(x, shape):
 
 
 # ------------------------------------------------------------------ CvT additions
-def dwconv_bn(x, w, gamma, beta, stride, eps):
-    """Depthwise 3x3 conv (SAME, no bias) + BatchNorm with batch statistics on the fp32 stream
-    [B,H,W,C] -> bf16 [B,Ho,Wo,C] (cvt_attention.py:25-36)."""
+def dwconv_bn(x, w, gamma, beta, stride, eps, running=None, momentum=0.9, training=True, update=False):
+    """Depthwise 3x3 conv (SAME, no bias) + BatchNorm on the fp32 stream [B,H,W,C] -> bf16
+    [B,Ho,Wo,C] (cvt_attention.py:25-36).  training: batch statistics, and -- when `update` (the
+    'batch_stats' collection is mutable) -- running = (ra_mean, ra_var) <- momentum * ra +
+    (1 - momentum) * batch statistic (flax nn.BatchNorm).  Eval: normalise with the running averages."""
     t = x.v
     B, H, W, C = t.shape
     if _meta(t):
@@ -715,7 +717,15 @@ def dwconv_bn(x, w, gamma, beta, stride, eps):
     tc = t.contiguous()
     w9 = w.master.reshape(9, C)
     y, stats = ops.dwconv3x3_fwd(tc, w9, stride)
+    if not training:
+        if running is None:
+            raise ValueError("BatchNorm in eval mode needs the 'batch_stats' running averages")
+        # use_running_average=True (cvt_attention.py:33): no statistics, no state update
+        return Var(ops.batchnorm_eval(y, running[0], running[1], gamma.master, beta.master, eps),
+                   requires_grad=False)
     z, mrv = ops.batchnorm_fwd(y, stats, gamma.master, beta.master, eps)
+    if update and running is not None:
+        ops.bn_update_running(mrv[0], mrv[2], running[0], running[1], momentum)
     out = Var(z)
 
     def bwd():
@@ -808,3 +818,151 @@ def pad_tokens_to_square(x):
         x.g16 = None
     record(bwd)
     return res, S
+
+
+# ------------------------------------------------------------------ rotary helpers
+def rotary(x, seq_axis=0):
+    """apply_rotary_pos_emb (position_embed.py:17-20) with sin / cos of the FixedPositionalEmbedding
+    frequencies; the gradient is rotated back (the rotation is orthogonal)."""
+    t = x.v
+    if _meta(t):
+        return Var(torch.empty(t.shape, dtype=t.dtype, device="meta"))
+    out = Var(ops.rotary(t.contiguous(), seq_axis))
+
+    def bwd():
+        g = out.take_grad()
+        if g is not None and x.requires_grad:
+            _add_grad(x, ops.rotary(g.contiguous(), seq_axis, inverse=True))
+    record(bwd)
+    return out
+
+
+# ------------------------------------------------------------------ dense convolutions / conv stems
+def _image_geometry(x):
+    """(tensor, B, H, W, C, element strides (b,h,w,c), producing Var or None) of a conv input:
+    train.HWCN images [H,W,C,N], a raw [B,H,W,C] tensor, or a contiguous Var [B,H,W,C]."""
+    from .train import HWCN
+    if isinstance(x, HWCN):
+        t = x.images
+        H, W, Cc, B = t.shape
+        return t, B, H, W, Cc, (1, W * Cc * B, Cc * B, B), None
+    if isinstance(x, Var):
+        t = x.v
+        if not _meta(t):
+            t = t.contiguous()
+        B, H, W, Cc = t.shape
+        return t, B, H, W, Cc, (H * W * Cc, W * Cc, Cc, 1), (x if x.requires_grad else None)
+    t = x if _meta(x) else x.contiguous()
+    B, H, W, Cc = t.shape
+    return t, B, H, W, Cc, (H * W * Cc, W * Cc, Cc, 1), None
+
+
+def conv2d_stream(x, kernel, bias, ksize, stride, padding="SAME"):
+    """nn.Conv (cvt.py:27-31) as im2col + tcgen05 GEMM: x [B,H,W,Cin] (fp32 stream Var, raw images,
+    or HWCN images) -> fp32 Var [B, Ho, Wo, Cout].  kernel: Param [kh,kw,cin,cout]; bias: Param or
+    None.  Reverse mode: dW = cols^T dY (split-K GEMM into the gradient arena), dbias = column sums,
+    dX = fold(dY W^T) (GEMM + gather col2im)."""
+    t, B, H, W, Cin, xs, src = _image_geometry(x)
+    Cout = kernel.shadow.shape[-1]
+    K = ksize * ksize * Cin
+    if _meta(t):
+        if padding == "SAME":
+            Ho, Wo = -(-H // stride), -(-W // stride)
+        else:
+            Ho = (H + 2 * int(padding) - ksize) // stride + 1
+            Wo = (W + 2 * int(padding) - ksize) // stride + 1
+        return Var(torch.empty((B, Ho, Wo, Cout), dtype=F32, device="meta"))
+    g = ops.conv2d_geom(B, H, W, Cin, ksize, stride, padding, xs)
+    cols = ops.im2col(t, g)
+    A = cols[:, :K]
+    W2 = kernel.shadow.reshape(K, Cout)
+    y = ops.gemm(A, W2, b_mn=True, out_fp32=True, bias=bias.master if bias is not None else None)
+    out = Var(y.view(B, g.Ho, g.Wo, Cout))
+
+    def bwd():
+        dy = out.take_grad()
+        dy16 = out.take_grad16()
+        if dy is None and dy16 is None:
+            return
+        if dy16 is None:
+            dy16 = torch.empty((B * g.Ho * g.Wo, Cout), dtype=BF16, device=t.device)
+            ops.cast_bf16(dy.contiguous().view(-1), dy16.view(-1))
+        dy16 = dy16.reshape(-1, Cout)
+        kernel.touch_grad()
+        ops.gemm(A, dy16, a_mn=True, b_mn=True, out=kernel.grad.reshape(K, Cout), accumulate=True, split_k=0)
+        if bias is not None:
+            bias.touch_grad()
+            ops.colsum(dy16, out=bias.grad, accumulate=True)
+        if src is not None:
+            dcols = torch.empty((B * g.Ho * g.Wo, g.ld), dtype=BF16, device=t.device)
+            ops.gemm(dy16, W2, b_mn=False, out=dcols[:, :K])
+            dx = torch.empty((B, H, W, Cin), dtype=F32, device=t.device)
+            ops.col2im(dcols, g, dx)
+            if src.g is None:
+                src.g, src.g16 = dx.view(src.v.shape), None
+            else:
+                _add_grad(src, dx.view(src.v.shape))
+    record(bwd)
+    return out
+
+
+def layernorm_stream(x, scale, bias, eps=1e-6):
+    """LayerNorm whose OUTPUT is the fp32 residual stream (cvt.py:34: the token embedding's LayerNorm
+    feeds StageBlock's `x + attention(x)` directly).  fp32 in, fp32 out."""
+    xv = x.v
+    if _meta(xv):
+        return Var(torch.empty(xv.shape, dtype=F32, device="meta"))
+    if xv.dtype != F32:
+        raise TypeError("layernorm_stream: fp32 input expected")
+    xc = xv.contiguous()
+    C = xc.shape[-1]
+    x2 = xc.view(-1, C)
+    y, mean, rstd = ops.layernorm_fwd_f32(x2, scale.master, bias.master, eps)
+    out = Var(y.view(xc.shape))
+
+    def bwd():
+        dy = out.take_grad()
+        out.g16 = None
+        if dy is None:
+            return
+        scale.touch_grad()
+        bias.touch_grad()
+        dx, dx16 = ops.layernorm_bwd_f32(dy.contiguous().view(-1, C), x2, scale.master, mean, rstd,
+                                         scale.grad, bias.grad)
+        if x.requires_grad:
+            if x.g is not None:
+                raise NotImplementedError("layernorm_stream input with a second consumer")
+            x.g, x.g16 = dx.view(xc.shape), dx16.view(xc.shape)
+    record(bwd)
+    return out
+
+
+def stream_first_token(x):
+    """x[:, 0] of the fp32 residual stream as a bf16 GEMM operand (cvt.py:165-170: the CvT head reads
+    the class token without a LayerNorm in between)."""
+    t = x.v
+    B, N, C = t.shape
+    if _meta(t):
+        return Var(torch.empty((B, C), dtype=BF16, device="meta"))
+    if t.dtype != F32:
+        raise TypeError("stream_first_token: fp32 residual stream expected")
+    tc = t.contiguous()
+    rows = tc.view(B * N, C)[::N]
+    out = Var(ops.scale_rows_cols(rows, None, None, 1))
+
+    def bwd():
+        g = out.take_grad()
+        if g is None or not x.requires_grad:
+            return
+        if x.g is not None:
+            raise NotImplementedError("stream_first_token on a stream Var with another consumer")
+        full = torch.empty((B * N, C), dtype=F32, device=t.device)
+        full16 = torch.empty((B * N, C), dtype=BF16, device=t.device)
+        ops.fill(full, 0.0)
+        ops.fill(full16.view(torch.float32), 0.0)
+        g2 = g.reshape(B, C).contiguous()
+        ops.cast2d_bf16_f32(g2, full[::N])
+        ops.copy2d(g2, full16[::N])
+        x.g, x.g16 = full.view(B, N, C), full16.view(B, N, C)
+    record(bwd)
+    return out

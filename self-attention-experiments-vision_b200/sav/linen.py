@@ -36,6 +36,8 @@ class _Run:
         self.device = device
         self.init_params = {}       # path -> temporary Param-like (init mode)
         self.gens = {}
+        self.batch_stats = {}       # path -> fp32 device tensor (flax 'batch_stats' collection)
+        self.mutable_stats = mode == "init"
 
 
 def _run():
@@ -227,6 +229,23 @@ class Module:
         run.init_params[key] = res
         return res
 
+    def variable(self, collection, name, init_fn, shape):
+        """self.variable('batch_stats', name, init, shape) of flax.linen: a non-trainable fp32 state
+        tensor.  Created during init(); during apply() it is taken from variables['batch_stats']."""
+        if collection != "batch_stats":
+            raise NotImplementedError(f"variable collection '{collection}'")
+        run = _run()
+        path = self._scope_path() + (name,)
+        if path not in run.batch_stats:
+            if run.mode == "apply":
+                raise KeyError(f"batch_stats/{'/'.join(path)} not found in variables (pass the "
+                               "'batch_stats' collection returned by init())")
+            run.batch_stats[path] = self._to_dev(init_fn(None, tuple(shape)), run)
+        return run.batch_stats[path]
+
+    def is_mutable_collection(self, collection):
+        return collection == "batch_stats" and _run().mutable_stats
+
     def _to_dev(self, val, run):
         if run.device.type == "meta":
             return torch.empty(val.shape, dtype=torch.float32, device="meta")
@@ -286,7 +305,10 @@ class Module:
         args = tuple(_to_run_device(a, device) for a in args)
         out = self._execute(run, args, kw)
         arena = run.builder.build(device)
-        return out, {"params": arena.tree()}
+        variables = {"params": arena.tree()}
+        if run.batch_stats:
+            variables["batch_stats"] = _nest(run.batch_stats)
+        return out, variables
 
     def init(self, rngs, *args, **kw):
         return self.init_with_output(rngs, *args, **kw)[1]
@@ -297,8 +319,37 @@ class Module:
             raise TypeError("apply() needs the arena-backed tree returned by init(); use "
                             "sav.load_params(model, tree, example_input) for foreign trees")
         run = _Run("apply", arena=params.arena, rngs=rngs or {}, device=params.arena.device)
+        if isinstance(variables, dict) and "batch_stats" in variables:
+            run.batch_stats = _flatten(variables["batch_stats"])
+        want_stats = bool(mutable) and ("batch_stats" in mutable or mutable is True)
+        run.mutable_stats = want_stats
         args = tuple(_to_run_device(a, params.arena.device) for a in args)
-        return self._execute(run, args, kw)
+        out = self._execute(run, args, kw)
+        if mutable:
+            # flax: apply(..., mutable=[...]) returns (output, updated collections); the running
+            # averages are updated in place on the device, the same tensors are handed back
+            return out, ({"batch_stats": _nest(run.batch_stats)} if want_stats else {})
+        return out
+
+
+def _nest(flat):
+    root = {}
+    for path, v in flat.items():
+        d = root
+        for k in path[:-1]:
+            d = d.setdefault(k, {})
+        d[path[-1]] = v
+    return root
+
+
+def _flatten(tree, prefix=()):
+    out = {}
+    for k, v in tree.items():
+        if isinstance(v, dict):
+            out.update(_flatten(v, prefix + (k,)))
+        else:
+            out[prefix + (k,)] = v
+    return out
 
 
 def _shadow_of(master):

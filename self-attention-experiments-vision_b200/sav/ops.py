@@ -437,3 +437,132 @@ def batchnorm_bwd(dz, y, mrv, gamma, dgamma, dbeta):
     check(lib().sav_batchnorm_bwd(_p(dz), _p(y), _p(mrv[0]), _p(mrv[1]), _p(gamma), _p(dgamma),
                                   _p(dbeta), _p(scratch), _p(dy), rows, Cc, _stream()))
     return dy
+
+
+# ------------------------------------------------------------------ rotary helpers
+def rotary(x, seq_axis, inverse=False):
+    """Rotate the (2i, 2i+1) pairs of the last axis of a contiguous bf16 / fp32 tensor by
+    t * inv_freq[i], t = index along `seq_axis` (position_embed.py:8-20)."""
+    assert x.is_contiguous() and x.dtype in (BF16, F32)
+    seq_axis %= x.dim()
+    assert seq_axis < x.dim() - 1
+    outer = 1
+    for s_ in x.shape[:seq_axis]:
+        outer *= s_
+    inner = 1
+    for s_ in x.shape[seq_axis + 1:-1]:
+        inner *= s_
+    y = torch.empty_like(x)
+    check(lib().sav_rotary(_p(x), _p(y), outer, x.shape[seq_axis], inner, x.shape[-1],
+                           int(x.dtype == F32), int(inverse), _stream()))
+    return y
+
+
+def rotary_table(n, dim, device):
+    emb = torch.empty((n, dim), dtype=F32, device=device)
+    check(lib().sav_rotary_table(_p(emb), n, dim, _stream()))
+    return emb
+
+
+# ------------------------------------------------------------------ dense convolutions (im2col + GEMM)
+def conv_same_geom(n, k, stride):
+    """flax padding='SAME': (out, pad_lo)."""
+    out, lo = C.c_int64(0), C.c_int32(0)
+    check(lib().sav_conv_same_geom(n, k, stride, C.byref(out), C.byref(lo)))
+    return int(out.value), int(lo.value)
+
+
+def conv2d_geom(B, H, W, Cin, k, stride, padding="SAME", x_strides=None):
+    """Geometry of a k x k / stride conv over [B,H,W,Cin]; padding 'SAME' or an explicit low-side
+    amount (botnet.py:294: padding=[(3,3),(3,3)])."""
+    from ._abi import Conv2dGeom
+    g = Conv2dGeom()
+    g.B, g.H, g.W, g.C = B, H, W, Cin
+    g.kh = g.kw = k
+    g.sh = g.sw = stride
+    if padding == "SAME":
+        g.Ho, g.pad_top = conv_same_geom(H, k, stride)
+        g.Wo, g.pad_left = conv_same_geom(W, k, stride)
+    else:
+        p = int(padding)
+        g.pad_top = g.pad_left = p
+        g.Ho = (H + 2 * p - k) // stride + 1
+        g.Wo = (W + 2 * p - k) // stride + 1
+    if x_strides is None:
+        x_strides = (H * W * Cin, W * Cin, Cin, 1)
+    g.xs_b, g.xs_h, g.xs_w, g.xs_c = x_strides
+    K = k * k * Cin
+    g.ld = (K + 7) // 8 * 8
+    return g
+
+
+def im2col(x, g):
+    """x fp32 / bf16 (addressed through g's strides) -> bf16 [B*Ho*Wo, ld]."""
+    assert x.dtype in (F32, BF16)
+    cols = torch.empty((g.B * g.Ho * g.Wo, g.ld), dtype=BF16, device=x.device)
+    check(lib().sav_im2col(_p(x), int(x.dtype == F32), _p(cols), C.byref(g), _stream()))
+    return cols
+
+
+def col2im(dcols, g, dx, accumulate=False):
+    """dx [B,H,W,C] contiguous fp32 / bf16 (+)= fold(dcols bf16 [B*Ho*Wo, ld])."""
+    from ._abi import Conv2dGeom
+    assert dcols.dtype == BF16 and dcols.stride(0) == g.ld and dx.is_contiguous()
+    gc = Conv2dGeom.from_buffer_copy(g)
+    gc.xs_b, gc.xs_h, gc.xs_w, gc.xs_c = g.H * g.W * g.C, g.W * g.C, g.C, 1
+    check(lib().sav_col2im(_p(dcols), _p(dx), int(dx.dtype == F32), int(accumulate), C.byref(gc), _stream()))
+    return dx
+
+
+def bn_stats(y):
+    """Per-channel (sum, sumsq) fp32 [2, C] of a bf16 [..., C] tensor."""
+    _req(y, BF16, "y")
+    Cc = y.shape[-1]
+    stats = torch.empty((2, Cc), dtype=F32, device=y.device)
+    check(lib().sav_bn_stats(_p(y), y.numel() // Cc, Cc, _p(stats[0]), _p(stats[1]), _stream()))
+    return stats
+
+
+def bn_update_running(mean, var, ra_mean, ra_var, momentum):
+    check(lib().sav_bn_update_running(_p(mean), _p(var), _p(ra_mean), _p(ra_var), float(momentum),
+                                      mean.numel(), _stream()))
+
+
+def batchnorm_eval(y, ra_mean, ra_var, gamma, beta, eps):
+    _req(y, BF16, "y")
+    Cc = y.shape[-1]
+    z = torch.empty_like(y)
+    check(lib().sav_batchnorm_eval(_p(y), _p(ra_mean), _p(ra_var), _p(gamma), _p(beta), float(eps), _p(z),
+                                   y.numel() // Cc, Cc, _stream()))
+    return z
+
+
+def layernorm_fwd_f32(x, scale, bias, eps=1e-6):
+    """fp32 [rows, C] -> fp32 [rows, C] (LayerNorm into the residual stream, cvt.py:34)."""
+    _req(x, F32, "x")
+    rows, C_ = x.shape
+    y = torch.empty((rows, C_), dtype=F32, device=x.device)
+    mean = torch.empty(rows, dtype=F32, device=x.device)
+    rstd = torch.empty(rows, dtype=F32, device=x.device)
+    check(lib().sav_layernorm_fwd_f32(_p(x), x.stride(0), _p(scale), _p(bias), _p(y), y.stride(0),
+                                      _p(mean), _p(rstd), rows, C_, eps, _stream()))
+    return y, mean, rstd
+
+
+def layernorm_bwd_f32(dy, x, scale, mean, rstd, dscale, dbias):
+    """dy fp32 (stream gradient) -> (dx fp32, dx16 bf16)."""
+    _req(dy, F32, "dy"); _req(x, F32, "x")
+    rows, C_ = x.shape
+    dx = torch.empty_like(x)
+    dx16 = torch.empty((rows, C_), dtype=BF16, device=x.device)
+    check(lib().sav_layernorm_bwd_f32(_p(dy), dy.stride(0), _p(x), x.stride(0), _p(scale), _p(mean),
+                                      _p(rstd), None, _p(dx), _p(dx16), _p(dscale), _p(dbias), rows, C_,
+                                      _stream()))
+    return dx, dx16
+
+
+def cast2d_bf16_f32(src, dst, accumulate=False):
+    rows, cols = src.shape
+    assert dst.shape == src.shape and src.stride(1) == 1 and dst.stride(1) == 1
+    check(lib().sav_cast2d_bf16_f32(_p(src), src.stride(0), _p(dst), dst.stride(0), rows, cols,
+                                    int(accumulate), _stream()))

@@ -56,21 +56,22 @@ def test_struct_layouts_agree_with_a_c_compiler(built_lib, tmp_path):
 #include <stddef.h>
 #include "{HEADER}"
 int main(void) {{
-  printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(sav_gemm_args), offsetof(sav_gemm_args, residual),
+  printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(sav_gemm_args), offsetof(sav_gemm_args, residual),
          sizeof(sav_attn_fwd_args), offsetof(sav_attn_fwd_args, scale),
          sizeof(sav_attn_bwd_args), offsetof(sav_attn_bwd_args, scale),
          sizeof(sav_bgemm_args), offsetof(sav_bgemm_args, a_mn),
-         sizeof(sav_thsoftmax_args), offsetof(sav_thsoftmax_args, scale));
+         sizeof(sav_thsoftmax_args), offsetof(sav_thsoftmax_args, scale),
+         sizeof(sav_conv2d_geom), offsetof(sav_conv2d_geom, ld));
   return 0;
 }}""")
     exe = tmp_path / "probe"
     subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", str(src), "-o", str(exe)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     G, F, B = built_lib.GemmArgs, built_lib.AttnFwdArgs, built_lib.AttnBwdArgs
-    BG, TS = built_lib.BGemmArgs, built_lib.ThSoftmaxArgs
+    BG, TS, CG = built_lib.BGemmArgs, built_lib.ThSoftmaxArgs, built_lib.Conv2dGeom
     assert got == [ctypes.sizeof(G), G.residual.offset, ctypes.sizeof(F), F.scale.offset,
                    ctypes.sizeof(B), B.scale.offset, ctypes.sizeof(BG), BG.a_mn.offset,
-                   ctypes.sizeof(TS), TS.scale.offset]
+                   ctypes.sizeof(TS), TS.scale.offset, ctypes.sizeof(CG), CG.ld.offset]
 
 
 def test_no_device_is_a_loud_error(built_lib):

@@ -274,3 +274,148 @@ def test_cvt_stage_block(B, L, C, heads):
     assert float(ours[kb].float().abs().max().cpu()) < 2e-2 * float(scale_ref.abs().max())
     del errs[kb]
     _check(f"cvt_stage_B{B}L{L}C{C}", errs)
+
+
+# ------------------------------------------------------------------------------ rotary helpers
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,axis,dtype", [
+    ((197, 6, 64), 0, torch.bfloat16),        # [seq, heads, dim], seq_dim = 0 (the reference default)
+    ((3, 50, 4, 48), 1, torch.bfloat16),      # batched [B, N, H, D]
+    ((33, 2, 128), 0, torch.float32),
+])
+def test_rotary_matches_oracle_forward_and_reverse(shape, axis, dtype):
+    """position_embed.py:8-45 (intended reading, parity unpinned): forward against the restated
+    helpers, reverse mode against autograd of the restatement, FixedPositionalEmbedding table."""
+    import sav
+    from models.layers import FixedPositionalEmbedding, RotaryPositionalEmbedding
+    from sav.tape import Var
+    g = torch.Generator().manual_seed(len(shape) * 10 + axis)
+    x = torch.randn(shape, generator=g).to(dtype)
+    cot = torch.randn(shape, generator=g).to(dtype)
+    xr = x.float().clone().requires_grad_(True)
+    y_ref = V.apply_rotary_pos_emb(xr, axis)
+    (y_ref * cot.float()).sum().backward()
+
+    model = RotaryPositionalEmbedding()
+    xv = Var(x.cuda())
+    variables = model.init({"params": 0}, xv, seq_dim=axis)
+    holder = {}
+
+    def fn(p, v):
+        holder["y"] = model.apply({"params": p}, v, seq_dim=axis)
+        return _Cotangent(holder["y"], cot.cuda())
+    sav.value_and_grad(fn)(variables["params"], xv)
+    torch.cuda.synchronize()
+    tol = 1e-2 if dtype == torch.bfloat16 else 2e-5     # one bf16 rounding of the output
+    assert _rel(holder["y"].v, y_ref) <= tol
+    assert _rel(xv.g, xr.grad) <= tol
+    emb = FixedPositionalEmbedding().apply({"params": variables["params"]}, xv, seq_dim=axis)
+    ref = V.fixed_positional_embedding(shape[axis], shape[-1])
+    assert torch.equal(emb.v.cpu(), ref)
+
+
+# ------------------------------------------------------------------------------ full CvT model
+def _small_cvt_cfg():
+    return dict(stage_sizes=(1, 1, 2), num_heads=(1, 3, 6), embed_dim=(64, 192, 384),
+                embed_kernel_size=(7, 3, 3), embed_strides=(4, 2, 2), num_classes=1000)
+
+
+@pytest.mark.gpu
+def test_cvt_model_logits_and_all_grads():
+    """CvT (cvt.py:116-171) end to end: conv token embedding (7x7 stride 4 / 3x3 stride 2 as im2col
+    + tcgen05 GEMM) -> LayerNorm into the stream -> StageBlocks -> class token in the last stage ->
+    head on the stream's class row.  CvT-13's widths and head counts at reduced depth, 96x96 images
+    (576 / 144 / 36+1 tokens: the last stage pads 37 tokens to a 7x7 map, keys on 4x4)."""
+    import sav
+    from models import CvT
+    from sav.train import HWCN, make_loss_fn
+    cfg = _small_cvt_cfg()
+    params = V.synthetic_cvt_params(cfg, seed=42)
+    images, labels = O.synthetic_batch(16, img_size=96, seed=0)
+    loss_ref, logits_ref, grads_ref = V.cvt_loss_and_grads(params, images, labels, cfg, 0.1)
+    model = CvT(num_classes=1000, stage_sizes=cfg["stage_sizes"], num_heads=cfg["num_heads"],
+                embed_dim=cfg["embed_dim"])
+    x = HWCN(images.cuda())
+    variables = sav.load_params(model, params, x, is_training=True)
+    (loss, logits), grads = sav.value_and_grad(make_loss_fn(model, 0.1), has_aux=True)(
+        variables["params"], x, labels.cuda())
+    torch.cuda.synchronize()
+    assert abs(loss.item() - float(loss_ref)) <= 2e-2 * abs(float(loss_ref))
+    errs = {"logits": _rel(logits.v, logits_ref)}
+    l2 = {}
+    ours = dict(O.tree_leaves(grads))
+    zero_ref = []
+    for path, g_ref in O.tree_leaves(grads_ref):
+        # the key projection's BatchNorm bias has an analytically zero gradient (softmax shift
+        # invariance, see test_cvt_stage_block): compare it on the scale of its sibling
+        if path.endswith("ConvProjectionBlock_1/BatchNorm_0/bias"):
+            zero_ref.append(path)
+            continue
+        errs[path] = _rel(ours[path], g_ref)
+        l2[path] = float((ours[path].float().cpu() - g_ref).norm() / g_ref.norm())
+    ref = dict(O.tree_leaves(grads_ref))
+    for path in zero_ref:
+        sib = ref[path.replace("ConvProjectionBlock_1", "ConvProjectionBlock_2")]
+        assert float(ours[path].float().abs().max().cpu()) < 2e-2 * float(sib.abs().max())
+    print("cvt worst relative L2:", sorted(l2.items(), key=lambda kv: -kv[1])[:4])
+    # Few tokens per weight gradient (36 .. 576 per image x 16 images) and three more bf16 operand
+    # sites per attention than ViT (depthwise-conv output, BatchNorm output, per projection): the
+    # edge-shape tolerance of tests/test_vit_parity_gpu.py applies to the max-norm, every tensor must
+    # be within 2.2e-2 in relative L2, the logits within the north-star 2e-2.
+    _check("cvt_small", errs, tol=3.5e-2)
+    assert max(l2.values()) <= 2.2e-2, sorted(l2.items(), key=lambda kv: -kv[1])[:5]
+    assert errs["logits"] <= TOL
+
+
+@pytest.mark.gpu
+def test_cvt_batchnorm_running_averages_and_eval_mode():
+    """cvt_attention.py:33-36: nn.BatchNorm(use_running_average=not is_training, momentum=0.9).
+    init() creates batch_stats (mean 0, var 1); apply(mutable=['batch_stats']) in training mode
+    folds the batch statistics in; eval mode normalises with them."""
+    import sav
+    from models import StageBlock
+    from sav.tape import Var
+    B, L, C, heads = 4, 197, 384, 6
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn((B, L, C), generator=g)
+    params = V.synthetic_cvt_stage_params(C, heads, seed=42)
+    model = StageBlock(num_heads=heads, embed_dim=C)
+    variables = model.init({"params": 0}, Var(x.cuda()), is_training=True)
+    variables = {"params": variables["params"].arena.load_tree(params), "batch_stats": variables["batch_stats"]}
+    bs = dict(O.tree_leaves(variables["batch_stats"]))
+    assert len(bs) == 6 and all(float(v.abs().max()) == 0 for k, v in bs.items() if k.endswith("mean"))
+    # training step with mutable batch_stats: ra = 0.9 * ra + 0.1 * batch stat
+    out, upd = model.apply(variables, Var(x.cuda()), is_training=True, mutable=["batch_stats"])
+    torch.cuda.synchronize()
+    S = 15
+    padded = torch.cat([x, x.new_zeros(B, S * S - L, C)], dim=1).reshape(B, S, S, C)
+    pa = params["CvTSelfAttentionBlock_0"]
+    new = dict(O.tree_leaves(upd["batch_stats"]))
+    ras = []
+    for i, stride in enumerate((1, 2, 2)):
+        mean, var = V.conv_projection_batch_stats(padded, pa[f"ConvProjectionBlock_{i}"], stride)
+        pre = f"CvTSelfAttentionBlock_0/ConvProjectionBlock_{i}/BatchNorm_0/"
+        ra_m, ra_v = 0.1 * mean, 0.9 + 0.1 * var
+        # the device statistics are taken over the bf16-rounded conv output's fp32 values
+        assert _rel(new[pre + "mean"], ra_m) <= 5e-3 and _rel(new[pre + "var"], ra_v) <= 5e-3
+        ras.append((new[pre + "mean"].cpu(), new[pre + "var"].cpu()))
+    # eval mode uses exactly those running averages
+    out_eval = model.apply({"params": variables["params"], "batch_stats": upd["batch_stats"]},
+                           Var(x.cuda()), is_training=False)
+    torch.cuda.synchronize()
+    q, k, v = (V.conv_projection_eval(padded, pa[f"ConvProjectionBlock_{i}"], s, *ras[i])
+               for i, s in enumerate((1, 2, 2)))
+    d = C // heads
+    q, k, v = (t.reshape(B, -1, heads, d) for t in (q, k, v))
+    w = V.softmax_last(torch.einsum("bqhd,bkhd->bhqk", q / math.sqrt(d), k))
+    a = torch.einsum("bqhd,hdc->bqc", torch.einsum("bhqk,bkhd->bqhd", w, v), pa["DenseGeneral_0"]["kernel"])
+    xr = a + padded.reshape(B, S * S, C)
+    ref = xr + V.ff_block(V.layer_norm(xr, params["LayerNorm_0"]["scale"], params["LayerNorm_0"]["bias"]),
+                          params["FFBlock_0"])
+    assert _rel(out_eval.v, ref) <= TOL
+    # without mutable the running averages are left alone (train.py's call shape, SURVEY D5)
+    before = {k: v.clone() for k, v in new.items()}
+    model.apply({"params": variables["params"], "batch_stats": upd["batch_stats"]}, Var(x.cuda()),
+                is_training=True)
+    torch.cuda.synchronize()
+    assert all(torch.equal(before[k], v) for k, v in O.tree_leaves(upd["batch_stats"]))

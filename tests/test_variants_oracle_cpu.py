@@ -200,3 +200,32 @@ def test_talking_heads_block_is_part_of_the_surface():
     from models.layers import TalkingHeadsBlock
     from models.layers.attentions import TalkingHeadsBlock as T2
     assert TalkingHeadsBlock is T2
+
+
+def test_rotary_helpers_are_exported_and_shape_only_on_meta():
+    """models/layers/__init__.py:4 exports RotaryPositionalEmbedding / FixedPositionalEmbedding."""
+    from models.layers import FixedPositionalEmbedding, RotaryPositionalEmbedding
+    from sav.tape import Var
+    x = Var(torch.empty((197, 6, 64), device="meta", dtype=torch.bfloat16))
+    out, variables = RotaryPositionalEmbedding().init_with_output({"params": 0}, x)
+    assert tuple(out.shape) == (197, 6, 64) and not list(O.tree_leaves(variables["params"]))
+    emb, _ = FixedPositionalEmbedding().init_with_output({"params": 0}, x)
+    assert tuple(emb.shape) == (197, 64)
+
+
+def test_rotary_oracle_properties():
+    """The restated helpers: rotate_every_two is the literal (-x1, x0, -x3, x2, ...) pattern, the
+    rotation is orthogonal (norm preserving, inverse = rotation by -theta), position 0 is the
+    identity, and the literal float32 frequency table is zero from the fifth frequency on."""
+    x = torch.arange(8.0).reshape(1, 1, 8)
+    assert V.rotate_every_two(x).flatten().tolist() == [-1, 0, -3, 2, -5, 4, -7, 6]
+    emb = V.fixed_positional_embedding(5, 64)
+    assert emb.shape == (5, 64) and torch.equal(emb[:, :32], emb[:, 32:])
+    assert float(emb[1, 0]) == 64.0 and float(emb[1, 1]) == pytest.approx(64.0 / 1e10)
+    assert torch.all(emb[:, 4:32] == 0)       # 10e4**8 overflows float32 -> 1/inf
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn((7, 3, 64), generator=g)
+    y = V.apply_rotary_pos_emb(x, 0)
+    assert torch.allclose(y[0], x[0]) and torch.allclose(y.norm(dim=-1), x.norm(dim=-1), rtol=1e-5)
+    pairs = lambda t: t.reshape(7, 3, 32, 2)
+    assert torch.allclose(pairs(y).norm(dim=-1), pairs(x).norm(dim=-1), rtol=1e-5)

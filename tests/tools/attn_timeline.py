@@ -18,7 +18,17 @@ EV = {1: "P kv_empty wait", 2: "P kv_empty ok", 10: "M kv_full wait", 11: "M kv_
       22: "S pass1 done", 40: "M sdp wait st_free", 41: "M st_free ok", 42: "M sdp issued", 43: "M grads wait pds", 44: "M pds_full ok", 45: "M grads issued", 50: "C wait st_full", 51: "C st_full ok", 52: "C math done", 53: "C pds_free ok", 54: "C smem written", 55: "C dkv_full ok", 56: "C dkv stored", 57: "C dq_full ok", 30: "E o_full g0", 31: "E o_full g1", 32: "E stored", 23: "S pass2 done", 24: "S o_full ok", 25: "S O read", 26: "S stored"}
 ROLES = ["producer", "mma0", "mma1", "softmax0", "softmax1", "epilogue"]
 if "--bwd" in sys.argv:
-    ROLES[1], ROLES[3], ROLES[4] = "mma", "comp_h0", "comp_h1"
+    # attn_bwd3_kernel (build with SAV_ATTN_DEV=1)
+    ROLES = ["producer", "issuerA", "issuerB", "math_w4", "math_w8", "epilogue", "stats"]
+    EV = {1: "P wait qdo_empty", 2: "P qdo_empty ok", 3: "P wait kv_empty", 4: "P kv_empty ok",
+          10: "A wait kv_full", 11: "A kv_full ok", 14: "A wait qdo_full", 15: "A qdo_full ok",
+          12: "A wait s_free", 13: "A s_free ok -> issue S/dP",
+          20: "B wait pds_full", 21: "B pds_full ok", 22: "B dkv/dq_free ok -> issue grads",
+          35: "M wait st_full", 36: "M st_full ok", 30: "M wait s_full", 31: "M s_full ok", 32: "M math done",
+          33: "M pds_free ok", 34: "M chunk written",
+          40: "E delta start", 41: "E delta done", 42: "E wait dkv_full", 43: "E dkv_full ok", 44: "E dV dK stored",
+          45: "E wait dq_full", 46: "E dq_full ok",
+          50: "S wait dl_ready", 51: "S dl_ready ok", 52: "S wait st_empty", 53: "S st_empty ok"}
 
 
 def main():
@@ -56,7 +66,8 @@ def main():
             events.append((clk - t0, name, EV.get(ev, str(ev))))
     events.sort()
     last = {}
-    for clk, name, ev in events[: a.items * 40]:
+    skip = int(os.environ.get("SKIP", "0"))
+    for clk, name, ev in events[skip: skip + a.items * 60]:
         d = clk - last.get(name, clk)
         last[name] = clk
         print(f"{clk:9d}  (+{d:6d})  {name:9s} {ev}")
