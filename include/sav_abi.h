@@ -303,10 +303,48 @@ int sav_col2im(const void* dcols, void* dx, int32_t dx_is_fp32, int32_t accumula
  * zero-fills sum / sumsq), the running-average update ra = momentum*ra + (1-momentum)*stat
  * (flax nn.BatchNorm, cvt_attention.py:33-36), and the eval-mode apply from running averages. */
 int sav_bn_stats(const void* y, int64_t rows, int64_t C, float* sum, float* sumsq, void* stream);
+/* mean, rstd = rsqrt(var + eps), biased var (flax nn.BatchNorm) from the sums over `rows` rows */
+int sav_bn_finalize(const float* sum, const float* sumsq, int64_t rows, float eps, float* mean,
+                    float* rstd, float* var, int64_t C, void* stream);
 int sav_bn_update_running(const float* mean, const float* var, float* ra_mean, float* ra_var,
                           float momentum, int64_t C, void* stream);
 int sav_batchnorm_eval(const void* y, const float* ra_mean, const float* ra_var, const float* gamma,
                        const float* beta, float eps, void* z, int64_t rows, int64_t C, void* stream);
+
+/* ---------------------------------------------------------------- BoTNet conv-stage pieces
+ * Channel-last bf16 [rows, C] tensors around the conv GEMMs of botnet.py:17-67,202-331.
+ * kind: 0 none, 1 swish (nn.swish, the BoTNet activation_fn), 2 sigmoid (SE gate), 3 relu.
+ *   sav_bn_act_fwd / bwd : z = act(BatchNorm(y)) from given mean / rstd (sav_bn_stats +
+ *       sav_batchnorm_fwd produce them); the reverse mode recomputes act' from y, accumulates
+ *       dgamma / dbeta, scratch fp32 [2C]                          (botnet.py:44-50,225-228)
+ *   sav_gate_res_act_fwd / bwd : out = act(residual + x * gate[b, c]) -- squeeze-excite gate, skip
+ *       connection and activation of a bottleneck block in one pass; gate bf16 [B, C] and residual
+ *       optional; reverse mode writes dx, dresidual (optional) and dgate fp32 [B, C] (zero-filled by
+ *       the callee)                                                 (botnet.py:54-67,244-252)
+ *   sav_spatial_mean_fwd / bwd : [B, rows_per_sample, C] <-> [B, C]  (jnp.mean(.., (1, 2)):
+ *       squeeze_excite.py:32, botnet.py:322)
+ *   sav_maxpool3x3s2_fwd / bwd : nn.max_pool((3,3), (2,2), 'SAME') (botnet.py:297), arg-max uint8
+ *   sav_act_fwd / bwd : elementwise activation on n bf16 elements (SE hidden swish, SE sigmoid) */
+int sav_act_fwd(const void* x, void* y, int64_t n, int32_t kind, void* stream);
+int sav_act_bwd(const void* x, const void* dy, void* dx, int64_t n, int32_t kind, void* stream);
+int sav_bn_act_fwd(const void* y, const float* mean, const float* rstd, const float* gamma,
+                   const float* beta, void* z, int64_t rows, int64_t C, int32_t kind, void* stream);
+int sav_bn_act_bwd(const void* dz, const void* y, const float* mean, const float* rstd,
+                   const float* gamma, const float* beta, float* dgamma, float* dbeta, float* scratch,
+                   void* dy, int64_t rows, int64_t C, int32_t kind, void* stream);
+int sav_gate_res_act_fwd(const void* x, const void* gate, const void* residual, void* out, int64_t B,
+                         int64_t rows_per_sample, int64_t C, int32_t kind, void* stream);
+int sav_gate_res_act_bwd(const void* dout, const void* x, const void* gate, const void* residual,
+                         void* dx, void* dresidual, float* dgate, int64_t B, int64_t rows_per_sample,
+                         int64_t C, int32_t kind, void* stream);
+int sav_spatial_mean_fwd(const void* x, void* out, int64_t B, int64_t rows_per_sample, int64_t C,
+                         void* stream);
+int sav_spatial_mean_bwd(const void* dout, void* dx, int64_t B, int64_t rows_per_sample, int64_t C,
+                         void* stream);
+int sav_maxpool3x3s2_fwd(const void* x, void* y, void* argmax, int64_t B, int64_t H, int64_t W,
+                         int64_t C, void* stream);
+int sav_maxpool3x3s2_bwd(const void* dy, const void* argmax, void* dx, int64_t B, int64_t H, int64_t W,
+                         int64_t C, void* stream);
 
 /* ---------------------------------------------------------------- rotary helpers
  * models/layers/position_embed.py:8-45 (unused by every reference model and unfinished there:

@@ -439,6 +439,189 @@ def cvt_loss_and_grads(params, images_hwcn, labels, cfg, label_smoothing=0.0):
     return loss.detach(), logits.detach(), grads
 
 
+# ----------------------------------------------------------------------------- BoTNet conv stages
+class _RoundBf16(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return x.bfloat16().float()
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.bfloat16().float()
+
+
+# When set, the conv-stage functions below round their results (and the gradients flowing back
+# through them) to bf16 at exactly the tensors a bf16 pipeline stores: conv operands and outputs,
+# BatchNorm(+activation) outputs, block outputs.  This "ideal bf16 pipeline" is the noise FLOOR the
+# CUDA path is compared with (BatchNorm'd conv stacks amplify operand rounding far more than the
+# LayerNorm'd transformer: its worst gradient is ~0.1 off the fp32 result at the test shapes).
+EMULATE_BF16 = [False]
+
+
+def _rb(x):
+    return _RoundBf16.apply(x) if EMULATE_BF16[0] else x
+
+
+def swish(x):
+    """flax.linen.swish: x * sigmoid(x) (botnet.py:31,216,264)."""
+    return _rb(x * torch.sigmoid(x))
+
+
+def batch_norm_train(y, p, eps=1e-5):
+    """flax nn.BatchNorm(use_running_average=False) (botnet.py:286-290): statistics over all axes
+    but the last, biased variance E[x^2] - E[x]^2."""
+    ax = tuple(range(y.dim() - 1))
+    mean = y.mean(dim=ax)
+    var = (y * y).mean(dim=ax) - mean * mean
+    return _rb((y - mean) * torch.rsqrt(var + eps) * p["scale"] + p["bias"])
+
+
+def conv2d_nobias(x, kernel, stride=1, padding="SAME"):
+    """nn.Conv(use_bias=False) on [B,H,W,Cin] with a Flax kernel [kh,kw,cin,cout]; padding 'SAME'
+    or an explicit symmetric amount (botnet.py:294)."""
+    x, kernel = _rb(x), _rb(kernel)
+    if padding == "SAME":
+        return _rb(conv2d_same(x, kernel, None, stride))
+    xi = torch.nn.functional.pad(x.permute(0, 3, 1, 2), (padding, padding, padding, padding))
+    return _rb(torch.nn.functional.conv2d(xi, kernel.permute(3, 2, 0, 1), stride=stride).permute(0, 2, 3, 1))
+
+
+def max_pool_3x3_s2_same(x):
+    """nn.max_pool(y, (3, 3), strides=(2, 2), padding='SAME') (botnet.py:297): -inf padding."""
+    B, H, W, C = x.shape
+    pt, pb = same_pad_amounts(H, 2, 3)
+    pl, pr = same_pad_amounts(W, 2, 3)
+    xi = torch.nn.functional.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb), value=float("-inf"))
+    return torch.nn.functional.max_pool2d(xi, 3, 2).permute(0, 2, 3, 1)
+
+
+def squeeze_excite(x, p, act=swish):
+    """SqueezeExciteBlock.__call__ (squeeze_excite.py:21-38), intended reading of :32-33:
+    x = mean(inputs, (1, 2), keepdims=True) -> Dense -> act -> Dense -> sigmoid(x) * inputs."""
+    s = x.mean(dim=(1, 2), keepdim=True)
+    s = act(s @ p["Dense_0"]["kernel"] + p["Dense_0"]["bias"])
+    s = s @ p["Dense_1"]["kernel"] + p["Dense_1"]["bias"]
+    return torch.sigmoid(s) * x
+
+
+def bottleneck_block(x, p, strides, se=True):
+    """BottleneckResNetBlock.__call__ (botnet.py:34-67)."""
+    residual = x
+    y = conv2d_nobias(x, p["Conv_0"]["kernel"])                                   # :43
+    y = swish(batch_norm_train(y, p["BatchNorm_0"]))                              # :44-45
+    y = conv2d_nobias(y, p["Conv_1"]["kernel"], strides)                          # :46
+    y = swish(batch_norm_train(y, p["BatchNorm_1"]))                              # :47-48
+    y = conv2d_nobias(y, p["Conv_2"]["kernel"])                                   # :49-50
+    y = batch_norm_train(y, p["BatchNorm_2"])                                     # :51
+    if se:
+        y = squeeze_excite(y, p["SqueezeExciteBlock_0"])                          # :53-56
+    if residual.shape != y.shape:                                                 # :58-63
+        residual = conv2d_nobias(residual, p["Conv_3"]["kernel"], strides)
+        residual = swish(batch_norm_train(residual, p["BatchNorm_3"]))
+    return swish(residual + y)                                                    # :65
+
+
+def bot_block(x, p, num_heads, head_dim):
+    """BoTBlock.__call__ (botnet.py:218-252) with strides (1, 1) (stride_one=True, every
+    create_model configuration)."""
+    residual = x
+    y = conv2d_nobias(x, p["Conv_0"]["kernel"])                                   # :229
+    y = swish(batch_norm_train(y, p["BatchNorm_0"]))                              # :230-231
+    y = bot_mhsa(y, p["BoTMHSA_0"], num_heads, head_dim)                          # :232
+    y = swish(batch_norm_train(y, p["BatchNorm_1"]))                              # :238-239
+    y = conv2d_nobias(y, p["Conv_1"]["kernel"])                                   # :240-241
+    y = batch_norm_train(y, p["BatchNorm_2"])                                     # :242
+    if residual.shape != y.shape:                                                 # :244-249
+        residual = conv2d_nobias(residual, p["Conv_2"]["kernel"])
+        residual = swish(batch_norm_train(residual, p["BatchNorm_3"]))
+    return swish(residual + y)                                                    # :251
+
+
+def botnet_forward(params, images_nhwc, cfg):
+    """BoTNet.__call__ (botnet.py:278-326), train=True."""
+    y = conv2d_nobias(images_nhwc, params["Conv_0"]["kernel"], 2, 3)              # :292-295
+    y = swish(batch_norm_train(y, params["BatchNorm_0"]))                         # :296-297
+    y = max_pool_3x3_s2_same(y)                                                   # :298
+    n = 0
+    sizes = cfg["stage_sizes"]
+    for i, block_size in enumerate(sizes[:-1]):                                   # :299-311
+        for j in range(block_size):
+            strides = 2 if i > 0 and j == 0 else 1
+            y = bottleneck_block(y, params[f"BottleneckResNetBlock_{n}"], strides)
+            n += 1
+    for j in range(sizes[-1]):                                                    # :312-320
+        y = bot_block(y, params[f"BoTBlock_{j}"], cfg["num_heads"], cfg["head_dim"])
+    y = y.mean(dim=(1, 2))                                                        # :321
+    return y @ params["Dense_0"]["kernel"] + params["Dense_0"]["bias"]            # :322-325
+
+
+def synthetic_botnet_params(cfg, img_size, seed=42, dtype=torch.float32):
+    """SURVEY 8d synthetic init with the Flax auto-names of botnet.py (the zero-initialised last
+    BatchNorm scale of each block, botnet.py:51,242, is given a non-degenerate value)."""
+    g = torch.Generator().manual_seed(seed)
+
+    def normal(shape, std):
+        return (torch.randn(shape, generator=g, dtype=torch.float64) * std).to(dtype)
+
+    def conv(k, cin, cout):
+        return {"kernel": normal((k, k, cin, cout), 1.0 / math.sqrt(k * k * cin))}
+
+    def bn(C):
+        return {"scale": 1.0 + normal((C,), 0.1), "bias": normal((C,), 0.1)}
+
+    f0, pf = cfg["initial_filters"], 4
+    sizes = cfg["stage_sizes"]
+    params = {"Conv_0": conv(7, 3, f0), "BatchNorm_0": bn(f0)}
+    cin, n = f0, 0
+    for i, block_size in enumerate(sizes[:-1]):
+        f = f0 * 2 ** i
+        for j in range(block_size):
+            strides = 2 if i > 0 and j == 0 else 1
+            hid = max(1, int(f * pf * 0.0625))
+            p = {"Conv_0": conv(1, cin, f), "BatchNorm_0": bn(f), "Conv_1": conv(3, f, f), "BatchNorm_1": bn(f),
+                 "Conv_2": conv(1, f, f * pf), "BatchNorm_2": bn(f * pf),
+                 "SqueezeExciteBlock_0": {
+                     "Dense_0": {"kernel": normal((f * pf, hid), 1.0 / math.sqrt(f * pf)), "bias": normal((hid,), 0.02)},
+                     "Dense_1": {"kernel": normal((hid, f * pf), 1.0 / math.sqrt(hid)), "bias": normal((f * pf,), 0.02)}}}
+            if cin != f * pf or strides != 1:
+                p["Conv_3"] = conv(1, cin, f * pf)
+                p["BatchNorm_3"] = bn(f * pf)
+            params[f"BottleneckResNetBlock_{n}"] = p
+            n += 1
+            cin = f * pf
+    f = f0 * 2 ** (len(sizes) - 1)
+    hw = img_size // 4
+    for i in range(1, len(sizes) - 1):
+        hw = -(-hw // 2)
+    h, d = cfg["num_heads"], cfg["head_dim"]
+    for j in range(sizes[-1]):
+        mh = synthetic_bot_params(f, h, d, hw, hw, seed=seed + 10 + j, dtype=dtype)
+        p = {"Conv_0": conv(1, cin, f), "BatchNorm_0": bn(f), "BoTMHSA_0": mh, "BatchNorm_1": bn(h * d),
+             "Conv_1": conv(1, h * d, f * pf), "BatchNorm_2": bn(f * pf)}
+        if cin != f * pf:
+            p["Conv_2"] = conv(1, cin, f * pf)
+            p["BatchNorm_3"] = bn(f * pf)
+        params[f"BoTBlock_{j}"] = p
+        cin = f * pf
+    nc = cfg["num_classes"]
+    params["Dense_0"] = {"kernel": normal((cin, nc), 0.02), "bias": normal((nc,), 0.02)}
+    return params
+
+
+def botnet_loss_and_grads(params, images_hwcn, labels, cfg, label_smoothing=0.0, emulate_bf16=False):
+    from .vit_oracle import hwcn_to_nhwc, loss_fn
+    p = tree_map(lambda t: t.detach().clone().requires_grad_(True), params)
+    EMULATE_BF16[0] = bool(emulate_bf16)
+    try:
+        logits = botnet_forward(p, hwcn_to_nhwc(images_hwcn), cfg)
+    finally:
+        EMULATE_BF16[0] = False
+    loss = loss_fn(logits, labels, cfg["num_classes"], label_smoothing)
+    loss.backward()
+    grads = tree_map(lambda t: t.grad if t.grad is not None else torch.zeros_like(t), p)
+    return loss.detach(), logits.detach(), grads
+
+
 # ----------------------------------------------------------------------------- rotary helpers
 def rotate_every_two(x):
     """position_embed.py:8-14 literally: x1 = x[:, :, ::2], x2 = x[:, :, 1::2],

@@ -334,6 +334,15 @@ extern "C" int sav_batchnorm_fwd(const void* y, const float* sum, const float* s
   return check_launch("sav_batchnorm_fwd");
 }
 
+extern "C" int sav_bn_finalize(const float* sum, const float* sumsq, int64_t rows, float eps, float* mean,
+                               float* rstd, float* var, int64_t C, void* stream) {
+  if (rows <= 0 || C <= 0) return set_error(SAV_ERR_SHAPE, "sav_bn_finalize: bad shape");
+  bn_finalize_kernel<<<(int)((C + 127) / 128), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      sum, sumsq, 1.f / (float)rows, eps, mean, rstd, var, (int)C);
+  count_launch();
+  return check_launch("sav_bn_finalize");
+}
+
 extern "C" int sav_batchnorm_bwd(const void* dz, const void* y, const float* mean, const float* rstd,
                                  const float* gamma, float* dgamma, float* dbeta, float* scratch,
                                  void* dy, int64_t rows, int64_t C, void* stream) {

@@ -787,12 +787,21 @@ static int num_sms() {
 
 static int pick_bn_batched(int64_t N) { return N <= 64 ? 64 : 128; }
 
+// Development overrides (tile width, CTA pairing, column-sum group width, debug switches) are read
+// from the environment ONLY in the -DSAV_GEMM_DEV build (SAV_GEMM_DEV=1 python build.py); the
+// production library has no tuning back door.
+static int dev_env(const char* name) {
+#ifdef SAV_GEMM_DEV
+  const char* e = getenv(name);
+  return e ? atoi(e) : 0;
+#else
+  (void)name;
+  return 0;
+#endif
+}
+
 static int pick_bn(int64_t N) {
-  static int forced = -1;
-  if (forced < 0) {
-    const char* e = getenv("SAV_GEMM_BN");
-    forced = e ? atoi(e) : 0;
-  }
+  static const int forced = dev_env("SAV_GEMM_BN");
   if (forced == 128 || forced == 192 || forced == 256) return forced;
   if (N % 256 == 0) return 256;
   if (N % 192 == 0) return 192;
@@ -847,11 +856,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
 
 // CTA pairs pay off when the pair tile (256 rows) is mostly full; SAV_GEMM_CTAS=1|2 overrides.
 static int pick_ctas(int64_t M) {
-  static int forced = -1;
-  if (forced < 0) {
-    const char* e = getenv("SAV_GEMM_CTAS");
-    forced = e ? atoi(e) : 0;
-  }
+  static const int forced = dev_env("SAV_GEMM_CTAS");
   if (forced == 1 || forced == 2) return forced;
   const int64_t pair_rows = ((M + 2 * BM - 1) / (2 * BM)) * (2 * BM);
   const int64_t single_rows = ((M + BM - 1) / BM) * BM;
@@ -908,8 +913,7 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
   p.bias = a->bias; p.col_scale = a->col_scale; p.row_scale = a->row_scale;
   p.rows_per_scale = a->rows_per_scale > 0 ? a->rows_per_scale : 1;
   {
-    static int dbg = -1;
-    if (dbg < 0) { const char* e = getenv("SAV_GEMM_DEBUG"); dbg = e ? atoi(e) : 0; }
+    static const int dbg = dev_env("SAV_GEMM_DEBUG");
     p.debug = dbg;
   }
   p.batch_inner = 1; p.nbatch = 1;
@@ -1033,11 +1037,7 @@ static void colsum_plan(int64_t N, int64_t* gx_out, int64_t* W_out) {
     const int64_t lanes = w / 8, active = lanes * (256 / lanes);
     if (active > best_active) { best_active = active; best_g = g; best_w = w; }
   }
-  static int forced = -1;   // development override: SAV_COLSUM_W=<group width>
-  if (forced < 0) {
-    const char* e = getenv("SAV_COLSUM_W");
-    forced = e ? atoi(e) : 0;
-  }
+  static const int forced = dev_env("SAV_COLSUM_W");   // development override: group width
   if (forced >= 8 && forced <= 2048 && forced % 8 == 0 && N % forced == 0) {
     best_g = N / forced;
     best_w = forced;

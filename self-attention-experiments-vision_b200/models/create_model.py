@@ -5,6 +5,7 @@ Names and hyper-parameters are the reference's; `deit_ti_patch16` / `deit_s_patc
 `dtype` is accepted for signature compatibility; the compute path is always bf16 storage with fp32
 accumulation / statistics.
 """
+from models.botnet import BoTNet
 from models.cait import CaiT
 from models.cvt import CvT
 from models.vit import ViT
@@ -35,6 +36,13 @@ _CAIT = {
 }
 
 
+_BOTNET = {
+    # name: stage_sizes                                          create_model.py:38-49
+    'botnet_t3': (3, 4, 6, 6),
+    'botnet_t4': (3, 4, 23, 6),
+    'botnet_t5': (3, 4, 23, 12),
+}
+
 _CVT = {
     # name: (stage_sizes, num_heads, embed_dim)                  create_model.py:169-183
     # the reference writes embed_dim (64, 192, 368) for cvt-13 / cvt-21; 368 % 6 heads != 0 trips its
@@ -55,6 +63,8 @@ def create_model(model_name: str, num_classes: int = 1000, dtype=None):
         return CaiT(num_classes=num_classes, num_layers=layers, num_layers_token_only=2,
                     num_heads=heads, embed_dim=dim, patch_shape=(16, 16), stoch_depth_rate=sd,
                     layerscale_eps=eps, dtype=dtype)
+    if model_name in _BOTNET:
+        return BoTNet(num_classes=num_classes, stage_sizes=_BOTNET[model_name], dtype=dtype)
     if model_name in _CVT:
         sizes, heads, dims = _CVT[model_name]
         return CvT(num_classes=num_classes, stage_sizes=sizes, num_heads=heads, embed_dim=dims)

@@ -6,3 +6,4 @@ from models.layers.position_embed import (AddAbsPosEmbed, FixedPositionalEmbeddi
                                            RotaryPositionalEmbedding)
 from models.layers.regularization import StochasticDepthBlock  # noqa: F401
 from models.layers.stems import PatchEmbedBlock  # noqa: F401
+from models.layers.squeeze_excite import SqueezeExciteBlock  # noqa: F401

@@ -137,8 +137,19 @@ SIGNATURES = {
     "sav_im2col": (C.c_int, [_P, _I32, _P, C.POINTER(Conv2dGeom), _P]),
     "sav_col2im": (C.c_int, [_P, _P, _I32, _I32, C.POINTER(Conv2dGeom), _P]),
     "sav_bn_stats": (C.c_int, [_P, _I64, _I64, _P, _P, _P]),
+    "sav_bn_finalize": (C.c_int, [_P, _P, _I64, _F, _P, _P, _P, _I64, _P]),
     "sav_bn_update_running": (C.c_int, [_P, _P, _P, _P, _F, _I64, _P]),
     "sav_batchnorm_eval": (C.c_int, [_P, _P, _P, _P, _P, _F, _P, _I64, _I64, _P]),
+    "sav_act_fwd": (C.c_int, [_P, _P, _I64, _I32, _P]),
+    "sav_act_bwd": (C.c_int, [_P, _P, _P, _I64, _I32, _P]),
+    "sav_bn_act_fwd": (C.c_int, [_P, _P, _P, _P, _P, _P, _I64, _I64, _I32, _P]),
+    "sav_bn_act_bwd": (C.c_int, [_P] * 10 + [_I64, _I64, _I32, _P]),
+    "sav_gate_res_act_fwd": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I64, _I32, _P]),
+    "sav_gate_res_act_bwd": (C.c_int, [_P] * 7 + [_I64, _I64, _I64, _I32, _P]),
+    "sav_spatial_mean_fwd": (C.c_int, [_P, _P, _I64, _I64, _I64, _P]),
+    "sav_spatial_mean_bwd": (C.c_int, [_P, _P, _I64, _I64, _I64, _P]),
+    "sav_maxpool3x3s2_fwd": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P]),
+    "sav_maxpool3x3s2_bwd": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P]),
     "sav_rotary": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _I32, _I32, _P]),
     "sav_rotary_table": (C.c_int, [_P, _I64, _I64, _P]),
     "sav_topk_correct": (C.c_int, [_P, _I64, _P, _I64, _I64, _I32, _I32, _I32, _I32, _I32, _P, _P]),

@@ -966,3 +966,171 @@ def stream_first_token(x):
         x.g, x.g16 = full.view(B, N, C), full16.view(B, N, C)
     record(bwd)
     return out
+
+
+# ------------------------------------------------------------------ BoTNet conv stages (bf16 NHWC)
+def conv2d(x, kernel, ksize, stride, padding="SAME"):
+    """nn.Conv(use_bias=False) of the BoTNet stem / bottleneck blocks (botnet.py:280-285,47-64):
+    x bf16 Var [B,H,W,Cin] (or raw / HWCN fp32 images for the stem) -> bf16 Var [B,Ho,Wo,Cout].
+    1x1 stride-1 convs are the GEMM itself; everything else goes through im2col / col2im."""
+    t, B, H, W, Cin, xs, src = _image_geometry(x)
+    Cout = kernel.shadow.shape[-1]
+    K = ksize * ksize * Cin
+    if _meta(t):
+        if padding == "SAME":
+            Ho, Wo = -(-H // stride), -(-W // stride)
+        else:
+            Ho = (H + 2 * int(padding) - ksize) // stride + 1
+            Wo = (W + 2 * int(padding) - ksize) // stride + 1
+        return Var(torch.empty((B, Ho, Wo, Cout), dtype=BF16, device="meta"))
+    W2 = kernel.shadow.reshape(K, Cout)
+    direct = ksize == 1 and stride == 1 and t.dtype == BF16 and isinstance(x, Var)
+    if direct:
+        g = None
+        A = t.view(B * H * W, Cin)
+        Ho, Wo = H, W
+    else:
+        g = ops.conv2d_geom(B, H, W, Cin, ksize, stride, padding, xs)
+        A = ops.im2col(t, g)[:, :K]
+        Ho, Wo = g.Ho, g.Wo
+    y = ops.gemm(A, W2, b_mn=True)
+    out = Var(y.view(B, Ho, Wo, Cout))
+
+    def bwd():
+        dy = out.take_grad()
+        if dy is None:
+            return
+        dy2 = dy.contiguous().view(-1, Cout)
+        kernel.touch_grad()
+        ops.gemm(A, dy2, a_mn=True, b_mn=True, out=kernel.grad.reshape(K, Cout), accumulate=True, split_k=0)
+        if src is None:
+            return
+        if direct:
+            dx = ops.gemm(dy2, W2, b_mn=False)
+        elif K % 8:
+            raise NotImplementedError("conv2d input gradient with kh*kw*cin not a multiple of 8 (only "
+                                      "the 3-channel image stems have that, and images carry no gradient)")
+        else:
+            dcols = torch.empty((B * Ho * Wo, g.ld), dtype=BF16, device=t.device)
+            ops.gemm(dy2, W2, b_mn=False, out=dcols[:, :K])
+            dx = torch.empty((B, H, W, Cin), dtype=t.dtype, device=t.device)
+            ops.col2im(dcols, g, dx)
+        _add_grad(src, dx.view(src.v.shape))
+    record(bwd)
+    return out
+
+
+def batchnorm_act(y, gamma, beta, eps, act="none", running=None, momentum=0.9, training=True,
+                  update=False):
+    """act(nn.BatchNorm(y)) on a bf16 [.., C] Var (botnet.py:286-290: batch statistics in training,
+    running averages otherwise; momentum update of `running` = (ra_mean, ra_var) when `update`)."""
+    t = y.v
+    if _meta(t):
+        return Var(torch.empty(t.shape, dtype=BF16, device="meta"))
+    tc = t.contiguous()
+    C = tc.shape[-1]
+    rows = tc.numel() // C
+    if not training:
+        if running is None:
+            raise ValueError("BatchNorm in eval mode needs the 'batch_stats' running averages")
+        ra_mean, ra_var = running
+        z = ops.batchnorm_eval(tc, ra_mean, ra_var, gamma.master, beta.master, eps)
+        if act != "none":
+            z = ops.act_fwd(z, act)
+        return Var(z, requires_grad=False)
+    mrv = ops.bn_finalize(ops.bn_stats(tc), rows, eps)
+    if update and running is not None:
+        ops.bn_update_running(mrv[0], mrv[2], running[0], running[1], momentum)
+    out = Var(ops.bn_act_fwd(tc, mrv[0], mrv[1], gamma.master, beta.master, act))
+
+    def bwd():
+        dz = out.take_grad()
+        if dz is None:
+            return
+        gamma.touch_grad()
+        beta.touch_grad()
+        dy = ops.bn_act_bwd(dz.contiguous(), tc, mrv[0], mrv[1], gamma.master, beta.master, gamma.grad,
+                            beta.grad, act)
+        if y.requires_grad:
+            _add_grad(y, dy.view(t.shape))
+    record(bwd)
+    return out
+
+
+def gate_residual_act(x, gate=None, residual=None, act="none"):
+    """act(residual + x * gate[b, c]) in one pass: the squeeze-excite gate, the skip connection and
+    the closing activation of a bottleneck block (botnet.py:54-67, squeeze_excite.py:37)."""
+    t = x.v
+    if _meta(t):
+        return Var(torch.empty(t.shape, dtype=BF16, device="meta"))
+    tc = t.contiguous()
+    gt = gate.v.contiguous() if gate is not None else None
+    rt = residual.v.contiguous() if residual is not None else None
+    out = Var(ops.gate_res_act_fwd(tc, gt, rt, act))
+
+    def bwd():
+        d = out.take_grad()
+        if d is None:
+            return
+        want_res = residual is not None and residual.requires_grad
+        dx, dres, dgate = ops.gate_res_act_bwd(d.contiguous(), tc, gt, rt, act, want_res)
+        if x.requires_grad:
+            _add_grad(x, dx.view(t.shape))
+        if want_res:
+            _add_grad(residual, dres.view(residual.v.shape))
+        if gate is not None and gate.requires_grad:
+            g16 = torch.empty(dgate.shape, dtype=BF16, device=dgate.device)
+            ops.cast_bf16(dgate.view(-1), g16.view(-1))
+            _add_grad(gate, g16.view(gate.v.shape))
+    record(bwd)
+    return out
+
+
+def spatial_mean(x):
+    """jnp.mean(x, axis=(1, 2)) of a bf16 [B,H,W,C] Var -> [B,C] (squeeze_excite.py:32, botnet.py:322)."""
+    t = x.v
+    if _meta(t):
+        return Var(torch.empty((t.shape[0], t.shape[-1]), dtype=BF16, device="meta"))
+    tc = t.contiguous()
+    out = Var(ops.spatial_mean_fwd(tc))
+
+    def bwd():
+        d = out.take_grad()
+        if d is not None and x.requires_grad:
+            _add_grad(x, ops.spatial_mean_bwd(d.contiguous(), tuple(tc.shape)).view(t.shape))
+    record(bwd)
+    return out
+
+
+def maxpool3x3s2(x):
+    """nn.max_pool(x, (3, 3), strides=(2, 2), padding='SAME') (botnet.py:297)."""
+    t = x.v
+    if _meta(t):
+        B, H, W, C = t.shape
+        return Var(torch.empty((B, -(-H // 2), -(-W // 2), C), dtype=BF16, device="meta"))
+    tc = t.contiguous()
+    y, arg = ops.maxpool3x3s2_fwd(tc)
+    out = Var(y)
+
+    def bwd():
+        d = out.take_grad()
+        if d is not None and x.requires_grad:
+            _add_grad(x, ops.maxpool3x3s2_bwd(d.contiguous(), arg, tuple(tc.shape)).view(t.shape))
+    record(bwd)
+    return out
+
+
+def activation(x, kind):
+    """Standalone swish / sigmoid / relu on a (small) bf16 Var: the SE hidden layer and gate."""
+    t = x.v
+    if _meta(t):
+        return Var(torch.empty(t.shape, dtype=BF16, device="meta"))
+    tc = t.contiguous()
+    out = Var(ops.act_fwd(tc, kind))
+
+    def bwd():
+        d = out.take_grad()
+        if d is not None and x.requires_grad:
+            _add_grad(x, ops.act_bwd(tc, d.contiguous(), kind).view(t.shape))
+    record(bwd)
+    return out

@@ -37,7 +37,10 @@ class _Run:
         self.init_params = {}       # path -> temporary Param-like (init mode)
         self.gens = {}
         self.batch_stats = {}       # path -> fp32 device tensor (flax 'batch_stats' collection)
-        self.mutable_stats = mode == "init"
+        # flax updates BatchNorm running averages only under apply(..., mutable=['batch_stats']); during
+        # init() the collection is created (mean 0, var 1) but not updated (is_initializing guard)
+        self.mutable_stats = False
+        self.had_batch_stats = False
 
 
 def _run():
@@ -237,9 +240,10 @@ class Module:
         run = _run()
         path = self._scope_path() + (name,)
         if path not in run.batch_stats:
-            if run.mode == "apply":
-                raise KeyError(f"batch_stats/{'/'.join(path)} not found in variables (pass the "
-                               "'batch_stats' collection returned by init())")
+            if run.mode == "apply" and run.had_batch_stats:
+                raise KeyError(f"batch_stats/{'/'.join(path)} not found in variables")
+            # apply() without the collection (train.py's call shape): a scratch state that
+            # the training-mode statistics never read
             run.batch_stats[path] = self._to_dev(init_fn(None, tuple(shape)), run)
         return run.batch_stats[path]
 
@@ -321,6 +325,7 @@ class Module:
         run = _Run("apply", arena=params.arena, rngs=rngs or {}, device=params.arena.device)
         if isinstance(variables, dict) and "batch_stats" in variables:
             run.batch_stats = _flatten(variables["batch_stats"])
+            run.had_batch_stats = True
         want_stats = bool(mutable) and ("batch_stats" in mutable or mutable is True)
         run.mutable_stats = want_stats
         args = tuple(_to_run_device(a, params.arena.device) for a in args)
@@ -441,8 +446,88 @@ class Dropout(Module):
         raise NotImplementedError("dropout with rate > 0 in training mode")
 
 
+class _Activation:
+    """Callable activation with a `kind` the fused kernels understand (BatchNorm + activation, the
+    closing activation of a bottleneck block).  Called directly it is the standalone kernel."""
+
+    def __init__(self, kind):
+        self.kind = kind
+
+    def __call__(self, x):
+        return F.activation(x, self.kind)
+
+
 class activation:
     gelu = staticmethod(F.gelu)
+    swish = _Activation("swish")
+    relu = _Activation("relu")
+    sigmoid = _Activation("sigmoid")
 
 
 gelu = F.gelu
+swish = activation.swish
+relu = activation.relu
+sigmoid = activation.sigmoid
+
+
+def _act_kind(fn):
+    if fn is None:
+        return "none"
+    kind = getattr(fn, "kind", None)
+    if kind is None:
+        raise NotImplementedError("conv-stage activation must be one of nn.swish / nn.relu / nn.sigmoid")
+    return kind
+
+
+class Conv(Module):
+    """flax.linen.Conv on channel-last bf16 activations (botnet.py:280-285): im2col + tcgen05 GEMM,
+    or the GEMM alone for 1x1 stride-1 kernels.  kernel [kh, kw, cin, cout]."""
+    features: int = 0
+    kernel_size: tuple = (1, 1)
+    strides: tuple = (1, 1)
+    padding: object = 'SAME'
+    use_bias: bool = True
+    dtype: object = None
+    precision: object = None
+    kernel_init: object = None
+
+    def __call__(self, inputs):
+        if self.use_bias:
+            raise NotImplementedError("nn.Conv(use_bias=True) on the bf16 conv-stage path (the CvT token "
+                                      "embedding uses functional.conv2d_stream)")
+        kh, kw = self.kernel_size
+        sh, sw = self.strides if not isinstance(self.strides, int) else (self.strides, self.strides)
+        if kh != kw or sh != sw:
+            raise NotImplementedError("nn.Conv: square kernels / equal strides only")
+        cin = inputs.shape[-1]
+        kernel = self.param("kernel", self.kernel_init or initializers.lecun_normal(in_axes=3),
+                            (kh, kw, cin, self.features))
+        pad = self.padding
+        if not isinstance(pad, str):
+            lo = {int(p[0]) for p in pad} | {int(p[1]) for p in pad}     # [(3, 3), (3, 3)], botnet.py:294
+            if len(lo) != 1:
+                raise NotImplementedError("nn.Conv: symmetric explicit padding only")
+            pad = lo.pop()
+        return F.conv2d(inputs, kernel, kh, sh, pad)
+
+
+class BatchNorm(Module):
+    """flax.linen.BatchNorm over the last axis (botnet.py:286-290): batch statistics (biased variance)
+    unless use_running_average; running averages in the 'batch_stats' collection.  `act` fuses the
+    activation that follows the norm in the reference (y = norm()(y); y = activation_fn(y))."""
+    use_running_average: bool = False
+    momentum: float = 0.99
+    epsilon: float = 1e-5
+    dtype: object = None
+    scale_init: object = None
+    bias_init: object = None
+
+    def __call__(self, inputs, act=None):
+        C = inputs.shape[-1]
+        scale = self.param("scale", self.scale_init or initializers.ones, (C,))
+        bias = self.param("bias", self.bias_init or initializers.zeros, (C,))
+        ra_mean = self.variable("batch_stats", "mean", initializers.zeros, (C,))
+        ra_var = self.variable("batch_stats", "var", initializers.ones, (C,))
+        return F.batchnorm_act(inputs, scale, bias, self.epsilon, _act_kind(act), running=(ra_mean, ra_var),
+                               momentum=self.momentum, training=not self.use_running_average,
+                               update=self.is_mutable_collection("batch_stats"))

@@ -566,3 +566,97 @@ def cast2d_bf16_f32(src, dst, accumulate=False):
     assert dst.shape == src.shape and src.stride(1) == 1 and dst.stride(1) == 1
     check(lib().sav_cast2d_bf16_f32(_p(src), src.stride(0), _p(dst), dst.stride(0), rows, cols,
                                     int(accumulate), _stream()))
+
+
+# ------------------------------------------------------------------ BoTNet conv-stage pieces (cnn.cu)
+ACT = {"none": 0, "swish": 1, "sigmoid": 2, "relu": 3}
+
+
+def act_fwd(x, kind):
+    _req(x, BF16, "x")
+    y = torch.empty_like(x)
+    check(lib().sav_act_fwd(_p(x), _p(y), x.numel(), ACT[kind], _stream()))
+    return y
+
+
+def act_bwd(x, dy, kind):
+    dx = torch.empty_like(x)
+    check(lib().sav_act_bwd(_p(x), _p(dy), _p(dx), x.numel(), ACT[kind], _stream()))
+    return dx
+
+
+def bn_finalize(stats, rows, eps):
+    """(sum, sumsq) [2, C] -> mrv fp32 [3, C] = (mean, rstd, biased var)."""
+    Cc = stats.shape[1]
+    mrv = torch.empty((3, Cc), dtype=F32, device=stats.device)
+    check(lib().sav_bn_finalize(_p(stats[0]), _p(stats[1]), rows, float(eps), _p(mrv[0]), _p(mrv[1]),
+                                _p(mrv[2]), Cc, _stream()))
+    return mrv
+
+
+def bn_act_fwd(y, mean, rstd, gamma, beta, kind):
+    _req(y, BF16, "y")
+    Cc = y.shape[-1]
+    z = torch.empty_like(y)
+    check(lib().sav_bn_act_fwd(_p(y), _p(mean), _p(rstd), _p(gamma), _p(beta), _p(z), y.numel() // Cc, Cc,
+                               ACT[kind], _stream()))
+    return z
+
+
+def bn_act_bwd(dz, y, mean, rstd, gamma, beta, dgamma, dbeta, kind):
+    Cc = y.shape[-1]
+    dy = torch.empty_like(y)
+    scratch = torch.empty(2 * Cc, dtype=F32, device=y.device)
+    check(lib().sav_bn_act_bwd(_p(dz), _p(y), _p(mean), _p(rstd), _p(gamma), _p(beta), _p(dgamma), _p(dbeta),
+                               _p(scratch), _p(dy), y.numel() // Cc, Cc, ACT[kind], _stream()))
+    return dy
+
+
+def gate_res_act_fwd(x, gate, res, kind):
+    """x bf16 [B, ..., C]; gate bf16 [B, C] or None; res like x or None."""
+    B, Cc = x.shape[0], x.shape[-1]
+    out = torch.empty_like(x)
+    check(lib().sav_gate_res_act_fwd(_p(x), _p(gate), _p(res), _p(out), B, x.numel() // (B * Cc), Cc,
+                                     ACT[kind], _stream()))
+    return out
+
+
+def gate_res_act_bwd(dout, x, gate, res, kind, want_dres):
+    B, Cc = x.shape[0], x.shape[-1]
+    dx = torch.empty_like(x)
+    dres = torch.empty_like(x) if want_dres else None
+    dgate = torch.empty((B, Cc), dtype=F32, device=x.device) if gate is not None else None
+    check(lib().sav_gate_res_act_bwd(_p(dout), _p(x), _p(gate), _p(res), _p(dx), _p(dres), _p(dgate), B,
+                                     x.numel() // (B * Cc), Cc, ACT[kind], _stream()))
+    return dx, dres, dgate
+
+
+def spatial_mean_fwd(x):
+    B, Cc = x.shape[0], x.shape[-1]
+    out = torch.empty((B, Cc), dtype=BF16, device=x.device)
+    check(lib().sav_spatial_mean_fwd(_p(x), _p(out), B, x.numel() // (B * Cc), Cc, _stream()))
+    return out
+
+
+def spatial_mean_bwd(dout, shape):
+    B, Cc = shape[0], shape[-1]
+    dx = torch.empty(shape, dtype=BF16, device=dout.device)
+    check(lib().sav_spatial_mean_bwd(_p(dout), _p(dx), B, dx.numel() // (B * Cc), Cc, _stream()))
+    return dx
+
+
+def maxpool3x3s2_fwd(x):
+    B, H, W, Cc = x.shape
+    Ho, _ = conv_same_geom(H, 3, 2)
+    Wo, _ = conv_same_geom(W, 3, 2)
+    y = torch.empty((B, Ho, Wo, Cc), dtype=BF16, device=x.device)
+    arg = torch.empty((B, Ho, Wo, Cc), dtype=torch.uint8, device=x.device)
+    check(lib().sav_maxpool3x3s2_fwd(_p(x), _p(y), _p(arg), B, H, W, Cc, _stream()))
+    return y, arg
+
+
+def maxpool3x3s2_bwd(dy, arg, shape):
+    B, H, W, Cc = shape
+    dx = torch.empty(shape, dtype=BF16, device=dy.device)
+    check(lib().sav_maxpool3x3s2_bwd(_p(dy), _p(arg), _p(dx), B, H, W, Cc, _stream()))
+    return dx
