@@ -53,7 +53,9 @@ def main():
         (_, _), g1 = sav.value_and_grad(make_loss_fn(model, 0.1, 1), has_aux=True)(v1["params"], xg, labels.cuda())
         torch.cuda.synchronize()
         single = dict(O.tree_leaves(g1))
-        out["worst_vs_single_rank"] = max(rel(ours[k], single[k].float().cpu()) for k in single)
+        vs = sorted(((rel(ours[k], single[k].float().cpu()), k) for k in single), reverse=True)
+        out["worst_vs_single_rank"] = vs[0][0]
+        out["worst_vs_single_rank_tensors"] = vs[:3]
     dist.barrier()
     # every rank must hold the same reduced gradients
     chk = variables["params"].arena.grad.double().sum().reshape(1)
