@@ -51,6 +51,7 @@ int64_t sav_launch_count(void);
  *   bf16 D + aux_out : (act=1) aux_out = bf16(acc + bias) [pre-activation saved for backward],
  *                      D = bf16(gelu_tanh(acc + bias))                       (ff.py:24-25)
  *   bf16 D + aux_in  : D = bf16(acc * gelu_tanh'(aux_in[m,n]))               (reverse of ff.py:25)
+ *                      (+ dgelu_colsum[n] += sum_m of that product, the reverse of ff.py:24's bias)
  *   fp32 D           : v = acc + bias; v *= col_scale; v *= row_scale; v += residual[m,n] (fp32);
  *                      D = v        -- the fp32 residual stream (vit.py:24,31; layerscale.py:20-23;
  *                      stochastic_depth.py:16-27)
@@ -81,6 +82,9 @@ typedef struct {
   int64_t ldr;
   void* workspace;         /* unused (kept for ABI stability); may be NULL */
   int64_t workspace_bytes;
+  float* dgelu_colsum;     /* aux_in mode only: fp32 [N], += column sums of acc * gelu'(aux_in) -- the
+                            * bias gradient of the Dense that produced aux_in (reverse of ff.py:24),
+                            * accumulated by the epilogue instead of a separate pass; or NULL */
 } sav_gemm_args;
 int64_t sav_gemm_workspace_bytes(const sav_gemm_args* a);
 int sav_gemm(const sav_gemm_args* a, void* stream);

@@ -45,6 +45,7 @@ struct GemmParams {
   const float* col_scale;
   const float* row_scale;
   int64_t rows_per_scale;
+  float* colsum;    // EPI_DGELU only: column sums of the (fp32) result accumulated here, or null
   int batch_inner;  // batched (BATCH=true) only: size of the inner batch dim (heads)
   int nbatch;       // total batches (1 when not batched)
   long long* dbg;   // development only: timeline buffer (tests/tools/gemm_timeline.py) or null
@@ -61,9 +62,13 @@ struct GemmCfg {
   static constexpr int kBBoxes = (kBCols + 63) / 64;
   static constexpr int kBBytes = B_MN ? kBBoxes * (BK * 128) : kBCols * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kFit = (kSmemBudget - kOutBytes - 1024 - 256) / kStageBytes;
+  // after the stages and the slab ring: 256 B of barriers, 2 KB of per-tile column-sum accumulators
+  // (2 x BN floats, EPI_DGELU with colsum).  The dynamic segment is declared __align__(1024), so
+  // no alignment slack is budgeted.
+  static constexpr int kTailBytes = 256 + 2048;
+  static constexpr int kFit = (kSmemBudget - kOutBytes - kTailBytes) / kStageBytes;
   static constexpr int kStages = kFit > 6 ? 6 : kFit;
-  static constexpr int kSmem = kStages * kStageBytes + kOutBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int kSmem = kStages * kStageBytes + kOutBytes + kTailBytes;
   static constexpr uint32_t kTmemCols = 512;  // 2 accumulators of BN <= 256 fp32 columns
   static_assert(kStageBytes % 1024 == 0, "stage must keep 1024 B alignment");
   static_assert(kStages >= 3, "too few stages");
@@ -205,10 +210,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
             const __grid_constant__ CUtensorMap tma_d, const __grid_constant__ CUtensorMap tma_x,
             const GemmParams p) {
   using Cfg = GemmCfg<BN, B_MN, CTAS>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;   // SW128 tiles need a 1024-byte aligned base (checked below)
   uint8_t* smem_out = smem + Cfg::kStages * Cfg::kStageBytes;  // 1024-aligned (stage bytes % 1024 == 0)
+  float* s_colsum = reinterpret_cast<float*>(smem_out + kOutBytes + 256);   // [2][BN]
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + kOutBytes);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
@@ -222,6 +227,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
+    if (smem_u32(smem) & 1023u) __trap();
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
     tma_prefetch_desc(&tma_d);
@@ -241,6 +247,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     if (CTAS == 2) tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot);
     else tmem_alloc<Cfg::kTmemCols>(tmem_slot);
   }
+  if (p.colsum)
+    for (int i = threadIdx.x; i < 2 * BN; i += blockDim.x) s_colsum[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   if (CTAS == 2) cluster_sync_all();  // the peer's barriers exist before anything signals them
@@ -473,6 +481,24 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           GEMM_STAMP(3, 27);
         }
         __syncwarp();
+        if (p.colsum && (sg % slabs_per_tile) == (uint32_t)(slabs_per_tile - 1)) {
+          // Last slab of a tile: the barrier above means all sixteen epilogue warps have added
+          // their column sums of this tile.  Flush the tile's accumulator (buffer = tile parity) to
+          // the global sums and clear it.  The epilogue warps never wait for this: they can only
+          // touch this buffer again two tiles later, behind slab slots this warp hands back after
+          // the flush (program order here).
+          const int itl = (int)(sg / slabs_per_tile);
+          const int tile = unit + itl * units;
+          const int n0 = ((tile % tiles_mn) % p.n_blocks) * BN;
+          float* acc_s = s_colsum + (itl & 1) * BN;
+#pragma unroll
+          for (int c = lane; c < BN; c += 32) {
+            const float vsum = acc_s[c];
+            acc_s[c] = 0.f;
+            if (n0 + c < p.N) atomicAdd(p.colsum + n0 + c, vsum);
+          }
+          __syncwarp();
+        }
       }
       if (elect_one()) {
         tma_store_wait<0>();
@@ -568,6 +594,41 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
               const float2 h = unpack_bf16(w[q]);
               dgelu_mul2(v[g * 8 + 2 * q], v[g * 8 + 2 * q + 1], h.x, h.y);
             }
+          }
+          if (p.colsum) {
+            // Column sums of this slab's 16 columns over the warp's 32 rows (the bias gradient of
+            // the Dense whose pre-activation gradient this GEMM produces): a transposing butterfly
+            // -- every step halves the columns a lane carries and doubles the rows they cover -- so
+            // 16 shuffles instead of 16 x 5, then one shared-memory add per column and warp.
+            // Rows >= M contribute 0 (zero-filled operands).
+            static_assert(CB == 16, "butterfly below is written for 16 columns per thread");
+            float t8[8], t4[4], t2[2], t1;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const float send = (lane & 16) ? v[k] : v[k + 8];
+              const float keep = (lane & 16) ? v[k + 8] : v[k];
+              t8[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const float send = (lane & 8) ? t8[k] : t8[k + 4];
+              const float keep = (lane & 8) ? t8[k + 4] : t8[k];
+              t4[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+            }
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              const float send = (lane & 4) ? t4[k] : t4[k + 2];
+              const float keep = (lane & 4) ? t4[k + 2] : t4[k];
+              t2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+            }
+            {
+              const float send = (lane & 2) ? t2[0] : t2[1];
+              const float keep = (lane & 2) ? t2[1] : t2[0];
+              t1 = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+            }
+            t1 += __shfl_xor_sync(0xffffffffu, t1, 1);
+            const int cc = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+            if (!(lane & 1)) atomicAdd(&s_colsum[(it & 1) * BN + j * SC + part * CB + cc], t1);
           }
           st_bf16<CB>(slab, r, part * CH, v);
         } else {
@@ -912,6 +973,9 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
   p.has_aux_in = (a->aux_in || a->residual) ? 1 : 0;
   p.bias = a->bias; p.col_scale = a->col_scale; p.row_scale = a->row_scale;
   p.rows_per_scale = a->rows_per_scale > 0 ? a->rows_per_scale : 1;
+  p.colsum = a->dgelu_colsum;
+  if (p.colsum && p.epi != EPI_DGELU)
+    return set_error(SAV_ERR_ARG, "sav_gemm: dgelu_colsum needs the aux_in (dGELU) epilogue");
   {
     static const int dbg = dev_env("SAV_GEMM_DEBUG");
     p.debug = dbg;

@@ -398,7 +398,9 @@ extern "C" int sav_layernorm_fwd(const float* x, int64_t ldx, const float* scale
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int grid = ln_grid(rows);
   const int chunks = (int)((C / 8 + 31) / 32);
-  if (C <= 512 && rows >= 1024) {
+  // (no row-count threshold: the same kernel -- the same summation order -- for every batch size,
+  // so per-sample results do not depend on how a batch is sharded over ranks)
+  if (C <= 512) {
     const int pieces = (int)((C / 4 + 31) / 32);
     const int64_t want = (rows + 15) / 16;
     const int grid_p = (int)(want < 148 * 8 ? want : 148 * 8);

@@ -6,32 +6,40 @@
 
 namespace sav {
 
-// images [H,W,C,N] fp32 (N contiguous).  One block: fixed image row h, fixed patch column gx,
-// 64 consecutive n.  Reads pw*C rows of 64 contiguous floats; writes, per n, pw*C contiguous bf16.
+// images [H,W,C,N] fp32 (N contiguous).  One block: PY consecutive image rows of one patch row,
+// one patch column gx, 32 consecutive n.  Reads 128-byte runs (32 floats along N) for each of the
+// PY * pw*C (row, w-in-patch, c) features; writes, per n, PY * pw*C CONTIGUOUS bf16 (the features of
+// consecutive rows of a patch are adjacent in the (ph pw c) order of patch_embed.py:19-22), i.e.
+// 384-byte runs at PY = 4 instead of the 96-byte runs of a one-row tile.
 // Algorithmic bytes: 4 (read) + 2 (write) per pixel-channel.
+template <int PY>
 __global__ void __launch_bounds__(256)
 patchify_hwcn_kernel(const float* __restrict__ img, bf16* __restrict__ out, int N, int H, int W,
                      int C, int ph, int pw) {
-  extern __shared__ float tile[];  // [pw*C][65]
+  extern __shared__ float tile[];  // [PY * pw*C][33]
   const int gw = W / pw, gh = H / ph;
+  const int rows_per_patch = ph / PY;            // row groups per patch row
   const int gx = blockIdx.x % gw;
-  const int h = blockIdx.x / gw;
-  const int n0 = blockIdx.y * 64;
-  const int F = pw * C;  // contiguous (w-in-patch, c) run
-  const int64_t in_base = ((int64_t)h * W + (int64_t)gx * pw) * C * N;
-  for (int i = threadIdx.x; i < F * 64; i += blockDim.x) {
-    const int f = i >> 6, n = i & 63;
-    tile[f * 65 + n] = (n0 + n < N) ? img[in_base + (int64_t)f * N + n0 + n] : 0.f;
+  const int hg = blockIdx.x / gw;                // row group index over the image
+  const int gy = hg / rows_per_patch, py0 = (hg % rows_per_patch) * PY;
+  const int n0 = blockIdx.y * 32;
+  const int F = pw * C;                          // contiguous (w-in-patch, c) run of one image row
+  const int FT = PY * F;
+  for (int i = threadIdx.x; i < FT * 32; i += blockDim.x) {
+    const int ft = i >> 5, n = i & 31;
+    const int r = ft / F, f = ft - r * F;
+    const int h = gy * ph + py0 + r;
+    const int64_t in = (((int64_t)h * W + (int64_t)gx * pw) * C + f) * N + n0 + n;
+    tile[ft * 33 + n] = (n0 + n < N) ? img[in] : 0.f;
   }
   __syncthreads();
-  const int gy = h / ph, py = h % ph;
-  const int K = ph * pw * C;
-  for (int i = threadIdx.x; i < 64 * (F / 2); i += blockDim.x) {
-    const int n = i / (F / 2), f2 = (i % (F / 2)) * 2;
+  const int K = ph * F;
+  for (int i = threadIdx.x; i < 32 * (FT / 2); i += blockDim.x) {
+    const int n = i / (FT / 2), f2 = (i - n * (FT / 2)) * 2;
     if (n0 + n < N) {
       const int64_t row = ((int64_t)(n0 + n) * gh + gy) * gw + gx;
-      const uint32_t v = pack_bf16(tile[f2 * 65 + n], tile[(f2 + 1) * 65 + n]);
-      *reinterpret_cast<uint32_t*>(out + row * K + (int64_t)py * F + f2) = v;
+      const uint32_t v = pack_bf16(tile[f2 * 33 + n], tile[(f2 + 1) * 33 + n]);
+      *reinterpret_cast<uint32_t*>(out + row * K + (int64_t)py0 * F + f2) = v;
     }
   }
 }
@@ -81,6 +89,35 @@ __global__ void embed_fwd_kernel(const bf16* __restrict__ tok, const float* __re
   }
 }
 
+// same, 8 channels per thread (16-byte bf16 load, two 16-byte fp32 stores); C % 8 == 0
+__global__ void embed_fwd8_kernel(const bf16* __restrict__ tok, const float* __restrict__ cls,
+                                  const float* __restrict__ pos, float* __restrict__ x, int64_t B,
+                                  int n_tok, int C8, int has_cls) {
+  const int NT = n_tok + has_cls;
+  const int64_t total = B * NT * (int64_t)C8;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C8) * 8;
+    const int64_t r = i / C8;
+    const int t = (int)(r % NT);
+    const int64_t b = r / NT;
+    float v[8];
+    if (has_cls && t == 0) {
+      const float4 a = *reinterpret_cast<const float4*>(cls + c), d = *reinterpret_cast<const float4*>(cls + c + 4);
+      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = d.x; v[5] = d.y; v[6] = d.z; v[7] = d.w;
+    } else {
+      const uint4 u = *reinterpret_cast<const uint4*>(tok + (b * n_tok + (t - has_cls)) * (int64_t)(C8 * 8) + c);
+      const float2 a = unpack_bf16(u.x), d = unpack_bf16(u.y), e = unpack_bf16(u.z), f = unpack_bf16(u.w);
+      v[0] = a.x; v[1] = a.y; v[2] = d.x; v[3] = d.y; v[4] = e.x; v[5] = e.y; v[6] = f.x; v[7] = f.y;
+    }
+    const float4 p0 = __ldg(reinterpret_cast<const float4*>(pos + (int64_t)t * C8 * 8 + c));
+    const float4 p1 = __ldg(reinterpret_cast<const float4*>(pos + (int64_t)t * C8 * 8 + c + 4));
+    float* o = x + (r * C8) * 8 + c;
+    *reinterpret_cast<float4*>(o) = make_float4(v[0] + p0.x, v[1] + p0.y, v[2] + p0.z, v[3] + p0.w);
+    *reinterpret_cast<float4*>(o + 4) = make_float4(v[4] + p1.x, v[5] + p1.y, v[6] + p1.z, v[7] + p1.w);
+  }
+}
+
 // thread per (t, c-pair): loops over b; writes dpos[t,c], dcls (t==0), copies dtok.
 __global__ void embed_bwd_kernel(const float* __restrict__ dx, bf16* __restrict__ dtok,
                                  float* __restrict__ dcls, float* __restrict__ dpos, int64_t B,
@@ -91,7 +128,20 @@ __global__ void embed_bwd_kernel(const float* __restrict__ dx, bf16* __restrict_
   const int c = (int)((i * 2) % C);
   const int t = (int)((i * 2) / C);
   float2 acc = make_float2(0.f, 0.f);
-  for (int64_t b = 0; b < B; ++b) {
+  int64_t b = 0;
+  for (; b + 8 <= B; b += 8) {   // eight independent loads in flight per thread
+    float2 f[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) f[u] = *reinterpret_cast<const float2*>(dx + ((b + u) * NT + t) * C + c);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      acc.x += f[u].x;
+      acc.y += f[u].y;
+      if (dtok && t >= has_cls)
+        *reinterpret_cast<uint32_t*>(dtok + ((b + u) * n_tok + (t - has_cls)) * C + c) = pack_bf16(f[u].x, f[u].y);
+    }
+  }
+  for (; b < B; ++b) {
     const float2 f = *reinterpret_cast<const float2*>(dx + (b * NT + t) * C + c);
     acc.x += f.x;
     acc.y += f.y;
@@ -116,11 +166,14 @@ extern "C" int sav_patchify(const float* images, void* patches, int64_t N, int64
     return set_error(SAV_ERR_SHAPE, "sav_patchify: H,W must be multiples of the patch shape");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (hwcn) {
-    dim3 grid((unsigned)(H * (W / pw)), (unsigned)((N + 63) / 64));
-    const size_t sm = (size_t)pw * C * 65 * sizeof(float);
+    const int PY = ph % 4 == 0 ? 4 : (ph % 2 == 0 ? 2 : 1);
+    dim3 grid((unsigned)((H / PY) * (W / pw)), (unsigned)((N + 31) / 32));
+    const size_t sm = (size_t)PY * pw * C * 33 * sizeof(float);
     if (sm > 48 * 1024) return set_error(SAV_ERR_SHAPE, "sav_patchify: pw*C too large");
-    patchify_hwcn_kernel<<<grid, 256, sm, st>>>(images, reinterpret_cast<bf16*>(patches), (int)N,
-                                                (int)H, (int)W, (int)C, (int)ph, (int)pw);
+    bf16* o = reinterpret_cast<bf16*>(patches);
+    if (PY == 4) patchify_hwcn_kernel<4><<<grid, 256, sm, st>>>(images, o, (int)N, (int)H, (int)W, (int)C, (int)ph, (int)pw);
+    else if (PY == 2) patchify_hwcn_kernel<2><<<grid, 256, sm, st>>>(images, o, (int)N, (int)H, (int)W, (int)C, (int)ph, (int)pw);
+    else patchify_hwcn_kernel<1><<<grid, 256, sm, st>>>(images, o, (int)N, (int)H, (int)W, (int)C, (int)ph, (int)pw);
   } else {
     const int64_t total2 = N * H * W * C / 2;
     int blocks = (int)((total2 + 255) / 256 < 148 * 16 ? (total2 + 255) / 256 : 148 * 16);
@@ -136,9 +189,17 @@ extern "C" int sav_embed_fwd(const void* tok, const float* cls, const float* pos
   if (B <= 0 || n_tok <= 0 || C % 2) return set_error(SAV_ERR_SHAPE, "sav_embed_fwd: bad shape");
   const int64_t total2 = B * (n_tok + has_cls) * C / 2;
   int blocks = (int)((total2 + 255) / 256 < 148 * 16 ? (total2 + 255) / 256 : 148 * 16);
-  embed_fwd_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const bf16*>(tok), cls, pos, reinterpret_cast<float*>(x), B, (int)n_tok,
-      (int)C, has_cls);
+  if (C % 8 == 0 && aligned16(tok) && aligned16(pos) && aligned16(x) && (!has_cls || aligned16(cls))) {
+    const int64_t total8 = B * (n_tok + has_cls) * (C / 8);
+    const int b8 = (int)((total8 + 255) / 256 < 148 * 16 ? (total8 + 255) / 256 : 148 * 16);
+    embed_fwd8_kernel<<<b8, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const bf16*>(tok), cls, pos, reinterpret_cast<float*>(x), B, (int)n_tok,
+        (int)(C / 8), has_cls);
+  } else {
+    embed_fwd_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const bf16*>(tok), cls, pos, reinterpret_cast<float*>(x), B, (int)n_tok,
+        (int)C, has_cls);
+  }
   count_launch();
   return check_launch("sav_embed_fwd");
 }

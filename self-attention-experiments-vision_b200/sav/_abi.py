@@ -28,6 +28,7 @@ class GemmArgs(C.Structure):
         ("col_scale", C.c_void_p), ("row_scale", C.c_void_p), ("rows_per_scale", C.c_int64),
         ("residual", C.c_void_p), ("ldr", C.c_int64),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_int64),
+        ("dgelu_colsum", C.c_void_p),
     ]
 
 

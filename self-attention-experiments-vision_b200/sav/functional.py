@@ -47,6 +47,9 @@ class Weight:
 # separate 14.4 us column-sum pass (profiles/r02d_membound.log; 13.29 -> 13.18 ms per DeiT-S step).
 # SAV_FUSE_BIAS_COLSUM=0 restores the separate pass (A/B switch).
 _FUSE_BIAS_COLSUM = os.environ.get("SAV_FUSE_BIAS_COLSUM", "1") == "1"
+# The FC1 bias gradient (column sums of dH * gelu') is accumulated by the FC2-dX GEMM's epilogue
+# (sav_gemm dgelu_colsum).  SAV_FUSE_DGELU_COLSUM=0 restores the separate column-sum pass (A/B).
+_FUSE_DGELU_COLSUM = os.environ.get("SAV_FUSE_DGELU_COLSUM", "1") == "1"
 
 
 def _grad16(var):
@@ -185,9 +188,20 @@ class LazyLinear(Var):
                                 self.col_scale.master, self.col_scale.grad)
         if x.requires_grad:
             # dX[M,K] = dY W^T (x gelu'(pre) when x is a fused-GELU output)
-            dx = ops.gemm(dy2, W.w, b_mn=False, aux_in=x.pre_act)
+            # When x is a fused-GELU Dense output, this GEMM's result IS that Dense's dY (the gradient
+            # of its pre-activation), so its bias gradient -- the column sums of the result -- is
+            # accumulated by the same epilogue (a 16-shuffle transpose-reduce per slab) instead of a
+            # separate 33 us pass over the 155 MB tensor.
+            fuse_bias = (_FUSE_DGELU_COLSUM and x.pre_act is not None and isinstance(x, LazyLinear)
+                         and x.g is None and x.bias is not None and x.col_scale is None and x.row_scale is None)
+            if fuse_bias:
+                x.bias.touch_grad()
+            dx = ops.gemm(dy2, W.w, b_mn=False, aux_in=x.pre_act,
+                          dgelu_colsum=x.bias.grad if fuse_bias else None)
             _add_grad(x, dx.view(x.v.shape) if x.v.is_contiguous() or dx.numel() == x.v.numel() else dx)
             x.g_is_pre = x.pre_act is not None
+            if fuse_bias:
+                x.bias_grad_from = dx
 
 
 def _add_grad(var, g):

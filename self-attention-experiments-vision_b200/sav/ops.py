@@ -43,7 +43,7 @@ def _workspace(nbytes, device, tag="gemm"):
 
 def gemm(A, B, *, a_mn=False, b_mn=False, out=None, out_fp32=False, bias=None, act=0,
          aux_out=None, aux_in=None, col_scale=None, row_scale=None, rows_per_scale=1,
-         residual=None, accumulate=False, split_k=1):
+         residual=None, accumulate=False, split_k=1, dgelu_colsum=None):
     """D[M,N] = epi(sum_k A[m,k] B[n,k]).  A: [M,K] (or [K,M] if a_mn); B: [N,K] (or [K,N] if b_mn).
 
     2-D bf16 tensors with unit inner stride; row strides are taken from the tensors, so column
@@ -81,6 +81,10 @@ def gemm(A, B, *, a_mn=False, b_mn=False, out=None, out_fp32=False, bias=None, a
         _req(residual, F32, "residual")
         assert residual.shape == (M, N) and residual.stride(1) == 1
         a.residual, a.ldr = residual.data_ptr(), residual.stride(0)
+    if dgelu_colsum is not None:
+        _req(dgelu_colsum, F32, "dgelu_colsum")
+        assert aux_in is not None and dgelu_colsum.numel() == N and dgelu_colsum.is_contiguous()
+        a.dgelu_colsum = dgelu_colsum.data_ptr()
     check(lib().sav_gemm(C.byref(a), _stream()))
     return out
 

@@ -112,8 +112,10 @@ def case_gemm_time(M=50432, N=1536, K=384, mode="gelu2", a_mn=False, b_mn=True, 
                   aux_out=torch.empty(M, N, device=dev, dtype=torch.bfloat16)); byt += 4 * M * N
     elif mode == "plain":
         byt += 2 * M * N
-    elif mode == "dgelu":
+    elif mode in ("dgelu", "dgelu_cs"):
         kw = dict(aux_in=torch.randn(M, N, device=dev).bfloat16()); byt += 4 * M * N
+        if mode == "dgelu_cs":     # + the bias column sums accumulated by the epilogue
+            kw["dgelu_colsum"] = torch.zeros(N, device=dev)
     elif mode == "resid":
         kw = dict(bias=torch.randn(N, device=dev), residual=torch.randn(M, N, device=dev),
                   out_fp32=True); byt += 8 * M * N
@@ -285,6 +287,7 @@ TIMING = {
     "t_fc1_fwd": dict(N=1536, K=384, mode="gelu2"),
     "t_fc2_fwd": dict(N=384, K=1536, mode="resid"),
     "t_fc2_dx": dict(N=1536, K=384, mode="dgelu", b_mn=False),
+    "t_fc2_dx_cs": dict(N=1536, K=384, mode="dgelu_cs", b_mn=False),
     "t_fc1_dx": dict(N=384, K=1536, mode="plain", b_mn=False),
     "t_qkv_dx": dict(N=384, K=1152, mode="plain", b_mn=False),
     "t_fc1_dw": dict(M=384, N=1536, K=50432, mode="dw", a_mn=True),

@@ -68,3 +68,35 @@ def test_colsum_rejects_small_workspace():
                                 ctypes.c_void_p(ws.data_ptr()), 16,
                                 ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
     assert rc != 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N,K", [(1576, 768, 192), (50432, 1536, 384), (300, 1000, 64), (129, 136, 128)])
+def test_dgelu_gemm_epilogue_accumulates_the_bias_gradient(M, N, K):
+    """sav_gemm aux_in mode with dgelu_colsum: D = bf16(acc * gelu'(pre)) AND dgelu_colsum[n] +=
+    sum_m acc * gelu'(pre) -- the FC1 bias gradient accumulated by the FC2-dX GEMM's epilogue
+    (reverse mode of ff.py:24-25), against an fp64 restatement on the same bf16 operands; partial
+    M / N tiles and 1-CTA / CTA-pair tile shapes are covered by the shapes."""
+    from sav import ops
+    g = torch.Generator().manual_seed(M + N + K)
+    dy = (torch.randn((M, K), generator=g) * 0.5).bfloat16()
+    w = (torch.randn((N, K), generator=g) / K ** 0.5).bfloat16()       # b_mn=False: [N, K]
+    pre = torch.randn((M, N), generator=g).bfloat16()
+    acc = dy.double() @ w.double().t()
+    x = pre.double()
+    u = 0.7978845608028654 * (x + 0.044715 * x ** 3)
+    t = torch.tanh(u)
+    dg = 0.5 * (1 + t) + 0.5 * x * (1 - t * t) * 0.7978845608028654 * (1 + 3 * 0.044715 * x * x)
+    ref = acc * dg
+    base = torch.randn((N,), generator=g)
+    colsum = base.clone().cuda()
+    out = ops.gemm(dy.cuda(), w.cuda(), b_mn=False, aux_in=pre.cuda(), dgelu_colsum=colsum)
+    plain = ops.gemm(dy.cuda(), w.cuda(), b_mn=False, aux_in=pre.cuda())
+    torch.cuda.synchronize()
+    assert torch.equal(out, plain)                       # the output itself is untouched
+    assert float((out.double().cpu() - ref).abs().max() / ref.abs().max()) <= 1e-2
+    want = ref.sum(0) + base.double()
+    mag = ref.abs().sum(0)
+    err = (colsum.double().cpu() - want).abs()
+    # fp32 sums of fp32 products (tanh.approx inside gelu': 2^-11 relative per term)
+    assert bool((err <= 2e-3 * mag / (M ** 0.5) + 1e-3 * mag + 1e-5).all()), float((err / (mag + 1e-6)).max())

@@ -8,4 +8,13 @@ for c in t_attn_bwd:attn_bwd3 t_attn_fwd:attn_fwd2 t_fc1_fwd:gemm_kernel t_qkv_f
   SAV_TIME_ONLY=$case timeout 120 python tests/gpu_diag.py --time > gpurun_out/${T}_plain_${case}.log 2>&1 &&
   SAV_TIME_ONLY=$case timeout 300 ncu --metrics $M --clock-control none -k regex:$k --launch-skip 3 -c 1 --csv --log-file gpurun_out/${T}_ncu_${case}.csv python tests/gpu_diag.py --time > gpurun_out/${T}_ncu_${case}.log 2>&1
 done
+timeout 120 python tests/tools/ln_once.py > gpurun_out/${T}_plain_ln.log 2>&1 &&
+for k in ln_bwd_pieces ln_fwd_pieces; do
+  timeout 300 ncu --metrics $M --clock-control none -k regex:$k --launch-skip 3 -c 1 --csv --log-file gpurun_out/${T}_ncu_${k}.csv python tests/tools/ln_once.py > gpurun_out/${T}_ncu_${k}.log 2>&1
+done
+# every launch of one bench step with its device time (shares of the step)
+timeout 200 python bench.py --steps 2 --warmup 1 --no-graph --no-cpu-baseline > gpurun_out/${T}_plain_bench_nograph.log 2>&1 &&
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/${T}_launches_bench_nograph.csv python bench.py --steps 2 --warmup 1 --no-graph --no-cpu-baseline > gpurun_out/${T}_ncu_list.log 2>&1
+# one full-set capture of the attention backward, with source correlation
+SAV_TIME_ONLY=t_attn_bwd timeout 300 ncu --set full --clock-control none --import-source on -k regex:attn_bwd3 --launch-skip 3 -c 1 -f -o gpurun_out/${T}_attn_bwd3_full python tests/gpu_diag.py --time > gpurun_out/${T}_ncu_full.log 2>&1
 ls gpurun_out | grep ${T}_ncu
