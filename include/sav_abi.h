@@ -85,7 +85,22 @@ typedef struct {
   float* dgelu_colsum;     /* aux_in mode only: fp32 [N], += column sums of acc * gelu'(aux_in) -- the
                             * bias gradient of the Dense that produced aux_in (reverse of ff.py:24),
                             * accumulated by the epilogue instead of a separate pass; or NULL */
+  /* Fused LayerNorm (vit.py:19,26 applied to the stream this GEMM produces; fp32 D + residual mode,
+   * no scales, sav_gemm_ln_tiles(N) != 0): besides D the epilogue writes ln_out = bf16(LayerNorm(D))
+   * with flax statistics (var = E[x^2] - E[x]^2, eps) and saves mean / rstd fp32 [M] for the
+   * reverse mode -- the rows never make a second trip through HBM.  ln_out NULL = off. */
+  void* ln_out;            /* bf16 [M,N] ld=ldy */
+  int64_t ldy;
+  const float* ln_gamma;   /* [N] */
+  const float* ln_beta;    /* [N] */
+  float* ln_mean;          /* [M] */
+  float* ln_rstd;          /* [M] */
+  float ln_eps;
+  int32_t reserved;
 } sav_gemm_args;
+/* 1 or 2 when a LayerNorm over N columns can be fused into sav_gemm's fp32-stream epilogue (the row
+ * fits the two TMEM accumulators at the tile width chosen for N: N = 128, 192, 256, 384, 512), else 0 */
+int32_t sav_gemm_ln_tiles(int64_t N);
 int64_t sav_gemm_workspace_bytes(const sav_gemm_args* a);
 int sav_gemm(const sav_gemm_args* a, void* stream);
 

@@ -46,6 +46,14 @@ struct GemmParams {
   const float* row_scale;
   int64_t rows_per_scale;
   float* colsum;    // EPI_DGELU only: column sums of the (fp32) result accumulated here, or null
+  // LayerNorm fused into the fp32-stream epilogue (EPI_F32 + residual): ln_tiles = N / BN (1 or 2)
+  // N-tiles make a complete row and are processed back to back by the same CTA (pair); 0 = off
+  int ln_tiles;
+  const float* ln_gamma;
+  const float* ln_beta;
+  float* ln_mean;
+  float* ln_rstd;
+  float ln_eps;
   int batch_inner;  // batched (BATCH=true) only: size of the inner batch dim (heads)
   int nbatch;       // total batches (1 when not batched)
   long long* dbg;   // development only: timeline buffer (tests/tools/gemm_timeline.py) or null
@@ -208,12 +216,16 @@ template <int BN, bool A_MN, bool B_MN, int CTAS, bool BATCH>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
             const __grid_constant__ CUtensorMap tma_d, const __grid_constant__ CUtensorMap tma_x,
-            const GemmParams p) {
+            const __grid_constant__ CUtensorMap tma_y, const GemmParams p) {
   using Cfg = GemmCfg<BN, B_MN, CTAS>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;   // SW128 tiles need a 1024-byte aligned base (checked below)
   uint8_t* smem_out = smem + Cfg::kStages * Cfg::kStageBytes;  // 1024-aligned (stage bytes % 1024 == 0)
   float* s_colsum = reinterpret_cast<float*>(smem_out + kOutBytes + 256);   // [2][BN]
+  // LayerNorm mode: the slab ring runs with three slots and the fourth holds the per-row partial
+  // statistics, [4 column parts][128 rows][sum, sum of squares] -- plain stores combined in a fixed
+  // order, so the normalised output is reproducible run to run (no floating-point atomics)
+  float* s_stats = reinterpret_cast<float*>(smem_out + 3 * SLAB_BYTES);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + kOutBytes);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
@@ -232,6 +244,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     tma_prefetch_desc(&tma_b);
     tma_prefetch_desc(&tma_d);
     if (p.epi == EPI_GELU2 || p.has_aux_in) tma_prefetch_desc(&tma_x);
+    if (p.ln_tiles) tma_prefetch_desc(&tma_y);
     for (int s = 0; s < Cfg::kStages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -262,6 +275,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   const int tiles_mn = p.m_blocks * p.n_blocks;
   const int tiles_per_batch = tiles_mn * p.split_k;
   const int num_tiles = tiles_per_batch * (BATCH ? p.nbatch : 1);
+  // Local tile sequence of this CTA (pair).  Normally tiles unit, unit + units, ...; with the fused
+  // LayerNorm the ln_tiles N-tiles of a row block are consecutive on the same CTA (pair), so that
+  // the epilogue sees complete rows.
+  const int lt = p.ln_tiles;
+  const int my_tiles_all = lt ? lt * max(0, (p.m_blocks - unit + units - 1) / units)
+                              : (num_tiles - unit + units - 1) / units;
+  auto tile_at = [&](int itl) { return lt ? (unit + (itl / lt) * units) * lt + (itl % lt) : unit + itl * units; };
 
   if (warp == 0) {
     // TMA producer: whole warp walks the loop, one elected lane issues (see the MMA warp)
@@ -271,7 +291,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       int stage = 0;
       uint32_t phase = 0;
       int dbg_n = 0;
-      for (int tile = unit; tile < num_tiles; tile += units) {
+      for (int itl = 0; itl < my_tiles_all; ++itl) {
+        const int tile = tile_at(itl);
         GEMM_STAMP(0, 1);
         const int z = BATCH ? tile / tiles_per_batch : 0;
         const int zi = BATCH ? z % p.batch_inner : 0, zo = BATCH ? z / p.batch_inner : 0;
@@ -335,7 +356,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       uint32_t phase = 0;
       int it = 0;
       int dbg_n = 0;
-      for (int tile = unit; tile < num_tiles; tile += units, ++it) {
+      for (; it < my_tiles_all; ++it) {
+        const int tile = tile_at(it);
         GEMM_STAMP(1, 10);
         const int split = (tile % tiles_per_batch) / tiles_mn;
         const int kb0 = split * p.k_per_split;
@@ -409,11 +431,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     const int SC = f32 ? 32 : 64;             // accumulator columns per slab
     const int slabs_per_tile = BN / SC;
     const bool two_out = (p.epi == EPI_GELU2);
-    const int nslot = two_out ? 2 : 4;
+    const int nslot = two_out ? 2 : (lt ? 3 : 4);
     const int slot_bytes = two_out ? 2 * SLAB_BYTES : SLAB_BYTES;
     const bool aux_in = p.has_aux_in != 0;
-    const int my_tiles = (num_tiles - unit + units - 1) / units;
-    const uint32_t total_slabs = (uint32_t)my_tiles * slabs_per_tile;
+    const int my_tiles = my_tiles_all;
+    // LayerNorm mode: per row block, ln_tiles * BN/32 fp32 slabs (the stream) then ln_tiles * BN/64
+    // bf16 slabs (the normalised operand)
+    constexpr int S32 = BN / 32, S64 = BN / 64;
+    const uint32_t total_slabs = lt ? (uint32_t)(my_tiles / lt) * (uint32_t)(lt * (S32 + S64))
+                                    : (uint32_t)my_tiles * slabs_per_tile;
     constexpr int kSlabBarThreads = kEpiThreads + 32;
 
     if (warp == kStoreWarp) {
@@ -421,7 +447,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
 #define STAMP_LANE (lane == 0)
       int dbg_n = 0;
       // global coordinates of slab sg of this CTA
+      // LayerNorm mode: slab sg of this CTA -> (row block, is it a bf16 slab of the normalised output,
+      // first column)
+      constexpr int kLnPer32 = BN / 32, kLnPer64 = BN / 64;
+      auto ln_slab = [&](uint32_t sg, bool& is_y, int& c0, int& row) {
+        const int per = lt * (kLnPer32 + kLnPer64);
+        const int kb = (int)(sg / per), pos = (int)(sg % per);
+        row = (unit + kb * units) * (BM * CTAS) + rank * BM;
+        if (pos < lt * kLnPer32) { is_y = false; c0 = (pos / kLnPer32) * BN + (pos % kLnPer32) * 32; }
+        else { const int q = pos - lt * kLnPer32; is_y = true; c0 = (q / kLnPer64) * BN + (q % kLnPer64) * 64; }
+      };
       auto slab_coords = [&](uint32_t sg, int& c0, int& row, int& zi, int& zo) {
+        if (lt) { bool is_y; ln_slab(sg, is_y, c0, row); zi = zo = 0; return; }
         const int tile = unit + (int)(sg / slabs_per_tile) * units;
         const int mn = tile % tiles_mn;
         c0 = (mn % p.n_blocks) * BN + (int)(sg % slabs_per_tile) * SC;
@@ -439,7 +476,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       };
       // hand the slot of slab t back: either directly, or by loading the next input into it
       auto recycle = [&](uint32_t t) {
-        if (aux_in) {
+        if (lt) {
+          // mixed ring: the fp32 stream slabs take an input (the residual), the bf16 slabs do not;
+          // every slot hand-over is signalled on slot_free, inputs additionally on aux_bar
+          if (t + nslot < total_slabs) {
+            bool is_y; int c0, row;
+            ln_slab(t + nslot, is_y, c0, row);
+            if (!is_y) issue_aux(t + nslot);
+          }
+          mbar_arrive(&slot_free[t % nslot]);
+        } else if (aux_in) {
           if (t + nslot < total_slabs) issue_aux(t + nslot);
         } else {
           mbar_arrive(&slot_free[t % nslot]);
@@ -449,7 +495,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         for (uint32_t sg = 0; sg < (uint32_t)nslot && sg < total_slabs; ++sg) issue_aux(sg);
       __syncwarp();
       // stores allowed to be still reading when the next one is issued
-      const uint32_t lag = nslot == 4 ? 1 : 0;
+      const uint32_t lag = nslot >= 3 ? 1 : 0;
       for (uint32_t sg = 0; sg < total_slabs; ++sg) {
         const int slot = sg % nslot;
         named_bar_sync(1 + slot, kSlabBarThreads);
@@ -458,7 +504,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           int c0, row, zi, zo;
           slab_coords(sg, c0, row, zi, zo);
           uint8_t* slab = smem_out + slot * slot_bytes;
-          if (p.epi == EPI_ACCUM) {
+          if (lt) {
+            bool is_y; int c0y, rowy;
+            ln_slab(sg, is_y, c0y, rowy);
+            tma_store_2d(is_y ? &tma_y : &tma_d, slab, c0, row);
+          } else if (p.epi == EPI_ACCUM) {
             tma_reduce_add_2d(&tma_d, slab, c0, row);
           } else if (GEMM_DBG(16)) {   // development: no global stores
           } else if (two_out) {
@@ -536,6 +586,111 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           bias_pre[q] = __ldg(reinterpret_cast<const float4*>(p.bias + col_n + 4 * q));
       }
     };
+    if (lt) {
+      // ------------------------------------------------------------------ fused LayerNorm
+      // x_new = acc + bias + residual goes out as the fp32 stream (as in EPI_F32) AND stays in TMEM
+      // (written back over the accumulator); row sums are per-thread (thread = row) over this
+      // warp's column quarter and are combined across the four warps of a sub-partition in shared
+      // memory.  Second pass: the normalised bf16 operand (vit.py:19,26) straight out of TMEM.
+      const uint32_t lane_off = (uint32_t)(sub * 32) << 16;
+      const int nblk = my_tiles / lt;
+      int slot = -1;
+      uint32_t slot_phase = 1, aux_par = 0;
+      auto next_slot = [&]() { if (++slot == nslot) { slot = 0; slot_phase ^= 1; } };
+      for (int kb = 0; kb < nblk; ++kb) {
+        const int m_idx = (unit + kb * units) * (BM * CTAS) + rank * BM;
+        float rsum = 0.f, rsq = 0.f;
+        for (int n = 0; n < lt; ++n) {
+          const int itn = kb * lt + n, acc = itn & 1;
+          mbar_wait(&tfull_bar[acc], (itn >> 1) & 1);
+          tc_fence_after();
+          for (int j = 0; j < S32; ++j) {
+            next_slot();
+            uint8_t* slab = smem_out + slot * SLAB_BYTES;
+            const uint32_t taddr = tmem_base + lane_off + acc * BN + j * 32 + part * CF;
+            const int col = n * BN + j * 32 + part * CF;
+            mbar_wait(&slot_free[slot], slot_phase);
+            uint32_t rr[CF];
+            tmem_ld8(taddr, rr);
+            tmem_ld_wait();
+            float v[CF];
+#pragma unroll
+            for (int i = 0; i < CF; ++i) v[i] = __uint_as_float(rr[i]);
+            epi_affine<CF>(p, v, col, 1.f);
+            mbar_wait(&aux_bar[slot], (aux_par >> slot) & 1u);
+            aux_par ^= 1u << slot;
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+              const float4 a = *reinterpret_cast<const float4*>(slab + slab_off(r, part * 2 + g));
+              v[g * 4] += a.x; v[g * 4 + 1] += a.y; v[g * 4 + 2] += a.z; v[g * 4 + 3] += a.w;
+            }
+#pragma unroll
+            for (int i = 0; i < CF; ++i) { rsum += v[i]; rsq += v[i] * v[i]; rr[i] = __float_as_uint(v[i]); }
+            tmem_st8(taddr, rr);
+#pragma unroll
+            for (int g = 0; g < 2; ++g)
+              *reinterpret_cast<float4*>(slab + slab_off(r, part * 2 + g)) =
+                  make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+            fence_proxy_async_smem();
+            named_bar_arrive(1 + slot, kSlabBarThreads);
+          }
+        }
+        tmem_st_wait();
+        // Single-buffered: a thread reaches this store for row block kb+1 only after its first
+        // pass has cycled through every ring slot, i.e. after the store warp has shipped the last
+        // second-pass slab of block kb -- which needs every epilogue thread's arrival, made after
+        // that thread read the statistics of block kb.
+        *reinterpret_cast<float2*>(s_stats + 2 * (part * BM + r)) = make_float2(rsum, rsq);
+        tc_fence_before();
+        named_bar_sync(6, kEpiThreads);
+        tc_fence_after();
+        float tot = 0.f, tot2 = 0.f;
+#pragma unroll
+        for (int q = 0; q < kColParts; ++q) {
+          const float2 s2 = *reinterpret_cast<const float2*>(s_stats + 2 * (q * BM + r));
+          tot += s2.x; tot2 += s2.y;
+        }
+        const float inv_n = 1.f / (float)p.N;
+        const float mean = tot * inv_n;
+        const float rstd = rsqrtf(fmaxf(tot2 * inv_n - mean * mean, 0.f) + p.ln_eps);
+        if (part == 0 && (int64_t)m_idx + r < p.M) {
+          p.ln_mean[m_idx + r] = mean;
+          p.ln_rstd[m_idx + r] = rstd;
+        }
+        for (int n = 0; n < lt; ++n) {
+          const int acc = (kb * lt + n) & 1;
+          uint8_t* slab = nullptr;
+          for (int j = 0; j < S32; ++j) {
+            if (!(j & 1)) {
+              next_slot();
+              slab = smem_out + slot * SLAB_BYTES;
+              mbar_wait(&slot_free[slot], slot_phase);
+            }
+            uint32_t rr[CF];
+            tmem_ld8(tmem_base + lane_off + acc * BN + j * 32 + part * CF, rr);
+            tmem_ld_wait();
+            if (j == S32 - 1) release_acc(acc);
+            const int col = n * BN + j * 32 + part * CF;
+            const float4 g0 = __ldg(reinterpret_cast<const float4*>(p.ln_gamma + col));
+            const float4 g1 = __ldg(reinterpret_cast<const float4*>(p.ln_gamma + col + 4));
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.ln_beta + col));
+            const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.ln_beta + col + 4));
+            const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+            const float bt[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            float y[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) y[i] = (__uint_as_float(rr[i]) - mean) * rstd * gm[i] + bt[i];
+            *reinterpret_cast<uint4*>(slab + slab_off(r, (j & 1) * 4 + part)) =
+                make_uint4(pack_bf16(y[0], y[1]), pack_bf16(y[2], y[3]), pack_bf16(y[4], y[5]),
+                           pack_bf16(y[6], y[7]));
+            if (j & 1) {
+              fence_proxy_async_smem();
+              named_bar_arrive(1 + slot, kSlabBarThreads);
+            }
+          }
+        }
+      }
+    } else {
     prefetch_bias(0, 0, tile_col0(0));
     int it = 0, j = -1, slot = -1;
     uint32_t slot_phase = 1;          // parity of the slot ring's current round, inverted
@@ -676,6 +831,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       if (!(GEMM_DBG(32))) fence_proxy_async_smem();
       GEMM_STAMP(2, 25);
       named_bar_arrive(1 + slot, kSlabBarThreads);   // never blocks: the store warp does the waiting
+    }
     }
     }
   }
@@ -884,7 +1040,8 @@ static int plan_split(const sav_gemm_args* a, int bn, int bm) {
 
 template <int BN, bool A_MN, bool B_MN, int CTAS, bool BATCH = false>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
-                       const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
+                       const CUtensorMap& tx, const CUtensorMap& ty, const GemmParams& p,
+                       cudaStream_t st) {
   using Cfg = GemmCfg<BN, B_MN, CTAS>;
   auto kern = gemm_kernel<BN, A_MN, B_MN, CTAS, BATCH>;
   static bool attr_set = false;  // benign race: idempotent
@@ -894,7 +1051,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
     if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "gemm smem attr: %s", cudaGetErrorString(e));
     attr_set = true;
   }
-  const int tiles = p.m_blocks * p.n_blocks * p.split_k * (BATCH ? p.nbatch : 1);
+  // (fused LayerNorm: a work unit is a whole row block = ln_tiles N-tiles)
+  const int tiles = p.ln_tiles ? p.m_blocks : p.m_blocks * p.n_blocks * p.split_k * (BATCH ? p.nbatch : 1);
   const int units = num_sms() / CTAS;
   const int grid = (tiles < units ? tiles : units) * CTAS;
   cudaLaunchConfig_t cfg = {};
@@ -909,7 +1067,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, td, tx, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, td, tx, ty, p);
   if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "sav_gemm launch: %s", cudaGetErrorString(e));
   count_launch();
   return check_launch("sav_gemm");
@@ -927,6 +1085,16 @@ static int pick_ctas(int64_t M) {
 }  // namespace sav
 
 using namespace sav;
+
+// N-tiles per row when the LayerNorm that follows can be fused into the fp32-stream epilogue: the
+// row must be complete within two accumulators of the tile width sav_gemm picks for this N.
+extern "C" int32_t sav_gemm_ln_tiles(int64_t N) {
+  if (N <= 0 || N % 64) return 0;
+  const int bn = pick_bn(N);
+  if (N == bn) return 1;
+  if (N == 2 * bn) return 2;
+  return 0;
+}
 
 extern "C" int64_t sav_gemm_workspace_bytes(const sav_gemm_args* a) {
   (void)a;
@@ -976,6 +1144,20 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
   p.colsum = a->dgelu_colsum;
   if (p.colsum && p.epi != EPI_DGELU)
     return set_error(SAV_ERR_ARG, "sav_gemm: dgelu_colsum needs the aux_in (dGELU) epilogue");
+  p.ln_tiles = 0;
+  p.ln_gamma = p.ln_beta = nullptr; p.ln_mean = p.ln_rstd = nullptr; p.ln_eps = 0.f;
+  if (a->ln_out) {
+    const int ltl = sav_gemm_ln_tiles(a->N);
+    if (!ltl || p.epi != EPI_F32 || !a->residual || a->col_scale || a->row_scale || split > 1)
+      return set_error(SAV_ERR_ARG, "sav_gemm: fused LayerNorm needs the fp32 residual epilogue without "
+                                    "scales and N = 1 or 2 tiles (sav_gemm_ln_tiles)");
+    if (!a->ln_gamma || !a->ln_beta || !a->ln_mean || !a->ln_rstd || a->ldy % 8 || !aligned16(a->ln_out) ||
+        !aligned16(a->ln_gamma) || !aligned16(a->ln_beta))
+      return set_error(SAV_ERR_ARG, "sav_gemm: fused LayerNorm needs gamma, beta, mean, rstd, ldy %% 8");
+    p.ln_tiles = ltl;
+    p.ln_gamma = a->ln_gamma; p.ln_beta = a->ln_beta; p.ln_mean = a->ln_mean; p.ln_rstd = a->ln_rstd;
+    p.ln_eps = a->ln_eps;
+  }
   {
     static const int dbg = dev_env("SAV_GEMM_DEBUG");
     p.debug = dbg;
@@ -1004,6 +1186,8 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
   else if (a->aux_in) rc = make_tmap_2d(&tx, a->aux_in, 2, a->N, a->M, a->ldd, 64, BM);
   else if (a->residual) rc = make_tmap_2d(&tx, a->residual, 4, a->N, a->M, a->ldr, 32, BM);
   if (rc) return rc;
+  CUtensorMap ty = td;
+  if (p.ln_tiles && (rc = make_tmap_2d(&ty, a->ln_out, 2, a->N, a->M, a->ldy, 64, BM))) return rc;
 
   if (split > 1 && !a->accumulate) {  // reduce-add target must start from zero
     const int64_t total = a->M * a->N;
@@ -1013,8 +1197,8 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
   }
 #define SAV_GEMM_CASE(BNv, AM, BMj)                                                  \
   if (bn == BNv && (a->a_mn != 0) == AM && (a->b_mn != 0) == BMj)                     \
-    rc = ctas == 2 ? launch_gemm<BNv, AM, BMj, 2>(ta, tb, td, tx, p, st)              \
-                   : launch_gemm<BNv, AM, BMj, 1>(ta, tb, td, tx, p, st);
+    rc = ctas == 2 ? launch_gemm<BNv, AM, BMj, 2>(ta, tb, td, tx, ty, p, st)          \
+                   : launch_gemm<BNv, AM, BMj, 1>(ta, tb, td, tx, ty, p, st);
   rc = SAV_ERR_ARG;
   SAV_GEMM_CASE(128, false, false) SAV_GEMM_CASE(128, false, true)
   SAV_GEMM_CASE(128, true, false)  SAV_GEMM_CASE(128, true, true)
@@ -1068,7 +1252,7 @@ extern "C" int sav_bgemm(const sav_bgemm_args* a, void* stream) {
   if ((rc = make_tmap_nd(&td, a->D, es, 4, dims, str, box))) return rc;
 #define SAV_BGEMM_CASE(BNv, AM, BMj)                                  \
   if (bn == BNv && (a->a_mn != 0) == AM && (a->b_mn != 0) == BMj)     \
-    rc = launch_gemm<BNv, AM, BMj, 1, true>(ta, tb, td, td, p, st);
+    rc = launch_gemm<BNv, AM, BMj, 1, true>(ta, tb, td, td, td, p, st);
   rc = SAV_ERR_ARG;
   SAV_BGEMM_CASE(64, false, false) SAV_BGEMM_CASE(64, false, true)
   SAV_BGEMM_CASE(64, true, false)  SAV_BGEMM_CASE(64, true, true)

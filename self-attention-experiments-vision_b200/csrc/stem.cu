@@ -25,12 +25,27 @@ patchify_hwcn_kernel(const float* __restrict__ img, bf16* __restrict__ out, int 
   const int n0 = blockIdx.y * 32;
   const int F = pw * C;                          // contiguous (w-in-patch, c) run of one image row
   const int FT = PY * F;
-  for (int i = threadIdx.x; i < FT * 32; i += blockDim.x) {
-    const int ft = i >> 5, n = i & 31;
-    const int r = ft / F, f = ft - r * F;
-    const int h = gy * ph + py0 + r;
-    const int64_t in = (((int64_t)h * W + (int64_t)gx * pw) * C + f) * N + n0 + n;
-    tile[ft * 33 + n] = (n0 + n < N) ? img[in] : 0.f;
+  if ((N & 3) == 0) {
+    // 16-byte loads along N, several per thread in flight (the loop is latency-bound otherwise)
+#pragma unroll 6
+    for (int i = threadIdx.x; i < FT * 8; i += blockDim.x) {
+      const int ft = i >> 3, n = (i & 7) * 4;
+      const int r = ft / F, f = ft - r * F;
+      const int h = gy * ph + py0 + r;
+      const int64_t in = (((int64_t)h * W + (int64_t)gx * pw) * C + f) * N + n0 + n;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (n0 + n < N) v = __ldcs(reinterpret_cast<const float4*>(img + in));
+      float* t = tile + ft * 33 + n;
+      t[0] = v.x; t[1] = v.y; t[2] = v.z; t[3] = v.w;
+    }
+  } else {
+    for (int i = threadIdx.x; i < FT * 32; i += blockDim.x) {
+      const int ft = i >> 5, n = i & 31;
+      const int r = ft / F, f = ft - r * F;
+      const int h = gy * ph + py0 + r;
+      const int64_t in = (((int64_t)h * W + (int64_t)gx * pw) * C + f) * N + n0 + n;
+      tile[ft * 33 + n] = (n0 + n < N) ? img[in] : 0.f;
+    }
   }
   __syncthreads();
   const int K = ph * F;

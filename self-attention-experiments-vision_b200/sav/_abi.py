@@ -29,6 +29,8 @@ class GemmArgs(C.Structure):
         ("residual", C.c_void_p), ("ldr", C.c_int64),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_int64),
         ("dgelu_colsum", C.c_void_p),
+        ("ln_out", C.c_void_p), ("ldy", C.c_int64), ("ln_gamma", C.c_void_p), ("ln_beta", C.c_void_p),
+        ("ln_mean", C.c_void_p), ("ln_rstd", C.c_void_p), ("ln_eps", C.c_float), ("reserved", C.c_int32),
     ]
 
 
@@ -103,6 +105,7 @@ SIGNATURES = {
     "sav_last_error": (C.c_char_p, []),
     "sav_device_check": (C.c_int, []),
     "sav_launch_count": (C.c_int64, []),
+    "sav_gemm_ln_tiles": (C.c_int32, [_I64]),
     "sav_gemm_workspace_bytes": (C.c_int64, [C.POINTER(GemmArgs)]),
     "sav_gemm": (C.c_int, [C.POINTER(GemmArgs), _P]),
     "sav_bgemm": (C.c_int, [C.POINTER(BGemmArgs), _P]),

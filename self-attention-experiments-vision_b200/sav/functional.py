@@ -20,7 +20,7 @@ import os
 import torch
 
 from . import ops
-from .tape import Var, record
+from .tape import Var, current_tape, record
 
 BF16 = torch.bfloat16
 F32 = torch.float32
@@ -50,6 +50,10 @@ _FUSE_BIAS_COLSUM = os.environ.get("SAV_FUSE_BIAS_COLSUM", "1") == "1"
 # The FC1 bias gradient (column sums of dH * gelu') is accumulated by the FC2-dX GEMM's epilogue
 # (sav_gemm dgelu_colsum).  SAV_FUSE_DGELU_COLSUM=0 restores the separate column-sum pass (A/B).
 _FUSE_DGELU_COLSUM = os.environ.get("SAV_FUSE_DGELU_COLSUM", "1") == "1"
+# LayerNorm of the stream (vit.py:19,26) computed by the epilogue of the GEMM that writes the stream
+# (out-projection / FC2 with bias + residual): the residual-fused Dense stays pending after `x + f(x)`
+# and the LayerNorm that reads it first runs both in one launch.
+_FUSE_LN_GEMM = os.environ.get("SAV_FUSE_LN_GEMM", "1") == "1"
 
 
 def _grad16(var):
@@ -110,7 +114,14 @@ class LazyLinear(Var):
             self._materialize()
         return self._v
 
-    def _materialize(self):
+    def ln_fusable(self):
+        """The pending stream-producing Dense can take the following LayerNorm into its epilogue."""
+        if not _FUSE_LN_GEMM or self._done or self.residual is None or self.act or \
+                self.col_scale is not None or self.row_scale is not None:
+            return False
+        return not _meta(self.weight.w) and ops.gemm_ln_tiles(self.weight.w.shape[1]) != 0
+
+    def _materialize(self, ln=None):
         self._done = True
         x, W = self.x, self.weight
         xin = x.v
@@ -132,14 +143,15 @@ class LazyLinear(Var):
             if res.dtype != F32:
                 raise TypeError("residual add: the skip input must be the fp32 residual stream")
             res = res.reshape(M, N)
-        ops.gemm(x2, W.w, b_mn=True, out=out,
-                 bias=self.bias.master if self.bias is not None else None, act=self.act,
-                 aux_out=pre,
-                 col_scale=self.col_scale.master if self.col_scale is not None else None,
-                 row_scale=self.row_scale, rows_per_scale=self.rows_per_scale, residual=res)
+        got = ops.gemm(x2, W.w, b_mn=True, out=out,
+                       bias=self.bias.master if self.bias is not None else None, act=self.act,
+                       aux_out=pre,
+                       col_scale=self.col_scale.master if self.col_scale is not None else None,
+                       row_scale=self.row_scale, rows_per_scale=self.rows_per_scale, residual=res, ln=ln)
         self._v = out.view(self.out_shape)
         self.pre_act = pre
         record(self._backward)
+        return got[1] if ln is not None else None
 
     def _backward(self):
         if self.g is None and self.g16 is None:
@@ -254,7 +266,13 @@ def add(a, b):
         if isinstance(lazy, LazyLinear) and not lazy._done and lazy.residual is None and \
                 lazy.act == 0 and isinstance(other, Var) and tuple(other.shape) == tuple(lazy.shape):
             lazy.residual = other
-            lazy.v  # materialise now so program order is preserved
+            if not lazy.ln_fusable():
+                lazy.v  # materialise now so program order is preserved
+            elif current_tape() is not None:
+                current_tape().defer(lazy)
+            # else: stays pending until its first reader -- a LayerNorm takes it into one launch,
+            # anything else (`.v`) materialises it as before; either way it is recorded on the tape
+            # before that reader
             return lazy
     raise NotImplementedError("standalone add: one side must be a pending Dense output")
 
@@ -293,7 +311,11 @@ class LazyLayerNorm(Var):
 
     def _materialize(self):
         self._done = True
-        x, xv = self.x, self.x.v
+        x = self.x
+        fused = None
+        if isinstance(x, LazyLinear) and x.ln_fusable() and not _meta(x.x.v):
+            fused = x._materialize(ln=(self.scale.master, self.bias.master, self.eps))
+        xv = x.v
         if _meta(xv):
             self._v = torch.empty(xv.shape, dtype=BF16, device="meta")
             return
@@ -301,7 +323,10 @@ class LazyLayerNorm(Var):
         xc = xv.contiguous()
         C = xc.shape[-1]
         x2 = xc.view(-1, C)
-        y, mean, rstd = ops.layernorm_fwd(x2, self.scale.master, self.bias.master, self.eps)
+        if fused is not None:
+            y, mean, rstd = fused
+        else:
+            y, mean, rstd = ops.layernorm_fwd(x2, self.scale.master, self.bias.master, self.eps)
         self._v = y.view(xc.shape)
         scale, bias = self.scale, self.bias
 

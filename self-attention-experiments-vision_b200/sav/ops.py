@@ -43,7 +43,7 @@ def _workspace(nbytes, device, tag="gemm"):
 
 def gemm(A, B, *, a_mn=False, b_mn=False, out=None, out_fp32=False, bias=None, act=0,
          aux_out=None, aux_in=None, col_scale=None, row_scale=None, rows_per_scale=1,
-         residual=None, accumulate=False, split_k=1, dgelu_colsum=None):
+         residual=None, accumulate=False, split_k=1, dgelu_colsum=None, ln=None):
     """D[M,N] = epi(sum_k A[m,k] B[n,k]).  A: [M,K] (or [K,M] if a_mn); B: [N,K] (or [K,N] if b_mn).
 
     2-D bf16 tensors with unit inner stride; row strides are taken from the tensors, so column
@@ -81,12 +81,30 @@ def gemm(A, B, *, a_mn=False, b_mn=False, out=None, out_fp32=False, bias=None, a
         _req(residual, F32, "residual")
         assert residual.shape == (M, N) and residual.stride(1) == 1
         a.residual, a.ldr = residual.data_ptr(), residual.stride(0)
+    ln_res = None
+    if ln is not None:
+        # fused LayerNorm of the fp32 stream this GEMM produces: ln = (gamma, beta, eps)
+        gamma, beta, eps = ln
+        y = torch.empty((M, N), dtype=BF16, device=A.device)
+        mean = torch.empty(M, dtype=F32, device=A.device)
+        rstd = torch.empty(M, dtype=F32, device=A.device)
+        a.ln_out, a.ldy = y.data_ptr(), y.stride(0)
+        a.ln_gamma, a.ln_beta = gamma.data_ptr(), beta.data_ptr()
+        a.ln_mean, a.ln_rstd, a.ln_eps = mean.data_ptr(), rstd.data_ptr(), float(eps)
+        ln_res = (y, mean, rstd)
     if dgelu_colsum is not None:
         _req(dgelu_colsum, F32, "dgelu_colsum")
         assert aux_in is not None and dgelu_colsum.numel() == N and dgelu_colsum.is_contiguous()
         a.dgelu_colsum = dgelu_colsum.data_ptr()
     check(lib().sav_gemm(C.byref(a), _stream()))
+    if ln_res is not None:
+        return out, ln_res
     return out
+
+
+def gemm_ln_tiles(N):
+    """Non-zero when a LayerNorm over N columns can ride in sav_gemm's fp32-stream epilogue."""
+    return int(lib().sav_gemm_ln_tiles(N))
 
 
 _COLSUM_WS = {}

@@ -16,9 +16,21 @@ def current_tape():
 class Tape:
     def __init__(self):
         self.nodes = []
+        self.pending = []
 
     def record(self, fn):
         self.nodes.append(fn)
+
+    def defer(self, var):
+        """A Var whose producing kernel has not been launched yet (it waits for a consumer to fuse
+        with); flush() launches whatever is still pending so that every forward op is on the tape
+        before the backward pass starts."""
+        self.pending.append(var)
+
+    def flush(self):
+        pending, self.pending = self.pending, []
+        for var in pending:
+            var.v
 
     def __enter__(self):
         self._prev = current_tape()
@@ -29,6 +41,7 @@ class Tape:
         _state.tape = self._prev
 
     def backward(self, after_node=None):
+        self.flush()
         nodes, self.nodes = self.nodes, []
         for i, fn in enumerate(reversed(nodes)):
             fn()
@@ -106,6 +119,7 @@ def value_and_grad(fn, has_aux=False, grad_hook=None):
             with Tape() as tape:
                 out = fn(params, *args, **kw)
                 loss = out[0] if has_aux else out
+                tape.flush()
                 loss.seed()
                 tape.backward(grad_hook.after_node if grad_hook is not None else None)
             if grad_hook is not None:

@@ -100,3 +100,38 @@ def test_dgelu_gemm_epilogue_accumulates_the_bias_gradient(M, N, K):
     err = (colsum.double().cpu() - want).abs()
     # fp32 sums of fp32 products (tanh.approx inside gelu': 2^-11 relative per term)
     assert bool((err <= 2e-3 * mag / (M ** 0.5) + 1e-3 * mag + 1e-5).all()), float((err / (mag + 1e-6)).max())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N,K", [(1576, 384, 384), (50432, 384, 1536), (300, 192, 192), (129, 256, 64),
+                                   (5000, 512, 128), (788, 128, 384)])
+def test_gemm_epilogue_with_fused_layernorm(M, N, K):
+    """sav_gemm fp32-stream epilogue (bias + residual, vit.py:24,31) with the LayerNorm that follows
+    fused in (vit.py:19,26): D is unchanged, ln_out = bf16(LayerNorm(D)) with flax statistics
+    (var = E[x^2] - E[x]^2, eps 1e-6), mean / rstd saved -- N = 1 or 2 tiles, 1-CTA and CTA-pair
+    tile shapes, partial M tiles."""
+    from sav import ops
+    assert ops.gemm_ln_tiles(N) in (1, 2) and ops.gemm_ln_tiles(768) == 0
+    g = torch.Generator().manual_seed(M + N + K)
+    a = torch.randn((M, K), generator=g).bfloat16()
+    w = (torch.randn((K, N), generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn((N,), generator=g)
+    res = torch.randn((M, N), generator=g)
+    gamma = 1.0 + 0.1 * torch.randn((N,), generator=g)
+    beta = 0.1 * torch.randn((N,), generator=g)
+    plain = ops.gemm(a.cuda(), w.cuda(), b_mn=True, out_fp32=True, bias=bias.cuda(), residual=res.cuda())
+    out, (y, mean, rstd) = ops.gemm(a.cuda(), w.cuda(), b_mn=True, out_fp32=True, bias=bias.cuda(),
+                                    residual=res.cuda(), ln=(gamma.cuda(), beta.cuda(), 1e-6))
+    torch.cuda.synchronize()
+    assert torch.equal(out, plain)                        # the stream itself is bit-identical
+    for _ in range(3):                                    # fixed-order statistics: reproducible bit for bit
+        out2, (y2, mean2, rstd2) = ops.gemm(a.cuda(), w.cuda(), b_mn=True, out_fp32=True, bias=bias.cuda(),
+                                            residual=res.cuda(), ln=(gamma.cuda(), beta.cuda(), 1e-6))
+        assert torch.equal(y, y2) and torch.equal(mean, mean2) and torch.equal(rstd, rstd2)
+    x = out.double().cpu()
+    mu = x.mean(-1, keepdim=True)
+    var = (x * x).mean(-1, keepdim=True) - mu * mu
+    ref = (x - mu) * torch.rsqrt(var + 1e-6) * gamma.double() + beta.double()
+    assert float((mean.double().cpu() - mu[:, 0]).abs().max()) <= 1e-5
+    assert float((rstd.double().cpu() * torch.sqrt(var[:, 0] + 1e-6) - 1).abs().max()) <= 1e-4
+    assert float((y.double().cpu() - ref).abs().max()) <= 2 ** -8 * float(ref.abs().max()) + 1e-3
