@@ -57,6 +57,11 @@ struct GemmParams {
   int batch_inner;  // batched (BATCH=true) only: size of the inner batch dim (heads)
   int nbatch;       // total batches (1 when not batched)
   long long* dbg;   // development only: timeline buffer (tests/tools/gemm_timeline.py) or null
+  // shared-memory split between the operand pipeline and the epilogue slab ring (the sum is fixed
+  // per tile shape): short-K GEMMs with an epilogue that streams as many bytes as the operands
+  // (FC2 dX with its pre-activation input, FC1 with two outputs, the LayerNorm mode) trade pipeline
+  // stages they do not need for more 16 KB slab slots in flight
+  int stages, nslot;
   int debug;        // development only (SAV_GEMM_DEBUG): 1 = skip TMA loads, 2 = skip MMAs
 };
 
@@ -73,11 +78,16 @@ struct GemmCfg {
   // after the stages and the slab ring: 256 B of barriers, 2 KB of per-tile column-sum accumulators
   // (2 x BN floats, EPI_DGELU with colsum).  The dynamic segment is declared __align__(1024), so
   // no alignment slack is budgeted.
-  static constexpr int kTailBytes = 256 + 2048;
+  static constexpr int kBarBytes = 320;
+  static constexpr int kTailBytes = kBarBytes + 2048;
   static constexpr int kFit = (kSmemBudget - kOutBytes - kTailBytes) / kStageBytes;
   static constexpr int kStages = kFit > 6 ? 6 : kFit;
   static constexpr int kSmem = kStages * kStageBytes + kOutBytes + kTailBytes;
-  static constexpr uint32_t kTmemCols = 512;  // 2 accumulators of BN <= 256 fp32 columns
+  static constexpr uint32_t kTmemCols = 512;  // kAcc accumulators of BN fp32 columns
+  // accumulator ring: 2 x 256 / 2 x 192 / 4 x 128 columns.  Four matter for the fused LayerNorm,
+  // where a row block keeps its N / BN accumulators until the row statistics are known: with
+  // N = 384 = 3 x 128 the fourth lets the next row block's MMAs start under that epilogue.
+  static constexpr int kAcc = BN <= 128 ? 4 : 2;
   static_assert(kStageBytes % 1024 == 0, "stage must keep 1024 B alignment");
   static_assert(kStages >= 3, "too few stages");
 };
@@ -220,19 +230,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   using Cfg = GemmCfg<BN, B_MN, CTAS>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;   // SW128 tiles need a 1024-byte aligned base (checked below)
-  uint8_t* smem_out = smem + Cfg::kStages * Cfg::kStageBytes;  // 1024-aligned (stage bytes % 1024 == 0)
-  float* s_colsum = reinterpret_cast<float*>(smem_out + kOutBytes + 256);   // [2][BN]
-  // LayerNorm mode: the slab ring runs with three slots and the fourth holds the per-row partial
+  const int nst = p.stages;                                    // <= Cfg::kStages
+  uint8_t* smem_out = smem + nst * Cfg::kStageBytes;           // 1024-aligned (stage bytes % 1024 == 0)
+  uint8_t* smem_tail = smem + Cfg::kStages * Cfg::kStageBytes + kOutBytes;
+  float* s_colsum = reinterpret_cast<float*>(smem_tail + Cfg::kBarBytes);   // [2][BN]
+  // LayerNorm mode: the slab ring runs with one slot less and the last holds the per-row partial
   // statistics, [4 column parts][128 rows][sum, sum of squares] -- plain stores combined in a fixed
   // order, so the normalised output is reproducible run to run (no floating-point atomics)
-  float* s_stats = reinterpret_cast<float*>(smem_out + 3 * SLAB_BYTES);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + kOutBytes);
+  float* s_stats = reinterpret_cast<float*>(smem_out + (p.nslot - 1) * SLAB_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_tail);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
-  uint64_t* tempty_bar = tfull_bar + 2;
-  uint64_t* aux_bar = tempty_bar + 2;  // [4]
-  uint64_t* slot_free = aux_bar + 4;  // [4] slab slot has been read by its TMA store
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(slot_free + 4);
+  uint64_t* tempty_bar = tfull_bar + 4;
+  uint64_t* aux_bar = tempty_bar + 4;  // [8]
+  uint64_t* slot_free = aux_bar + 8;  // [8] slab slot has been read by its TMA store
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(slot_free + 8);
+  static_assert((2 * Cfg::kStages + 8 + 16) * 8 + 4 <= Cfg::kBarBytes, "barrier block");
 
   // warp index through a shuffle so that the compiler knows the role branches are warp-uniform
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
@@ -249,11 +262,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < 4; ++s) {
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], kEpiWarps * CTAS);  // one arrival per epilogue warp (both CTAs)
     }
-    for (int s = 0; s < 4; ++s) { mbar_init(&aux_bar[s], 1); mbar_init(&slot_free[s], 1); }
+    for (int s = 0; s < 8; ++s) { mbar_init(&aux_bar[s], 1); mbar_init(&slot_free[s], 1); }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -311,7 +324,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           if (GEMM_DBG(1)) {  // MMA-only rate: operands are whatever the smem holds
             if (rank == 0 && elect_one()) mbar_arrive(&full_bar[stage]);
             __syncwarp();
-            if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+            if (++stage == nst) { stage = 0; phase ^= 1; }
             continue;
           }
           const int k_idx = kb * BK;
@@ -337,7 +350,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           }
           }
           __syncwarp();
-          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+          if (++stage == nst) { stage = 0; phase ^= 1; }
         }
       }
 #undef STAMP_LANE
@@ -362,8 +375,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         const int split = (tile % tiles_per_batch) / tiles_mn;
         const int kb0 = split * p.k_per_split;
         const int kb1 = min(kb0 + p.k_per_split, p.k_blocks);
-        const int acc = it & 1;
-        const uint32_t acc_phase = (it >> 1) & 1;
+        const int acc = it % Cfg::kAcc;
+        const uint32_t acc_phase = (it / Cfg::kAcc) & 1;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         GEMM_STAMP(1, 11);
@@ -403,7 +416,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
             }
           }
           __syncwarp();
-          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+          if (++stage == nst) { stage = 0; phase ^= 1; }
         }
         if (elect_one()) {
           if (CTAS == 2) umma_commit_pair(&tfull_bar[acc]);
@@ -431,7 +444,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     const int SC = f32 ? 32 : 64;             // accumulator columns per slab
     const int slabs_per_tile = BN / SC;
     const bool two_out = (p.epi == EPI_GELU2);
-    const int nslot = two_out ? 2 : (lt ? 3 : 4);
+    const int nslot = two_out ? p.nslot / 2 : (lt ? p.nslot - 1 : p.nslot);
     const int slot_bytes = two_out ? 2 * SLAB_BYTES : SLAB_BYTES;
     const bool aux_in = p.has_aux_in != 0;
     const int my_tiles = my_tiles_all;
@@ -601,8 +614,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         const int m_idx = (unit + kb * units) * (BM * CTAS) + rank * BM;
         float rsum = 0.f, rsq = 0.f;
         for (int n = 0; n < lt; ++n) {
-          const int itn = kb * lt + n, acc = itn & 1;
-          mbar_wait(&tfull_bar[acc], (itn >> 1) & 1);
+          const int itn = kb * lt + n, acc = itn % Cfg::kAcc;
+          mbar_wait(&tfull_bar[acc], (itn / Cfg::kAcc) & 1);
           tc_fence_after();
           for (int j = 0; j < S32; ++j) {
             next_slot();
@@ -642,7 +655,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         // that thread read the statistics of block kb.
         *reinterpret_cast<float2*>(s_stats + 2 * (part * BM + r)) = make_float2(rsum, rsq);
         tc_fence_before();
-        named_bar_sync(6, kEpiThreads);
+        named_bar_sync(10, kEpiThreads);
         tc_fence_after();
         float tot = 0.f, tot2 = 0.f;
 #pragma unroll
@@ -658,7 +671,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           p.ln_rstd[m_idx + r] = rstd;
         }
         for (int n = 0; n < lt; ++n) {
-          const int acc = (kb * lt + n) & 1;
+          const int acc = (kb * lt + n) % Cfg::kAcc;
           uint8_t* slab = nullptr;
           for (int j = 0; j < S32; ++j) {
             if (!(j & 1)) {
@@ -707,9 +720,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         }
         m_idx = (mn / p.n_blocks) * (BM * CTAS) + rank * BM;
         n_idx = (mn % p.n_blocks) * BN;
-        acc = it & 1;
+        acc = it % Cfg::kAcc;
         GEMM_STAMP(2, 20);
-        mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
+        mbar_wait(&tfull_bar[acc], (it / Cfg::kAcc) & 1);
         tc_fence_after();
         GEMM_STAMP(2, 21);
         if (p.row_scale) {
@@ -1067,7 +1080,27 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, td, tx, ty, p);
+  // operand stages vs slab slots (see GemmParams::stages)
+  GemmParams q = p;
+  q.stages = Cfg::kStages;
+  q.nslot = 4;
+  {
+    static const int f_stages = dev_env("SAV_GEMM_STAGES"), f_slots = dev_env("SAV_GEMM_SLOTS");
+    const bool streaming_epi = p.has_aux_in || p.epi == EPI_GELU2 || p.ln_tiles;
+    // measured (profiles/r02aa_split_sweep.txt): with K = 384 one stage less and two slabs more is
+    // 2-9 % faster for FC1 / out-projection / FC2 dX; with K = 1536 the pipeline needs its stages
+    if (streaming_epi && p.k_per_split <= 8 && Cfg::kStages >= 5) q.stages = Cfg::kStages - 1;
+    if (streaming_epi && f_stages >= 3 && f_stages <= Cfg::kStages) q.stages = f_stages;
+    const int room = ((Cfg::kStages - q.stages) * Cfg::kStageBytes + kOutBytes) / SLAB_BYTES;
+    // LayerNorm mode: at most five ring slots + the statistics slot (the single-buffered statistics
+    // rely on a row block spanning more slabs than the ring holds)
+    const int cap = p.ln_tiles ? 6 : 8;
+    int ns = room < cap ? room : cap;
+    if (f_slots >= 2 && f_slots < ns) ns = f_slots;
+    if (p.epi == EPI_GELU2) ns &= ~1;
+    q.nslot = q.stages == Cfg::kStages ? 4 : ns;
+  }
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, td, tx, ty, q);
   if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "sav_gemm launch: %s", cudaGetErrorString(e));
   count_launch();
   return check_launch("sav_gemm");
@@ -1087,13 +1120,17 @@ static int pick_ctas(int64_t M) {
 using namespace sav;
 
 // N-tiles per row when the LayerNorm that follows can be fused into the fp32-stream epilogue: the
-// row must be complete within two accumulators of the tile width sav_gemm picks for this N.
-extern "C" int32_t sav_gemm_ln_tiles(int64_t N) {
-  if (N <= 0 || N % 64) return 0;
-  const int bn = pick_bn(N);
-  if (N == bn) return 1;
-  if (N == 2 * bn) return 2;
+// row must be complete within the accumulator ring (4 x 128 columns; 192 as one tile).
+static int ln_plan(int64_t N, int* bn) {
+  if (N > 0 && N % 128 == 0 && N <= 512) { *bn = 128; return (int)(N / 128); }
+  if (N == 192) { *bn = 192; return 1; }
+  *bn = 0;
   return 0;
+}
+
+extern "C" int32_t sav_gemm_ln_tiles(int64_t N) {
+  int bn;
+  return ln_plan(N, &bn);
 }
 
 extern "C" int64_t sav_gemm_workspace_bytes(const sav_gemm_args* a) {
@@ -1112,7 +1149,10 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
       !aligned16(a->aux_in) || !aligned16(a->aux_out) || !aligned16(a->residual) ||
       !aligned16(a->col_scale))
     return set_error(SAV_ERR_ALIGN, "sav_gemm: pointers must be 16 B aligned");
-  const int bn = pick_bn(a->N);
+  int bn = pick_bn(a->N);
+  if (a->ln_out && !ln_plan(a->N, &bn))
+    return set_error(SAV_ERR_ARG, "sav_gemm: fused LayerNorm needs N = 192 or a multiple of 128 up to 512 "
+                                  "(sav_gemm_ln_tiles)");
   const int ctas = pick_ctas(a->M);
   const int bm = BM * ctas;
   const int split = plan_split(a, bn, bm);
@@ -1150,7 +1190,7 @@ extern "C" int sav_gemm(const sav_gemm_args* a, void* stream) {
     const int ltl = sav_gemm_ln_tiles(a->N);
     if (!ltl || p.epi != EPI_F32 || !a->residual || a->col_scale || a->row_scale || split > 1)
       return set_error(SAV_ERR_ARG, "sav_gemm: fused LayerNorm needs the fp32 residual epilogue without "
-                                    "scales and N = 1 or 2 tiles (sav_gemm_ln_tiles)");
+                                    "scales, unsplit");
     if (!a->ln_gamma || !a->ln_beta || !a->ln_mean || !a->ln_rstd || a->ldy % 8 || !aligned16(a->ln_out) ||
         !aligned16(a->ln_gamma) || !aligned16(a->ln_beta))
       return set_error(SAV_ERR_ARG, "sav_gemm: fused LayerNorm needs gamma, beta, mean, rstd, ldy %% 8");

@@ -116,9 +116,11 @@ def case_gemm_time(M=50432, N=1536, K=384, mode="gelu2", a_mn=False, b_mn=True, 
         kw = dict(aux_in=torch.randn(M, N, device=dev).bfloat16()); byt += 4 * M * N
         if mode == "dgelu_cs":     # + the bias column sums accumulated by the epilogue
             kw["dgelu_colsum"] = torch.zeros(N, device=dev)
-    elif mode == "resid":
+    elif mode in ("resid", "resid_ln"):
         kw = dict(bias=torch.randn(N, device=dev), residual=torch.randn(M, N, device=dev),
                   out_fp32=True); byt += 8 * M * N
+        if mode == "resid_ln":     # + the LayerNorm of the result (bf16 operand, mean, rstd)
+            kw["ln"] = (torch.ones(N, device=dev), torch.zeros(N, device=dev), 1e-6); byt += 2 * M * N
     elif mode == "dw":
         kw = dict(out=torch.zeros(M, N, device=dev), accumulate=True, split_k=0); byt += 4 * M * N
     out = kw.pop("out", None)
@@ -286,6 +288,8 @@ TIMING = {
     "t_out_fwd": dict(N=384, K=384, mode="resid"),
     "t_fc1_fwd": dict(N=1536, K=384, mode="gelu2"),
     "t_fc2_fwd": dict(N=384, K=1536, mode="resid"),
+    "t_out_fwd_ln": dict(N=384, K=384, mode="resid_ln"),
+    "t_fc2_fwd_ln": dict(N=384, K=1536, mode="resid_ln"),
     "t_fc2_dx": dict(N=1536, K=384, mode="dgelu", b_mn=False),
     "t_fc2_dx_cs": dict(N=1536, K=384, mode="dgelu_cs", b_mn=False),
     "t_fc1_dx": dict(N=384, K=1536, mode="plain", b_mn=False),

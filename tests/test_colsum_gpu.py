@@ -111,7 +111,7 @@ def test_gemm_epilogue_with_fused_layernorm(M, N, K):
     (var = E[x^2] - E[x]^2, eps 1e-6), mean / rstd saved -- N = 1 or 2 tiles, 1-CTA and CTA-pair
     tile shapes, partial M tiles."""
     from sav import ops
-    assert ops.gemm_ln_tiles(N) in (1, 2) and ops.gemm_ln_tiles(768) == 0
+    assert ops.gemm_ln_tiles(N) in (1, 2, 3, 4) and ops.gemm_ln_tiles(768) == 0
     g = torch.Generator().manual_seed(M + N + K)
     a = torch.randn((M, K), generator=g).bfloat16()
     w = (torch.randn((K, N), generator=g) / K ** 0.5).bfloat16()
