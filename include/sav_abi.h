@@ -295,6 +295,14 @@ int sav_layernorm_bwd_f32(const float* dy, int64_t ldy, const float* x, int64_t 
 /* dst fp32 [rows, cols] ldd (+)= src bf16 [rows, cols] lds */
 int sav_cast2d_bf16_f32(const void* src, int64_t lds, float* dst, int64_t ldd, int64_t rows,
                         int64_t cols, int32_t accumulate, void* stream);
+/* Batched transpose with zero padding -- rearrange '... l d -> ... d l' and back around the
+ * token-mixing FFBlock of MLP-Mixer (models/mlp_mixer.py:18-23).  Per batch b (in: R rows of pitch
+ * ld_in, out: C rows of pitch ld_out, residual: C rows of pitch ld_res):
+ *   out[b, c, r] = in[b, r, c] (+ residual[b, c, r])   r < R, c < C;   out[b, c, R..out_cols-1] = 0.
+ * in / out are bf16 unless in_fp32 / out_fp32; residual (optional) is fp32. */
+int sav_transpose_pad(const void* in, int32_t in_fp32, int64_t ld_in, void* out, int32_t out_fp32,
+                      int64_t ld_out, const float* residual, int64_t ld_res, int64_t B, int64_t R,
+                      int64_t C, int64_t out_cols, void* stream);
 
 /* ---------------------------------------------------------------- dense convolutions (im2col + GEMM)
  * nn.Conv of the CvT token embedding (cvt.py:27-31: 7x7 / 3x3, stride 4 / 2, SAME, bias) and of the

@@ -656,3 +656,76 @@ def apply_rotary_pos_emb(x, n_axis=0):
     shape = [1] * x.dim()
     shape[n_axis], shape[-1] = n, dim
     return x * cos.view(shape) + rotate_every_two(x) * sin.view(shape)
+
+
+# ----------------------------------------------------------------------------- MLP-Mixer
+def mixer_block(x, p):
+    """MixerBlock.__call__ (mlp_mixer.py:16-31)."""
+    y = layer_norm(x, p["LayerNorm_0"]["scale"], p["LayerNorm_0"]["bias"])      # :18
+    y = y.transpose(-1, -2)                                                     # :19 '... l d -> ... d l'
+    y = ff_block(y, p["FFBlock_0"])                                             # :20-22 over the tokens
+    y = y.transpose(-1, -2)                                                     # :23
+    x = y + x                                                                   # :24
+    y = layer_norm(x, p["LayerNorm_1"]["scale"], p["LayerNorm_1"]["bias"])      # :26
+    y = ff_block(y, p["FFBlock_1"])                                             # :27-29 over the channels
+    return x + y                                                                # :30
+
+
+def mixer_forward(params, images_nhwc, cfg):
+    """MLPMixer.__call__ (mlp_mixer.py:44-60): patch embedding with bias, blocks, LayerNorm, mean over
+    the tokens, Dense head."""
+    ph, pw = cfg["patch_shape"]
+    pe = params["PatchEmbedBlock_0"]["Dense_0"]
+    x = patch_embed(images_nhwc, pe["kernel"], ph, pw, bias=pe["bias"])         # :46-49
+    for i in range(cfg["num_layers"]):
+        x = mixer_block(x, params[f"MixerBlock_{i}"])                           # :51-55
+    x = layer_norm(x, params["LayerNorm_0"]["scale"], params["LayerNorm_0"]["bias"])   # :57
+    x = x.mean(dim=1)                                                           # :58
+    return x @ params["Dense_0"]["kernel"] + params["Dense_0"]["bias"]          # :59
+
+
+def mixer_config(name):
+    """create_model.py:184-213 (the unreachable second 'mixer_s_patch32' entry is B/16)."""
+    cfgs = {"mixer_s_patch32": (8, 512, 32), "mixer_s_patch16": (8, 512, 16),
+            "mixer_b_patch32": (12, 768, 32), "mixer_b_patch16": (12, 768, 16),
+            "mixer_l_patch32": (24, 1024, 32), "mixer_l_patch16": (32, 1024, 16)}
+    layers, dim, p = cfgs[name]
+    return dict(num_layers=layers, embed_dim=dim, patch_shape=(p, p), tokens_expand_ratio=0.5,
+                channels_expand_ratio=4, num_classes=1000)
+
+
+def synthetic_mixer_params(cfg, img_size=224, seed=42, dtype=torch.float32):
+    """SURVEY 8d synthetic init with the Flax auto-names of mlp_mixer.py."""
+    g = torch.Generator().manual_seed(seed)
+
+    def normal(shape, std):
+        return (torch.randn(shape, generator=g, dtype=torch.float64) * std).to(dtype)
+
+    def dense(k, n):
+        return {"kernel": normal((k, n), 1.0 / math.sqrt(k)), "bias": normal((n,), 0.02)}
+
+    def ln(c):
+        return {"scale": 1.0 + normal((c,), 0.02), "bias": normal((c,), 0.02)}
+    ph, pw = cfg["patch_shape"]
+    C = cfg["embed_dim"]
+    L = (img_size // ph) * (img_size // pw)
+    ht = max(1, int(cfg["tokens_expand_ratio"] * L))        # ff.py:22-23 on the token axis
+    hc = max(1, int(cfg["channels_expand_ratio"] * C))
+    params = {"PatchEmbedBlock_0": {"Dense_0": dense(ph * pw * 3, C)}}
+    for i in range(cfg["num_layers"]):
+        params[f"MixerBlock_{i}"] = {
+            "LayerNorm_0": ln(C), "FFBlock_0": {"Dense_0": dense(L, ht), "Dense_1": dense(ht, L)},
+            "LayerNorm_1": ln(C), "FFBlock_1": {"Dense_0": dense(C, hc), "Dense_1": dense(hc, C)}}
+    params["LayerNorm_0"] = ln(C)
+    nc = cfg["num_classes"]
+    params["Dense_0"] = {"kernel": normal((C, nc), 0.02), "bias": normal((nc,), 0.02)}
+    return params
+
+
+def mixer_loss_and_grads(params, images_hwcn, labels, cfg, label_smoothing=0.0):
+    p = tree_map(lambda t: t.detach().clone().requires_grad_(True), params)
+    logits = mixer_forward(p, hwcn_to_nhwc(images_hwcn), cfg)
+    loss = loss_fn(logits, labels, cfg["num_classes"], label_smoothing)
+    loss.backward()
+    grads = tree_map(lambda t: t.grad if t.grad is not None else torch.zeros_like(t), p)
+    return loss.detach(), logits.detach(), grads

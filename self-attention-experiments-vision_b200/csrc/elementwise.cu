@@ -230,3 +230,70 @@ extern "C" int sav_cast2d_bf16_f32(const void* src, int64_t lds, float* dst, int
   count_launch();
   return check_launch("sav_cast2d_bf16_f32");
 }
+
+// ---- batched transpose with zero padding: out[b, c, r] = in[b, r, c] (+ residual[b, c, r]) for
+// r < R, c < C; columns R .. out_cols-1 of every output row are written as zeros.  The token-mixing
+// MLP of MLP-Mixer (mlp_mixer.py:18-23: '... l d -> ... d l', FFBlock over the token axis, and
+// back) runs its two Dense layers as ordinary GEMMs over [B*C, L] rows; L = 196 is not a multiple
+// of 8 (the GEMM's pitch unit), so the transposed activations and weights live in buffers padded to
+// the next multiple of 8 whose pad columns are exact zeros.
+namespace sav {
+__device__ __forceinline__ float to_f32(float v) { return v; }
+__device__ __forceinline__ float to_f32(bf16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ void from_f32(float& d, float v) { d = v; }
+__device__ __forceinline__ void from_f32(bf16& d, float v) { d = __float2bfloat16_rn(v); }
+
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(256)
+transpose_pad_kernel(const TIn* __restrict__ in, int64_t ld_in, TOut* __restrict__ out, int64_t ld_out,
+                     const float* __restrict__ res, int64_t ld_res, int64_t R, int64_t C,
+                     int64_t out_cols) {
+  __shared__ float tile[32][33];
+  const int64_t b = blockIdx.z;
+  const int64_t r0 = (int64_t)blockIdx.x * 32, c0 = (int64_t)blockIdx.y * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
+  const TIn* src = in + b * R * ld_in;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t r = r0 + ty + i * 8, c = c0 + tx;
+    float v = 0.f;
+    if (r < R && c < C) v = to_f32(src[r * ld_in + c]);
+    tile[ty + i * 8][tx] = v;
+  }
+  __syncthreads();
+  TOut* dst = out + b * C * ld_out;
+  const float* rs = res ? res + b * C * ld_res : nullptr;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t c = c0 + ty + i * 8, r = r0 + tx;
+    if (c < C && r < out_cols) {
+      float v = tile[tx][ty + i * 8];
+      if (rs && r < R) v += rs[c * ld_res + r];
+      from_f32(dst[c * ld_out + r], v);
+    }
+  }
+}
+}  // namespace sav
+
+extern "C" int sav_transpose_pad(const void* in, int32_t in_fp32, int64_t ld_in, void* out,
+                                 int32_t out_fp32, int64_t ld_out, const float* residual,
+                                 int64_t ld_res, int64_t B, int64_t R, int64_t C, int64_t out_cols,
+                                 void* stream) {
+  using namespace sav;
+  if (B <= 0 || R <= 0 || C <= 0) return SAV_OK;
+  if (!in || !out || out_cols < R || ld_out < out_cols || ld_in < C || (residual && ld_res < R) ||
+      B > 65535 || (C + 31) / 32 > 65535)
+    return set_error(SAV_ERR_SHAPE, "sav_transpose_pad: R <= out_cols <= ld_out, C <= ld_in, B <= 65535");
+  const dim3 grid((unsigned)((out_cols + 31) / 32), (unsigned)((C + 31) / 32), (unsigned)B), block(32, 8);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+#define SAV_TP(TI, TO)                                                                          \
+  transpose_pad_kernel<TI, TO><<<grid, block, 0, st>>>(reinterpret_cast<const TI*>(in), ld_in,  \
+      reinterpret_cast<TO*>(out), ld_out, residual, ld_res, R, C, out_cols)
+  if (in_fp32 && out_fp32) SAV_TP(float, float);
+  else if (in_fp32) SAV_TP(float, bf16);
+  else if (out_fp32) SAV_TP(bf16, float);
+  else SAV_TP(bf16, bf16);
+#undef SAV_TP
+  count_launch();
+  return check_launch("sav_transpose_pad");
+}

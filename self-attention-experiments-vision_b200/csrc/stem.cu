@@ -181,7 +181,8 @@ extern "C" int sav_patchify(const float* images, void* patches, int64_t N, int64
     return set_error(SAV_ERR_SHAPE, "sav_patchify: H,W must be multiples of the patch shape");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (hwcn) {
-    const int PY = ph % 4 == 0 ? 4 : (ph % 2 == 0 ? 2 : 1);
+    int PY = ph % 4 == 0 ? 4 : (ph % 2 == 0 ? 2 : 1);
+    while (PY > 1 && (size_t)PY * pw * C * 33 * sizeof(float) > 48 * 1024) PY /= 2;   // 32-wide patches
     dim3 grid((unsigned)((H / PY) * (W / pw)), (unsigned)((N + 31) / 32));
     const size_t sm = (size_t)PY * pw * C * 33 * sizeof(float);
     if (sm > 48 * 1024) return set_error(SAV_ERR_SHAPE, "sav_patchify: pw*C too large");

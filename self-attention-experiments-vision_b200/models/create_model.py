@@ -8,6 +8,7 @@ accumulation / statistics.
 from models.botnet import BoTNet
 from models.cait import CaiT
 from models.cvt import CvT
+from models.mlp_mixer import MLPMixer
 from models.vit import ViT
 
 _VIT = {
@@ -53,6 +54,17 @@ _CVT = {
 }
 
 
+_MIXER = {
+    # create_model.py:184-213 verbatim (layers, embed_dim, patch).  The reference spells the B/16
+    # entry 'mixer_s_patch32' a second time (create_model.py:199), so it is unreachable there; it is
+    # offered here under the name the pattern implies.  mixer_l_patch16 has 32 layers in
+    # create_model.py:209-213 against 24 in mlp_mixer_test.py:19: the named surface wins.
+    'mixer_s_patch32': (8, 512, 32), 'mixer_s_patch16': (8, 512, 16),
+    'mixer_b_patch32': (12, 768, 32), 'mixer_b_patch16': (12, 768, 16),
+    'mixer_l_patch32': (24, 1024, 32), 'mixer_l_patch16': (32, 1024, 16),
+}
+
+
 def create_model(model_name: str, num_classes: int = 1000, dtype=None):
     if model_name in _VIT:
         layers, heads, dim, p = _VIT[model_name]
@@ -68,4 +80,7 @@ def create_model(model_name: str, num_classes: int = 1000, dtype=None):
     if model_name in _CVT:
         sizes, heads, dims = _CVT[model_name]
         return CvT(num_classes=num_classes, stage_sizes=sizes, num_heads=heads, embed_dim=dims)
+    if model_name in _MIXER:
+        layers, dim, p = _MIXER[model_name]
+        return MLPMixer(num_classes=num_classes, num_layers=layers, embed_dim=dim, patch_shape=(p, p))
     raise NotImplementedError(f'{model_name} is not built yet (see DESIGN.md status table)')

@@ -85,7 +85,7 @@ def _as2d(t, K):
 
 class LazyLinear(Var):
     __slots__ = ("bias_grad_from", "x", "weight", "bias", "act", "col_scale", "row_scale", "rows_per_scale",
-                 "residual", "out_shape", "_done")
+                 "residual", "out_shape", "_done", "f32_out")
 
     def __init__(self, x, weight, bias, out_shape):
         super().__init__(None)
@@ -95,6 +95,7 @@ class LazyLinear(Var):
         self.rows_per_scale = 1
         self.out_shape = tuple(out_shape)
         self._done = False
+        self.f32_out = False      # written as the fp32 stream without a skip input (to_stream)
 
     @property
     def shape(self):
@@ -106,7 +107,7 @@ class LazyLinear(Var):
 
     @property
     def dtype(self):
-        return F32 if self.residual is not None else BF16
+        return F32 if self.residual is not None or self.f32_out else BF16
 
     @property
     def v(self):
@@ -126,7 +127,7 @@ class LazyLinear(Var):
         x, W = self.x, self.weight
         xin = x.v
         K, N = W.w.shape
-        stream = self.residual is not None
+        stream = self.residual is not None or self.f32_out
         if _meta(xin):
             self._v = torch.empty(self.out_shape, dtype=F32 if stream else BF16, device="meta")
             return
@@ -138,7 +139,7 @@ class LazyLinear(Var):
         out = torch.empty((M, N), dtype=F32 if stream else BF16, device=x2.device)
         pre = torch.empty((M, N), dtype=BF16, device=x2.device) if self.act else None
         res = None
-        if stream:
+        if self.residual is not None:
             res = self.residual.v
             if res.dtype != F32:
                 raise TypeError("residual add: the skip input must be the fp32 residual stream")
@@ -238,10 +239,23 @@ def linear(x, weight, bias=None, out_features_shape=None):
 
 def gelu(x):
     """jax.nn.gelu (tanh form) -- only as the epilogue of the producing linear (ff.py:24-25)."""
+    if isinstance(x, TokenMix) and not x._done and x.layers and x.layers[-1][2] == 0:
+        x.layers[-1][2] = 1
+        return x
     if isinstance(x, LazyLinear) and not x._done and x.act == 0 and x.residual is None:
         x.act = 1
         return x
     raise NotImplementedError("standalone gelu: apply it directly to a Dense output")
+
+
+def to_stream(x):
+    """Start the fp32 residual stream from a Dense output that has no skip input (MLP-Mixer: the
+    patch embedding itself is the stream, mlp_mixer.py:46-49): the pending GEMM writes fp32."""
+    if isinstance(x, LazyLinear) and not x._done and x.act == 0 and x.residual is None \
+            and x.col_scale is None and x.row_scale is None:
+        x.f32_out = True
+        return x
+    raise NotImplementedError("to_stream: apply it directly to a Dense output")
 
 
 def scale_channels(x, scale_param):
@@ -262,6 +276,10 @@ def scale_rows(x, per_sample_scale, rows_per_sample):
 
 def add(a, b):
     """Residual add (vit.py:24,31): folded into the pending linear's epilogue (fp32 stream out)."""
+    for lazy, other in ((a, b), (b, a)):
+        if isinstance(lazy, TokenMix) and not lazy._done and lazy.closed and isinstance(other, Var) \
+                and tuple(other.shape) == tuple(lazy.shape):
+            return lazy.run(other)     # mlp_mixer.py:24: the transpose back carries the add
     for lazy, other in ((a, b), (b, a)):
         if isinstance(lazy, LazyLinear) and not lazy._done and lazy.residual is None and \
                 lazy.act == 0 and isinstance(other, Var) and tuple(other.shape) == tuple(lazy.shape):
@@ -1173,3 +1191,166 @@ def activation(x, kind):
             _add_grad(x, ops.act_bwd(tc, d.contiguous(), kind).view(t.shape))
     record(bwd)
     return out
+
+
+# ------------------------------------------------------------------ MLP-Mixer token mixing
+def _pad8(n):
+    return (n + 7) // 8 * 8
+
+
+class TokenMix(Var):
+    """The token-mixing branch of a MixerBlock (mlp_mixer.py:18-23), collected lazily:
+
+        x = rearrange(LN(inputs), '... l d -> ... d l'); x = FFBlock(...)(x)
+        x = rearrange(x, '... d l -> ... l d'); x = x + inputs
+
+    `swap_tokens_channels` on the LayerNorm output opens it, the two Dense layers and the GELU of the
+    FFBlock append to it, the second swap closes it and the residual add runs it: transpose (zero
+    padded to a multiple of 8 tokens) -> GEMM + bias + GELU -> GEMM + bias -> transpose back fused
+    with the residual add into the fp32 stream.  Shapes seen by module code are the logical ones
+    ([B, C, L] / [B, C, hidden]); the padding never leaves this class."""
+    __slots__ = ("src", "layers", "closed", "_done", "logical")
+
+    def __init__(self, src):
+        super().__init__(None)
+        self.src = src
+        self.layers = []          # [kernel Param, bias Param or None, act]
+        self.closed = False
+        self._done = False
+        B, L, C = src.shape
+        self.logical = (B, C, L)
+
+    @property
+    def shape(self):
+        if self.closed:
+            B, C, L = self.logical
+            return (B, L, C)
+        return self.logical
+
+    @property
+    def ndim(self):
+        return 3
+
+    @property
+    def dtype(self):
+        return self._v.dtype if self._done else BF16
+
+    @property
+    def v(self):
+        if not self._done:
+            self.run(None)
+        return self._v
+
+    def dense(self, kernel, bias, features):
+        if self.closed or self._done:
+            raise NotImplementedError("token mixing: Dense after the closing rearrange")
+        self.layers.append([kernel, bias, 0])
+        self.logical = self.logical[:2] + (features,)
+        return self
+
+    def run(self, residual):
+        """Launch the branch; with `residual` (fp32 stream Var [B, L, C]) the result is the new
+        fp32 stream, without it the bf16 [B, L, C] activation."""
+        self._done = True
+        src = self.src
+        xv = src.v
+        B, L, C = xv.shape
+        if len(self.layers) != 2 or self.layers[0][2] != 1 or self.layers[1][2] != 0 or \
+                not self.closed or self.logical[2] != L:
+            raise NotImplementedError("token mixing: expected Dense -> gelu -> Dense back to the "
+                                      "token count (FFBlock, ff.py:24-27)")
+        (k0, b0, _), (k1, b1, _) = self.layers
+        H = k0.master.shape[1]
+        if _meta(xv):
+            self._v = torch.empty((B, L, C), dtype=F32 if residual is not None else BF16, device="meta")
+            return self
+        dev = xv.device
+        Lp, Hp = _pad8(L), _pad8(H)
+        M = B * C
+
+        def padded_weight(kernel, rows, cols, rp, cp):
+            # bf16 W^T [cols -> cp rows, rows -> rp pitch] from the fp32 master [rows, cols]
+            wt = torch.zeros((1, cp, rp), dtype=BF16, device=dev)
+            ops.transpose_pad(kernel.master.view(1, rows, cols), rows, cols, wt, rp)
+            return wt[0]
+
+        def padded_bias(bias, n, npad):
+            bp = torch.zeros((npad,), dtype=F32, device=dev)
+            if bias is not None:     # (a 1 x n "transpose": no alignment demands on the arena view)
+                ops.transpose_pad(bias.master.view(1, 1, n), 1, n, bp.view(1, npad, 1), 1)
+            return bp
+
+        w0t = padded_weight(k0, L, H, Lp, Hp)        # [Hp, Lp]  = B operand [N, K] of Dense_0
+        w1t = padded_weight(k1, H, L, Hp, Lp)        # [Lp, Hp]
+        b0p, b1p = padded_bias(b0, H, Hp), padded_bias(b1, L, Lp)
+        xt = torch.empty((B, C, Lp), dtype=BF16, device=dev)
+        ops.transpose_pad(xv.contiguous(), L, C, xt, Lp)
+        xt2 = xt.view(M, Lp)
+        pre = torch.empty((M, Hp), dtype=BF16, device=dev)
+        h = ops.gemm(xt2, w0t, bias=b0p, act=1, aux_out=pre)
+        y = ops.gemm(h, w1t, bias=b1p)               # [M, Lp]
+        res = None
+        if residual is not None:
+            res = residual.v
+            if res.dtype != F32:
+                raise TypeError("residual add: the skip input must be the fp32 residual stream")
+            res = res.contiguous()
+        out = torch.empty((B, L, C), dtype=F32 if res is not None else BF16, device=dev)
+        ops.transpose_pad(y.view(B, C, Lp), C, L, out, C, residual=res)
+        self._v = out
+
+        def bwd():
+            g = self.take_grad()
+            g16 = self.take_grad16()
+            if g is None and g16 is None:
+                return
+            if residual is not None and residual.requires_grad:
+                if residual.g is not None:
+                    raise NotImplementedError("residual-stream Var with a second consumer before its "
+                                              "LayerNorm backward")
+                residual.g = g
+            gin = g16 if g16 is not None else g
+            dy = torch.empty((B, C, Lp), dtype=BF16, device=dev)
+            ops.transpose_pad(gin.contiguous().view(B, L, C), L, C, dy, Lp)
+            dy2 = dy.view(M, Lp)
+
+            def grads_into(kernel, bias, x2, d2, rows, cols, rp, cp, bias_tmp=None):
+                # dW [rows, cols] += (x2^T d2)[:rows, :cols]; dbias += colsum(d2)[:cols].  The GEMM
+                # writes the padded transpose (d2^T x2) and the un-padding transpose adds it into the
+                # arena view in place (any size, any alignment).
+                gwt = torch.zeros((1, cp, rp), dtype=F32, device=dev)
+                ops.gemm(d2, x2, a_mn=True, b_mn=True, out=gwt[0], accumulate=True, split_k=0)
+                kernel.touch_grad()
+                kg = kernel.grad.view(1, rows, cols)
+                ops.transpose_pad(gwt, cols, rows, kg, cols, residual=kg)
+                if bias is not None:
+                    if bias_tmp is None:
+                        bias_tmp = torch.zeros((cp,), dtype=F32, device=dev)
+                        ops.colsum(d2, out=bias_tmp, accumulate=True)
+                    bias.touch_grad()
+                    bg = bias.grad.view(1, cols, 1)
+                    ops.transpose_pad(bias_tmp.view(1, 1, cp), 1, cols, bg, 1, residual=bg)
+
+            grads_into(k1, b1, h, dy2, H, L, Hp, Lp)
+            db0 = torch.zeros((Hp,), dtype=F32, device=dev)
+            dh = ops.gemm(dy2, w1t, b_mn=True, aux_in=pre, dgelu_colsum=db0)     # [M, Hp], x gelu'(pre)
+            grads_into(k0, b0, xt2, dh, L, H, Lp, Hp, bias_tmp=db0)
+            if src.requires_grad:
+                dxt = ops.gemm(dh, w0t, b_mn=True)                                # [M, Lp]
+                dx = torch.empty((B, L, C), dtype=BF16, device=dev)
+                ops.transpose_pad(dxt.view(B, C, Lp), C, L, dx, C)
+                _add_grad(src, dx)
+        record(bwd)
+        return self
+
+
+def swap_tokens_channels(x):
+    """einops.rearrange(x, '... l d -> ... d l') around the token-mixing FFBlock (mlp_mixer.py:19,23)."""
+    if isinstance(x, TokenMix) and not x._done:
+        if x.closed:
+            raise NotImplementedError("token mixing: rearranged twice after the FFBlock")
+        x.closed = True
+        return x
+    if x.ndim != 3:
+        raise NotImplementedError("swap_tokens_channels: [B, L, C] activations only")
+    return TokenMix(x)

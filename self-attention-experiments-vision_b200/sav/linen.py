@@ -419,6 +419,8 @@ class Dense(Module):
         kernel = self.param("kernel", self.kernel_init or initializers.lecun_normal(), (K, self.features))
         bias = self.param("bias", self.bias_init or initializers.zeros, (self.features,)) \
             if self.use_bias else None
+        if isinstance(inputs, F.TokenMix):      # Dense over the token axis (mlp_mixer.py:18-23)
+            return inputs.dense(kernel, bias, self.features)
         return F.linear(inputs, F.Weight(kernel.shadow, kernel.grad, [kernel], wm=kernel.master), bias)
 
 

@@ -590,6 +590,25 @@ def cast2d_bf16_f32(src, dst, accumulate=False):
                                     int(accumulate), _stream()))
 
 
+def transpose_pad(src, R, C, out, out_cols, residual=None):
+    """out[b, c, r] = src[b, r, c] (+ residual[b, c, r]); columns R..out_cols-1 of `out` zeroed.
+    src: [B, R, >=C] (bf16 or fp32, pitch = stride(1)); out: [B, C, >=out_cols]; batches dense."""
+    B = src.shape[0]
+    assert src.dim() == 3 and out.dim() == 3 and src.stride(2) == 1 and out.stride(2) == 1
+    assert B == 1 or (src.stride(0) == R * src.stride(1) and out.stride(0) == C * out.stride(1))
+    assert src.shape[1] >= R and out.shape[1] >= C and out.shape[0] == B
+    assert src.dtype in (BF16, F32) and out.dtype in (BF16, F32)
+    if residual is not None:
+        _req(residual, F32, "residual")
+        assert residual.stride(2) == 1 and (B == 1 or residual.stride(0) == C * residual.stride(1))
+    check(lib().sav_transpose_pad(_p(src), int(src.dtype == F32), src.stride(1), _p(out),
+                                  int(out.dtype == F32), out.stride(1),
+                                  _p(residual) if residual is not None else None,
+                                  residual.stride(1) if residual is not None else 0,
+                                  B, R, C, out_cols, _stream()))
+    return out
+
+
 # ------------------------------------------------------------------ BoTNet conv-stage pieces (cnn.cu)
 ACT = {"none": 0, "swish": 1, "sigmoid": 2, "relu": 3}
 
