@@ -360,7 +360,6 @@ def main():
         # of the same shapes (profiles/, captured under ncu, not in this run).
         ents = kernel_rooflines(torch, ops, B, cfg, pk, total_ms / K)
         top = ents[0]
-        traffic = {"attn_bwd3_kernel": None, "attn_fwd2_kernel": None}
         try:
             with open(os.path.join(ROOT, "profiles", "r02_ncu_counters.json")) as f:
                 ncu = json.load(f)
@@ -393,12 +392,31 @@ def main():
                                              f"not installable in this image"}
         print(json.dumps(out), flush=True)
     if world > 1:
-        # the captured step holds NCCL kernels; tearing the communicator down under a live CUDA graph
-        # can block, so leave together and let process exit release everything
+        # Clean teardown: the captured step holds NCCL kernels, so the graph (and everything that
+        # refers to it) goes first, then the communicator.  destroy_process_group() runs under a
+        # watchdog -- if a rank is still inside NCCL after 20 s the bench has printed its line long
+        # ago and the process leaves through os._exit rather than hang the driver.
+        import gc
+        import threading
         dist.barrier()
         torch.cuda.synchronize()
         sys.stdout.flush()
-        os._exit(0)
+        step = g = state = dp = None   # noqa: F841
+        gc.collect()
+        torch.cuda.synchronize()
+        done = threading.Event()
+
+        def _teardown():
+            try:
+                dist.destroy_process_group()
+            finally:
+                done.set()
+        t = threading.Thread(target=_teardown, daemon=True)
+        t.start()
+        if not done.wait(20.0):
+            sys.stderr.write("bench: communicator teardown did not finish in 20 s, leaving\n")
+            sys.stderr.flush()
+            os._exit(0)
 
 
 if __name__ == "__main__":
