@@ -341,6 +341,7 @@ def main():
         "config": {"workload": "DeiT-S/16 224^2 training step (fwd+bwd+grad mean+clip+Adam)",
                    "batch_per_gpu": B, "global_batch": B * world, "tokens": 197,
                    "parallelism": f"dp{world}", "cuda_graph": not args.no_graph,
+                   "grad_exchange": (dp.stats.get("transport", dp.transport) if dp is not None else None),
                    "l2": "inputs larger than L2 (activations ~GBs per step)"},
         "e2e": {"value": e2e_value, "unit": "images/s",
                 "h2d_bytes_per_step": images_host.numel() * 4 + labels_host.numel() * 4,

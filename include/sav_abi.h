@@ -463,6 +463,25 @@ int sav_layerscale_grad(const float* W, int64_t ldw, const float* dW, int64_t ld
 int sav_copy2d_f32(const float* src, int64_t lds, float* dst, int64_t ldd, int64_t rows,
                    int64_t cols, int32_t accumulate, void* stream);
 
+/* ---------------------------------------------------------------- data-parallel gradient exchange
+ * lax.pmean(grads) of train.py:96 as one kernel over NVLink / NVSwitch peer memory (csrc/dp.cu):
+ * in-place SUM all-reduce of buf[offset, offset + n) where `buf` is the same symmetric allocation on
+ * every rank.  The caller (sav/dp.py through torch's symmetric-memory rendezvous, or any cuMem /
+ * cuMulticast owner) provides
+ *   multicast_ptr        multicast address of the allocation (NVLS: multimem.ld_reduce / multimem.st),
+ *                        or 0 -> peer loads / stores through peer_ptrs_dev instead
+ *   peer_ptrs_dev        device array of `world` pointers to every rank's copy (own included)
+ *   signal_pad_ptrs_dev  device array of `world` pointers to every rank's zero-initialised signal pad
+ *                        of signal_pad_bytes; the kernel uses blocks * world 32-bit words of it and
+ *                        leaves them zero
+ * offset, n in floats, multiples of 4.  Every rank must enqueue the call with identical offset, n,
+ * world and blocks (0 = default); the kernel waits for its peers on the device, never on the host,
+ * and can be captured in a CUDA graph.  Replaces ncclAllReduce on the path. */
+int sav_dp_allreduce_sum_f32(uint64_t multicast_ptr, const uint64_t* peer_ptrs_dev,
+                             const uint64_t* signal_pad_ptrs_dev, int64_t signal_pad_bytes,
+                             int64_t offset, int64_t n, int32_t rank, int32_t world, int32_t blocks,
+                             void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -10,8 +10,20 @@ issued asynchronously (torch's NCCL process group runs it on its own stream behi
 compute stream), so the exchange over NVLink/NVSwitch overlaps the remaining backward kernels.  The
 optimizer waits on all buckets.  Everything is CUDA-graph capturable (fork/join through events).
 
+Transport.  On NVLink / NVSwitch boxes the exchange is not a library collective: the gradient arena
+is re-homed into symmetric memory (torch.distributed._symmetric_memory does the allocation and the
+handle exchange -- plumbing), and ONE kernel of ours (csrc/dp.cu, `sav_dp_allreduce_sum_f32`) sums
+the whole arena in place right after the last backward kernel: `multimem.ld_reduce` / `multimem.st`
+through the switch (NVLS) when the allocation has a multicast address, peer loads / stores otherwise.
+It runs when nothing else does, so it does not share SMs with the persistent one-CTA-per-SM backward
+kernels the way NCCL's overlapped CTAs do.  `transport="nccl"` (or a box where
+the symmetric-memory rendezvous fails) keeps the bucketed, overlapped NCCL path.
+
 Works on CPU tensors with the gloo backend too (tests/test_dp_cpu.py): only the transport differs.
 """
+import os
+import warnings
+
 import torch
 import torch.distributed as dist
 
@@ -55,10 +67,14 @@ def _leaf_span(p):
 class DataParallel:
     """Gradient hook for sav.tape.value_and_grad: begin() / wrote(path) / after_node(i) / finish()."""
 
-    def __init__(self, bucket_mb=16.0, group=None, overlap=True, reference_double_scale=False):
+    def __init__(self, bucket_mb=16.0, group=None, overlap=True, reference_double_scale=False,
+                 transport=None):
         if not dist.is_initialized():
             raise RuntimeError("DataParallel needs an initialised torch.distributed process group")
         self.group = group
+        # "peer" = our kernel over symmetric memory (default on CUDA), "nccl" = bucketed NCCL
+        self.transport = transport or os.environ.get("SAV_DP_TRANSPORT", "peer")
+        self._symm = None         # symmetric-memory handle of the re-homed gradient arena
         self.world_size = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.bucket_elems = int(bucket_mb * (1 << 20) / 4)
@@ -81,15 +97,52 @@ class DataParallel:
         """flax.jax_utils.replicate (train.py:228): every rank starts from rank 0's parameters."""
         dist.broadcast(arena.master, src=src, group=self.group)
         arena.refresh_shadow()
+        self.attach(arena)
+
+    def attach(self, arena):
+        """Re-home the arena's gradient buffer into symmetric memory (collective; call it on every
+        rank before the first step / graph capture).  Falls back to the NCCL transport, with a
+        warning, when symmetric memory cannot be set up on this box."""
+        if self.transport != "peer" or self._symm is not None or not arena.grad.is_cuda:
+            if not arena.grad.is_cuda:
+                self.transport = "nccl"     # gloo / CPU tests
+            return
+        ok = torch.ones(1, device=arena.grad.device)
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            buf = symm_mem.empty(arena.size, dtype=torch.float32, device=arena.grad.device)
+            hdl = symm_mem.rendezvous(buf, self.group if self.group is not None else dist.group.WORLD)
+            buf.zero_()
+            self._symm = (buf, hdl)
+        except Exception as e:   # noqa: BLE001 -- any failure means "not on this box"
+            warnings.warn(f"sav.dp: symmetric-memory transport unavailable ({type(e).__name__}: {e}); "
+                          f"using NCCL")
+            ok.zero_()
+        # all ranks take the same branch
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        if float(ok.item()) < 1.0:
+            self._symm = None
+            self.transport = "nccl"
+            return
+        buf, hdl = self._symm
+        arena.grad = buf                      # Param.grad views are taken from arena.grad on access
+        self._arena_attached = arena
+        mc = int(hdl.multicast_ptr) and os.environ.get("SAV_DP_MULTICAST", "1") == "1"
+        self.stats["transport"] = "peer/multimem" if mc else "peer/p2p"
 
     def _plan(self, arena):
         leaves = [(path, p.offset, _leaf_span(p)) for path, p in arena.params.items()]
         self.buckets = plan_buckets(leaves, self.bucket_elems)
-        self.stats = {"buckets": len(self.buckets),
-                      "bytes": sum((hi - lo) * 4 for lo, hi, _ in self.buckets)}
+        self.stats.update({"buckets": len(self.buckets),
+                           "bytes": sum((hi - lo) * 4 for lo, hi, _ in self.buckets)})
 
     # -- hook protocol (called by tape.value_and_grad) -------------------------------------------
     def begin(self, arena):
+        if self.transport == "peer" and self._symm is None and not arena.grad.is_cuda:
+            self.transport = "nccl"         # gloo / CPU tensors
+        if self.transport == "peer" and self._symm is None:
+            raise RuntimeError("DataParallel: call attach(arena) (or broadcast_params) on every rank "
+                               "before the first step")
         if self.buckets is None or arena is not self._arena:
             self._arena = arena
             self._plan(arena)
@@ -105,13 +158,26 @@ class DataParallel:
 
     def after_node(self, i):
         self._node = i
-        if self.fire_after is not None and self.overlap:
+        if self.fire_after is not None and self.overlap and self.transport == "nccl":
             for b in self.fire_after.get(i, ()):
                 self._launch(b)
 
     def finish(self):
         """Called after the last backward node: reduce what is left and make the compute stream
         wait for every bucket (never-written leaves are already zero: arena.begin_grad())."""
+        if self.transport == "peer":
+            # one kernel over the whole arena, on the compute stream, after the last gradient kernel
+            from . import ops
+            buf, hdl = self._symm
+            if self._arena.grad.data_ptr() != buf.data_ptr():
+                raise RuntimeError("DataParallel: the arena's gradient buffer is not the symmetric one")
+            n = (self._arena.size + 3) // 4 * 4
+            mc = hdl.multicast_ptr if os.environ.get("SAV_DP_MULTICAST", "1") == "1" else 0
+            ops.dp_allreduce_sum(mc, hdl.buffer_ptrs_dev, hdl.signal_pad_ptrs_dev,
+                                 hdl.signal_pad_size, 0, min(n, buf.numel()), self.rank, self.world_size,
+                                 int(os.environ.get("SAV_DP_BLOCKS", "0")))
+            self.stats["bytes"] = self._arena.size * 4
+            return
         if self.fire_after is None:
             # learning pass: derive the firing schedule for the following steps
             sched = {}

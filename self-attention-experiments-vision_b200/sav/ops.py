@@ -286,6 +286,15 @@ def sumsq(g, out):
     check(lib().sav_sumsq(_p(g), g.numel(), _p(out), _stream()))
 
 
+def dp_allreduce_sum(multicast_ptr, peer_ptrs_dev, signal_pad_ptrs_dev, signal_pad_bytes, offset, n,
+                     rank, world, blocks=0):
+    """In-place SUM over the ranks of floats [offset, offset + n) of a symmetric allocation
+    (csrc/dp.cu); the pointer tables are device addresses (ints)."""
+    check(lib().sav_dp_allreduce_sum_f32(int(multicast_ptr), int(peer_ptrs_dev), int(signal_pad_ptrs_dev),
+                                         int(signal_pad_bytes), int(offset), int(n), int(rank),
+                                         int(world), int(blocks), _stream()))
+
+
 def fill(t, v):
     check(lib().sav_fill_f32(_p(t), float(v), t.numel(), _stream()))
 

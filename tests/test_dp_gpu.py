@@ -13,7 +13,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 @pytest.mark.gpu
-def test_two_rank_gradients_equal_global_batch_gradients():
+@pytest.mark.parametrize("transport", ["peer/multimem", "peer/p2p", "nccl"])
+def test_two_rank_gradients_equal_global_batch_gradients(transport):
+    """Every transport of sav/dp.py: our all-reduce kernel over symmetric memory through the switch's
+    multicast (multimem.ld_reduce / multimem.st), the same kernel with peer loads / stores, and the
+    bucketed NCCL path."""
     import torch
     n = torch.cuda.device_count()
     if n < 2:
@@ -22,12 +26,17 @@ def test_two_rank_gradients_equal_global_batch_gradients():
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", "29731",
            os.path.join(ROOT, "tests", "tools", "dp_parity_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    env = dict(os.environ, SAV_DP_TRANSPORT=transport.split("/")[0],
+               SAV_DP_MULTICAST="0" if transport == "peer/p2p" else "1")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0, r.stderr[-3000:]
     line = [l for l in r.stdout.splitlines() if l.startswith("DPRESULT ")][-1]
     out = json.loads(line[len("DPRESULT "):])
     print(out)
     assert out["world"] == world and out["buckets"] >= 2 and out["checksums_equal"]
+    if out["transport"] != transport:
+        # symmetric memory / multicast not available on this box: the fallback must still be right
+        print("transport fell back to", out["transport"])
     # vs the fp32 oracle: the bf16 floor of DeiT-Ti at 8 images (tests/test_vit_parity_gpu.py)
     assert out["worst_l2_vs_oracle"] <= 1.7e-2 and out["worst_vs_oracle"] <= 1.3 * 1.95e-2
     # vs one rank on the same kernels: only the fp32 summation order of the exchange differs

@@ -39,7 +39,7 @@ def main():
     for _ in range(2):      # first pass learns the bucket schedule, second runs overlapped
         (loss, _), grads = sav.value_and_grad(loss_fn, has_aux=True, grad_hook=dp)(variables["params"], x, y)
     torch.cuda.synchronize()
-    out = {"world": world, "buckets": dp.stats["buckets"]}
+    out = {"world": world, "buckets": dp.stats["buckets"], "transport": dp.stats.get("transport", dp.transport)}
     if rank == 0:
         _, _, grads_ref = O.vit_loss_and_grads(params, images, labels, cfg, 0.1)
         ours = dict(O.tree_leaves(grads))
