@@ -5,6 +5,7 @@ libsav_b200.so; nothing here falls back to torch ops.
 """
 import ctypes as C
 import math
+import os
 
 import torch
 
@@ -197,9 +198,14 @@ def _bnhd_strides(t):
     return t.stride(0), t.stride(1)
 
 
-def attn_fwd(q, k, v, scale=None, save_lo=True):
+_ATTN_SAVE_LO = os.environ.get("SAV_ATTN_SAVE_LO", "1") == "1"
+
+
+def attn_fwd(q, k, v, scale=None, save_lo=None):
     """q [B,Nq,H,D], k/v [B,Nk,H,D] bf16 (strided views ok) -> o [2,B,Nq,H,D] (o[0] = output,
     o[1] = its low half for backward when save_lo), lse [B,H,Nq]."""
+    if save_lo is None:
+        save_lo = _ATTN_SAVE_LO
     B, Nq, H, D = q.shape
     Nk = k.shape[1]
     o2 = torch.empty((2 if save_lo else 1, B, Nq, H, D), dtype=BF16, device=q.device)
