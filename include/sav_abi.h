@@ -135,6 +135,18 @@ int sav_colsum_bf16(const void* X, int64_t M, int64_t N, int64_t ldx, float* out
 int64_t sav_colsum_workspace_bytes(int64_t M, int64_t N);
 int sav_colsum_bf16_ws(const void* X, int64_t M, int64_t N, int64_t ldx, float* out,
                        int32_t accumulate, void* workspace, int64_t workspace_bytes, void* stream);
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * it).  sav_colsum_bf16_ws with its scratch in a file-scope `static __device__` array of
+ * sav_colsum_static_max_bytes() = 4 MiB inside the library (every GPU that loads the library holds
+ * it until exit); the call allocates nothing and takes no workspace.  Shapes whose
+ * sav_colsum_workspace_bytes(M, N) exceeds the array are rejected with SAV_ERR_SHAPE (every
+ * bias-gradient shape of the models here needs <= 1.9 MiB).  All calls on a device share the
+ * array: calls that overlap on the GPU (different streams, parallel graph branches) race -- keep
+ * them on one stream or order them with events.  The array's previous contents never matter. */
+int64_t sav_colsum_static_max_bytes(void);
+int sav_colsum_bf16_static(const void* X, int64_t M, int64_t N, int64_t ldx, float* out,
+                           int32_t accumulate, void* stream);
 
 /* ---------------------------------------------------------------- LayerNorm (vit.py:19,26,57)
  * Flax nn.LayerNorm: fp32 stats, var = E[x^2]-E[x]^2, eps inside rsqrt, y = xhat*scale + bias.

@@ -18,6 +18,8 @@
 // split over K (tokens) and the partial tiles are combined with TMA reduce-add (fp32) in L2.
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "common.cuh"
 #include "host.h"
 
@@ -1384,4 +1386,67 @@ extern "C" int sav_colsum_bf16(const void* X, int64_t M, int64_t N, int64_t ldx,
   colsum_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const bf16*>(X), M, N, ldx, out);
   count_launch();
   return check_launch("sav_colsum_bf16");
+}
+
+// ---- Column sums without any allocation or caller-provided workspace.
+// No counterpart in the reference; added for callers that
+// cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+// it).  The row-split partial sums of sav_colsum_bf16_ws go to a file-scope device array instead of a
+// caller workspace.  Every GPU that loads the library holds the 4 MiB until exit.  All calls share
+// the array: two calls that overlap on the GPU (different streams, or graph branches) race on it.
+// The array keeps the previous call's contents, which is harmless here: the partial kernel writes
+// every word [0, splits * N) before the finishing kernel reads it, so nothing has to start at zero.
+constexpr int64_t kColsumStaticBytes = 4ll << 20;
+static __device__ __align__(256) unsigned char g_colsum_static_scratch[kColsumStaticBytes];
+
+// In host code `g_colsum_static_scratch` is a host-side stand-in for the symbol, not a device
+// address: the address a kernel can use comes from cudaGetSymbolAddress, taken once per device with
+// that device current (set-up, cached; not an allocation).
+static int colsum_static_scratch(float** out_ptr) {
+  constexpr int kMaxDevices = 64;
+  static void* cached[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices)
+    return set_error(SAV_ERR_CUDA, "sav_colsum_bf16_static: cudaGetDevice: %s (device %d)",
+                     cudaGetErrorString(e), dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!cached[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_colsum_static_scratch);
+    if (e != cudaSuccess || !p)
+      return set_error(SAV_ERR_CUDA, "sav_colsum_bf16_static: cudaGetSymbolAddress: %s",
+                       cudaGetErrorString(e));
+    cached[dev] = p;
+  }
+  *out_ptr = reinterpret_cast<float*>(cached[dev]);
+  return SAV_OK;
+}
+
+extern "C" int64_t sav_colsum_static_max_bytes(void) { return kColsumStaticBytes; }
+
+extern "C" int sav_colsum_bf16_static(const void* X, int64_t M, int64_t N, int64_t ldx, float* out,
+                                      int32_t accumulate, void* stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!X || !out || M <= 0 || N <= 0 || N % 8 || ldx % 8 || !aligned16(X))
+    return set_error(SAV_ERR_SHAPE, "sav_colsum: need N, ldx multiples of 8 and a 16 B aligned base");
+  const int64_t need = sav_colsum_workspace_bytes(M, N);
+  if (need > kColsumStaticBytes)
+    return set_error(SAV_ERR_SHAPE,
+                     "sav_colsum_bf16_static: M=%lld, N=%lld needs %lld bytes of scratch, the built-in "
+                     "array holds %lld; use sav_colsum_bf16_ws with a caller workspace",
+                     (long long)M, (long long)N, (long long)need, (long long)kColsumStaticBytes);
+  float* part = nullptr;
+  if (int rc = colsum_static_scratch(&part)) return rc;
+  const int64_t Y = colsum_splits(M, N);
+  int64_t gx, W;
+  colsum_plan(N, &gx, &W);
+  dim3 grid((unsigned)gx, (unsigned)Y);
+  colsum_partial_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const bf16*>(X), M, N, ldx, part, (int)W);
+  count_launch();
+  if (int rc = check_launch("sav_colsum_bf16_static")) return rc;
+  colsum_finish_kernel<<<(unsigned)((N + 31) / 32), 1024, 0, st>>>(part, Y, N, out, accumulate);
+  count_launch();
+  return check_launch("sav_colsum_bf16_static");
 }

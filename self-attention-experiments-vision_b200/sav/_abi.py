@@ -122,6 +122,8 @@ SIGNATURES = {
     "sav_colsum_bf16": (C.c_int, [_P, _I64, _I64, _I64, _P, _I32, _P]),
     "sav_colsum_workspace_bytes": (C.c_int64, [_I64, _I64]),
     "sav_colsum_bf16_ws": (C.c_int, [_P, _I64, _I64, _I64, _P, _I32, _P, _I64, _P]),
+    "sav_colsum_static_max_bytes": (C.c_int64, []),
+    "sav_colsum_bf16_static": (C.c_int, [_P, _I64, _I64, _I64, _P, _I32, _P]),
     "sav_layernorm_fwd": (C.c_int, [_P, _I64, _P, _P, _P, _I64, _P, _P, _I64, _I64, _F, _P]),
     "sav_layernorm_bwd": (C.c_int, [_P, _I64, _P, _I64] + [_P] * 8 + [_I64, _I64, _P]),
     "sav_layernorm_bwd_colsum": (C.c_int, [_P, _I64, _P, _I64] + [_P] * 9 + [_I64, _I64, _P]),
