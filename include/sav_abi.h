@@ -475,6 +475,20 @@ int sav_layerscale_grad(const float* W, int64_t ldw, const float* dW, int64_t ld
 int sav_copy2d_f32(const float* src, int64_t lds, float* dst, int64_t ldd, int64_t rows,
                    int64_t cols, int32_t accumulate, void* stream);
 
+/* ---------------------------------------------------------------- TNT (models/tnt.py)
+ * Pixel-embedding input (tnt.py:19-26): fp32 images ([N,H,W,C], or [H,W,C,N] if hwcn) -> bf16
+ * [N*(H/ph)*(W/pw), (ph/th)*(pw/tw), C*th*tw], feature order (c, t1, t2). */
+int sav_pixel_patchify(const float* images, void* out, int64_t N, int64_t H, int64_t W, int64_t C,
+                       int64_t ph, int64_t pw, int64_t th, int64_t tw, int32_t hwcn, void* stream);
+/* attention.py:39-58 for short sequences with narrow heads (TNT's inner transformer, tnt.py:60-69:
+ * 16 tokens, head dim 6 / 10): qkv bf16 contiguous [B, N, 3, H, D] (the fused projection output),
+ * o / d_o bf16 [B, N, H, D], dqkv like qkv; N <= 32, D <= 16; fp32 CUDA-core math, P recomputed in
+ * the backward pass (nothing saved). */
+int sav_attn_small_fwd(const void* qkv, void* o, int64_t B, int64_t N, int64_t H, int64_t D, float scale,
+                       void* stream);
+int sav_attn_small_bwd(const void* qkv, const void* d_o, void* dqkv, int64_t B, int64_t N, int64_t H,
+                       int64_t D, float scale, void* stream);
+
 /* ---------------------------------------------------------------- data-parallel gradient exchange
  * lax.pmean(grads) of train.py:96 as one kernel over NVLink / NVSwitch peer memory (csrc/dp.cu):
  * in-place SUM all-reduce of buf[offset, offset + n) where `buf` is the same symmetric allocation on

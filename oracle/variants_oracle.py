@@ -729,3 +729,122 @@ def mixer_loss_and_grads(params, images_hwcn, labels, cfg, label_smoothing=0.0):
     loss.backward()
     grads = tree_map(lambda t: t.grad if t.grad is not None else torch.zeros_like(t), p)
     return loss.detach(), logits.detach(), grads
+
+
+# ----------------------------------------------------------------------------- TNT
+def pixel_embed(images_nhwc, p, patch_shape, sub_shape):
+    """PixelEmbedBlock.__call__ (tnt.py:16-30): 'b (h p1) (w p2) c -> (b h w) p1 p2 c', then
+    'n (p1 t1) (p2 t2) c -> n (p1 p2) (c t1 t2)', then Dense(+bias)."""
+    b, H, W, c = images_nhwc.shape
+    ph, pw = patch_shape
+    t1, t2 = sub_shape
+    gh, gw = H // ph, W // pw
+    x = images_nhwc.reshape(b, gh, ph, gw, pw, c).permute(0, 1, 3, 2, 4, 5).reshape(b * gh * gw, ph, pw, c)
+    q1, q2 = ph // t1, pw // t2
+    x = x.reshape(-1, q1, t1, q2, t2, c).permute(0, 1, 3, 5, 2, 4).reshape(-1, q1 * q2, c * t1 * t2)
+    return x @ p["Dense_0"]["kernel"] + p["Dense_0"]["bias"]
+
+
+def tnt_encoder_block(patch_inputs, pixel_inputs, p, inner_heads, outer_heads):
+    """tnt.py EncoderBlock.__call__ (tnt.py:59-87)."""
+    from .vit_oracle import attention
+    ln = lambda x, q: layer_norm(x, q["scale"], q["bias"])   # noqa: E731
+    inner_x = ln(pixel_inputs, p["LayerNorm_0"])                                          # :61
+    inner_x = attention(inner_x, inner_x, p["SelfAttentionBlock_0"], inner_heads)         # :62-66
+    inner_x = inner_x + pixel_inputs                                                      # :67
+    inner_y = ff_block(ln(inner_x, p["LayerNorm_1"]), p["FFBlock_0"])                     # :68-71
+    inner_output = inner_x + inner_y                                                      # :72
+    # Inner2OuterBlock (tnt.py:36-45)
+    b = patch_inputs.shape[0]
+    d2 = p["Inner2OuterBlock_0"]["Dense_0"]
+    x = inner_output.reshape(inner_output.shape[0], -1)                                   # :40
+    x = x @ d2["kernel"] + d2["bias"]                                                     # :41
+    x = x.reshape(b, -1, x.shape[-1])                                                     # :42
+    x = torch.nn.functional.pad(x, (0, 0, 1, 0))                                          # :43
+    outer_x = x + patch_inputs                                                            # :44
+    outer_x = ln(outer_x, p["LayerNorm_2"])                                               # :75
+    outer_x = attention(outer_x, outer_x, p["SelfAttentionBlock_1"], outer_heads)         # :76-80
+    outer_x = outer_x + patch_inputs                                                      # :81
+    outer_y = ff_block(ln(outer_x, p["LayerNorm_3"]), p["FFBlock_1"])                     # :82-85
+    return outer_x + outer_y, inner_output                                                # :86-87
+
+
+def tnt_forward(params, images_nhwc, cfg):
+    """TNT.__call__ (tnt.py:133-178)."""
+    pixel = pixel_embed(images_nhwc, params["PixelEmbedBlock_0"], cfg["patch_shape"],
+                        cfg["transformed_patch_shape"])                                   # :135-139
+    pe = params["PatchEmbedBlock_0"]["Dense_0"]
+    patch = patch_embed(images_nhwc, pe["kernel"], *cfg["patch_shape"], bias=pe["bias"])  # :141-144
+    b = patch.shape[0]
+    patch = torch.cat([params["cls"].expand(b, -1, -1), patch], dim=1)                    # :146-153
+    pixel = pixel + params["AddAbsPosEmbed_0"]["pos_embed"]                               # :155
+    patch = patch + params["AddAbsPosEmbed_1"]["pos_embed"]                               # :156
+    for i in range(cfg["num_layers"]):
+        patch, pixel = tnt_encoder_block(patch, pixel, params["Encoder_0"][f"EncoderBlock_{i}"],
+                                         cfg["inner_num_heads"], cfg["outer_num_heads"])
+    cls = patch[:, 0]                                                                     # :172
+    return cls @ params["Dense_0"]["kernel"] + params["Dense_0"]["bias"]                  # :173-177
+
+
+def tnt_config(name):
+    """create_model.py:50-63."""
+    cfgs = {"tnt_s_patch16": (4, 10, 40, 640), "tnt_b_patch16": (4, 6, 24, 384)}
+    ih, oh, idim, odim = cfgs[name]
+    return dict(num_layers=12, inner_num_heads=ih, outer_num_heads=oh, inner_embed_dim=idim,
+                outer_embed_dim=odim, patch_shape=(16, 16), transformed_patch_shape=(4, 4),
+                inner_expand_ratio=4, outer_expand_ratio=4, num_classes=1000)
+
+
+def synthetic_tnt_params(cfg, img_size=224, seed=42, dtype=torch.float32):
+    """SURVEY 8d synthetic init with the Flax auto-names of tnt.py."""
+    g = torch.Generator().manual_seed(seed)
+
+    def normal(shape, std):
+        return (torch.randn(shape, generator=g, dtype=torch.float64) * std).to(dtype)
+
+    def dense(k, n):
+        return {"kernel": normal((k, n), 1.0 / math.sqrt(k)), "bias": normal((n,), 0.02)}
+
+    def ln(c):
+        return {"scale": 1.0 + normal((c,), 0.02), "bias": normal((c,), 0.02)}
+
+    def attn(c, h):
+        d = c // h
+        return {"queries": {"kernel": normal((c, h, d), 1.0 / math.sqrt(c))},
+                "keys": {"kernel": normal((c, h, d), 1.0 / math.sqrt(c))},
+                "values": {"kernel": normal((c, h, d), 1.0 / math.sqrt(c))},
+                "DenseGeneral_0": {"kernel": normal((h, d, c), 1.0 / math.sqrt(c))}}
+    ph, pw = cfg["patch_shape"]
+    t1, t2 = cfg["transformed_patch_shape"]
+    ci, co = cfg["inner_embed_dim"], cfg["outer_embed_dim"]
+    L = (img_size // ph) * (img_size // pw)
+    npix = (ph // t1) * (pw // t2)
+    enc = {}
+    for i in range(cfg["num_layers"]):
+        enc[f"EncoderBlock_{i}"] = {
+            "LayerNorm_0": ln(ci), "SelfAttentionBlock_0": attn(ci, cfg["inner_num_heads"]),
+            "LayerNorm_1": ln(ci),
+            "FFBlock_0": {"Dense_0": dense(ci, int(cfg["inner_expand_ratio"] * ci)),
+                          "Dense_1": dense(int(cfg["inner_expand_ratio"] * ci), ci)},
+            "Inner2OuterBlock_0": {"Dense_0": dense(npix * ci, co)},
+            "LayerNorm_2": ln(co), "SelfAttentionBlock_1": attn(co, cfg["outer_num_heads"]),
+            "LayerNorm_3": ln(co),
+            "FFBlock_1": {"Dense_0": dense(co, int(cfg["outer_expand_ratio"] * co)),
+                          "Dense_1": dense(int(cfg["outer_expand_ratio"] * co), co)}}
+    nc = cfg["num_classes"]
+    return {"PixelEmbedBlock_0": {"Dense_0": dense(3 * t1 * t2, ci)},
+            "PatchEmbedBlock_0": {"Dense_0": dense(ph * pw * 3, co)},
+            "cls": normal((1, 1, co), 0.02),
+            "AddAbsPosEmbed_0": {"pos_embed": normal((1, npix, ci), 0.02)},
+            "AddAbsPosEmbed_1": {"pos_embed": normal((1, L + 1, co), 0.02)},
+            "Encoder_0": enc,
+            "Dense_0": {"kernel": normal((co, nc), 0.02), "bias": normal((nc,), 0.02)}}
+
+
+def tnt_loss_and_grads(params, images_hwcn, labels, cfg, label_smoothing=0.0):
+    p = tree_map(lambda t: t.detach().clone().requires_grad_(True), params)
+    logits = tnt_forward(p, hwcn_to_nhwc(images_hwcn), cfg)
+    loss = loss_fn(logits, labels, cfg["num_classes"], label_smoothing)
+    loss.backward()
+    grads = tree_map(lambda t: t.grad if t.grad is not None else torch.zeros_like(t), p)
+    return loss.detach(), logits.detach(), grads

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libsav_b200.so")
 SOURCES = ["host.cu", "gemm.cu", "attn.cu", "attn_fwd.cu", "attn_bwd.cu", "norm.cu", "stem.cu", "optim.cu",
-           "attn_mat.cu", "elementwise.cu", "conv.cu", "conv2d.cu", "cnn.cu", "dp.cu"]
+           "attn_mat.cu", "elementwise.cu", "conv.cu", "conv2d.cu", "cnn.cu", "dp.cu", "attn_small.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]

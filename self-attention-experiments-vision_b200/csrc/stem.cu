@@ -231,3 +231,51 @@ extern "C" int sav_embed_bwd(const void* dx, void* dtok, float* dcls, float* dpo
   count_launch();
   return check_launch("sav_embed_bwd");
 }
+
+// ---- TNT pixel embedding input (models/tnt.py:19-26): 'b (h p1) (w p2) c -> (b h w) p1 p2 c' then
+// 'n (p1 t1) (p2 t2) c -> n (p1 p2) (c t1 t2)': every ph x pw patch becomes (ph/th)*(pw/tw) "pixel"
+// tokens of C*th*tw features, feature order (c, t1, t2) with t2 fastest.  fp32 image in ([N,H,W,C]
+// or the loader's [H,W,C,N], train.py:80), bf16 GEMM operand out; a pure gather (images need no
+// gradient).
+namespace sav {
+__global__ void __launch_bounds__(256)
+pixel_patchify_kernel(const float* __restrict__ img, bf16* __restrict__ out, int64_t total, int N, int H,
+                      int W, int C, int ph, int pw, int th, int tw, int64_t sy, int64_t sx, int64_t sc,
+                      int64_t sb) {
+  const int gw = W / pw, gh = H / ph, q1 = ph / th, q2 = pw / tw;
+  const int feat = C * th * tw;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = idx;
+    const int f = (int)(r % feat); r /= feat;
+    const int pos = (int)(r % (q1 * q2)); r /= (q1 * q2);
+    const int w = (int)(r % gw); r /= gw;
+    const int h = (int)(r % gh); r /= gh;
+    const int b = (int)r;
+    const int t2 = f % tw, t1 = (f / tw) % th, c = f / (tw * th);
+    const int p2 = pos % q2, p1 = pos / q2;
+    const int y = h * ph + p1 * th + t1, x = w * pw + p2 * tw + t2;
+    out[idx] = __float2bfloat16(img[y * sy + x * sx + c * sc + b * sb]);
+  }
+}
+}  // namespace sav
+
+extern "C" int sav_pixel_patchify(const float* images, void* out, int64_t N, int64_t H, int64_t W,
+                                  int64_t C, int64_t ph, int64_t pw, int64_t th, int64_t tw, int32_t hwcn,
+                                  void* stream) {
+  using namespace sav;
+  if (N <= 0 || !images || !out || ph <= 0 || pw <= 0 || th <= 0 || tw <= 0 || H % ph || W % pw ||
+      ph % th || pw % tw)
+    return set_error(SAV_ERR_SHAPE, "sav_pixel_patchify: H,W multiples of the patch, patch of the sub-patch");
+  const int64_t total = N * H * W * C;
+  int64_t sy, sx, sc, sb;
+  if (hwcn) { sb = 1; sc = N; sx = C * N; sy = W * C * N; }
+  else { sc = 1; sx = C; sy = W * C; sb = H * W * C; }
+  const int64_t blocks = (total + 255) / 256;
+  pixel_patchify_kernel<<<(unsigned)(blocks < 148 * 32 ? blocks : 148 * 32), 256, 0,
+                          reinterpret_cast<cudaStream_t>(stream)>>>(
+      images, reinterpret_cast<bf16*>(out), total, (int)N, (int)H, (int)W, (int)C, (int)ph, (int)pw,
+      (int)th, (int)tw, sy, sx, sc, sb);
+  count_launch();
+  return check_launch("sav_pixel_patchify");
+}

@@ -48,8 +48,12 @@ class AttentionBlock(nn.Module):
         fused = mix is None and d == 64
         if inputs_q is inputs_kv:
             qkv = F.linear(inputs_q, w_qkv)                  # attention.py:35-37, one GEMM
-            ctx = F.self_attention_core(qkv, H, d) if fused else \
-                F.mat_self_attention_core(qkv, H, d, mix)    # attention.py:39-58
+            if mix is None and d <= 16 and inputs_q.shape[1] <= 32:
+                # TNT's inner transformer (tnt.py:60-69): 16 tokens, head dim 6 / 10
+                ctx = F.small_self_attention_core(qkv, H, d)
+            else:
+                ctx = F.self_attention_core(qkv, H, d) if fused else \
+                    F.mat_self_attention_core(qkv, H, d, mix)    # attention.py:39-58
         else:
             hd = H * d
             gq = w_qkv.gw[:, :hd] if w_qkv.gw is not None else None

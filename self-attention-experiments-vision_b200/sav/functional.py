@@ -1354,3 +1354,118 @@ def swap_tokens_channels(x):
     if x.ndim != 3:
         raise NotImplementedError("swap_tokens_channels: [B, L, C] activations only")
     return TokenMix(x)
+
+
+# ------------------------------------------------------------------ TNT (models/tnt.py)
+def pixel_patchify(images, ph, pw, th, tw, hwcn):
+    """'b (h p1) (w p2) c -> (b h w) p1 p2 c' + 'n (p1 t1) (p2 t2) c -> n (p1 p2) (c t1 t2)'
+    (tnt.py:19-26) of the fp32 input images; no gradient."""
+    if _meta(images):
+        if hwcn:
+            H, W, C, N = images.shape
+        else:
+            N, H, W, C = images.shape
+        return Var(torch.empty((N * (H // ph) * (W // pw), (ph // th) * (pw // tw), C * th * tw),
+                               dtype=BF16, device="meta"), requires_grad=False)
+    return Var(ops.pixel_patchify(images.contiguous(), ph, pw, th, tw, hwcn), requires_grad=False)
+
+
+def small_self_attention_core(qkv, num_heads, head_ch):
+    """attention.py:39-58 for TNT's inner transformer (16 tokens, head dim 6 / 10): the FP32
+    CUDA-core kernel of csrc/attn_small.cu on the fused QKV activation [B,N,3*H*d] -> [B,N,H*d]."""
+    t = qkv.v
+    B, N, _ = t.shape
+    H, D = num_heads, head_ch
+    if _meta(t):
+        return Var(torch.empty((B, N, H * D), dtype=BF16, device="meta"))
+    t5 = t.contiguous().view(B, N, 3, H, D)
+    scale = 1.0 / math.sqrt(D)
+    out = Var(ops.attn_small_fwd(t5, scale).view(B, N, H * D))
+
+    def bwd():
+        d_o = out.take_grad()
+        if d_o is None:
+            return
+        dqkv = ops.attn_small_bwd(t5, d_o.contiguous().view(B, N, H, D), scale)
+        _add_grad(qkv, dqkv.view(B, N, 3 * H * D))
+    record(bwd)
+    return out
+
+
+def stream_to_operand(x, shape):
+    """The fp32 residual stream as a bf16 GEMM operand under another shape (tnt.py:37: the inner
+    transformer's output '... n d -> ... (n d)' feeds Inner2OuterBlock's Dense) while the stream itself
+    goes on to the next block: the operand's gradient is added into the stream's fp32 gradient."""
+    t = x.v
+    if _meta(t):
+        return Var(torch.empty(t.shape, dtype=BF16, device="meta").reshape(shape))
+    if t.dtype != F32:
+        raise TypeError("stream_to_operand: fp32 residual stream expected")
+    tc = t.contiguous()
+    y = torch.empty(tc.shape, dtype=BF16, device=t.device)
+    ops.cast_bf16(tc, y)
+    out = Var(y.view(shape))
+
+    def bwd():
+        g = out.take_grad()
+        if g is None or not x.requires_grad:
+            return
+        C = tc.shape[-1]
+        g2 = g.contiguous().view(-1, C)
+        if x.g is None:
+            full = torch.empty(tc.shape, dtype=F32, device=t.device)
+            ops.cast2d_bf16_f32(g2, full.view(-1, C))
+            x.g = full
+            x.g16 = None
+            return
+        ops.cast2d_bf16_f32(g2, x.g.view(-1, C), accumulate=True)
+        # This consumer runs AFTER the next block's LayerNorm backward in reverse order (tnt.py: the
+        # pixel stream feeds Inner2OuterBlock of block i, then block i+1).  If that LayerNorm already
+        # folded the producing Dense's bias gradient (column sums of the bf16 stream-gradient copy,
+        # `bias_grad_from`), add this contribution's column sums too and hand the Dense a fresh bf16
+        # copy of the total so that it neither recomputes nor misses anything.
+        folded = getattr(x, "bias_grad_from", None) if isinstance(x, LazyLinear) else None
+        if folded is not None:
+            ops.colsum(g2, out=x.bias.grad.reshape(C), accumulate=True)
+            g16 = torch.empty(tc.shape, dtype=BF16, device=t.device)
+            ops.cast_bf16(x.g.contiguous(), g16)
+            x.g16 = g16
+            x.bias_grad_from = g16
+        else:
+            x.g16 = None
+    record(bwd)
+    return out
+
+
+def inner_to_outer(patch_inputs, inner):
+    """Inner2OuterBlock's tail (tnt.py:39-42): x = pad(inner, one zero row in front of every
+    sequence) + patch_inputs.  patch_inputs: fp32 stream [B, 1 + L, C]; inner: bf16 [B*L, C] (the
+    Dense output) -> new fp32 stream."""
+    pv, iv = patch_inputs.v, inner.v
+    B, L1, C = pv.shape
+    L = L1 - 1
+    if _meta(pv):
+        return Var(torch.empty((B, L1, C), dtype=F32, device="meta"))
+    if pv.dtype != F32:
+        raise TypeError("inner_to_outer: the patch embeddings must be the fp32 residual stream")
+    out_t = torch.empty((B, L1, C), dtype=F32, device=pv.device)
+    ops.copy2d_f32(pv.contiguous().view(B, L1 * C), out_t.view(B, L1 * C))
+    ops.cast2d_bf16_f32(iv.contiguous().view(B, L * C), out_t.view(B, L1 * C)[:, C:], accumulate=True)
+    out = Var(out_t)
+
+    def bwd():
+        g = out.take_grad()
+        out.g16 = None
+        if g is None:
+            return
+        g = g.contiguous()
+        if inner.requires_grad:
+            tmp = torch.empty((B, L * C), dtype=F32, device=g.device)
+            ops.copy2d_f32(g.view(B, L1 * C)[:, C:], tmp)
+            d16 = torch.empty((B * L, C), dtype=BF16, device=g.device)
+            ops.cast_bf16(tmp, d16)
+            _add_grad(inner, d16.view(iv.shape))
+        if patch_inputs.requires_grad:
+            _add_grad(patch_inputs, g)
+    record(bwd)
+    return out

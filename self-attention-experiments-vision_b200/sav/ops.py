@@ -605,6 +605,36 @@ def cast2d_bf16_f32(src, dst, accumulate=False):
                                     int(accumulate), _stream()))
 
 
+def pixel_patchify(images, ph, pw, th, tw, hwcn):
+    """tnt.py:19-26: fp32 images -> bf16 [N*(H/ph)*(W/pw), (ph/th)*(pw/tw), C*th*tw]."""
+    _req(images, F32, "images")
+    if hwcn:
+        H, W, Cc, N = images.shape
+    else:
+        N, H, W, Cc = images.shape
+    out = torch.empty((N * (H // ph) * (W // pw), (ph // th) * (pw // tw), Cc * th * tw), dtype=BF16,
+                      device=images.device)
+    check(lib().sav_pixel_patchify(_p(images), _p(out), N, H, W, Cc, ph, pw, th, tw, int(hwcn), _stream()))
+    return out
+
+
+def attn_small_fwd(qkv5, scale):
+    """qkv5 bf16 contiguous [B, N, 3, H, D] -> o [B, N, H, D] (N <= 32, D <= 16)."""
+    _req(qkv5, BF16, "qkv")
+    B, N, _, H, D = qkv5.shape
+    o = torch.empty((B, N, H, D), dtype=BF16, device=qkv5.device)
+    check(lib().sav_attn_small_fwd(_p(qkv5), _p(o), B, N, H, D, float(scale), _stream()))
+    return o
+
+
+def attn_small_bwd(qkv5, d_o, scale):
+    _req(qkv5, BF16, "qkv"); _req(d_o, BF16, "d_o")
+    B, N, _, H, D = qkv5.shape
+    dqkv = torch.empty_like(qkv5)
+    check(lib().sav_attn_small_bwd(_p(qkv5), _p(d_o), _p(dqkv), B, N, H, D, float(scale), _stream()))
+    return dqkv
+
+
 def transpose_pad(src, R, C, out, out_cols, residual=None):
     """out[b, c, r] = src[b, r, c] (+ residual[b, c, r]); columns R..out_cols-1 of `out` zeroed.
     src: [B, R, >=C] (bf16 or fp32, pitch = stride(1)); out: [B, C, >=out_cols]; batches dense."""
