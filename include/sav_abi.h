@@ -352,7 +352,8 @@ int sav_batchnorm_eval(const void* y, const float* ra_mean, const float* ra_var,
 
 /* ---------------------------------------------------------------- BoTNet conv-stage pieces
  * Channel-last bf16 [rows, C] tensors around the conv GEMMs of botnet.py:17-67,202-331.
- * kind: 0 none, 1 swish (nn.swish, the BoTNet activation_fn), 2 sigmoid (SE gate), 3 relu.
+ * kind: 0 none, 1 swish (nn.swish, the BoTNet activation_fn), 2 sigmoid (SE gate), 3 relu,
+ * 4 tanh-GELU (CeiT's LeFF block, leff.py:43,55,61).
  *   sav_bn_act_fwd / bwd : z = act(BatchNorm(y)) from given mean / rstd (sav_bn_stats +
  *       sav_batchnorm_fwd produce them); the reverse mode recomputes act' from y, accumulates
  *       dgamma / dbeta, scratch fp32 [2C]                          (botnet.py:44-50,225-228)
@@ -474,6 +475,18 @@ int sav_layerscale_grad(const float* W, int64_t ldw, const float* dW, int64_t ld
  * cait.py:97,175 and its reverse mode; fan-in of fp32 stream gradients) */
 int sav_copy2d_f32(const float* src, int64_t lds, float* dst, int64_t ldd, int64_t rows,
                    int64_t cols, int32_t accumulate, void* stream);
+
+/* ---------------------------------------------------------------- CeiT (models/ceit.py)
+ * nn.max_pool(x, (3,3), strides (2,2)) with flax's default 'VALID' padding (image_to_token.py:33-37);
+ * same buffers as sav_maxpool3x3s2_*, Ho = (H - 3) / 2 + 1. */
+int sav_maxpool3x3s2_valid_fwd(const void* x, void* y, void* argmax, int64_t B, int64_t H, int64_t W,
+                               int64_t C, void* stream);
+int sav_maxpool3x3s2_valid_bwd(const void* dy, const void* argmax, void* dx, int64_t B, int64_t H,
+                               int64_t W, int64_t C, void* stream);
+/* 'b (h ph) (w pw) c -> b (h w) (ph pw c)' of a bf16 activation [B,H,W,C] (image_to_token.py:38-43);
+ * inverse != 0: the permutation back (src [B, tokens, ph*pw*C] -> dst [B,H,W,C]), i.e. its gradient. */
+int sav_patchify_act(const void* src, void* dst, int64_t B, int64_t H, int64_t W, int64_t C, int64_t ph,
+                     int64_t pw, int32_t inverse, void* stream);
 
 /* ---------------------------------------------------------------- TNT (models/tnt.py)
  * Pixel-embedding input (tnt.py:19-26): fp32 images ([N,H,W,C], or [H,W,C,N] if hwcn) -> bf16

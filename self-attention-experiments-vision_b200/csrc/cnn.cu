@@ -13,13 +13,14 @@
 
 namespace sav {
 
-enum { ACT_NONE = 0, ACT_SWISH = 1, ACT_SIGMOID = 2, ACT_RELU = 3 };
+enum { ACT_NONE = 0, ACT_SWISH = 1, ACT_SIGMOID = 2, ACT_RELU = 3, ACT_GELU = 4 };
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
 __device__ __forceinline__ float act_apply(float x, int kind) {
   if (kind == ACT_SWISH) return x * sigmoidf_(x);
   if (kind == ACT_SIGMOID) return sigmoidf_(x);
   if (kind == ACT_RELU) return fmaxf(x, 0.f);
+  if (kind == ACT_GELU) return gelu_tanh(x);      // jax.nn.gelu default (leff.py:13,43,55,61)
   return x;
 }
 // d act(x) / dx
@@ -27,6 +28,7 @@ __device__ __forceinline__ float act_grad(float x, int kind) {
   if (kind == ACT_SWISH) { const float s = sigmoidf_(x); return s * (1.f + x * (1.f - s)); }
   if (kind == ACT_SIGMOID) { const float s = sigmoidf_(x); return s * (1.f - s); }
   if (kind == ACT_RELU) return x > 0.f ? 1.f : 0.f;
+  if (kind == ACT_GELU) return dgelu_tanh(x);
   return 1.f;
 }
 
@@ -386,9 +388,14 @@ extern "C" int sav_spatial_mean_bwd(const void* dout, void* dx, int64_t B, int64
   return check_launch("sav_spatial_mean_bwd");
 }
 
-static int pool_geom(PoolGeom& g, int64_t B, int64_t H, int64_t W, int64_t C) {
+static int pool_geom(PoolGeom& g, int64_t B, int64_t H, int64_t W, int64_t C, bool valid = false) {
   if (B <= 0 || H <= 0 || W <= 0 || C <= 0) return set_error(SAV_ERR_SHAPE, "maxpool: bad shape");
   g.B = (int)B; g.H = (int)H; g.W = (int)W; g.C = (int)C;
+  if (valid) {   // padding 'VALID' (flax nn.max_pool default, image_to_token.py:33-37): no padding
+    if (H < 3 || W < 3) return set_error(SAV_ERR_SHAPE, "maxpool VALID: H, W >= 3");
+    g.Ho = (int)((H - 3) / 2 + 1); g.Wo = (int)((W - 3) / 2 + 1); g.pt = g.pl = 0;
+    return SAV_OK;
+  }
   int64_t o; int32_t lo;
   sav_conv_same_geom(H, 3, 2, &o, &lo); g.Ho = (int)o; g.pt = lo;
   sav_conv_same_geom(W, 3, 2, &o, &lo); g.Wo = (int)o; g.pl = lo;
@@ -415,4 +422,63 @@ extern "C" int sav_maxpool3x3s2_bwd(const void* dy, const void* argmax, void* dx
       reinterpret_cast<const bf16*>(dy), reinterpret_cast<const uint8_t*>(argmax), reinterpret_cast<bf16*>(dx), g);
   count_launch();
   return check_launch("sav_maxpool3x3s2_bwd");
+}
+
+// nn.max_pool(x, (3,3), strides=(2,2)) with flax's default 'VALID' padding (CeiT's Image2TokenBlock,
+// image_to_token.py:33-37): the same kernels with no padding and Ho = (H - 3) / 2 + 1.
+extern "C" int sav_maxpool3x3s2_valid_fwd(const void* x, void* y, void* argmax, int64_t B, int64_t H,
+                                          int64_t W, int64_t C, void* stream) {
+  PoolGeom g;
+  int rc = pool_geom(g, B, H, W, C, true);
+  if (rc) return rc;
+  maxpool_fwd_kernel<<<cnn_blocks((int64_t)g.B * g.Ho * g.Wo * g.C), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const bf16*>(x), reinterpret_cast<bf16*>(y), reinterpret_cast<uint8_t*>(argmax), g);
+  count_launch();
+  return check_launch("sav_maxpool3x3s2_valid_fwd");
+}
+
+extern "C" int sav_maxpool3x3s2_valid_bwd(const void* dy, const void* argmax, void* dx, int64_t B, int64_t H,
+                                          int64_t W, int64_t C, void* stream) {
+  PoolGeom g;
+  int rc = pool_geom(g, B, H, W, C, true);
+  if (rc) return rc;
+  maxpool_bwd_kernel<<<cnn_blocks((int64_t)g.B * g.H * g.W * g.C), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const bf16*>(dy), reinterpret_cast<const uint8_t*>(argmax), reinterpret_cast<bf16*>(dx), g);
+  count_launch();
+  return check_launch("sav_maxpool3x3s2_valid_bwd");
+}
+
+// 'b (h ph) (w pw) c -> b (h w) (ph pw c)' of a bf16 ACTIVATION [B,H,W,C] (image_to_token.py:38-43:
+// the pooled feature map cut into 4x4 patches) and its inverse (the gradient's way back): a pure
+// permutation, two bf16 elements per thread (C even, so a pair never straddles a pixel).
+namespace sav {
+__global__ void patchify_act_kernel(const bf16* __restrict__ src, bf16* __restrict__ dst, int64_t total2,
+                                    int H, int W, int C2, int ph, int pw, int inverse) {
+  const int gw = W / pw;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total2; i += (int64_t)gridDim.x * blockDim.x) {
+    // i indexes the [B,H,W,C/2] image layout
+    const int c2 = (int)(i % C2);
+    int64_t t = i / C2;
+    const int x = (int)(t % W); t /= W;
+    const int y = (int)(t % H);
+    const int64_t b = t / H;
+    const int hy = y / ph, py = y - hy * ph, wx = x / pw, px = x - wx * pw;
+    const int64_t tok = (b * (H / ph) + hy) * gw + wx;
+    const int64_t j = (tok * ph * pw + py * pw + px) * C2 + c2;     // [B, tokens, ph, pw, C/2]
+    if (inverse) reinterpret_cast<uint32_t*>(dst)[i] = reinterpret_cast<const uint32_t*>(src)[j];
+    else reinterpret_cast<uint32_t*>(dst)[j] = reinterpret_cast<const uint32_t*>(src)[i];
+  }
+}
+}  // namespace sav
+
+extern "C" int sav_patchify_act(const void* src, void* dst, int64_t B, int64_t H, int64_t W, int64_t C,
+                                int64_t ph, int64_t pw, int32_t inverse, void* stream) {
+  if (B <= 0 || !src || !dst || ph <= 0 || pw <= 0 || H % ph || W % pw || C % 2)
+    return set_error(SAV_ERR_SHAPE, "sav_patchify_act: H, W multiples of the patch shape, C even");
+  const int64_t total2 = B * H * W * (C / 2);
+  patchify_act_kernel<<<cnn_blocks(total2), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const bf16*>(src), reinterpret_cast<bf16*>(dst), total2, (int)H, (int)W, (int)(C / 2),
+      (int)ph, (int)pw, inverse);
+  count_launch();
+  return check_launch("sav_patchify_act");
 }

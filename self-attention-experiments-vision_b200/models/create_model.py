@@ -10,6 +10,7 @@ from models.cait import CaiT
 from models.cvt import CvT
 from models.mlp_mixer import MLPMixer
 from models.tnt import TNT
+from models.ceit import CeiT
 from models.vit import ViT
 
 _VIT = {
@@ -58,6 +59,9 @@ _CVT = {
 # create_model.py:50-63: (inner heads, outer heads, inner dim, outer dim), 12 layers
 _TNT = {'tnt_s_patch16': (4, 10, 40, 640), 'tnt_b_patch16': (4, 6, 24, 384)}
 
+# create_model.py:64-78: (heads, embed_dim), 12 layers
+_CEIT = {'ceit_t': (3, 192), 'ceit_s': (6, 384), 'ceit_b': (12, 768)}
+
 _MIXER = {
     # create_model.py:184-213 verbatim (layers, embed_dim, patch).  The reference spells the B/16
     # entry 'mixer_s_patch32' a second time (create_model.py:199), so it is unreachable there; it is
@@ -87,6 +91,9 @@ def create_model(model_name: str, num_classes: int = 1000, dtype=None):
     if model_name in _MIXER:
         layers, dim, p = _MIXER[model_name]
         return MLPMixer(num_classes=num_classes, num_layers=layers, embed_dim=dim, patch_shape=(p, p))
+    if model_name in _CEIT:
+        heads, dim = _CEIT[model_name]
+        return CeiT(num_classes=num_classes, num_layers=12, num_heads=heads, embed_dim=dim)
     if model_name in _TNT:
         ih, oh, idim, odim = _TNT[model_name]
         return TNT(num_classes=num_classes, num_layers=12, inner_num_heads=ih, outer_num_heads=oh,

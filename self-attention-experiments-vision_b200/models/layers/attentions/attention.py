@@ -45,7 +45,9 @@ class AttentionBlock(nn.Module):
             mix = (TalkingHeadsBlock(num_heads=H)(), TalkingHeadsBlock(num_heads=H)())
         # plain attention with d = 64 runs in the fused TMEM kernel; talking heads and other head
         # dims go through the materialised-logits path (batched GEMMs + one row kernel)
-        fused = mix is None and d == 64
+        # (a handful of query rows -- CeiT's layer-wise class attention, one query over 12 keys -- is
+        # not worth a 128-row TMEM tile either)
+        fused = mix is None and d == 64 and inputs_q.shape[1] >= 8
         if inputs_q is inputs_kv:
             qkv = F.linear(inputs_q, w_qkv)                  # attention.py:35-37, one GEMM
             if mix is None and d <= 16 and inputs_q.shape[1] <= 32:

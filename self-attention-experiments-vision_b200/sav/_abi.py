@@ -140,6 +140,9 @@ SIGNATURES = {
     "sav_layernorm_bwd_f32": (C.c_int, [_P, _I64, _P, _I64] + [_P] * 8 + [_I64, _I64, _P]),
     "sav_cast2d_bf16_f32": (C.c_int, [_P, _I64, _P, _I64, _I64, _I64, _I32, _P]),
     "sav_dp_allreduce_sum_f32": (C.c_int, [C.c_uint64, _P, _P, _I64, _I64, _I64, _I32, _I32, _I32, _P]),
+    "sav_maxpool3x3s2_valid_fwd": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P]),
+    "sav_maxpool3x3s2_valid_bwd": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P]),
+    "sav_patchify_act": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _I64, _I64, _I32, _P]),
     "sav_pixel_patchify": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _I64, _I64, _I64, _I64, _I32, _P]),
     "sav_attn_small_fwd": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _F, _P]),
     "sav_attn_small_bwd": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _F, _P]),

@@ -162,9 +162,11 @@ class LazyLinear(Var):
         if self.residual is not None and self.residual.requires_grad:
             # the skip path passes the fp32 stream gradient on; the branch below uses the bf16 copy
             if self.residual.g is not None:
-                raise NotImplementedError("residual-stream Var with a second consumer before its "
-                                          "LayerNorm backward")
-            self.residual.g = self.g.view(self.residual.v.shape)
+                # a skip input with another consumer whose gradient arrived first (CeiT: a block's
+                # output also feeds the class-token list, ceit.py:66-70)
+                _add_grad(self.residual, self.g.view(self.residual.v.shape))
+            else:
+                self.residual.g = self.g.view(self.residual.v.shape)
         scaled = self.col_scale is not None or self.row_scale is not None
         if scaled:
             # reverse mode of the LayerScale / drop-path epilogue: the branch gradient is the fp32
@@ -1026,7 +1028,7 @@ def stream_first_token(x):
 
 
 # ------------------------------------------------------------------ BoTNet conv stages (bf16 NHWC)
-def conv2d(x, kernel, ksize, stride, padding="SAME"):
+def conv2d(x, kernel, ksize, stride, padding="SAME", bias=None):
     """nn.Conv(use_bias=False) of the BoTNet stem / bottleneck blocks (botnet.py:280-285,47-64):
     x bf16 Var [B,H,W,Cin] (or raw / HWCN fp32 images for the stem) -> bf16 Var [B,Ho,Wo,Cout].
     1x1 stride-1 convs are the GEMM itself; everything else goes through im2col / col2im."""
@@ -1050,7 +1052,7 @@ def conv2d(x, kernel, ksize, stride, padding="SAME"):
         g = ops.conv2d_geom(B, H, W, Cin, ksize, stride, padding, xs)
         A = ops.im2col(t, g)[:, :K]
         Ho, Wo = g.Ho, g.Wo
-    y = ops.gemm(A, W2, b_mn=True)
+    y = ops.gemm(A, W2, b_mn=True, bias=bias.master if bias is not None else None)
     out = Var(y.view(B, Ho, Wo, Cout))
 
     def bwd():
@@ -1059,6 +1061,9 @@ def conv2d(x, kernel, ksize, stride, padding="SAME"):
             return
         dy2 = dy.contiguous().view(-1, Cout)
         kernel.touch_grad()
+        if bias is not None:
+            bias.touch_grad()
+            ops.colsum(dy2, out=bias.grad, accumulate=True)
         ops.gemm(A, dy2, a_mn=True, b_mn=True, out=kernel.grad.reshape(K, Cout), accumulate=True, split_k=0)
         if src is None:
             return
@@ -1159,20 +1164,23 @@ def spatial_mean(x):
     return out
 
 
-def maxpool3x3s2(x):
-    """nn.max_pool(x, (3, 3), strides=(2, 2), padding='SAME') (botnet.py:297)."""
+def maxpool3x3s2(x, valid=False):
+    """nn.max_pool(x, (3, 3), strides=(2, 2), padding='SAME') (botnet.py:297); valid=True is flax's
+    default 'VALID' padding (image_to_token.py:33-37)."""
     t = x.v
     if _meta(t):
         B, H, W, C = t.shape
+        if valid:
+            return Var(torch.empty((B, (H - 3) // 2 + 1, (W - 3) // 2 + 1, C), dtype=BF16, device="meta"))
         return Var(torch.empty((B, -(-H // 2), -(-W // 2), C), dtype=BF16, device="meta"))
     tc = t.contiguous()
-    y, arg = ops.maxpool3x3s2_fwd(tc)
+    y, arg = ops.maxpool3x3s2_fwd(tc, valid)
     out = Var(y)
 
     def bwd():
         d = out.take_grad()
         if d is not None and x.requires_grad:
-            _add_grad(x, ops.maxpool3x3s2_bwd(d.contiguous(), arg, tuple(tc.shape)).view(t.shape))
+            _add_grad(x, ops.maxpool3x3s2_bwd(d.contiguous(), arg, tuple(tc.shape), valid).view(t.shape))
     record(bwd)
     return out
 
@@ -1467,5 +1475,137 @@ def inner_to_outer(patch_inputs, inner):
             _add_grad(inner, d16.view(iv.shape))
         if patch_inputs.requires_grad:
             _add_grad(patch_inputs, g)
+    record(bwd)
+    return out
+
+
+# ------------------------------------------------------------------ CeiT (models/ceit.py)
+def patchify_act(x, ph, pw):
+    """'b (h ph) (w pw) c -> b (h w) (ph pw c)' of a bf16 activation (image_to_token.py:38-43)."""
+    t = x.v
+    B, H, W, C = t.shape
+    if _meta(t):
+        return Var(torch.empty((B, (H // ph) * (W // pw), ph * pw * C), dtype=BF16, device="meta"))
+    out = Var(ops.patchify_act(t.contiguous(), B, H, W, C, ph, pw))
+
+    def bwd():
+        g = out.take_grad()
+        if g is not None and x.requires_grad:
+            _add_grad(x, ops.patchify_act(g.contiguous(), B, H, W, C, ph, pw, inverse=True))
+    record(bwd)
+    return out
+
+
+def stream_tokens_operand(x):
+    """inputs[:, 1:] of the fp32 stream as a bf16 operand (leff.py:22: LeFF works on the patch tokens,
+    the class token bypasses it); its gradient is added into rows 1.. of the stream's gradient."""
+    t = x.v
+    B, L1, C = t.shape
+    L = L1 - 1
+    if _meta(t):
+        return Var(torch.empty((B, L, C), dtype=BF16, device="meta"))
+    if t.dtype != F32:
+        raise TypeError("stream_tokens_operand: fp32 residual stream expected")
+    tc = t.contiguous()
+    out = Var(ops.scale_rows_cols(tc.view(B, L1 * C)[:, C:], None, None, 1).view(B, L, C))
+
+    def bwd():
+        g = out.take_grad()
+        if g is None or not x.requires_grad:
+            return
+        if x.g is None:
+            full = torch.empty((B, L1 * C), dtype=F32, device=t.device)
+            ops.fill(full, 0.0)
+            x.g = full.view(B, L1, C)
+        ops.cast2d_bf16_f32(g.contiguous().view(B, L * C), x.g.view(B, L1 * C)[:, C:], accumulate=True)
+        x.g16 = None
+    record(bwd)
+    return out
+
+
+def leff_residual(x, tokens):
+    """y = x + concat([x[:, :1], tokens]) (leff.py:63-65 + ceit.py:42): the class token passes LeFF
+    unchanged and is then added to itself, the patch tokens get the LeFF branch.  x: fp32 stream
+    [B, 1 + L, C]; tokens: bf16 [B, L, C] -> new fp32 stream."""
+    xv, tv = x.v, tokens.v
+    B, L1, C = xv.shape
+    L = L1 - 1
+    if _meta(xv):
+        return Var(torch.empty((B, L1, C), dtype=F32, device="meta"))
+    if xv.dtype != F32:
+        raise TypeError("leff_residual: the skip input must be the fp32 residual stream")
+    xc = xv.contiguous().view(B, L1 * C)
+    y = torch.empty((B, L1 * C), dtype=F32, device=xv.device)
+    ops.copy2d_f32(xc, y)
+    ops.copy2d_f32(xc[:, :C], y[:, :C], accumulate=True)
+    ops.cast2d_bf16_f32(tv.contiguous().view(B, L * C), y[:, C:], accumulate=True)
+    out = Var(y.view(B, L1, C))
+
+    def bwd():
+        g = out.take_grad()
+        out.g16 = None
+        if g is None:
+            return
+        g2 = g.contiguous().view(B, L1 * C)
+        if tokens.requires_grad:
+            tmp = torch.empty((B, L * C), dtype=F32, device=g.device)
+            ops.copy2d_f32(g2[:, C:], tmp)
+            d16 = torch.empty((B, L, C), dtype=BF16, device=g.device)
+            ops.cast_bf16(tmp, d16)
+            _add_grad(tokens, d16.view(tv.shape))
+        if x.requires_grad:
+            gx = torch.empty((B, L1 * C), dtype=F32, device=g.device)
+            ops.copy2d_f32(g2, gx)
+            ops.copy2d_f32(g2[:, :C], gx[:, :C], accumulate=True)
+            _add_grad(x, gx.view(B, L1, C))
+    record(bwd)
+    return out
+
+
+def stack_tokens(rows):
+    """jnp.concatenate([expand_dims(r, 1) for r in rows], axis=1) of bf16 [B, C] Vars -> [B, n, C]
+    (ceit.py:66-72: the class tokens of every encoder block)."""
+    n = len(rows)
+    B, C = rows[0].shape
+    if _meta(rows[0].v):
+        return Var(torch.empty((B, n, C), dtype=BF16, device="meta"))
+    buf = torch.empty((B, n * C), dtype=BF16, device=rows[0].v.device)
+    for i, r in enumerate(rows):
+        ops.copy2d(r.v.reshape(B, C), buf[:, i * C:(i + 1) * C])
+    out = Var(buf.view(B, n, C))
+
+    def bwd():
+        g = out.take_grad()
+        if g is None:
+            return
+        g2 = g.contiguous().view(B, n * C)
+        for i, r in enumerate(rows):
+            if r.requires_grad:
+                gi = torch.empty((B, C), dtype=BF16, device=g2.device)
+                ops.copy2d(g2[:, i * C:(i + 1) * C], gi)
+                _add_grad(r, gi.view(r.v.shape))
+    record(bwd)
+    return out
+
+
+def last_token(x):
+    """inputs[:, -1:, :] of a bf16 [B, n, C] Var (ceit.py:14: the query of the layer-wise class
+    attention) -> [B, 1, C]."""
+    t = x.v
+    B, n, C = t.shape
+    if _meta(t):
+        return Var(torch.empty((B, 1, C), dtype=BF16, device="meta"))
+    q = torch.empty((B, C), dtype=BF16, device=t.device)
+    ops.copy2d(t.contiguous().view(B, n * C)[:, (n - 1) * C:], q)
+    out = Var(q.view(B, 1, C))
+
+    def bwd():
+        g = out.take_grad()
+        if g is None or not x.requires_grad:
+            return
+        full = torch.empty((B, n * C), dtype=BF16, device=t.device)
+        ops.fill(full.view(torch.float32), 0.0)
+        ops.copy2d(g.contiguous().view(B, C), full[:, (n - 1) * C:])
+        _add_grad(x, full.view(B, n, C))
     record(bwd)
     return out

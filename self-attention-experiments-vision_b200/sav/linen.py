@@ -428,11 +428,15 @@ class LayerNorm(Module):
     """flax.linen.LayerNorm (vit.py:19,26,57): epsilon 1e-6, scale ones, bias zeros."""
     epsilon: float = 1e-6
     dtype: object = None
+    stream_out: bool = False     # (not a flax field) the OUTPUT is the fp32 residual stream: post-LN
+                                 # blocks add their branches to the normalised tensor (ceit.py:36-44)
 
     def __call__(self, inputs):
         C = inputs.shape[-1]
         scale = self.param("scale", initializers.ones, (C,))
         bias = self.param("bias", initializers.zeros, (C,))
+        if self.stream_out:
+            return F.layernorm_stream(inputs, scale, bias, self.epsilon)
         return F.layernorm(inputs, scale, bias, self.epsilon)
 
 
@@ -475,6 +479,8 @@ sigmoid = activation.sigmoid
 def _act_kind(fn):
     if fn is None:
         return "none"
+    if fn is F.gelu:
+        return "gelu"
     kind = getattr(fn, "kind", None)
     if kind is None:
         raise NotImplementedError("conv-stage activation must be one of nn.swish / nn.relu / nn.sigmoid")
@@ -494,9 +500,6 @@ class Conv(Module):
     kernel_init: object = None
 
     def __call__(self, inputs):
-        if self.use_bias:
-            raise NotImplementedError("nn.Conv(use_bias=True) on the bf16 conv-stage path (the CvT token "
-                                      "embedding uses functional.conv2d_stream)")
         kh, kw = self.kernel_size
         sh, sw = self.strides if not isinstance(self.strides, int) else (self.strides, self.strides)
         if kh != kw or sh != sw:
@@ -510,7 +513,8 @@ class Conv(Module):
             if len(lo) != 1:
                 raise NotImplementedError("nn.Conv: symmetric explicit padding only")
             pad = lo.pop()
-        return F.conv2d(inputs, kernel, kh, sh, pad)
+        bias = self.param("bias", initializers.zeros, (self.features,)) if self.use_bias else None
+        return F.conv2d(inputs, kernel, kh, sh, pad, bias=bias)
 
 
 class BatchNorm(Module):

@@ -655,7 +655,7 @@ def transpose_pad(src, R, C, out, out_cols, residual=None):
 
 
 # ------------------------------------------------------------------ BoTNet conv-stage pieces (cnn.cu)
-ACT = {"none": 0, "swish": 1, "sigmoid": 2, "relu": 3}
+ACT = {"none": 0, "swish": 1, "sigmoid": 2, "relu": 3, "gelu": 4}
 
 
 def act_fwd(x, kind):
@@ -731,18 +731,32 @@ def spatial_mean_bwd(dout, shape):
     return dx
 
 
-def maxpool3x3s2_fwd(x):
+def maxpool3x3s2_fwd(x, valid=False):
     B, H, W, Cc = x.shape
-    Ho, _ = conv_same_geom(H, 3, 2)
-    Wo, _ = conv_same_geom(W, 3, 2)
+    if valid:
+        Ho, Wo = (H - 3) // 2 + 1, (W - 3) // 2 + 1
+    else:
+        Ho, _ = conv_same_geom(H, 3, 2)
+        Wo, _ = conv_same_geom(W, 3, 2)
     y = torch.empty((B, Ho, Wo, Cc), dtype=BF16, device=x.device)
     arg = torch.empty((B, Ho, Wo, Cc), dtype=torch.uint8, device=x.device)
-    check(lib().sav_maxpool3x3s2_fwd(_p(x), _p(y), _p(arg), B, H, W, Cc, _stream()))
+    fn = lib().sav_maxpool3x3s2_valid_fwd if valid else lib().sav_maxpool3x3s2_fwd
+    check(fn(_p(x), _p(y), _p(arg), B, H, W, Cc, _stream()))
     return y, arg
 
 
-def maxpool3x3s2_bwd(dy, arg, shape):
+def maxpool3x3s2_bwd(dy, arg, shape, valid=False):
     B, H, W, Cc = shape
     dx = torch.empty(shape, dtype=BF16, device=dy.device)
-    check(lib().sav_maxpool3x3s2_bwd(_p(dy), _p(arg), _p(dx), B, H, W, Cc, _stream()))
+    fn = lib().sav_maxpool3x3s2_valid_bwd if valid else lib().sav_maxpool3x3s2_bwd
+    check(fn(_p(dy), _p(arg), _p(dx), B, H, W, Cc, _stream()))
     return dx
+
+
+def patchify_act(src, B, H, W, Cc, ph, pw, inverse=False):
+    """bf16 [B,H,W,C] -> [B, (H/ph)(W/pw), ph*pw*C] (image_to_token.py:38-43), or back."""
+    _req(src, BF16, "src")
+    shape = (B, H, W, Cc) if inverse else (B, (H // ph) * (W // pw), ph * pw * Cc)
+    dst = torch.empty(shape, dtype=BF16, device=src.device)
+    check(lib().sav_patchify_act(_p(src), _p(dst), B, H, W, Cc, ph, pw, int(inverse), _stream()))
+    return dst
