@@ -848,3 +848,149 @@ def tnt_loss_and_grads(params, images_hwcn, labels, cfg, label_smoothing=0.0):
     loss.backward()
     grads = tree_map(lambda t: t.grad if t.grad is not None else torch.zeros_like(t), p)
     return loss.detach(), logits.detach(), grads
+
+
+# ----------------------------------------------------------------------------- CeiT
+def image_to_token(images_nhwc, p, cfg, eps=1e-5):
+    """Image2TokenBlock.__call__ (image_to_token.py:22-48): Conv k x k / stride s with explicit
+    padding = the patch shape, no bias -> BatchNorm (batch statistics) -> max_pool (flax default
+    padding 'VALID') -> 'b (h ph) (w pw) c -> b (h w) (ph pw c)' -> Dense without bias."""
+    ph, pw = cfg["patch_shape"]
+    assert ph == pw
+    y = conv2d_nobias(images_nhwc, p["Conv_0"]["kernel"], cfg["conv_stride"], ph)         # :24-29
+    y = batch_norm_train(y, p["BatchNorm_0"], eps)                                        # :30-33
+    y = torch.nn.functional.max_pool2d(y.permute(0, 3, 1, 2), cfg["pool_window_size"],
+                                       cfg["pool_stride"]).permute(0, 2, 3, 1)            # :34-38
+    return _rb(patch_embed(_rb(y), _rb(p["Dense_0"]["kernel"]), ph, pw))                  # :39-48
+
+
+def leff_block(x, p, kernel_size, eps=1e-5):
+    """LeFFBlock.__call__ (leff.py:20-63), expand_ratio given: the class token bypasses the block;
+    the patch tokens go Dense -> BatchNorm -> gelu -> (on the sqrt(l) x sqrt(l) grid) Conv k x k
+    'SAME' with bias -> BatchNorm -> gelu -> Dense -> BatchNorm -> gelu."""
+    from .vit_oracle import gelu_tanh
+    cls, tokens = x[:, 0], x[:, 1:]                                                       # :22
+    b, l, c = tokens.shape
+    act = lambda t: _rb(gelu_tanh(t))   # noqa: E731
+    h = _rb(_rb(tokens) @ _rb(p["Dense_0"]["kernel"]) + p["Dense_0"]["bias"])             # :41
+    h = act(batch_norm_train(h, p["BatchNorm_0"], eps))                                   # :42-43
+    side = int(math.sqrt(l))                                                              # :45
+    h = h.reshape(b, side, side, -1)                                                      # :46
+    h = _rb(conv2d_same(_rb(h), _rb(p["Conv_0"]["kernel"]), p["Conv_0"]["bias"], 1))      # :48-53
+    h = act(batch_norm_train(h, p["BatchNorm_1"], eps))                                   # :54-55
+    h = h.reshape(b, l, -1)                                                               # :57
+    h = _rb(_rb(h) @ _rb(p["Dense_1"]["kernel"]) + p["Dense_1"]["bias"])                  # :59
+    h = act(batch_norm_train(h, p["BatchNorm_2"], eps))                                   # :60-61
+    return torch.cat([cls[:, None], h], dim=1)                                            # :63-65
+
+
+def _ceit_attention(xq, xkv, p, num_heads):
+    """attention.py:21-67 through vit_oracle.attention; under EMULATE_BF16 the same arithmetic with
+    round-to-bf16 at the tensors a bf16 pipeline stores (operand, weights, q / k / v, P, context)."""
+    if not EMULATE_BF16[0]:
+        return attention(xq, xkv, p, num_heads)
+    wq, wk, wv = (_rb(p[n]["kernel"]) for n in ("queries", "keys", "values"))
+    xq, xkv = _rb(xq), _rb(xkv)
+    q = _rb(torch.einsum("bqc,chd->bqhd", xq, wq))
+    k = _rb(torch.einsum("bkc,chd->bkhd", xkv, wk))
+    v = _rb(torch.einsum("bkc,chd->bkhd", xkv, wv))
+    w = softmax_last(torch.einsum("bqhd,bkhd->bhqk", q / math.sqrt(wq.shape[-1]), k))
+    o = _rb(torch.einsum("bhqk,bkhd->bqhd", _rb(w), v))
+    return torch.einsum("bqhd,hdc->bqc", o, _rb(p["DenseGeneral_0"]["kernel"]))
+
+
+def ceit_encoder_block(x, p, num_heads, kernel_size):
+    """ceit.py EncoderBlock.__call__ (ceit.py:28-44), post-LN."""
+    ln = lambda t, q: layer_norm(t, q["scale"], q["bias"])   # noqa: E731
+    y = _ceit_attention(x, x, p["SelfAttentionBlock_0"], num_heads)                       # :29-31
+    y = y + x                                                                             # :32
+    y = ln(y, p["LayerNorm_0"])                                                           # :33
+    z = leff_block(y, p["LeFFBlock_0"], kernel_size)                                      # :35-40
+    return ln(y + z, p["LayerNorm_1"])                                                    # :41-43
+
+
+def ceit_forward(params, images_nhwc, cfg):
+    """CeiT.__call__ (ceit.py:114-154) + Encoder.__call__ (ceit.py:57-72) + LCSelfAttentionBlock
+    (ceit.py:11-16)."""
+    x = image_to_token(images_nhwc, params["Image2TokenBlock_0"], cfg)                    # :117-126
+    b = x.shape[0]
+    x = torch.cat([params["cls"].expand(b, -1, -1), x], dim=1)                            # :128-133
+    enc = params["Encoder_0"]
+    cls_tokens = []
+    for i in range(cfg["num_layers"]):                                                    # :66-70
+        x = ceit_encoder_block(x, enc[f"EncoderBlock_{i}"], cfg["num_heads"], cfg["leff_kernel_size"])
+        cls_tokens.append(x[:, :1])
+    t = torch.cat(cls_tokens, dim=1)                                                      # :72
+    t = _rb(t)
+    t = _ceit_attention(t[:, -1:], t, params["LCSelfAttentionBlock_0"], cfg["num_heads"])  # :14-16,143-147
+    cls = _rb(t[:, -1])                                                                   # :148
+    return cls @ _rb(params["Dense_0"]["kernel"]) + params["Dense_0"]["bias"]             # :149-153
+
+
+def ceit_config(name):
+    """create_model.py:64-78 + the CeiT dataclass defaults (ceit.py:100-112)."""
+    heads, dim = {"ceit_t": (3, 192), "ceit_s": (6, 384), "ceit_b": (12, 768)}[name]
+    return dict(num_layers=12, num_heads=heads, embed_dim=dim, patch_shape=(4, 4), num_ch=32,
+                conv_kernel_size=7, conv_stride=2, pool_window_size=3, pool_stride=2, expand_ratio=4,
+                leff_kernel_size=3, num_classes=1000)
+
+
+def synthetic_ceit_params(cfg, seed=42, dtype=torch.float32):
+    """SURVEY 8d synthetic init with the Flax auto-names of ceit.py / leff.py / image_to_token.py."""
+    g = torch.Generator().manual_seed(seed)
+
+    def normal(shape, std):
+        return (torch.randn(shape, generator=g, dtype=torch.float64) * std).to(dtype)
+
+    def dense(k, n, bias=True):
+        d = {"kernel": normal((k, n), 1.0 / math.sqrt(k))}
+        if bias:
+            d["bias"] = normal((n,), 0.02)
+        return d
+
+    def bn(c):
+        return {"scale": 1.0 + normal((c,), 0.1), "bias": normal((c,), 0.1)}
+
+    def ln(c):
+        return {"scale": 1.0 + normal((c,), 0.02), "bias": normal((c,), 0.02)}
+
+    def attn(c, h):
+        d = c // h
+        return {"queries": {"kernel": normal((c, h, d), 1.0 / math.sqrt(c))},
+                "keys": {"kernel": normal((c, h, d), 1.0 / math.sqrt(c))},
+                "values": {"kernel": normal((c, h, d), 1.0 / math.sqrt(c))},
+                "DenseGeneral_0": {"kernel": normal((h, d, c), 1.0 / math.sqrt(c))}}
+    C, H = cfg["embed_dim"], cfg["num_heads"]
+    ph, pw = cfg["patch_shape"]
+    k, nch = cfg["conv_kernel_size"], cfg["num_ch"]
+    hid = max(1, int(cfg["expand_ratio"] * C))
+    kl = cfg["leff_kernel_size"]
+    enc = {}
+    for i in range(cfg["num_layers"]):
+        enc[f"EncoderBlock_{i}"] = {
+            "SelfAttentionBlock_0": attn(C, H), "LayerNorm_0": ln(C),
+            "LeFFBlock_0": {"Dense_0": dense(C, hid), "BatchNorm_0": bn(hid),
+                            "Conv_0": {"kernel": normal((kl, kl, hid, hid), 1.0 / math.sqrt(kl * kl * hid)),
+                                       "bias": normal((hid,), 0.02)},
+                            "BatchNorm_1": bn(hid), "Dense_1": dense(hid, C), "BatchNorm_2": bn(C)},
+            "LayerNorm_1": ln(C)}
+    nc = cfg["num_classes"]
+    return {"Image2TokenBlock_0": {"Conv_0": {"kernel": normal((k, k, 3, nch), 1.0 / math.sqrt(k * k * 3))},
+                                   "BatchNorm_0": bn(nch), "Dense_0": dense(ph * pw * nch, C, bias=False)},
+            "cls": normal((1, 1, C), 0.02),
+            "Encoder_0": enc,
+            "LCSelfAttentionBlock_0": attn(C, H),
+            "Dense_0": {"kernel": normal((C, nc), 0.02), "bias": normal((nc,), 0.02)}}
+
+
+def ceit_loss_and_grads(params, images_hwcn, labels, cfg, label_smoothing=0.0, emulate_bf16=False):
+    p = tree_map(lambda t: t.detach().clone().requires_grad_(True), params)
+    EMULATE_BF16[0] = bool(emulate_bf16)
+    try:
+        logits = ceit_forward(p, hwcn_to_nhwc(images_hwcn), cfg)
+    finally:
+        EMULATE_BF16[0] = False
+    loss = loss_fn(logits, labels, cfg["num_classes"], label_smoothing)
+    loss.backward()
+    grads = tree_map(lambda t: t.grad if t.grad is not None else torch.zeros_like(t), p)
+    return loss.detach(), logits.detach(), grads

@@ -1013,8 +1013,15 @@ def stream_first_token(x):
         g = out.take_grad()
         if g is None or not x.requires_grad:
             return
+        g2 = g.reshape(B, C).contiguous()
         if x.g is not None:
-            raise NotImplementedError("stream_first_token on a stream Var with another consumer")
+            # the stream has later consumers whose gradients arrived first (CeiT: every block's
+            # class token is collected while the stream goes on to the next block, ceit.py:66-70)
+            if not x.g.is_contiguous():
+                x.g = x.g.contiguous()
+            ops.cast2d_bf16_f32(g2, x.g.view(B * N, C)[::N], accumulate=True)
+            x.g16 = None
+            return
         full = torch.empty((B * N, C), dtype=F32, device=t.device)
         full16 = torch.empty((B * N, C), dtype=BF16, device=t.device)
         ops.fill(full, 0.0)
