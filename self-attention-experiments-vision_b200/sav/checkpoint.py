@@ -93,6 +93,10 @@ def state_dict_of(train_state):
     arena = train_state.arena
     step = _i32(train_state.step)
     sd = {"step": step, "params": {"params": _tree_to_numpy(arena.tree())}}
+    if getattr(train_state, "batch_stats", None):
+        # the reference keeps the whole model.init() variables under `params` (train.py:31-37), so
+        # the BatchNorm running averages sit beside the parameter tree
+        sd["params"]["batch_stats"] = _tree_to_numpy(train_state.batch_stats)
     if arena.m is not None:
         sd["opt_state"] = {
             "0": {},
@@ -108,7 +112,8 @@ def state_dict_of(train_state):
 def _strip_params_level(tree):
     """The reference stores whole variables ({'params': tree}); older files of this repo stored the
     tree directly.  Return the parameter tree either way."""
-    if isinstance(tree, dict) and set(tree.keys()) == {"params"} and isinstance(tree["params"], dict):
+    if isinstance(tree, dict) and "params" in tree and set(tree.keys()) <= {"params", "batch_stats"} \
+            and isinstance(tree["params"], dict):
         return tree["params"]
     return tree
 
@@ -161,6 +166,9 @@ def restore_checkpoint(ckpt_dir_or_file, train_state=None, prefix="checkpoint_")
         import torch
         arena = train_state.arena
         arena.load_tree(_map(_strip_params_level(sd["params"]), torch.from_numpy))
+        saved_stats = sd["params"].get("batch_stats") if isinstance(sd["params"], dict) else None
+        if saved_stats is not None and getattr(train_state, "batch_stats", None):
+            _copy_into(train_state.batch_stats, saved_stats)
         if "opt_state" in sd:
             mu, nu, _count = _adam_state(sd["opt_state"])
             arena.ensure_moments()
@@ -172,6 +180,16 @@ def restore_checkpoint(ckpt_dir_or_file, train_state=None, prefix="checkpoint_")
         else:
             train_state.step = step
     return sd
+
+
+def _copy_into(dst_tree, src_tree):
+    """In-place load of a nested dict of numpy arrays into same-named device tensors."""
+    import torch
+    for k, v in dst_tree.items():
+        if isinstance(v, dict):
+            _copy_into(v, src_tree[k])
+        else:
+            v.copy_(torch.from_numpy(np.ascontiguousarray(src_tree[k])).to(v.dtype))
 
 
 def _map(tree, fn):

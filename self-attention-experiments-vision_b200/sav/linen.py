@@ -243,8 +243,17 @@ class Module:
             if run.mode == "apply" and run.had_batch_stats:
                 raise KeyError(f"batch_stats/{'/'.join(path)} not found in variables")
             # apply() without the collection (train.py's call shape): a scratch state that
-            # the training-mode statistics never read
-            run.batch_stats[path] = self._to_dev(init_fn(None, tuple(shape)), run)
+            # the training-mode statistics never read.  It is created once per arena and reused by
+            # later apply() calls: a captured step must not issue a host -> device copy.
+            cache = getattr(run.arena, "_scratch_stats", None) if run.arena is not None else None
+            if cache is None and run.arena is not None:
+                cache = run.arena._scratch_stats = {}
+            if cache is not None and path in cache:
+                run.batch_stats[path] = cache[path]
+            else:
+                run.batch_stats[path] = self._to_dev(init_fn(None, tuple(shape)), run)
+                if cache is not None:
+                    cache[path] = run.batch_stats[path]
         return run.batch_stats[path]
 
     def is_mutable_collection(self, collection):

@@ -21,7 +21,10 @@ def load_params(model, tree, *example_args, device="cuda", **example_kw):
     e.g. the oracle's or a reference checkpoint's) into it.  Returns {'params': ParamTree}."""
     variables = model.init({"params": 0}, *example_args, device=device, **example_kw)
     arena = variables["params"].arena
-    return {"params": arena.load_tree(tree)}
+    out = {"params": arena.load_tree(tree)}
+    if "batch_stats" in variables:      # BatchNorm running averages as init() made them (0 / 1)
+        out["batch_stats"] = variables["batch_stats"]
+    return out
 
 
 class WarmupCosine:
@@ -57,13 +60,20 @@ def reference_schedule(lr, batch_size, steps_per_epoch):
     return WarmupCosine(0.0, lr * (batch_size / 512), 5 * steps_per_epoch, 30 * steps_per_epoch, 1e-5)
 
 
-def make_loss_fn(model, label_smoothing=0.0, world_size=1, rngs=None, reference_double_scale=False):
+def make_loss_fn(model, label_smoothing=0.0, world_size=1, rngs=None, reference_double_scale=False,
+                 batch_stats=None):
     """train.py:79-92.  `batch` form: loss_fn(params, images, labels, mix_labels=None, ratio=None)
     (the 'mix_labels' / 'ratio' keys of train.py:84-87).  reference_double_scale reproduces the
     reference's `loss / device_count` FOLLOWED by pmean (net 1/world^2); the default is
-    the plain global mean."""
+    the plain global mean.  batch_stats: the BatchNorm running averages of a CvT / BoTNet / CeiT
+    state; they are updated in place on the device (apply(..., mutable=['batch_stats']) -- the
+    reference's own train.py omits the collection and cannot train those models)."""
     def loss_fn(params, images, labels, mix_labels=None, ratio=None):
-        logits = model.apply({"params": params}, images, is_training=True, rngs=rngs)
+        if batch_stats is not None:
+            logits, _ = model.apply({"params": params, "batch_stats": batch_stats}, images,
+                                    is_training=True, rngs=rngs, mutable=["batch_stats"])
+        else:
+            logits = model.apply({"params": params}, images, is_training=True, rngs=rngs)
         w = world_size * world_size if reference_double_scale else world_size
         loss = F.softmax_cross_entropy(logits, labels, label_smoothing, w, mix_labels, ratio)
         return loss, logits
@@ -90,6 +100,8 @@ class TrainState:
         self.model = model
         self.apply_fn = model.apply
         self.params = variables["params"]
+        # flax 'batch_stats' collection (BatchNorm running averages) when the model has one
+        self.batch_stats = variables.get("batch_stats") if isinstance(variables, dict) else None
         self.arena = self.params.arena
         self.arena.ensure_moments()
         self.step = 0                       # host mirror of step_dev
@@ -165,7 +177,7 @@ def train_step(state, images, labels, label_smoothing=0.0, dp=None, mix_labels=N
     world = dp.world_size if dp is not None else 1
     double = bool(getattr(dp, "reference_double_scale", False))
     loss_fn = make_loss_fn(state.model, label_smoothing, world, rngs=state.rngs,
-                           reference_double_scale=double)
+                           reference_double_scale=double, batch_stats=getattr(state, "batch_stats", None))
     # dp is the gradient hook: finished buckets are all-reduced while backward is still running
     (loss, _logits), _grads = value_and_grad(loss_fn, has_aux=True, grad_hook=dp)(
         state.params, images, labels, mix_labels, ratio)
@@ -188,7 +200,10 @@ def eval_step(state, images, labels, dp=None):
     """train.py:112-120: logits with is_training=False, plain one-hot softmax cross entropy (no
     smoothing, no mixup), mean over the local batch, / device_count, psum over ranks.  The
     collective (train.py:120) is one all-reduce of the per-rank loss sum."""
-    logits = state.apply_fn({"params": state.params}, images, is_training=False)
+    variables = {"params": state.params}
+    if getattr(state, "batch_stats", None) is not None:
+        variables["batch_stats"] = state.batch_stats      # BatchNorm: use_running_average (eval mode)
+    logits = state.apply_fn(variables, images, is_training=False)
     lv = logits.v
     B = lv.shape[0]
     _dl, stats = ops.softmax_xent(lv.contiguous(), labels, 0.0, 0.0)

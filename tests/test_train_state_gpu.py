@@ -161,3 +161,69 @@ def test_eval_step_matches_oracle():
                            cfg["patch_shape"])
     ref = float(O.loss_fn(logits, labels, 1000, 0.0))
     assert abs(loss.item() - ref) <= 2e-2 * abs(ref), (loss.item(), ref)
+
+
+@pytest.mark.gpu
+def test_batchnorm_model_trains_under_graph_capture_with_running_averages(tmp_path):
+    """CvT / BoTNet / CeiT carry flax's 'batch_stats' collection.  The reference's train.py applies the
+    model without it (and so cannot train them); TrainState here keeps the running averages,
+    the captured step updates them in place on the device (momentum 0.9, leff.py:35-39), eval_step
+    normalises with them (use_running_average), and the checkpoint stores them beside the parameters.
+    Also: a state WITHOUT the collection (the reference's call shape) still captures -- its scratch
+    statistics are created once, not by a host -> device copy inside the graph."""
+    import sav
+    from models import CeiT
+    from oracle import variants_oracle as V
+    from sav import checkpoint as C
+    from sav.train import HWCN, GraphedTrainStep, TrainState, eval_step
+    cfg = V.ceit_config("ceit_t")
+    cfg["num_layers"] = 2
+    params = V.synthetic_ceit_params(cfg, seed=7)
+    images, labels = O.synthetic_batch(8, img_size=224, seed=0)
+    x, y = HWCN(images.cuda()), labels.cuda()
+
+    def make(with_stats):
+        model = CeiT(num_classes=1000, num_layers=2, num_heads=cfg["num_heads"], embed_dim=cfg["embed_dim"])
+        variables = sav.load_params(model, params, x, is_training=True)
+        if not with_stats:
+            variables = {"params": variables["params"]}
+        return TrainState(model, variables, lr=1e-5, weight_decay=1e-4, clip_grad=1.0)
+
+    st = make(True)
+    key = ("Image2TokenBlock_0", "BatchNorm_0")
+    ra_mean = st.batch_stats[key[0]][key[1]]["mean"]
+    ra_var = st.batch_stats[key[0]][key[1]]["var"]
+    assert float(ra_mean.abs().max()) == 0.0 and float((ra_var - 1).abs().max()) == 0.0
+    # batch statistics of the stem convolution from the oracle: the running averages must move
+    # towards them as 1 - 0.9^t
+    conv = V.conv2d_nobias(O.hwcn_to_nhwc(images), params["Image2TokenBlock_0"]["Conv_0"]["kernel"], 2, 4)
+    b_mean, b_var = conv.mean(dim=(0, 1, 2)), conv.var(dim=(0, 1, 2), unbiased=False)
+    step = GraphedTrainStep(st, x, y, 0.1, warmup=1)          # 1 eager step (capturing executes nothing)
+    t = 1
+    for _ in range(3):
+        loss = step()
+        t += 1
+    torch.cuda.synchronize()
+    assert math.isfinite(loss.item())
+    w = 1.0 - 0.9 ** t
+    # (lr = 1e-5: the convolution kernel barely moves over the four steps)
+    assert float((ra_mean.cpu() - w * b_mean).abs().max()) <= 0.02 * float(b_mean.abs().max()) + 1e-3
+    assert float((ra_var.cpu() - (w * b_var + (1 - w))).abs().max()) <= 0.02 * float(b_var.abs().max()) + 1e-3
+    # eval mode normalises with the running averages: finite, and different from train mode's value
+    ev = eval_step(st, x, y).item()
+    assert math.isfinite(ev)
+    # checkpoint round trip keeps the collection beside the parameters (reference layout: whole
+    # variables under `params`)
+    C.save_checkpoint(str(tmp_path), st, int(st.step))
+    sd = C.restore_checkpoint(str(tmp_path))
+    assert set(sd["params"]) == {"params", "batch_stats"}
+    st2 = make(True)
+    C.restore_checkpoint(str(tmp_path), st2)
+    assert torch.equal(st2.batch_stats[key[0]][key[1]]["mean"], ra_mean)
+    assert abs(eval_step(st2, x, y).item() - ev) <= 1e-6 * abs(ev)
+    # the reference's call shape (no collection) still captures and replays
+    st3 = make(False)
+    step3 = GraphedTrainStep(st3, x, y, 0.1, warmup=1)
+    l3 = step3()
+    torch.cuda.synchronize()
+    assert math.isfinite(l3.item())

@@ -57,12 +57,18 @@ def main():
     _abi._lib = Proxy()
 
     torch.cuda.set_device(0)
-    cfg = O.vit_config(a.model)
     images, labels = O.synthetic_batch(a.batch, 224, seed=0)
     model = create_model(a.model)
     x = HWCN(images.cuda())
-    variables = sav.load_params(model, O.synthetic_vit_params(cfg, 224, seed=42), x, is_training=True)
-    st = TrainState(model, variables, lr=1e-3, weight_decay=1e-4, clip_grad=1.0)
+    try:
+        cfg = O.vit_config(a.model)
+        variables = sav.load_params(model, O.synthetic_vit_params(cfg, 224, seed=42), x, is_training=True)
+    except KeyError:
+        # any other create_model name (cait / cvt / botnet / mixer / tnt / ceit): random parameters
+        variables = model.init({"params": 0, "stochastic_depth": 1}, x, is_training=True)
+        variables["params"].arena.master.normal_(0.0, 0.02)
+        variables["params"].arena.refresh_shadow()
+    st = TrainState(model, variables, lr=1e-3, weight_decay=1e-4, clip_grad=1.0, seed=1)
     # warm-up eagerly (unrecorded), then capture with recording on
     orig_init = GraphedTrainStep.__init__
     step = GraphedTrainStep.__new__(GraphedTrainStep)

@@ -2,7 +2,7 @@
 CaiT-S24 224^2 (B=128), ViT-B/16 384^2 (B=64, 577 tokens), BoTNet MHSA block (B=256, 14x14x512).
 Development / DESIGN.md numbers -- not the bench metric.
 
-    python tests/tools/variant_time.py [cait|vitb384|bot]
+    python tests/tools/variant_time.py [cait|vitb384|bot|botnet|cvt|mixer|tnt|ceit]
 """
 import json
 import os
@@ -37,7 +37,7 @@ def model_case(name, batch, img, rngs=None):
     model = create_model(name)
     images = torch.randn((img, img, 3, batch), device="cuda")
     labels = torch.randint(0, 1000, (batch,), device="cuda", dtype=torch.int32)
-    variables = model.init({"params": 0}, HWCN(images), is_training=False)
+    variables = model.init({"params": 0, **(rngs or {})}, HWCN(images), is_training=True)
     arena = variables["params"].arena
     # non-degenerate head (the reference's zero-init head makes every other gradient zero)
     arena.master.normal_(0.0, 0.02)
@@ -80,12 +80,22 @@ def bot_case(batch=256):
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["cait", "vitb384", "bot"]
+    which = sys.argv[1:] or ["cait", "vitb384", "bot", "botnet", "cvt", "mixer", "tnt", "ceit"]
     for w in which:
         if w == "cait":
             r = model_case("cait_s_24", 128, 224, rngs={"stochastic_depth": 1})
         elif w == "vitb384":
             r = model_case("vit_b_patch16", 64, 384)
+        elif w == "botnet":
+            r = model_case("botnet_t3", 64, 224)      # BASELINE config 5 as a whole model
+        elif w == "cvt":
+            r = model_case("cvt-13", 64, 224)
+        elif w == "mixer":
+            r = model_case("mixer_b_patch16", 128, 224)
+        elif w == "tnt":
+            r = model_case("tnt_s_patch16", 64, 224)
+        elif w == "ceit":
+            r = model_case("ceit_s", 64, 224)
         else:
             r = bot_case()
         print("RESULT " + json.dumps(r), flush=True)
