@@ -35,7 +35,11 @@ __global__ void scale_rows_cols_kernel(const float* __restrict__ g, int64_t ldg,
   }
 }
 
-// out[n] += (sum_k W[k,n] G[k,n] + b[n] gb[n]) / cs[n];  one block per 32 columns, 8 row lanes
+// out[n] += (sum_k W[k,n] G[k,n] + b[n] gb[n]) / cs[n].  Block (x, y) owns 32 columns and the
+// kLsRows-row slice y of K (8 row lanes); slices combine with one fp32 atomicAdd per column, like the
+// split-K partials of dW itself.  (One block per 32 columns over the whole of K left 12 blocks on
+// 148 SMs walking 192 dependent loads each: 30-43 us per call, 52 calls per CaiT-S24 step.)
+constexpr int kLsRows = 64;
 __global__ void layerscale_grad_kernel(const float* __restrict__ W, int64_t ldw,
                                        const float* __restrict__ G, int64_t ldg, int64_t K, int64_t N,
                                        const float* __restrict__ b, const float* __restrict__ gb,
@@ -43,16 +47,20 @@ __global__ void layerscale_grad_kernel(const float* __restrict__ W, int64_t ldw,
   __shared__ float red[8][32];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int64_t n = (int64_t)blockIdx.x * 32 + tx;
+  const int64_t k0 = (int64_t)blockIdx.y * kLsRows;
+  const int64_t k1 = k0 + kLsRows < K ? k0 + kLsRows : K;
   float acc = 0.f;
-  if (n < N)
-    for (int64_t k = ty; k < K; k += 8) acc = fmaf(W[k * ldw + n], G[k * ldg + n], acc);
+  if (n < N) {
+#pragma unroll 8
+    for (int64_t k = k0 + ty; k < k1; k += 8) acc = fmaf(W[k * ldw + n], G[k * ldg + n], acc);
+  }
   red[ty][tx] = acc;
   __syncthreads();
   if (ty == 0 && n < N) {
     for (int j = 1; j < 8; ++j) acc += red[j][tx];
-    if (b) acc = fmaf(b[n], gb[n], acc);
+    if (b && blockIdx.y == 0) acc = fmaf(b[n], gb[n], acc);
     const float s = cs[n];
-    if (s != 0.f) out[n] += acc / s;
+    if (s != 0.f) atomicAdd(out + n, acc / s);
   }
 }
 
@@ -172,7 +180,8 @@ extern "C" int sav_layerscale_grad(const float* W, int64_t ldw, const float* dW,
   if (K <= 0 || N <= 0) return set_error(SAV_ERR_SHAPE, "sav_layerscale_grad: bad shape");
   if (!W || !dW || !col_scale || !dcol_scale || ((bias == nullptr) != (dbias == nullptr)))
     return set_error(SAV_ERR_ARG, "sav_layerscale_grad: W, dW, col_scale, dcol_scale required");
-  layerscale_grad_kernel<<<(int)((N + 31) / 32), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  layerscale_grad_kernel<<<dim3((unsigned)((N + 31) / 32), (unsigned)((K + kLsRows - 1) / kLsRows)), 256, 0,
+                           reinterpret_cast<cudaStream_t>(stream)>>>(
       W, ldw, dW, ldg, K, N, bias, dbias, col_scale, dcol_scale);
   count_launch();
   return check_launch("sav_layerscale_grad");

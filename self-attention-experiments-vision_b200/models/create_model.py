@@ -98,4 +98,4 @@ def create_model(model_name: str, num_classes: int = 1000, dtype=None):
         ih, oh, idim, odim = _TNT[model_name]
         return TNT(num_classes=num_classes, num_layers=12, inner_num_heads=ih, outer_num_heads=oh,
                    inner_embed_dim=idim, outer_embed_dim=odim)
-    raise NotImplementedError(f'{model_name} is not built yet (see DESIGN.md status table)')
+    raise RuntimeError('Model not found.')                  # create_model.py:214-215

@@ -247,7 +247,11 @@ def gelu(x):
     if isinstance(x, LazyLinear) and not x._done and x.act == 0 and x.residual is None:
         x.act = 1
         return x
-    raise NotImplementedError("standalone gelu: apply it directly to a Dense output")
+    # anything else (an activation that is not a pending Dense output): the standalone kernel pair
+    # on the materialised bf16 tensor (sav_act_fwd / sav_act_bwd, kind 4)
+    if x.dtype != BF16:
+        raise TypeError("gelu: a bf16 activation expected (apply LayerNorm to the fp32 residual stream first)")
+    return activation(x, "gelu")
 
 
 def to_stream(x):
@@ -294,7 +298,45 @@ def add(a, b):
             # anything else (`.v`) materialises it as before; either way it is recorded on the tape
             # before that reader
             return lazy
-    raise NotImplementedError("standalone add: one side must be a pending Dense output")
+    return _plain_add(a, b)
+
+
+def _plain_add(a, b):
+    """a + b of two materialised Vars of one shape and dtype (no pending Dense to fold the add into):
+    one elementwise kernel; the gradient fans out to both inputs unchanged."""
+    if not (isinstance(a, Var) and isinstance(b, Var)) or tuple(a.shape) != tuple(b.shape):
+        raise TypeError("add: two activations of the same shape expected")
+    ta, tb = a.v, b.v
+    if ta.dtype != tb.dtype:
+        raise TypeError("add: mixed precisions (cast the fp32 residual stream with LayerNorm / "
+                        "stream_to_operand first)")
+    if _meta(ta):
+        return Var(torch.empty(ta.shape, dtype=ta.dtype, device="meta"))
+    if ta.dtype == BF16:
+        out = Var(ops.add(ta.contiguous(), tb.contiguous()).view(ta.shape))
+    else:
+        y = torch.empty(ta.shape, dtype=F32, device=ta.device)
+        C = ta.shape[-1]
+        ops.copy2d_f32(ta.contiguous().view(-1, C), y.view(-1, C))
+        ops.copy2d_f32(tb.contiguous().view(-1, C), y.view(-1, C), accumulate=True)
+        out = Var(y)
+
+    def bwd():
+        g = out.take_grad()
+        out.g16 = None
+        if g is None:
+            return
+        for var in (a, b):
+            if var.requires_grad:
+                if var.g is None and g.dtype == F32:
+                    # fp32 gradients are accumulated in place by later consumers: hand out a copy
+                    gc = torch.empty(g.shape, dtype=F32, device=g.device)
+                    ops.copy2d_f32(g.contiguous().view(-1, g.shape[-1]), gc.view(-1, g.shape[-1]))
+                    var.g = gc
+                else:
+                    _add_grad(var, g)
+    record(bwd)
+    return out
 
 
 class LazyLayerNorm(Var):

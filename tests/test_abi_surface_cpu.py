@@ -151,6 +151,14 @@ def test_ffblock_requires_ratio_or_hidden():
 
 
 def test_unknown_model_name():
+    """create_model.py:214-215: RuntimeError('Model not found.'); every name the reference knows builds."""
     from models import create_model
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(RuntimeError, match="Model not found"):
         create_model("resnet50")
+    ref_names = ['vit_b_patch32', 'vit_b_patch16', 'vit_l_patch32', 'vit_l_patch16', 'botnet_t3', 'botnet_t4',
+                 'botnet_t5', 'tnt_s_patch16', 'tnt_b_patch16', 'ceit_t', 'ceit_s', 'ceit_b', 'cait_xxs_24',
+                 'cait_xxs_36', 'cait_xs_24', 'cait_xs_36', 'cait_s_24', 'cait_s_36', 'cait_s_48', 'cait_m_24',
+                 'cait_m_36', 'cait_m_48', 'cvt-13', 'cvt-21', 'cvt-w24', 'mixer_s_patch32', 'mixer_s_patch16', 'mixer_b_patch32',
+                 'mixer_l_patch32', 'mixer_l_patch16']
+    for name in ref_names:
+        assert create_model(name, num_classes=10) is not None, name
