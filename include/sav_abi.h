@@ -225,7 +225,8 @@ typedef struct {
   void* dk;
   void* dv;
   float* delta;      /* workspace fp32 [B,H,Nq] */
-  float* dq_accum;   /* workspace fp32 [B,Nq,H,D] (zeroed by the callee); only used when Nq > 256 */
+  float* dq_accum;   /* unused (may be NULL): sequences beyond 256 queries run as query groups whose dK / dV
+                        partial tiles are reduce-added in bf16 by the TMA unit into the zero-filled dk / dv */
   int64_t B, H, Nq, Nk, D;
   int64_t q_batch_stride, q_row_stride; /* shared by q and dq */
   int64_t k_batch_stride, k_row_stride; /* shared by k and dk */

@@ -307,7 +307,14 @@ extern "C" int sav_attn_bwd(const sav_attn_bwd_args* a, void* stream) {
     return set_error(SAV_ERR_SHAPE, "sav_attn_bwd: empty shape");
   if (!a->delta) return set_error(SAV_ERR_ARG, "sav_attn_bwd: delta workspace required");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (a->Nq <= 256) return launch_attn_bwd2(a, st);  // whole (b,h) per CTA, dQ accumulated in TMEM
+  // every shape runs the resident-query kernel of attn_bwd.cu (query groups of <= 256 rows).  The
+  // older key-tile-per-CTA kernel below (fp32 dQ accumulation + a conversion pass; 921 us against
+  // the new path on ViT-B/16 384^2) is kept for A/B runs of the development build only.
+#ifndef SAV_ATTN_DEV
+  return launch_attn_bwd2(a, st);
+#else
+  if (a->Nq <= 256 || !getenv("SAV_ATTN_BWD_GENERIC")) return launch_attn_bwd2(a, st);
+#endif
   if (!a->dq_accum) return set_error(SAV_ERR_ARG, "sav_attn_bwd: dq_accum workspace required for Nq > 256");
   CUtensorMap tq, tk, tv, tdo;
   int rc;

@@ -1,9 +1,15 @@
-// Fused attention backward for sm_100a, Nq <= 256 and Nk <= 256 (reverse mode of attention.py:39-58):
+// Fused attention backward for sm_100a, any Nq / Nk (reverse mode of attention.py:39-58):
 //   S = q k^T * scale, P = exp(S - lse), dP = dO v^T, dS = P o (dP - delta) * scale,
 //   dV = P^T dO, dK = dS^T q, dQ = dS k.
-// One persistent CTA owns a whole (b, h): both 128-row query tiles (Q, dO) stay resident in shared
-// memory, the key tiles stream through a 2-stage TMA ring, and S / P / dP / dS never leave the SM.
-// dQ accumulates in TMEM across key tiles, dK / dV across the query tiles (no fp32 red.add to HBM).
+// One persistent CTA owns a work item (b, h, query group): the group's one or two 128-row query tiles
+// (Q, dO) stay resident in shared memory, ALL key tiles stream through a 2-stage TMA ring, and
+// S / P / dP / dS never leave the SM.  dQ accumulates in TMEM across the key tiles and is stored once;
+// dK / dV accumulate in TMEM across the group's query tiles.  Up to 256 queries there is one group per
+// (b, h) and dK / dV are plain stores; longer sequences (ViT-B/16 384^2: 577 tokens = groups of 256,
+// 256, 65; CvT: 3136 x 784) have G = ceil(Nq / 256) groups per (b, h) whose dK / dV partial tiles are
+// combined by the TMA unit itself (cp.reduce.async.bulk.tensor .add on the zero-filled bf16
+// gradients): no fp32 workspace, no conversion pass; the sum of G bf16-rounded partials arrives in
+// arbitrary order, so those two gradients are reproducible to bf16 rounding, not bit for bit.
 //
 // The transposed problem is computed (S^T = K Q^T, dP^T = V dO^T: TMEM lane = key row), so P^T / dS^T
 // rows come out K-major for dV += P^T dO, dK += dS^T Q, and the same dS^T buffer read MN-major is
@@ -50,9 +56,10 @@ struct AttnBwd2Params {
   const bf16* d_o;
   long long o_bs, o_rs;
   int B, H, Nq, Nk;
-  int n_items;   // B * H
-  int nkt;       // key tiles (1 or 2)
-  int nqt;       // query tiles (1 or 2)
+  int n_items;   // B * H * G
+  int nkt;       // key tiles (any number)
+  int G;         // query groups of <= 256 rows per (b, h); G > 1: dK / dV tiles are reduce-added
+  int nqt;       // query tiles of the only group when G == 1 (1 or 2)
   float scale, scale_log2;
   long long* dbg;
 };
@@ -93,6 +100,42 @@ static_assert(kBwd2Smem <= 232448, "attention backward exceeds the 227 KB shared
 
 __device__ __forceinline__ int round16(int x) { return (x + 15) & ~15; }
 
+// work item -> (b, h, first query row, query rows, query tiles); the groups of one (b, h) are
+// neighbours in the item order, so they run at the same time and share K / V through L2
+struct BwdItem {
+  int b, h, bh, q0, nq, nqt;
+};
+template <bool kGroups>
+__device__ __forceinline__ BwdItem bwd_item(const AttnBwd2Params& p, int item) {
+  BwdItem it;
+  if (!kGroups) {   // one group per (b, h): nothing to decode (the DeiT / CaiT shapes)
+    it.bh = item;
+    it.h = item % p.H;
+    it.b = item / p.H;
+    it.q0 = 0;
+    it.nq = p.Nq;
+    it.nqt = p.nqt;      // (a kernel parameter: a value computed here is hoisted and spilled)
+    return it;
+  }
+  const int qg = item % p.G;
+  it.bh = item / p.G;
+  it.h = it.bh % p.H;
+  it.b = it.bh / p.H;
+  it.q0 = qg * 2 * BT;
+  it.nq = min(2 * BT, p.Nq - it.q0);
+  it.nqt = (it.nq + BT - 1) / BT;
+  return it;
+}
+
+__device__ __forceinline__ void tma_reduce_add_3d(const CUtensorMap* m, const void* src, int c0, int c1,
+                                                  int c2) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+          reinterpret_cast<uint64_t>(m)),
+      "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+
 __device__ __forceinline__ void pack_rows_to_stage(uint8_t* stage, int r, const uint32_t (&pk)[32]) {
 #pragma unroll
   for (int g = 0; g < 8; ++g)
@@ -115,6 +158,7 @@ __device__ __forceinline__ void tmem_row64_to_bf16(uint32_t taddr, float f, uint
     pk[16 + e] = pack_bf16(__uint_as_float(r0[2 * e]) * f, __uint_as_float(r0[2 * e + 1]) * f);
 }
 
+template <bool kGroups>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                  const __grid_constant__ CUtensorMap tv, const __grid_constant__ CUtensorMap tdo,
@@ -195,17 +239,18 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      uint32_t gk = 0;
+      uint32_t gk = 0, quse[2] = {0, 0};   // quse[i]: how often query buffer i has been filled
       for (int itl = 0; itl < my_items; ++itl) {
-        const int item = blockIdx.x + itl * gridDim.x;
-        const int h = item % p.H, b = item / p.H;
+        const BwdItem it = bwd_item<kGroups>(p, blockIdx.x + itl * gridDim.x);
+        const int h = it.h, b = it.b;
         auto load_qdo = [&](int i) {
           BWD_STAMP(0, 1);
-          mbar_wait_sleep(&qdo_empty[i], (itl & 1) ^ 1);
+          mbar_wait_sleep(&qdo_empty[i], (quse[i] & 1) ^ 1);
+          ++quse[i];
           BWD_STAMP(0, 2);
           mbar_expect_tx(&qdo_full[i], 2 * BT_BYTES);
-          tma_load_3d(sQ + i * BT_BYTES, &tq, &qdo_full[i], h * BD, i * BT, b);
-          tma_load_3d(sdO + i * BT_BYTES, &tdo, &qdo_full[i], h * BD, i * BT, b);
+          tma_load_3d(sQ + i * BT_BYTES, &tq, &qdo_full[i], h * BD, it.q0 + i * BT, b);
+          tma_load_3d(sdO + i * BT_BYTES, &tdo, &qdo_full[i], h * BD, it.q0 + i * BT, b);
         };
         auto load_kv = [&](int j) {
           const int st = gk & 1;
@@ -219,7 +264,7 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         };
         load_qdo(0);
         load_kv(0);
-        if (p.nqt > 1) load_qdo(1);
+        if (it.nqt > 1) load_qdo(1);
         for (int j = 1; j < p.nkt; ++j) load_kv(j);
       }
     }
@@ -231,17 +276,23 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     const uint64_t ddO0 = make_smem_desc(smem_u32(sdO), 16, 1024);          // K-major B of dP^T
     const uint64_t dK0 = make_smem_desc(smem_u32(sKV), 16, 1024);           // K-major A of S^T
     const uint64_t dV0 = make_smem_desc(smem_u32(sKV + BT_BYTES), 16, 1024);
-    uint32_t n = 0, gk = 0;
+    uint32_t n = 0, gk = 0, quse[2] = {0, 0};
     for (int itl = 0; itl < my_items; ++itl) {
+      const BwdItem it = bwd_item<kGroups>(p, blockIdx.x + itl * gridDim.x);
       for (int j = 0; j < p.nkt; ++j, ++gk) {
         const int st = gk & 1;
         BWD_STAMP(1, 10);
         mbar_wait_sleep(&kv_full[st], (gk >> 1) & 1);
         BWD_STAMP(1, 11);
         const uint32_t a_k = lo(dK0) + st * 2 * TILE16, a_v = lo(dV0) + st * 2 * TILE16;
-        for (int i = 0; i < p.nqt; ++i) {
-          if (j == 0) { BWD_STAMP(1, 14); mbar_wait_sleep(&qdo_full[i], itl & 1); BWD_STAMP(1, 15); }
-          const int nq_cur = round16(min(BT, p.Nq - i * BT));
+        for (int i = 0; i < it.nqt; ++i) {
+          if (j == 0) {
+            BWD_STAMP(1, 14);
+            mbar_wait_sleep(&qdo_full[i], quse[i] & 1);
+            ++quse[i];
+            BWD_STAMP(1, 15);
+          }
+          const int nq_cur = round16(min(BT, it.nq - i * BT));
           const int nch = (nq_cur + BC - 1) / BC;
           for (int cc = 0; cc < nch; ++cc, ++n) {
             const int ncols = min(BC, nq_cur - cc * BC);
@@ -262,7 +313,7 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
               for (int k = 0; k < BD / 16; ++k)
                 umma_f16_lh(tdP + buf * BC, a_v + k * 2, hi(dV0), b_do + k * 2, hi(ddO0), id_s, k > 0);
               umma_commit(&s_full[buf]);
-              if (i == p.nqt - 1 && cc == nch - 1) umma_commit(&kv_empty[st]);
+              if (i == it.nqt - 1 && cc == nch - 1) umma_commit(&kv_empty[st]);
               if (j == p.nkt - 1 && cc == nch - 1) umma_commit(&qdo_empty[i]);
             }
             __syncwarp();
@@ -282,12 +333,13 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     constexpr uint32_t id_mnmn = make_idesc_bf16(BT, BD, true, true);
     uint32_t gk = 0, use_cc[2] = {0, 0};
     for (int itl = 0; itl < my_items; ++itl) {
+      const BwdItem it = bwd_item<kGroups>(p, blockIdx.x + itl * gridDim.x);
       for (int j = 0; j < p.nkt; ++j, ++gk) {
         const int st = gk & 1;
         const int nk_steps = round16(min(BT, p.Nk - j * BT)) >> 4;
         const uint32_t b_k = lo(dKm0) + st * 2 * TILE16;
-        for (int i = 0; i < p.nqt; ++i) {
-          const int nq_cur = round16(min(BT, p.Nq - i * BT));
+        for (int i = 0; i < it.nqt; ++i) {
+          const int nq_cur = round16(min(BT, it.nq - i * BT));
           const int nch = (nq_cur + BC - 1) / BC;
           for (int cc = 0; cc < nch; ++cc) {
             const int ksteps = min(BC, nq_cur - cc * BC) >> 4;
@@ -325,12 +377,12 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
                     umma_f16_lh(tdQ + i * BD, lo(ddSm0) + ks * 128, hi(ddSm0), b_k + ks * 128,
                                 hi(dKm0), id_mnmn, ks > 0 ? 1u : (j > 0 ? 1u : 0u));
                 umma_commit(pds_free);
-                if (i == p.nqt - 1) {
+                if (i == it.nqt - 1) {
                   umma_commit(dkv_full);
                   umma_commit(&kv_empty[st]);
                 }
                 if (j == p.nkt - 1) umma_commit(&qdo_empty[i]);
-                if (j == p.nkt - 1 && i == p.nqt - 1) umma_commit(dq_full);
+                if (j == p.nkt - 1 && i == it.nqt - 1) umma_commit(dq_full);
               }
             }
             __syncwarp();
@@ -344,8 +396,8 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     // the loads of item itl are issued before waiting for the math warps to release the buffer,
     // so only a shared-memory store sits on the critical path.
     for (int itl = 0; itl < my_items; ++itl) {
-      const int item = blockIdx.x + itl * gridDim.x;
-      const int64_t base = (int64_t)item * p.Nq;   // lse / delta are [B, H, Nq]
+      const BwdItem it = bwd_item<kGroups>(p, blockIdx.x + itl * gridDim.x);
+      const int64_t base = (int64_t)it.bh * p.Nq + it.q0;   // lse / delta are [B, H, Nq]
       float nl[8], nd[8];
       BWD_STAMP(6, 50);
       mbar_wait_sleep(&dl_ready[itl & 1], (itl >> 1) & 1);
@@ -353,8 +405,8 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         const int c = lane * 8 + e;
-        nl[e] = (c < p.Nq) ? -p.lse[base + c] * B_LOG2E : -INFINITY;
-        nd[e] = (c < p.Nq) ? -__ldcg(p.delta + base + c) : 0.f;
+        nl[e] = (c < it.nq) ? -p.lse[base + c] * B_LOG2E : -INFINITY;
+        nd[e] = (c < it.nq) ? -__ldcg(p.delta + base + c) : 0.f;
       }
       // (the values are consumed by the stores below, i.e. the loads have completed by then)
       BWD_STAMP(6, 52);
@@ -383,6 +435,7 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     const int mrole = (warp == 4) ? 3 : (warp == 8 ? 4 : 7);
 #endif
     for (int itl = 0; itl < my_items; ++itl) {
+      const BwdItem it = bwd_item<kGroups>(p, blockIdx.x + itl * gridDim.x);
       BWD_STAMP(mrole, 35);
       mbar_wait(st_full, itl & 1);
       BWD_STAMP(mrole, 36);
@@ -390,8 +443,8 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         // key rows at or beyond the (16-rounded) key count of this tile are never read: as K of
         // the dQ MMAs they are cut by nk_steps, as M rows of dV / dK they are clipped by the store
         const bool rows_live = sub * 32 < round16(min(BT, p.Nk - j * BT));
-        for (int i = 0; i < p.nqt; ++i, ++tiles) {
-          const int nq_cur = round16(min(BT, p.Nq - i * BT));
+        for (int i = 0; i < it.nqt; ++i, ++tiles) {
+          const int nq_cur = round16(min(BT, it.nq - i * BT));
           const int nch = (nq_cur + BC - 1) / BC;
           for (int cc = 0; cc < nch; ++cc, ++n) {
             const int ncols = min(BC, nq_cur - cc * BC);
@@ -470,7 +523,8 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     uint32_t gk = 0, nstore = 0;
     // one [128 x 64] bf16 tile: registers -> staging buffer (nstore & 1) -> TMA store.  The buffer
     // is reused every second store: the leader keeps at most one store group reading.
-    auto store_tile = [&](const CUtensorMap* map, const uint32_t (&pk)[32], int c0, int c1, int c2) {
+    auto store_tile = [&](const CUtensorMap* map, const uint32_t (&pk)[32], int c0, int c1, int c2,
+                          bool reduce) {
       uint8_t* stage = sStage + (nstore & 1) * BT_BYTES;
       if (leader) tma_store_wait_read<1>();
       named_barrier_sync(2, 128);
@@ -478,14 +532,16 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       fence_proxy_async_smem();
       named_barrier_sync(2, 128);
       if (leader) {
-        tma_store_3d(map, stage, c0, c1, c2);
+        if (reduce) tma_reduce_add_3d(map, stage, c0, c1, c2);   // partial of one query group
+        else tma_store_3d(map, stage, c0, c1, c2);
         tma_store_commit();
       }
       ++nstore;
     };
+    constexpr bool red = kGroups;
     for (int itl = 0; itl < my_items; ++itl) {
-      const int item = blockIdx.x + itl * gridDim.x;
-      const int h = item % p.H, b = item / p.H;
+      const BwdItem it = bwd_item<kGroups>(p, blockIdx.x + itl * gridDim.x);
+      const int h = it.h, b = it.b;
       for (int j = 0; j < p.nkt; ++j, ++gk) {
         uint32_t pk[32];
         BWD_STAMP(5, 42);
@@ -493,12 +549,12 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         BWD_STAMP(5, 43);
         tc_fence_after();
         tmem_row64_to_bf16(tdV + lane_off, 1.f, pk);
-        store_tile(&tdv, pk, h * BD, j * BT, b);     // key rows >= Nk are clipped by the map
+        store_tile(&tdv, pk, h * BD, j * BT, b, red);   // key rows >= Nk are clipped by the map
         tmem_row64_to_bf16(tdK + lane_off, p.scale, pk);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(dkv_free);        // next key tile may overwrite dV / dK
-        store_tile(&tdk, pk, h * BD, j * BT, b);
+        store_tile(&tdk, pk, h * BD, j * BT, b, red);
         BWD_STAMP(5, 44);
       }
       BWD_STAMP(5, 45);
@@ -508,18 +564,18 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       {
         uint32_t pk[32];
         tmem_row64_to_bf16(tdQ + lane_off, p.scale, pk);
-        if (p.nqt == 1) {
+        if (it.nqt == 1) {
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(dq_free);       // next item may overwrite dQ
         }
-        store_tile(&tdq, pk, h * BD, 0, b);          // rows >= Nq clipped
-        if (p.nqt > 1) {
+        store_tile(&tdq, pk, h * BD, it.q0, b, false);   // rows >= Nq clipped
+        if (it.nqt > 1) {
           tmem_row64_to_bf16(tdQ + BD + lane_off, p.scale, pk);
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(dq_free);
-          store_tile(&tdq, pk, h * BD, BT, b);
+          store_tile(&tdq, pk, h * BD, it.q0 + BT, b, false);
         }
       }
     }
@@ -533,18 +589,18 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     const int dt = tid - 512;
     const int part = dt & 7, row0 = dt >> 3;
     for (int itl = 0; itl < my_items; ++itl) {
-      const int item = blockIdx.x + itl * gridDim.x;
-      const int h = item % p.H, b = item / p.H;
-      const int64_t base = (int64_t)b * p.o_bs + h * BD + part * 8;
-      float* dout = p.delta + (int64_t)item * p.Nq;
+      const BwdItem it = bwd_item<kGroups>(p, blockIdx.x + itl * gridDim.x);
+      const int h = it.h, b = it.b;
+      const int64_t base = (int64_t)b * p.o_bs + (int64_t)it.q0 * p.o_rs + h * BD + part * 8;
+      float* dout = p.delta + (int64_t)it.bh * p.Nq + it.q0;
       if (itl >= 2) mbar_wait_sleep(&dl_free[itl & 1], ((itl - 2) >> 1) & 1);
       constexpr int PB = 4;
-      for (int q0 = 0; q0 < p.Nq; q0 += 16 * PB) {
+      for (int q0 = 0; q0 < it.nq; q0 += 16 * PB) {
         uint4 a[PB], l[PB], g[PB];
 #pragma unroll
         for (int u = 0; u < PB; ++u) {
           const int q = q0 + u * 16 + row0;
-          if (q < p.Nq) {
+          if (q < it.nq) {
             const int64_t off = base + (int64_t)q * p.o_rs;
             a[u] = __ldcg(reinterpret_cast<const uint4*>(p.o + off));
             g[u] = __ldcg(reinterpret_cast<const uint4*>(p.d_o + off));
@@ -555,7 +611,7 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         for (int u = 0; u < PB; ++u) {
           const int q = q0 + u * 16 + row0;
           float sum = 0.f;
-          if (q < p.Nq) {
+          if (q < it.nq) {
             const uint32_t aw[4] = {a[u].x, a[u].y, a[u].z, a[u].w}, gw[4] = {g[u].x, g[u].y, g[u].z, g[u].w};
             const uint32_t lw[4] = {l[u].x, l[u].y, l[u].z, l[u].w};
 #pragma unroll
@@ -567,7 +623,7 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           sum += __shfl_xor_sync(0xffffffffu, sum, 1);
           sum += __shfl_xor_sync(0xffffffffu, sum, 2);
           sum += __shfl_xor_sync(0xffffffffu, sum, 4);
-          if (q < p.Nq && part == 0) dout[q] = sum;
+          if (q < it.nq && part == 0) dout[q] = sum;
         }
       }
       mbar_arrive(&dl_ready[itl & 1]);   // release: this thread's global stores are ordered before
@@ -589,7 +645,31 @@ static int make_bnhd_map128(CUtensorMap* m, const void* base, int64_t H, int64_t
   return make_tmap_bf16(m, base, 3, dims, str, box);
 }
 
-// Nq <= 256 path of sav_attn_bwd (called from attn.cu)
+// zero a [B, N, H*64] bf16 view (element strides bs / rs): the target of the dK / dV reduce-adds
+__global__ void zero_bnhd_kernel(bf16* __restrict__ base, int64_t total16, int N, int row16, int64_t bs,
+                                 int64_t rs) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total16;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % row16);
+    const int64_t t = i / row16;
+    const int n = (int)(t % N);
+    const int64_t b = t / N;
+    *reinterpret_cast<uint4*>(base + b * bs + (int64_t)n * rs + c * 8) = make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
+static int zero_bnhd(void* base, int64_t B, int64_t N, int64_t H, int64_t bs, int64_t rs, cudaStream_t st) {
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (bs % 8) || (rs % 8))
+    return set_error(SAV_ERR_ALIGN, "sav_attn_bwd: dk / dv need 16-byte aligned rows");
+  const int row16 = (int)(H * BD / 8);
+  const int64_t total16 = B * N * row16;
+  const int blocks = (int)((total16 + 255) / 256 < 148 * 8 ? (total16 + 255) / 256 : 148 * 8);
+  zero_bnhd_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<bf16*>(base), total16, (int)N, row16, bs, rs);
+  count_launch();
+  return check_launch("sav_attn_bwd (zero dk / dv)");
+}
+
+// sav_attn_bwd for every shape (called from attn.cu)
 int launch_attn_bwd2(const sav_attn_bwd_args* a, cudaStream_t st) {
   CUtensorMap tq, tk, tv, tdo, tdq, tdk, tdv;
   int rc;
@@ -602,7 +682,9 @@ int launch_attn_bwd2(const sav_attn_bwd_args* a, cudaStream_t st) {
   if ((rc = make_bnhd_map128(&tdv, a->dv, a->H, a->Nk, a->B, a->v_batch_stride, a->v_row_stride))) return rc;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(attn_bwd3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwd2Smem);
+    cudaError_t e = cudaFuncSetAttribute(attn_bwd3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwd2Smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(attn_bwd3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwd2Smem);
     if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "attn bwd2 smem attr: %s", cudaGetErrorString(e));
     attr = true;
   }
@@ -612,16 +694,23 @@ int launch_attn_bwd2(const sav_attn_bwd_args* a, cudaStream_t st) {
   p.d_o = reinterpret_cast<const bf16*>(a->d_o);
   p.o_bs = a->o_batch_stride; p.o_rs = a->o_row_stride;
   p.B = (int)a->B; p.H = (int)a->H; p.Nq = (int)a->Nq; p.Nk = (int)a->Nk;
-  p.n_items = p.B * p.H;
+  p.G = (p.Nq + 2 * BT - 1) / (2 * BT);
+  p.n_items = p.B * p.H * p.G;
   p.nkt = (p.Nk + BT - 1) / BT;
   p.nqt = (p.Nq + BT - 1) / BT;
+  if (p.G > 1) {
+    // several query groups per (b, h): their dK / dV partial tiles are reduce-added into zeros
+    if ((rc = zero_bnhd(a->dk, a->B, a->Nk, a->H, a->k_batch_stride, a->k_row_stride, st))) return rc;
+    if ((rc = zero_bnhd(a->dv, a->B, a->Nk, a->H, a->v_batch_stride, a->v_row_stride, st))) return rc;
+  }
   p.scale = a->scale; p.scale_log2 = a->scale * B_LOG2E;
   p.dbg = reinterpret_cast<long long*>(sav_debug_buffer());
   int sms = 148, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int grid = p.n_items < sms ? p.n_items : sms;
-  attn_bwd3_kernel<<<grid, kBwdThreads, kBwd2Smem, st>>>(tq, tk, tv, tdo, tdq, tdk, tdv, p);
+  if (p.G > 1) attn_bwd3_kernel<true><<<grid, kBwdThreads, kBwd2Smem, st>>>(tq, tk, tv, tdo, tdq, tdk, tdv, p);
+  else attn_bwd3_kernel<false><<<grid, kBwdThreads, kBwd2Smem, st>>>(tq, tk, tv, tdo, tdq, tdk, tdv, p);
   count_launch();
   return check_launch("sav_attn_bwd (resident-Q path)");
 }
