@@ -906,6 +906,363 @@ static int launch_th_bwd_mma(const SoftArgs& a, cudaStream_t st) {
   return SAV_OK;
 }
 
+// ---- talking heads entirely on the tensor cores (H <= 8, rows of <= 224 keys).
+// Both head mixes are [keys x 8] x [8 x 8] products, so a warp walks its row in blocks of 16 keys
+// with mma.sync.m16n8k8 (TF32): M = 16 keys, K = N = heads.  Lane (g, t) = (lane / 4, lane % 4) loads
+// the A fragment of the raw logits straight from global memory (heads t, t + 4 at keys g, g + 8: each
+// group of eight lanes reads one 32-byte sector per head) -- no shared-memory staging -- and the
+// accumulator fragment it gets back (keys g, g + 8 x heads 2t, 2t + 1) IS the A fragment of the next
+// product once the contraction index is renumbered (column t <-> head 2t, column t + 4 <-> head 2t + 1)
+// and the constant B fragment is permuted the same way.  The softmax statistics of a head are a
+// register reduction plus three shuffles over g.  The pre-softmax mix uses the error-compensated
+// 3 x TF32 split (hi * hi + lo * hi + hi * lo): logits keep fp32 accuracy; the post-softmax mix of
+// probabilities in [0, 1] is rounded to bf16 right after, one TF32 product is enough.
+__device__ __forceinline__ uint32_t tf32_rna(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void mma_tf32_m16n8k8(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                                 uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+      "{%0, %1, %2, %3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// c += A * B with A (fp32 values) split into TF32 hi + lo and B given as (hi, lo)
+__device__ __forceinline__ void mma_3xtf32(float (&c)[4], const float (&av)[4], uint32_t bh0, uint32_t bh1,
+                                           uint32_t bl0, uint32_t bl1) {
+  uint32_t ah[4], al[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    ah[e] = tf32_rna(av[e]);
+    al[e] = tf32_rna(av[e] - __uint_as_float(ah[e]));
+  }
+  mma_tf32_m16n8k8(c, al[0], al[1], al[2], al[3], bh0, bh1);
+  mma_tf32_m16n8k8(c, ah[0], ah[1], ah[2], ah[3], bl0, bl1);
+  mma_tf32_m16n8k8(c, ah[0], ah[1], ah[2], ah[3], bh0, bh1);
+}
+
+constexpr int kTcBlocks = 2 * kKPL;    // 16-key blocks of a row (<= 224 keys)
+
+// mixed, scaled logits of the whole row as accumulator fragments: tm[blk] = (keys g, g + 8) x (heads
+// 2t, 2t + 1) of block blk; -inf at keys >= Nk
+template <int H>
+__device__ __forceinline__ void th_tc_logits(const SoftArgs& a, const float* s0, int64_t hs, int g, int t,
+                                             uint32_t bh0, uint32_t bh1, uint32_t bl0, uint32_t bl1,
+                                             float (&tm)[kTcBlocks][4]) {
+  // all loads of the row first (one DRAM round trip per row, not one per block), parked in the
+  // registers that receive the products
+#pragma unroll
+  for (int blk = 0; blk < kTcBlocks; ++blk) {
+    const int k0 = 16 * blk + g, k1 = k0 + 8;
+    tm[blk][0] = (t < H && k0 < a.Nk) ? __ldg(s0 + t * hs + k0) : 0.f;
+    tm[blk][1] = (t < H && k1 < a.Nk) ? __ldg(s0 + t * hs + k1) : 0.f;
+    tm[blk][2] = (t + 4 < H && k0 < a.Nk) ? __ldg(s0 + (t + 4) * hs + k0) : 0.f;
+    tm[blk][3] = (t + 4 < H && k1 < a.Nk) ? __ldg(s0 + (t + 4) * hs + k1) : 0.f;
+  }
+#pragma unroll
+  for (int blk = 0; blk < kTcBlocks; ++blk) {
+    if (16 * blk < a.Nk) {                         // warp-uniform
+      const int k0 = 16 * blk + g, k1 = k0 + 8;
+      const float av[4] = {tm[blk][0], tm[blk][1], tm[blk][2], tm[blk][3]};
+      float c[4] = {0.f, 0.f, 0.f, 0.f};
+      mma_3xtf32(c, av, bh0, bh1, bl0, bl1);
+      tm[blk][0] = (k0 < a.Nk) ? c[0] : -INFINITY;
+      tm[blk][1] = (k0 < a.Nk) ? c[1] : -INFINITY;
+      tm[blk][2] = (k1 < a.Nk) ? c[2] : -INFINITY;
+      tm[blk][3] = (k1 < a.Nk) ? c[3] : -INFINITY;
+    } else {
+      tm[blk][0] = tm[blk][1] = tm[blk][2] = tm[blk][3] = -INFINITY;
+    }
+  }
+}
+
+// max / sum over the keys of this lane's two heads (all lanes of equal t agree afterwards);
+// tm becomes exp2(tm - max)
+__device__ __forceinline__ void th_tc_softmax(float (&tm)[kTcBlocks][4], float (&inv)[2]) {
+  float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+  for (int blk = 0; blk < kTcBlocks; ++blk) {
+    m0 = fmaxf(m0, fmaxf(tm[blk][0], tm[blk][2]));
+    m1 = fmaxf(m1, fmaxf(tm[blk][1], tm[blk][3]));
+  }
+#pragma unroll
+  for (int o = 4; o < 32; o <<= 1) {
+    m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, o));
+    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, o));
+  }
+  float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int blk = 0; blk < kTcBlocks; ++blk) {
+    tm[blk][0] = ex2_fast(tm[blk][0] - m0);   // exp2(-inf) = 0 for the padded keys
+    tm[blk][2] = ex2_fast(tm[blk][2] - m0);
+    tm[blk][1] = ex2_fast(tm[blk][1] - m1);
+    tm[blk][3] = ex2_fast(tm[blk][3] - m1);
+    s0 += tm[blk][0] + tm[blk][2];
+    s1 += tm[blk][1] + tm[blk][3];
+  }
+#pragma unroll
+  for (int o = 4; o < 32; o <<= 1) {
+    s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+  }
+  inv[0] = 1.f / s0;
+  inv[1] = 1.f / s1;
+}
+
+template <int H>
+__global__ void __launch_bounds__(kRowWarps * 32)
+thsoftmax_fwd_tc_kernel(const SoftArgs a) {
+  static_assert(H <= 8, "one m16n8k8 tile holds the H x H transform");
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int64_t rows = (int64_t)a.B * a.Nq;
+  const int64_t hs = (int64_t)a.Nq * a.ld;
+  const float sc = a.scale * kLog2e;
+  // B of the pre-softmax mix: [k = h][n = i] = T1[h][i] * scale * log2(e), lane holds (h = t, t + 4; i = g)
+  const float b1a = (t < H && g < H) ? a.mix_pre[t * H + g] * sc : 0.f;
+  const float b1b = (t + 4 < H && g < H) ? a.mix_pre[(t + 4) * H + g] * sc : 0.f;
+  const uint32_t bh0 = tf32_rna(b1a), bh1 = tf32_rna(b1b);
+  const uint32_t bl0 = tf32_rna(b1a - __uint_as_float(bh0)), bl1 = tf32_rna(b1b - __uint_as_float(bh1));
+  // B of the post-softmax mix with the contraction index renumbered (k = t <-> i = 2t, k = t + 4 <-> 2t + 1):
+  // [i][n = j] = T2[i][j], lane holds (i = 2t, 2t + 1; j = g)
+  const uint32_t b2a = tf32_rna((2 * t < H && g < H) ? a.mix_post[(2 * t) * H + g] : 0.f);
+  const uint32_t b2b = tf32_rna((2 * t + 1 < H && g < H) ? a.mix_post[(2 * t + 1) * H + g] : 0.f);
+  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + (threadIdx.x >> 5); row < rows;
+       row += (int64_t)gridDim.x * kRowWarps) {
+    const int q = (int)(row % a.Nq);
+    const int64_t b = row / a.Nq;
+    const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
+    const float* s0 = a.S + off;
+    bf16* p0 = a.P + off;
+    float tm[kTcBlocks][4], inv[2];
+    th_tc_logits<H>(a, s0, hs, g, t, bh0, bh1, bl0, bl1, tm);
+    th_tc_softmax(tm, inv);
+#pragma unroll
+    for (int blk = 0; blk < kTcBlocks; ++blk) {
+      if (16 * blk < a.ld) {                       // warp-uniform
+        float c[4] = {0.f, 0.f, 0.f, 0.f};
+        // A = probabilities: (key g, col t <-> head 2t), (key g + 8, col t), (key g, col t + 4 <-> 2t + 1), ...
+        mma_tf32_m16n8k8(c, tf32_rna(tm[blk][0] * inv[0]), tf32_rna(tm[blk][2] * inv[0]),
+                         tf32_rna(tm[blk][1] * inv[1]), tf32_rna(tm[blk][3] * inv[1]), b2a, b2b);
+        // c = mixed probabilities: keys g, g + 8 x output heads 2t, 2t + 1
+        const int k0 = 16 * blk + g, k1 = k0 + 8;
+        if (2 * t < H) {
+          if (k0 < a.ld) p0[(2 * t) * hs + k0] = __float2bfloat16(c[0]);
+          if (k1 < a.ld) p0[(2 * t) * hs + k1] = __float2bfloat16(c[2]);
+        }
+        if (2 * t + 1 < H) {
+          if (k0 < a.ld) p0[(2 * t + 1) * hs + k0] = __float2bfloat16(c[1]);
+          if (k1 < a.ld) p0[(2 * t + 1) * hs + k1] = __float2bfloat16(c[3]);
+        }
+      }
+    }
+  }
+}
+
+// Backward of the same design.  Per row: raw dP goes straight to shared memory with cp.async (issued
+// first, it lands while the logits are recomputed); the probabilities stay in accumulator-fragment
+// registers.  The two transform gradients contract over the KEYS, which sit on the wrong fragment
+// axis (rows), so p -- and later dt -- take one trip through shared memory as [head][key] rows of
+// kTcRow = 228 floats (228 = 4 mod 32: conflict-free both for the fragment-layout stores, bank
+// 8t + g, and for the [head g][key 8m + t] operand loads, bank 4g + t).  The softmax correction
+// needs no second pass: delta_i = sum_k p_i[k] dp_i[k] = sum_j T2[i][j] (sum_k p_i[k] dP_j[k]) is
+// read off the row's own d mix_post tile.  dp = T2 dP and dS = T1 dt are one MMA each per 16 keys,
+// chained through registers like the forward.
+constexpr int kTcRow = 228;
+
+template <int H>
+__global__ void __launch_bounds__(kRowWarps * 32, 3)
+thsoftmax_bwd_tc_kernel(const SoftArgs a) {
+  static_assert(H <= 8, "one m16n8k8 tile holds the H x H transform");
+  extern __shared__ float park[];   // [kRowWarps][2][8][kTcRow]: p / dt rows, raw dP rows
+  __shared__ float red1[64], red2[64];
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) { red1[i] = 0.f; red2[i] = 0.f; }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+  float* bufP = park + (size_t)warp * 2 * 8 * kTcRow;
+  float* bufD = bufP + 8 * kTcRow;
+  const int64_t rows = (int64_t)a.B * a.Nq;
+  const int64_t hs = (int64_t)a.Nq * a.ld;
+  const float sc = a.scale * kLog2e;
+  auto T1 = [&](int h, int i) { return (h < H && i < H) ? a.mix_pre[h * H + i] : 0.f; };
+  auto T2 = [&](int i, int j) { return (i < H && j < H) ? a.mix_post[i * H + j] : 0.f; };
+  // pre-softmax mix, 3 x TF32: B[k = h][n = i] = T1[h][i] * scale * log2(e); lane: h = t, t + 4; i = g
+  const float b1a = T1(t, g) * sc, b1b = T1(t + 4, g) * sc;
+  const uint32_t bh0 = tf32_rna(b1a), bh1 = tf32_rna(b1b);
+  const uint32_t bl0 = tf32_rna(b1a - __uint_as_float(bh0)), bl1 = tf32_rna(b1b - __uint_as_float(bh1));
+  // dp^T[keys x i] = dP^T[keys x j] T2^T: B[k = j][n = i] = T2[i][j]; lane: j = t, t + 4; i = g
+  const uint32_t bd0 = tf32_rna(T2(g, t)), bd1 = tf32_rna(T2(g, t + 4));
+  // dS^T[keys x h] = dt[keys x i] T1^T with i renumbered (k = t <-> 2t, k = t + 4 <-> 2t + 1):
+  // B[i][n = h] = T1[h][i]; lane: i = 2t, 2t + 1; h = g
+  const uint32_t bs0 = tf32_rna(T1(g, 2 * t)), bs1 = tf32_rna(T1(g, 2 * t + 1));
+  // delta from the row's d mix_post tile: lane holds [i = g][j = 2t, 2t + 1]
+  const float w0 = T2(g, 2 * t), w1 = T2(g, 2 * t + 1);
+  float c1[2][4], c2[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) { c1[0][e] = 0.f; c1[1][e] = 0.f; c2[e] = 0.f; }
+  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + warp; row < rows;
+       row += (int64_t)gridDim.x * kRowWarps) {
+    const int q = (int)(row % a.Nq);
+    const int64_t b = row / a.Nq;
+    const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
+    const float* s0 = a.S + off;
+    const float* d0 = a.dP + off;
+    bf16* ds0 = a.dS + off;
+    // (a) raw dP -> bufD[j][key], zeros beyond Nk (the MMAs read whole blocks); lane: j = t, t + 4; keys g, g + 8
+#pragma unroll
+    for (int blk = 0; blk < kTcBlocks; ++blk) {
+      if (16 * blk < a.Nk) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int j = t + 4 * (e >> 1), k = 16 * blk + g + 8 * (e & 1);
+          if (j < H && k < a.Nk) cp_async4(&bufD[j * kTcRow + k], d0 + j * hs + k);
+          else bufD[j * kTcRow + k] = 0.f;
+        }
+      }
+    }
+    // (b) probabilities in fragment registers: tm[blk] = keys (g, g + 8) x heads (2t, 2t + 1)
+    float tm[kTcBlocks][4], inv[2];
+    th_tc_logits<H>(a, s0, hs, g, t, bh0, bh1, bl0, bl1, tm);
+    th_tc_softmax(tm, inv);
+    // (c) p -> bufP[i][key]
+#pragma unroll
+    for (int blk = 0; blk < kTcBlocks; ++blk) {
+      if (16 * blk < a.Nk) {
+        const int k0 = 16 * blk + g;
+        tm[blk][0] *= inv[0]; tm[blk][2] *= inv[0];
+        tm[blk][1] *= inv[1]; tm[blk][3] *= inv[1];
+        bufP[(2 * t) * kTcRow + k0] = tm[blk][0];
+        bufP[(2 * t + 1) * kTcRow + k0] = tm[blk][1];
+        bufP[(2 * t) * kTcRow + k0 + 8] = tm[blk][2];
+        bufP[(2 * t + 1) * kTcRow + k0 + 8] = tm[blk][3];
+      }
+    }
+    cp_async_wait_all();
+    __syncwarp();
+    // (e) this row's d mix_post tile: r2[i][j] = sum_k p_i[k] dP_j[k]; A = p [i = g][keys t, t + 4],
+    //     B = dP [keys t, t + 4][j = g]; two chains
+    float r2[2][4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { r2[0][e] = 0.f; r2[1][e] = 0.f; }
+#pragma unroll
+    for (int mb = 0; mb < 2 * kTcBlocks; ++mb) {
+      if (8 * mb < a.Nk) {                          // warp-uniform
+        const int o = g * kTcRow + 8 * mb + t;
+        mma_tf32_m16n8k8(r2[mb & 1], __float_as_uint(bufP[o]), 0u, __float_as_uint(bufP[o + 4]), 0u,
+                         __float_as_uint(bufD[o]), __float_as_uint(bufD[o + 4]));
+      }
+    }
+    const float g2a = r2[0][0] + r2[1][0], g2b = r2[0][1] + r2[1][1];
+    c2[0] += g2a;
+    c2[1] += g2b;
+    // (f) delta_i for i = g on every lane of group g, then for this lane's heads 2t, 2t + 1
+    float dl = w0 * g2a + w1 * g2b;
+    dl += __shfl_xor_sync(0xffffffffu, dl, 1);
+    dl += __shfl_xor_sync(0xffffffffu, dl, 2);
+    const float dl0 = __shfl_sync(0xffffffffu, dl, 8 * t), dl1 = __shfl_sync(0xffffffffu, dl, 8 * t + 4);
+    // (g) per 16 keys: dp = T2 dP, dt = p (dp - delta) scale, dS = T1 dt
+#pragma unroll
+    for (int blk = 0; blk < kTcBlocks; ++blk) {
+      if (16 * blk < a.ld) {                        // warp-uniform
+        const int k0 = 16 * blk + g, k1 = k0 + 8;
+        float dp[4] = {0.f, 0.f, 0.f, 0.f};
+        mma_tf32_m16n8k8(dp, __float_as_uint(bufD[t * kTcRow + k0]), __float_as_uint(bufD[t * kTcRow + k1]),
+                         __float_as_uint(bufD[(t + 4) * kTcRow + k0]),
+                         __float_as_uint(bufD[(t + 4) * kTcRow + k1]), bd0, bd1);
+        // dp: keys (g, g + 8) x heads (2t, 2t + 1), like tm
+        tm[blk][0] = tm[blk][0] * (dp[0] - dl0) * a.scale;
+        tm[blk][1] = tm[blk][1] * (dp[1] - dl1) * a.scale;
+        tm[blk][2] = tm[blk][2] * (dp[2] - dl0) * a.scale;
+        tm[blk][3] = tm[blk][3] * (dp[3] - dl1) * a.scale;
+        float ds[4] = {0.f, 0.f, 0.f, 0.f};
+        mma_tf32_m16n8k8(ds, tf32_rna(tm[blk][0]), tf32_rna(tm[blk][2]), tf32_rna(tm[blk][1]),
+                         tf32_rna(tm[blk][3]), bs0, bs1);
+        // ds: keys (g, g + 8) x raw heads (2t, 2t + 1)
+        if (2 * t < H) {
+          if (k0 < a.ld) ds0[(2 * t) * hs + k0] = __float2bfloat16(ds[0]);
+          if (k1 < a.ld) ds0[(2 * t) * hs + k1] = __float2bfloat16(ds[2]);
+        }
+        if (2 * t + 1 < H) {
+          if (k0 < a.ld) ds0[(2 * t + 1) * hs + k0] = __float2bfloat16(ds[1]);
+          if (k1 < a.ld) ds0[(2 * t + 1) * hs + k1] = __float2bfloat16(ds[3]);
+        }
+      }
+    }
+    __syncwarp();        // every lane has read p from bufP
+    // (h) dt -> bufP[i][key]
+#pragma unroll
+    for (int blk = 0; blk < kTcBlocks; ++blk) {
+      if (16 * blk < a.Nk) {
+        const int k0 = 16 * blk + g;
+        bufP[(2 * t) * kTcRow + k0] = tm[blk][0];
+        bufP[(2 * t + 1) * kTcRow + k0] = tm[blk][1];
+        bufP[(2 * t) * kTcRow + k0 + 8] = tm[blk][2];
+        bufP[(2 * t + 1) * kTcRow + k0 + 8] = tm[blk][3];
+      }
+    }
+    __syncwarp();
+    // (i) d mix_pre[h][i] += sum_k s_h[k] dt_i[k]: A = raw S [h = g][keys t, t + 4] (L2 resident, the
+    //     loads of 32 keys issued together), B = dt [keys t, t + 4][i = g]
+#pragma unroll
+    for (int kk = 0; kk < kKPL; ++kk) {
+      if (32 * kk < a.Nk) {                         // warp-uniform
+        const float* sg = s0 + (g < H ? g : 0) * hs + 32 * kk + t;
+        float a0[4], a2[4];
+#pragma unroll
+        for (int mb = 0; mb < 4; ++mb) {
+          const int k0 = 32 * kk + 8 * mb + t;
+          a0[mb] = (g < H && k0 < a.Nk) ? __ldg(sg + 8 * mb) : 0.f;
+          a2[mb] = (g < H && k0 + 4 < a.Nk) ? __ldg(sg + 8 * mb + 4) : 0.f;
+        }
+#pragma unroll
+        for (int mb = 0; mb < 4; ++mb) {
+          if (32 * kk + 8 * mb < a.Nk) {            // warp-uniform
+            const int o = g * kTcRow + 32 * kk + 8 * mb + t;
+            mma_tf32_m16n8k8(c1[mb & 1], __float_as_uint(a0[mb]), 0u, __float_as_uint(a2[mb]), 0u,
+                             __float_as_uint(bufP[o]), __float_as_uint(bufP[o + 4]));
+          }
+        }
+      }
+    }
+    __syncwarp();   // the next row overwrites bufP / bufD
+  }
+  // lane (g, t) holds entries [g][2t], [g][2t + 1] of both gradients
+  if (g < H) {
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int col = 2 * t + e;
+      if (col < H) {
+        atomicAdd(&red1[g * H + col], c1[0][e] + c1[1][e]);
+        atomicAdd(&red2[g * H + col], c2[e]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
+    atomicAdd(a.dmix_pre + i, red1[i]);
+    atomicAdd(a.dmix_post + i, red2[i]);
+  }
+}
+
+template <int H>
+static int launch_th_bwd_tc(const SoftArgs& a, cudaStream_t st) {
+  const size_t sm = (size_t)kRowWarps * 2 * 8 * kTcRow * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(thsoftmax_bwd_tc_kernel<H>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "thsoftmax smem attr: %s", cudaGetErrorString(e));
+    attr_set = true;
+  }
+  // three resident blocks per SM (3 x 58 KB of shared memory); every block ends with 2 H^2 atomics
+  const int64_t blocks = ((int64_t)a.B * a.Nq + kRowWarps - 1) / kRowWarps;
+  const int grid = (int)(blocks < 148 * 3 ? blocks : 148 * 3);
+  thsoftmax_bwd_tc_kernel<H><<<grid, kRowWarps * 32, sm, st>>>(a);
+  return SAV_OK;
+}
+
 template <int H>
 static int launch_th_bwd_res(const SoftArgs& a, int grid, cudaStream_t st) {
   const size_t sm = (size_t)kRowWarps * 2 * kKPL * H * 32 * sizeof(float);
@@ -965,7 +1322,7 @@ extern "C" int sav_thsoftmax_fwd(const sav_thsoftmax_args* x, void* stream) {
     switch (a.H) {
 #define SAV_TH_CASE(Hv)                                                              \
   case Hv:                                                                           \
-    if (res) thsoftmax_fwd_res_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a);       \
+    if (res) thsoftmax_fwd_tc_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a);        \
     else thsoftmax_fwd_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a);               \
     break;
       SAV_TH_CASE(2) SAV_TH_CASE(3) SAV_TH_CASE(4) SAV_TH_CASE(6) SAV_TH_CASE(8)
@@ -1001,7 +1358,7 @@ extern "C" int sav_thsoftmax_bwd(const sav_thsoftmax_args* x, void* stream) {
     switch (a.H) {
 #define SAV_TH_CASE(Hv)                                                              \
   case Hv:                                                                           \
-    if (res) { if ((rc = launch_th_bwd_mma<Hv>(a, st))) return rc; }                 \
+    if (res) { if ((rc = launch_th_bwd_tc<Hv>(a, st))) return rc; }                  \
     else thsoftmax_bwd_kernel<Hv><<<grid, kRowWarps * 32, 0, st>>>(a);               \
     break;
       SAV_TH_CASE(2) SAV_TH_CASE(3) SAV_TH_CASE(4) SAV_TH_CASE(6) SAV_TH_CASE(8)
