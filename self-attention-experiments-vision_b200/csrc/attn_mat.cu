@@ -9,7 +9,11 @@
 //   * BoTNet 2-D relative position logits (botnet.py:70-141): the per-query tables q.r^W, q.r^H
 //     (one skinny GEMM) are gathered into the logits here, and their gradient is scattered back;
 //   * class attention (cait.py:10-15, Nq = 1) and head dims other than 64 need nothing special.
-// One warp per row, lanes stride over the keys (coalesced 128-byte accesses per head), fp32
+// One warp per row.  Rows of up to 224 keys with at most 8 heads (every CaiT-XXS / XS / S layer) run
+// on the tensor cores: both H x H mixes, the backward's dp / dS products and the two transform
+// gradients are TF32 mma.sync tiles over 16-key blocks (see "talking heads entirely on the tensor
+// cores" below).  Everything else (12 / 16 heads, longer rows, relative logits, independent heads)
+// uses the CUDA-core kernels: lanes stride over the keys (coalesced 128-byte accesses per head), fp32
 // statistics by warp shuffle, three passes over L1/L2-resident rows (max+sum, delta, outputs).
 #include "common.cuh"
 #include "host.h"
@@ -433,477 +437,16 @@ static void launch_th_bwd_slices(const SoftArgs& a, int grid, cudaStream_t st) {
   if constexpr (I0 + HS < H) launch_th_bwd_slices<H, HS, I0 + HS>(a, grid, st);
 }
 
-// ---- register / shared-memory resident variants for Nk <= 32 * KPL (CaiT: 196 / 197 keys).
-// The row's mixed logits are computed ONCE: forward keeps exp(t - m) for the lane's keys in
-// registers between the statistics and the output pass; backward parks p and dp in shared memory
-// (conflict-free [slot][lane] layout) so that S is read twice and dP once, instead of 4x / 2x.
+// ---- rows of up to 32 * kKPL = 224 keys (CaiT: 196 / 197) have dedicated kernels below
 constexpr int kKPL = 7;
 
-// 4-byte asynchronous global -> shared copy: the whole row (H x Nk logits and their gradients) is
-// requested up front without holding a register per element, so one warp keeps ~14 KB in flight
+// 4-byte asynchronous global -> shared copy: a row's dP is requested up front without holding a
+// register per element
 __device__ __forceinline__ void cp_async4(float* dst, const float* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() {
   asm volatile("cp.async.wait_all;" ::: "memory");
-}
-
-template <int H>
-__global__ void __launch_bounds__(kRowWarps * 32)
-thsoftmax_fwd_res_kernel(const SoftArgs a) {
-  __shared__ float t1[H * H], t2[H * H];
-  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
-    t1[i] = a.mix_pre[i];
-    t2[i] = a.mix_post[i];
-  }
-  __syncthreads();
-  const int lane = threadIdx.x & 31;
-  const int64_t rows = (int64_t)a.B * a.Nq;
-  const int64_t hs = (int64_t)a.Nq * a.ld;
-  const float sc = a.scale * kLog2e;
-  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + (threadIdx.x >> 5); row < rows;
-       row += (int64_t)gridDim.x * kRowWarps) {
-    const int q = (int)(row % a.Nq);
-    const int64_t b = row / a.Nq;
-    const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
-    const float* s0 = a.S + off;
-    bf16* p0 = a.P + off;
-    float e[kKPL][H], m[H], inv[H];
-#pragma unroll
-    for (int i = 0; i < H; ++i) m[i] = -INFINITY;
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      const int k = lane + 32 * kk;
-      if (k < a.Nk) {
-        float s[H];
-        th_logits<H>(a, s0, hs, k, t1, sc, s, e[kk]);
-#pragma unroll
-        for (int i = 0; i < H; ++i) m[i] = fmaxf(m[i], e[kk][i]);
-      } else {
-#pragma unroll
-        for (int i = 0; i < H; ++i) e[kk][i] = -INFINITY;
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < H; ++i) { m[i] = warp_max(m[i]); inv[i] = 0.f; }
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk)
-#pragma unroll
-      for (int i = 0; i < H; ++i) {
-        e[kk][i] = ex2_fast(e[kk][i] - m[i]);   // exp2(-inf) = 0 for the padded keys
-        inv[i] += e[kk][i];
-      }
-#pragma unroll
-    for (int i = 0; i < H; ++i) inv[i] = 1.f / warp_sum(inv[i]);
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      const int k = lane + 32 * kk;
-      if (k < a.ld) {
-#pragma unroll
-        for (int j = 0; j < H; ++j) {
-          float acc = 0.f;
-#pragma unroll
-          for (int i = 0; i < H; ++i) acc = fmaf(t2[i * H + j], e[kk][i] * inv[i], acc);
-          p0[j * hs + k] = __float2bfloat16(acc);
-        }
-      }
-    }
-  }
-}
-
-template <int H>
-__global__ void __launch_bounds__(kRowWarps * 32)
-thsoftmax_bwd_res_kernel(const SoftArgs a) {
-  extern __shared__ float park[];   // [kRowWarps][2][kKPL * H][32]
-  __shared__ float t1[H * H], t2[H * H];
-  __shared__ float red1[H * H], red2[H * H];
-  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
-    t1[i] = a.mix_pre[i];
-    t2[i] = a.mix_post[i];
-    red1[i] = 0.f;
-    red2[i] = 0.f;
-  }
-  __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float* pp = park + (size_t)warp * 2 * kKPL * H * 32 + lane;   // p  at pp[(kk*H+i)*32]
-  float* dd = pp + kKPL * H * 32;                               // dp at dd[(kk*H+i)*32]
-  const int64_t rows = (int64_t)a.B * a.Nq;
-  const int64_t hs = (int64_t)a.Nq * a.ld;
-  const float sc = a.scale * kLog2e;
-  float g1[H * H], g2[H * H];
-#pragma unroll
-  for (int i = 0; i < H * H; ++i) { g1[i] = 0.f; g2[i] = 0.f; }
-  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + warp; row < rows;
-       row += (int64_t)gridDim.x * kRowWarps) {
-    const int q = (int)(row % a.Nq);
-    const int64_t b = row / a.Nq;
-    const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
-    const float* s0 = a.S + off;
-    const float* d0 = a.dP + off;
-    bf16* ds0 = a.dS + off;
-    float m[H], inv[H], delta[H];
-#pragma unroll
-    for (int i = 0; i < H; ++i) m[i] = -INFINITY;
-    // pass 0: request the row -- raw logits into the p slots, dP into the dp slots
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      const int k = lane + 32 * kk;
-      if (k < a.Nk) {
-#pragma unroll
-        for (int h = 0; h < H; ++h) {
-          cp_async4(&pp[(kk * H + h) * 32], s0 + h * hs + k);
-          cp_async4(&dd[(kk * H + h) * 32], d0 + h * hs + k);
-        }
-      }
-    }
-    cp_async_wait_all();
-    // pass 1: mixed logits (in place), running max
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      const int k = lane + 32 * kk;
-      float t[H];
-      if (k < a.Nk) {
-        float s[H];
-#pragma unroll
-        for (int h = 0; h < H; ++h) s[h] = pp[(kk * H + h) * 32];
-#pragma unroll
-        for (int i = 0; i < H; ++i) {
-          float acc = 0.f;
-#pragma unroll
-          for (int h = 0; h < H; ++h) acc = fmaf(t1[h * H + i], s[h], acc);
-          t[i] = acc * sc;
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < H; ++i) t[i] = -INFINITY;
-      }
-#pragma unroll
-      for (int i = 0; i < H; ++i) {
-        m[i] = fmaxf(m[i], t[i]);
-        pp[(kk * H + i) * 32] = t[i];
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < H; ++i) { m[i] = warp_max(m[i]); inv[i] = 0.f; }
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk)
-#pragma unroll
-      for (int i = 0; i < H; ++i) {
-        const float ev = ex2_fast(pp[(kk * H + i) * 32] - m[i]);
-        pp[(kk * H + i) * 32] = ev;
-        inv[i] += ev;
-      }
-#pragma unroll
-    for (int i = 0; i < H; ++i) { inv[i] = 1.f / warp_sum(inv[i]); delta[i] = 0.f; }
-    // pass 2: p, dp = T2 dP', delta, d mix_post
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      const int k = lane + 32 * kk;
-      if (k < a.Nk) {
-        float dpo[H];
-#pragma unroll
-        for (int j = 0; j < H; ++j) dpo[j] = dd[(kk * H + j) * 32];
-#pragma unroll
-        for (int i = 0; i < H; ++i) {
-          const float pi = pp[(kk * H + i) * 32] * inv[i];
-          pp[(kk * H + i) * 32] = pi;
-          float dpi = 0.f;
-#pragma unroll
-          for (int j = 0; j < H; ++j) {
-            dpi = fmaf(t2[i * H + j], dpo[j], dpi);
-            g2[i * H + j] = fmaf(pi, dpo[j], g2[i * H + j]);
-          }
-          dd[(kk * H + i) * 32] = dpi;
-          delta[i] = fmaf(pi, dpi, delta[i]);
-        }
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < H; ++i) delta[i] = warp_sum(delta[i]);
-    // pass 3: d logits, dS = T1 dt, d mix_pre (raw S re-read: L1 / L2 resident)
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      const int k = lane + 32 * kk;
-      if (k < a.ld) {
-        float dt[H], s[H];
-        if (k < a.Nk) {
-#pragma unroll
-          for (int i = 0; i < H; ++i) {
-            dt[i] = pp[(kk * H + i) * 32] * (dd[(kk * H + i) * 32] - delta[i]) * a.scale;
-            s[i] = s0[i * hs + k];
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < H; ++i) { dt[i] = 0.f; s[i] = 0.f; }
-        }
-#pragma unroll
-        for (int h = 0; h < H; ++h) {
-          float acc = 0.f;
-#pragma unroll
-          for (int i = 0; i < H; ++i) {
-            acc = fmaf(t1[h * H + i], dt[i], acc);
-            g1[h * H + i] = fmaf(s[h], dt[i], g1[h * H + i]);
-          }
-          ds0[h * hs + k] = __float2bfloat16(acc);
-        }
-      }
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < H * H; ++i) {
-    const float v1 = warp_sum(g1[i]);
-    const float v2 = warp_sum(g2[i]);
-    if (lane == 0) {
-      atomicAdd(&red1[i], v1);
-      atomicAdd(&red2[i], v2);
-    }
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
-    atomicAdd(a.dmix_pre + i, red1[i]);
-    atomicAdd(a.dmix_post + i, red2[i]);
-  }
-}
-
-// ---- backward with the two H x H transform gradients on the tensor cores (H <= 8).
-// d mix_post[i][j] = sum_k p_i[k] dP_j[k] and d mix_pre[h][i] = sum_k s_h[k] dt_i[k] are contractions
-// over the keys.  Held as per-lane outer-product accumulators they cost 2 * H * H registers and
-// 2 * H * H FMAs per key (255 registers, 8 warps per SM, 35 % issue utilisation at H = 8:
-// profiles/r02ar_thsoftmax_bwd_hot.txt).  Here the operands are already parked in shared memory
-// ([slot][lane] rows of kParkStride = 36 floats: conflict-free for the per-lane passes AND for the
-// mma fragment pattern bank = 4 g + t), so each block of 8 keys is one
-// mma.sync.m16n8k8 (TF32 inputs, fp32 accumulate; rows 8..15 of A are zero padding) per transform
-// and the accumulators are 4 registers each.  TF32 rounds p, dP, s, dt to 11 bits for THESE TWO
-// [H, H] gradients only (sums over B * Nq * Nk terms; 1.5e-2 test tolerance, measured < 1e-3);
-// logits, probabilities and dS keep the fp32 path.
-constexpr int kParkStride = 36;
-
-__device__ __forceinline__ void mma_tf32_m16n8k8_top(float (&c)[4], float a0, float a2, float b0, float b1) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
-      "{%0, %1, %2, %3};"
-      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-      : "r"(__float_as_uint(a0)), "r"(0u), "r"(__float_as_uint(a2)), "r"(0u), "r"(__float_as_uint(b0)),
-        "r"(__float_as_uint(b1)));
-}
-
-template <int H>
-__global__ void __launch_bounds__(kRowWarps * 32, 3)
-thsoftmax_bwd_mma_kernel(const SoftArgs a) {
-  static_assert(H <= 8, "one m16n8k8 tile holds the H x H transform gradient");
-  extern __shared__ float park[];   // [kRowWarps][2][kKPL * H][kParkStride]
-  __shared__ float t1[H * H], t2[H * H];
-  __shared__ float red1[H * H], red2[H * H];
-  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
-    t1[i] = a.mix_pre[i];
-    t2[i] = a.mix_post[i];
-    red1[i] = 0.f;
-    red2[i] = 0.f;
-  }
-  __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int g = lane >> 2, t = lane & 3;                          // mma fragment coordinates
-  constexpr int kHalf = kKPL * H * kParkStride;
-  float* pw = park + (size_t)warp * 2 * kHalf;                    // p  rows of this warp
-  float* dw = pw + kHalf;                                          // dp rows
-  float* pp = pw + lane;                                           // p  at pp[(kk*H+i)*kParkStride]
-  float* dd = dw + lane;                                           // dp at dd[(kk*H+i)*kParkStride]
-  const int64_t rows = (int64_t)a.B * a.Nq;
-  const int64_t hs = (int64_t)a.Nq * a.ld;
-  const float sc = a.scale * kLog2e;
-  const bool grow = g < H;                                         // this lane's A row / B column exists
-  // four independent accumulator tiles per transform (one per 8-key block of a 32-key slot): a
-  // single tile would chain 28 dependent MMAs per row
-  float c1[4][4], c2[4][4];
-#pragma unroll
-  for (int u = 0; u < 4; ++u)
-#pragma unroll
-    for (int e = 0; e < 4; ++e) { c1[u][e] = 0.f; c2[u][e] = 0.f; }
-  for (int64_t row = (int64_t)blockIdx.x * kRowWarps + warp; row < rows;
-       row += (int64_t)gridDim.x * kRowWarps) {
-    const int q = (int)(row % a.Nq);
-    const int64_t b = row / a.Nq;
-    const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
-    const float* s0 = a.S + off;
-    const float* d0 = a.dP + off;
-    bf16* ds0 = a.dS + off;
-    float m[H], inv[H], delta[H];
-#pragma unroll
-    for (int i = 0; i < H; ++i) m[i] = -INFINITY;
-    // pass 0: request the row -- raw logits into the p slots, dP into the dp slots (zeros beyond Nk:
-    // the transform-gradient MMAs read whole 8-key blocks)
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      const int k = lane + 32 * kk;
-      if (k < a.Nk) {
-#pragma unroll
-        for (int h = 0; h < H; ++h) {
-          cp_async4(&pp[(kk * H + h) * kParkStride], s0 + h * hs + k);
-          cp_async4(&dd[(kk * H + h) * kParkStride], d0 + h * hs + k);
-        }
-      } else {
-#pragma unroll
-        for (int h = 0; h < H; ++h) dd[(kk * H + h) * kParkStride] = 0.f;
-      }
-    }
-    cp_async_wait_all();
-    // pass 1: mixed logits (in place), running max
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      const int k = lane + 32 * kk;
-      float tt[H];
-      if (k < a.Nk) {
-        float s[H];
-#pragma unroll
-        for (int h = 0; h < H; ++h) s[h] = pp[(kk * H + h) * kParkStride];
-#pragma unroll
-        for (int i = 0; i < H; ++i) {
-          float acc = 0.f;
-#pragma unroll
-          for (int h = 0; h < H; ++h) acc = fmaf(t1[h * H + i], s[h], acc);
-          tt[i] = acc * sc;
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < H; ++i) tt[i] = -INFINITY;
-      }
-#pragma unroll
-      for (int i = 0; i < H; ++i) {
-        m[i] = fmaxf(m[i], tt[i]);
-        pp[(kk * H + i) * kParkStride] = tt[i];
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < H; ++i) { m[i] = warp_max(m[i]); inv[i] = 0.f; }
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk)
-#pragma unroll
-      for (int i = 0; i < H; ++i) {
-        const float ev = ex2_fast(pp[(kk * H + i) * kParkStride] - m[i]);   // 0 for the padded keys
-        pp[(kk * H + i) * kParkStride] = ev;
-        inv[i] += ev;
-      }
-#pragma unroll
-    for (int i = 0; i < H; ++i) { inv[i] = 1.f / warp_sum(inv[i]); delta[i] = 0.f; }
-    // pass 2a: normalised probabilities in place
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk)
-#pragma unroll
-      for (int i = 0; i < H; ++i) pp[(kk * H + i) * kParkStride] *= inv[i];
-    __syncwarp();
-    // d mix_post[i][j] += sum_k p_i[k] dP_j[k]: A = p [i x 8 keys], B = dP [8 keys x j]
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk)
-#pragma unroll
-      for (int mb = 0; mb < 4; ++mb) {
-        if (32 * kk + 8 * mb < a.Nk) {           // warp-uniform
-          const int o = (kk * H + (grow ? g : 0)) * kParkStride + 8 * mb + t;
-          const float a0 = grow ? pw[o] : 0.f, a2 = grow ? pw[o + 4] : 0.f;
-          const float b0 = grow ? dw[o] : 0.f, b1 = grow ? dw[o + 4] : 0.f;
-          mma_tf32_m16n8k8_top(c2[mb], a0, a2, b0, b1);
-        }
-      }
-    __syncwarp();
-    // pass 2b: dp = T2 dP' (in place), delta
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      const int k = lane + 32 * kk;
-      if (k < a.Nk) {
-        float dpo[H];
-#pragma unroll
-        for (int j = 0; j < H; ++j) dpo[j] = dd[(kk * H + j) * kParkStride];
-#pragma unroll
-        for (int i = 0; i < H; ++i) {
-          float dpi = 0.f;
-#pragma unroll
-          for (int j = 0; j < H; ++j) dpi = fmaf(t2[i * H + j], dpo[j], dpi);
-          dd[(kk * H + i) * kParkStride] = dpi;
-          delta[i] = fmaf(pp[(kk * H + i) * kParkStride], dpi, delta[i]);
-        }
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < H; ++i) delta[i] = warp_sum(delta[i]);
-    // pass 3: d logits (parked over p for the second MMA), dS = T1 dt
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      const int k = lane + 32 * kk;
-      if (k < a.ld) {
-        float dt[H];
-#pragma unroll
-        for (int i = 0; i < H; ++i) {
-          dt[i] = (k < a.Nk) ? pp[(kk * H + i) * kParkStride] * (dd[(kk * H + i) * kParkStride] - delta[i]) * a.scale
-                             : 0.f;
-          pp[(kk * H + i) * kParkStride] = dt[i];
-        }
-#pragma unroll
-        for (int h = 0; h < H; ++h) {
-          float acc = 0.f;
-#pragma unroll
-          for (int i = 0; i < H; ++i) acc = fmaf(t1[h * H + i], dt[i], acc);
-          ds0[h * hs + k] = __float2bfloat16(acc);
-        }
-      }
-    }
-    __syncwarp();
-    // d mix_pre[h][i] += sum_k s_h[k] dt_i[k]: A = raw S [h x 8 keys] (L1 / L2 resident; the eight
-    // fragment loads of a slot are issued together, ahead of its MMAs), B = dt
-#pragma unroll
-    for (int kk = 0; kk < kKPL; ++kk) {
-      if (32 * kk < a.Nk) {                        // warp-uniform
-        const float* sg = s0 + (grow ? g : 0) * hs + 32 * kk + t;
-        float a0[4], a2[4];
-#pragma unroll
-        for (int mb = 0; mb < 4; ++mb) {
-          const int k0 = 32 * kk + 8 * mb + t;
-          a0[mb] = (grow && k0 < a.Nk) ? __ldg(sg + 8 * mb) : 0.f;
-          a2[mb] = (grow && k0 + 4 < a.Nk) ? __ldg(sg + 8 * mb + 4) : 0.f;
-        }
-#pragma unroll
-        for (int mb = 0; mb < 4; ++mb) {
-          if (32 * kk + 8 * mb < a.Nk) {           // warp-uniform
-            const int o = (kk * H + (grow ? g : 0)) * kParkStride + 8 * mb + t;
-            const float b0 = grow ? pw[o] : 0.f, b1 = grow ? pw[o + 4] : 0.f;
-            mma_tf32_m16n8k8_top(c1[mb], a0[mb], a2[mb], b0, b1);
-          }
-        }
-      }
-    }
-    __syncwarp();   // the next row's copies overwrite what other lanes have just read
-  }
-  // lane (g, t) holds entries [g][2t], [g][2t+1] of both gradients
-  if (grow) {
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int col = 2 * t + e;
-      if (col < H) {
-        atomicAdd(&red1[g * H + col], (c1[0][e] + c1[1][e]) + (c1[2][e] + c1[3][e]));
-        atomicAdd(&red2[g * H + col], (c2[0][e] + c2[1][e]) + (c2[2][e] + c2[3][e]));
-      }
-    }
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < H * H; i += blockDim.x) {
-    atomicAdd(a.dmix_pre + i, red1[i]);
-    atomicAdd(a.dmix_post + i, red2[i]);
-  }
-}
-
-template <int H>
-static int launch_th_bwd_mma(const SoftArgs& a, cudaStream_t st) {
-  const size_t sm = (size_t)kRowWarps * 2 * kKPL * H * kParkStride * sizeof(float);
-  static bool attr_set = false;
-  if (!attr_set && sm > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(thsoftmax_bwd_mma_kernel<H>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "thsoftmax smem attr: %s", cudaGetErrorString(e));
-    attr_set = true;
-  }
-  // three resident blocks per SM (shared memory: 3 x 64.5 KB at H = 8); every block ends with 2 H^2 atomics
-  const int64_t blocks = ((int64_t)a.B * a.Nq + kRowWarps - 1) / kRowWarps;
-  const int grid = (int)(blocks < 148 * 3 ? blocks : 148 * 3);
-  thsoftmax_bwd_mma_kernel<H><<<grid, kRowWarps * 32, sm, st>>>(a);
-  return SAV_OK;
 }
 
 // ---- talking heads entirely on the tensor cores (H <= 8, rows of <= 224 keys).
@@ -1260,20 +803,6 @@ static int launch_th_bwd_tc(const SoftArgs& a, cudaStream_t st) {
   const int64_t blocks = ((int64_t)a.B * a.Nq + kRowWarps - 1) / kRowWarps;
   const int grid = (int)(blocks < 148 * 3 ? blocks : 148 * 3);
   thsoftmax_bwd_tc_kernel<H><<<grid, kRowWarps * 32, sm, st>>>(a);
-  return SAV_OK;
-}
-
-template <int H>
-static int launch_th_bwd_res(const SoftArgs& a, int grid, cudaStream_t st) {
-  const size_t sm = (size_t)kRowWarps * 2 * kKPL * H * 32 * sizeof(float);
-  static bool attr_set = false;
-  if (!attr_set && sm > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(thsoftmax_bwd_res_kernel<H>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    if (e != cudaSuccess) return set_error(SAV_ERR_CUDA, "thsoftmax smem attr: %s", cudaGetErrorString(e));
-    attr_set = true;
-  }
-  thsoftmax_bwd_res_kernel<H><<<grid, kRowWarps * 32, sm, st>>>(a);
   return SAV_OK;
 }
 
