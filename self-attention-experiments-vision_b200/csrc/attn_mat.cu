@@ -497,25 +497,26 @@ __device__ __forceinline__ void th_tc_logits(const SoftArgs& a, const float* s0,
                                              float (&tm)[kTcBlocks][4]) {
   // all loads of the row first (one DRAM round trip per row, not one per block), parked in the
   // registers that receive the products
+  const float* sa = s0 + (t < H ? t : 0) * hs + g;            // head t,     key g of block 0
+  const float* sb = s0 + (t + 4 < H ? t + 4 : 0) * hs + g;    // head t + 4
+  const int nk_g = a.Nk - g;                                   // key 16 blk + g (+ 8) < Nk  <=>  16 blk (+ 8) < nk_g
 #pragma unroll
   for (int blk = 0; blk < kTcBlocks; ++blk) {
-    const int k0 = 16 * blk + g, k1 = k0 + 8;
-    tm[blk][0] = (t < H && k0 < a.Nk) ? __ldg(s0 + t * hs + k0) : 0.f;
-    tm[blk][1] = (t < H && k1 < a.Nk) ? __ldg(s0 + t * hs + k1) : 0.f;
-    tm[blk][2] = (t + 4 < H && k0 < a.Nk) ? __ldg(s0 + (t + 4) * hs + k0) : 0.f;
-    tm[blk][3] = (t + 4 < H && k1 < a.Nk) ? __ldg(s0 + (t + 4) * hs + k1) : 0.f;
+    tm[blk][0] = (t < H && 16 * blk < nk_g) ? __ldg(sa + 16 * blk) : 0.f;
+    tm[blk][1] = (t < H && 16 * blk + 8 < nk_g) ? __ldg(sa + 16 * blk + 8) : 0.f;
+    tm[blk][2] = (t + 4 < H && 16 * blk < nk_g) ? __ldg(sb + 16 * blk) : 0.f;
+    tm[blk][3] = (t + 4 < H && 16 * blk + 8 < nk_g) ? __ldg(sb + 16 * blk + 8) : 0.f;
   }
 #pragma unroll
   for (int blk = 0; blk < kTcBlocks; ++blk) {
     if (16 * blk < a.Nk) {                         // warp-uniform
-      const int k0 = 16 * blk + g, k1 = k0 + 8;
       const float av[4] = {tm[blk][0], tm[blk][1], tm[blk][2], tm[blk][3]};
       float c[4] = {0.f, 0.f, 0.f, 0.f};
       mma_3xtf32(c, av, bh0, bh1, bl0, bl1);
-      tm[blk][0] = (k0 < a.Nk) ? c[0] : -INFINITY;
-      tm[blk][1] = (k0 < a.Nk) ? c[1] : -INFINITY;
-      tm[blk][2] = (k1 < a.Nk) ? c[2] : -INFINITY;
-      tm[blk][3] = (k1 < a.Nk) ? c[3] : -INFINITY;
+      tm[blk][0] = (16 * blk < nk_g) ? c[0] : -INFINITY;
+      tm[blk][1] = (16 * blk < nk_g) ? c[1] : -INFINITY;
+      tm[blk][2] = (16 * blk + 8 < nk_g) ? c[2] : -INFINITY;
+      tm[blk][3] = (16 * blk + 8 < nk_g) ? c[3] : -INFINITY;
     } else {
       tm[blk][0] = tm[blk][1] = tm[blk][2] = tm[blk][3] = -INFINITY;
     }
@@ -579,6 +580,9 @@ thsoftmax_fwd_tc_kernel(const SoftArgs a) {
     const int64_t off = (b * a.H * a.Nq + q) * (int64_t)a.ld;
     const float* s0 = a.S + off;
     bf16* p0 = a.P + off;
+    bf16* pa = p0 + (2 * t < H ? 2 * t : 0) * hs + g;          // output head 2t,     key g of block 0
+    bf16* pb = p0 + (2 * t + 1 < H ? 2 * t + 1 : 0) * hs + g;  // output head 2t + 1
+    const int ld_g = a.ld - g;
     float tm[kTcBlocks][4], inv[2];
     th_tc_logits<H>(a, s0, hs, g, t, bh0, bh1, bl0, bl1, tm);
     th_tc_softmax(tm, inv);
@@ -590,14 +594,13 @@ thsoftmax_fwd_tc_kernel(const SoftArgs a) {
         mma_tf32_m16n8k8(c, tf32_rna(tm[blk][0] * inv[0]), tf32_rna(tm[blk][2] * inv[0]),
                          tf32_rna(tm[blk][1] * inv[1]), tf32_rna(tm[blk][3] * inv[1]), b2a, b2b);
         // c = mixed probabilities: keys g, g + 8 x output heads 2t, 2t + 1
-        const int k0 = 16 * blk + g, k1 = k0 + 8;
         if (2 * t < H) {
-          if (k0 < a.ld) p0[(2 * t) * hs + k0] = __float2bfloat16(c[0]);
-          if (k1 < a.ld) p0[(2 * t) * hs + k1] = __float2bfloat16(c[2]);
+          if (16 * blk < ld_g) pa[16 * blk] = __float2bfloat16(c[0]);
+          if (16 * blk + 8 < ld_g) pa[16 * blk + 8] = __float2bfloat16(c[2]);
         }
         if (2 * t + 1 < H) {
-          if (k0 < a.ld) p0[(2 * t + 1) * hs + k0] = __float2bfloat16(c[1]);
-          if (k1 < a.ld) p0[(2 * t + 1) * hs + k1] = __float2bfloat16(c[3]);
+          if (16 * blk < ld_g) pb[16 * blk] = __float2bfloat16(c[1]);
+          if (16 * blk + 8 < ld_g) pb[16 * blk + 8] = __float2bfloat16(c[3]);
         }
       }
     }
@@ -653,16 +656,25 @@ thsoftmax_bwd_tc_kernel(const SoftArgs a) {
     const float* s0 = a.S + off;
     const float* d0 = a.dP + off;
     bf16* ds0 = a.dS + off;
+    bf16* dsa = ds0 + (2 * t < H ? 2 * t : 0) * hs + g;
+    bf16* dsb = ds0 + (2 * t + 1 < H ? 2 * t + 1 : 0) * hs + g;
+    const int ld_g = a.ld - g, nk_g = a.Nk - g;
+    const float* da = d0 + (t < H ? t : 0) * hs + g;            // dP head t,     key g of block 0
+    const float* db = d0 + (t + 4 < H ? t + 4 : 0) * hs + g;    // dP head t + 4
+    float* bda = bufD + t * kTcRow + g;
+    float* bdb = bufD + (t + 4) * kTcRow + g;
     // (a) raw dP -> bufD[j][key], zeros beyond Nk (the MMAs read whole blocks); lane: j = t, t + 4; keys g, g + 8
 #pragma unroll
     for (int blk = 0; blk < kTcBlocks; ++blk) {
       if (16 * blk < a.Nk) {
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int j = t + 4 * (e >> 1), k = 16 * blk + g + 8 * (e & 1);
-          if (j < H && k < a.Nk) cp_async4(&bufD[j * kTcRow + k], d0 + j * hs + k);
-          else bufD[j * kTcRow + k] = 0.f;
-        }
+        if (t < H && 16 * blk < nk_g) cp_async4(bda + 16 * blk, da + 16 * blk);
+        else bda[16 * blk] = 0.f;
+        if (t < H && 16 * blk + 8 < nk_g) cp_async4(bda + 16 * blk + 8, da + 16 * blk + 8);
+        else bda[16 * blk + 8] = 0.f;
+        if (t + 4 < H && 16 * blk < nk_g) cp_async4(bdb + 16 * blk, db + 16 * blk);
+        else bdb[16 * blk] = 0.f;
+        if (t + 4 < H && 16 * blk + 8 < nk_g) cp_async4(bdb + 16 * blk + 8, db + 16 * blk + 8);
+        else bdb[16 * blk + 8] = 0.f;
       }
     }
     // (b) probabilities in fragment registers: tm[blk] = keys (g, g + 8) x heads (2t, 2t + 1)
@@ -709,11 +721,9 @@ thsoftmax_bwd_tc_kernel(const SoftArgs a) {
 #pragma unroll
     for (int blk = 0; blk < kTcBlocks; ++blk) {
       if (16 * blk < a.ld) {                        // warp-uniform
-        const int k0 = 16 * blk + g, k1 = k0 + 8;
         float dp[4] = {0.f, 0.f, 0.f, 0.f};
-        mma_tf32_m16n8k8(dp, __float_as_uint(bufD[t * kTcRow + k0]), __float_as_uint(bufD[t * kTcRow + k1]),
-                         __float_as_uint(bufD[(t + 4) * kTcRow + k0]),
-                         __float_as_uint(bufD[(t + 4) * kTcRow + k1]), bd0, bd1);
+        mma_tf32_m16n8k8(dp, __float_as_uint(bda[16 * blk]), __float_as_uint(bda[16 * blk + 8]),
+                         __float_as_uint(bdb[16 * blk]), __float_as_uint(bdb[16 * blk + 8]), bd0, bd1);
         // dp: keys (g, g + 8) x heads (2t, 2t + 1), like tm
         tm[blk][0] = tm[blk][0] * (dp[0] - dl0) * a.scale;
         tm[blk][1] = tm[blk][1] * (dp[1] - dl1) * a.scale;
@@ -724,12 +734,12 @@ thsoftmax_bwd_tc_kernel(const SoftArgs a) {
                          tf32_rna(tm[blk][3]), bs0, bs1);
         // ds: keys (g, g + 8) x raw heads (2t, 2t + 1)
         if (2 * t < H) {
-          if (k0 < a.ld) ds0[(2 * t) * hs + k0] = __float2bfloat16(ds[0]);
-          if (k1 < a.ld) ds0[(2 * t) * hs + k1] = __float2bfloat16(ds[2]);
+          if (16 * blk < ld_g) dsa[16 * blk] = __float2bfloat16(ds[0]);
+          if (16 * blk + 8 < ld_g) dsa[16 * blk + 8] = __float2bfloat16(ds[2]);
         }
         if (2 * t + 1 < H) {
-          if (k0 < a.ld) ds0[(2 * t + 1) * hs + k0] = __float2bfloat16(ds[1]);
-          if (k1 < a.ld) ds0[(2 * t + 1) * hs + k1] = __float2bfloat16(ds[3]);
+          if (16 * blk < ld_g) dsb[16 * blk] = __float2bfloat16(ds[1]);
+          if (16 * blk + 8 < ld_g) dsb[16 * blk + 8] = __float2bfloat16(ds[3]);
         }
       }
     }

@@ -133,17 +133,21 @@ __global__ void embed_fwd8_kernel(const bf16* __restrict__ tok, const float* __r
   }
 }
 
-// thread per (t, c-pair): loops over b; writes dpos[t,c], dcls (t==0), copies dtok.
+// thread per (t, c-pair): loops over b; writes dpos[t,c], dcls (t==0), copies dtok.  When there are
+// few (t, c) pairs and many sequences (TNT's pixel stream: 16 x 40 features, 12 544 sequences per
+// 64 images -- 320 threads looped over all of them in 2.9 ms, profiles/r02ay_timeline_tnt_s_patch16.txt)
+// blockIdx.y splits the batch and the slices combine with atomicAdd (accumulate mode only).
 __global__ void embed_bwd_kernel(const float* __restrict__ dx, bf16* __restrict__ dtok,
-                                 float* __restrict__ dcls, float* __restrict__ dpos, int64_t B,
-                                 int n_tok, int C, int has_cls, int accumulate) {
+                                 float* __restrict__ dcls, float* __restrict__ dpos, int64_t Bfull,
+                                 int n_tok, int C, int has_cls, int accumulate, int64_t chunk) {
   const int NT = n_tok + has_cls;
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= (int64_t)NT * C / 2) return;
   const int c = (int)((i * 2) % C);
   const int t = (int)((i * 2) / C);
   float2 acc = make_float2(0.f, 0.f);
-  int64_t b = 0;
+  int64_t b = (int64_t)blockIdx.y * chunk;
+  const int64_t B = b + chunk < Bfull ? b + chunk : Bfull;
   for (; b + 8 <= B; b += 8) {   // eight independent loads in flight per thread
     float2 f[8];
 #pragma unroll
@@ -164,6 +168,12 @@ __global__ void embed_bwd_kernel(const float* __restrict__ dx, bf16* __restrict_
       *reinterpret_cast<uint32_t*>(dtok + (b * n_tok + (t - has_cls)) * C + c) = pack_bf16(f.x, f.y);
   }
   float* p = dpos + (int64_t)t * C + c;
+  if (gridDim.y > 1) {
+    atomicAdd(p, acc.x);
+    atomicAdd(p + 1, acc.y);
+    if (has_cls && t == 0 && dcls) { atomicAdd(dcls + c, acc.x); atomicAdd(dcls + c + 1, acc.y); }
+    return;
+  }
   if (accumulate) { p[0] += acc.x; p[1] += acc.y; } else { p[0] = acc.x; p[1] = acc.y; }
   if (has_cls && t == 0 && dcls) {
     if (accumulate) { dcls[c] += acc.x; dcls[c + 1] += acc.y; }
@@ -225,9 +235,20 @@ extern "C" int sav_embed_bwd(const void* dx, void* dtok, float* dcls, float* dpo
                              void* stream) {
   if (B <= 0 || n_tok <= 0 || C % 2) return set_error(SAV_ERR_SHAPE, "sav_embed_bwd: bad shape");
   const int64_t work = (n_tok + has_cls) * C / 2;
-  embed_bwd_kernel<<<(int)((work + 127) / 128), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  // enough threads to fill the machine: split the batch when (tokens x channels) alone cannot
+  int64_t split = 1;
+  if (accumulate && work < 148 * 1024) {
+    split = (148 * 2048 + work - 1) / work;
+    if (split > B / 8) split = B / 8;
+    if (split < 1) split = 1;
+    if (split > 65535) split = 65535;
+  }
+  const int64_t chunk = (B + split - 1) / split;
+  split = (B + chunk - 1) / chunk;
+  embed_bwd_kernel<<<dim3((unsigned)((work + 127) / 128), (unsigned)split), 128, 0,
+                     reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float*>(dx), reinterpret_cast<bf16*>(dtok), dcls, dpos, B, (int)n_tok,
-      (int)C, has_cls, accumulate);
+      (int)C, has_cls, accumulate, chunk);
   count_launch();
   return check_launch("sav_embed_bwd");
 }
