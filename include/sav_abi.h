@@ -225,8 +225,8 @@ typedef struct {
   void* dk;
   void* dv;
   float* delta;      /* workspace fp32 [B,H,Nq] */
-  float* dq_accum;   /* unused (may be NULL): sequences beyond 256 queries run as query groups whose dK / dV
-                        partial tiles are reduce-added in bf16 by the TMA unit into the zero-filled dk / dv */
+  float* dq_accum;   /* workspace, only for Nq > 256 (else may be NULL): fp32 [2][B,Nk,H,D], zeroed by the callee --
+                        the dK / dV accumulators of the query groups (TMA reduce-add), converted to bf16 at the end */
   int64_t B, H, Nq, Nk, D;
   int64_t q_batch_stride, q_row_stride; /* shared by q and dq */
   int64_t k_batch_stride, k_row_stride; /* shared by k and dk */

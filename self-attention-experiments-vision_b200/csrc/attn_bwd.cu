@@ -7,9 +7,11 @@
 // dK / dV accumulate in TMEM across the group's query tiles.  Up to 256 queries there is one group per
 // (b, h) and dK / dV are plain stores; longer sequences (ViT-B/16 384^2: 577 tokens = groups of 256,
 // 256, 65; CvT: 3136 x 784) have G = ceil(Nq / 256) groups per (b, h) whose dK / dV partial tiles are
-// combined by the TMA unit itself (cp.reduce.async.bulk.tensor .add on the zero-filled bf16
-// gradients): no fp32 workspace, no conversion pass; the sum of G bf16-rounded partials arrives in
-// arbitrary order, so those two gradients are reproducible to bf16 rounding, not bit for bit.
+// combined by the TMA unit itself: cp.reduce.async.bulk.tensor .add of fp32 half tiles into a
+// zero-filled fp32 workspace [2][B, Nk, H * 64], converted to bf16 once at the end.  (Adding the
+// partials in bf16 straight into the gradients was tried first: 0.1 ms faster at 577 tokens, but the
+// order-dependent roundings of up to 13 partials moved CvT's worst parity tensor by +-0.5e-2 from
+// run to run.)  In fp32 the arrival order changes the sum by ~1e-7; the bf16 rounding happens once.
 //
 // The transposed problem is computed (S^T = K Q^T, dP^T = V dO^T: TMEM lane = key row), so P^T / dS^T
 // rows come out K-major for dV += P^T dO, dK += dS^T Q, and the same dS^T buffer read MN-major is
@@ -538,7 +540,37 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       }
       ++nstore;
     };
-    constexpr bool red = kGroups;
+    // partial tile of one query group: 64 fp32 TMEM columns -> two [128 x 32] fp32 half tiles
+    // (128-byte rows, same swizzle) -> reduce-add into the fp32 workspace
+    auto reduce_tile_f32 = [&](const CUtensorMap* map, uint32_t taddr, float f, int c0, int c1, int c2,
+                               bool release) {
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t r0[32];
+        tmem_ld32(taddr + half * 32, r0);
+        tmem_ld_wait();
+        if (release && half == 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(dkv_free);      // next key tile may overwrite dV / dK
+        }
+        uint8_t* stage = sStage + (nstore & 1) * BT_BYTES;
+        if (leader) tma_store_wait_read<1>();
+        named_barrier_sync(2, 128);
+#pragma unroll
+        for (int gi = 0; gi < 8; ++gi)
+          *reinterpret_cast<float4*>(stage + bsw128(r, gi)) =
+              make_float4(__uint_as_float(r0[gi * 4]) * f, __uint_as_float(r0[gi * 4 + 1]) * f,
+                          __uint_as_float(r0[gi * 4 + 2]) * f, __uint_as_float(r0[gi * 4 + 3]) * f);
+        fence_proxy_async_smem();
+        named_barrier_sync(2, 128);
+        if (leader) {
+          tma_reduce_add_3d(map, stage, c0 + half * 32, c1, c2);
+          tma_store_commit();
+        }
+        ++nstore;
+      }
+    };
     for (int itl = 0; itl < my_items; ++itl) {
       const BwdItem it = bwd_item<kGroups>(p, blockIdx.x + itl * gridDim.x);
       const int h = it.h, b = it.b;
@@ -548,13 +580,18 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         mbar_wait(dkv_full, gk & 1);
         BWD_STAMP(5, 43);
         tc_fence_after();
-        tmem_row64_to_bf16(tdV + lane_off, 1.f, pk);
-        store_tile(&tdv, pk, h * BD, j * BT, b, red);   // key rows >= Nk are clipped by the map
-        tmem_row64_to_bf16(tdK + lane_off, p.scale, pk);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(dkv_free);        // next key tile may overwrite dV / dK
-        store_tile(&tdk, pk, h * BD, j * BT, b, red);
+        if (kGroups) {
+          reduce_tile_f32(&tdv, tdV + lane_off, 1.f, h * BD, j * BT, b, false);
+          reduce_tile_f32(&tdk, tdK + lane_off, p.scale, h * BD, j * BT, b, true);
+        } else {
+          tmem_row64_to_bf16(tdV + lane_off, 1.f, pk);
+          store_tile(&tdv, pk, h * BD, j * BT, b, false);   // key rows >= Nk are clipped by the map
+          tmem_row64_to_bf16(tdK + lane_off, p.scale, pk);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(dkv_free);        // next key tile may overwrite dV / dK
+          store_tile(&tdk, pk, h * BD, j * BT, b, false);
+        }
         BWD_STAMP(5, 44);
       }
       BWD_STAMP(5, 45);
@@ -645,28 +682,32 @@ static int make_bnhd_map128(CUtensorMap* m, const void* base, int64_t H, int64_t
   return make_tmap_bf16(m, base, 3, dims, str, box);
 }
 
-// zero a [B, N, H*64] bf16 view (element strides bs / rs): the target of the dK / dV reduce-adds
-__global__ void zero_bnhd_kernel(bf16* __restrict__ base, int64_t total16, int N, int row16, int64_t bs,
-                                 int64_t rs) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total16;
+// fp32 accumulator [B, N, H*64] (contiguous) -> bf16 view with element strides bs / rs
+__global__ void acc_to_bnhd_kernel(const float* __restrict__ acc, bf16* __restrict__ base, int64_t total8,
+                                   int N, int row8, int64_t bs, int64_t rs) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total8;
        i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % row16);
-    const int64_t t = i / row16;
+    const int c = (int)(i % row8);
+    const int64_t t = i / row8;
     const int n = (int)(t % N);
     const int64_t b = t / N;
-    *reinterpret_cast<uint4*>(base + b * bs + (int64_t)n * rs + c * 8) = make_uint4(0u, 0u, 0u, 0u);
+    const float4 lo = __ldcs(reinterpret_cast<const float4*>(acc + i * 8));
+    const float4 hi = __ldcs(reinterpret_cast<const float4*>(acc + i * 8) + 1);
+    *reinterpret_cast<uint4*>(base + b * bs + (int64_t)n * rs + c * 8) =
+        make_uint4(pack_bf16(lo.x, lo.y), pack_bf16(lo.z, lo.w), pack_bf16(hi.x, hi.y), pack_bf16(hi.z, hi.w));
   }
 }
 
-static int zero_bnhd(void* base, int64_t B, int64_t N, int64_t H, int64_t bs, int64_t rs, cudaStream_t st) {
+static int acc_to_bnhd(const float* acc, void* base, int64_t B, int64_t N, int64_t H, int64_t bs, int64_t rs,
+                       cudaStream_t st) {
   if ((reinterpret_cast<uintptr_t>(base) & 15) || (bs % 8) || (rs % 8))
     return set_error(SAV_ERR_ALIGN, "sav_attn_bwd: dk / dv need 16-byte aligned rows");
-  const int row16 = (int)(H * BD / 8);
-  const int64_t total16 = B * N * row16;
-  const int blocks = (int)((total16 + 255) / 256 < 148 * 8 ? (total16 + 255) / 256 : 148 * 8);
-  zero_bnhd_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<bf16*>(base), total16, (int)N, row16, bs, rs);
+  const int row8 = (int)(H * BD / 8);
+  const int64_t total8 = B * N * row8;
+  const int blocks = (int)((total8 + 255) / 256 < 148 * 8 ? (total8 + 255) / 256 : 148 * 8);
+  acc_to_bnhd_kernel<<<blocks, 256, 0, st>>>(acc, reinterpret_cast<bf16*>(base), total8, (int)N, row8, bs, rs);
   count_launch();
-  return check_launch("sav_attn_bwd (zero dk / dv)");
+  return check_launch("sav_attn_bwd (dk / dv conversion)");
 }
 
 // sav_attn_bwd for every shape (called from attn.cu)
@@ -678,8 +719,21 @@ int launch_attn_bwd2(const sav_attn_bwd_args* a, cudaStream_t st) {
   if ((rc = make_bnhd_map128(&tv, a->v, a->H, a->Nk, a->B, a->v_batch_stride, a->v_row_stride))) return rc;
   if ((rc = make_bnhd_map128(&tdo, a->d_o, a->H, a->Nq, a->B, a->o_batch_stride, a->o_row_stride))) return rc;
   if ((rc = make_bnhd_map128(&tdq, a->dq, a->H, a->Nq, a->B, a->q_batch_stride, a->q_row_stride))) return rc;
-  if ((rc = make_bnhd_map128(&tdk, a->dk, a->H, a->Nk, a->B, a->k_batch_stride, a->k_row_stride))) return rc;
-  if ((rc = make_bnhd_map128(&tdv, a->dv, a->H, a->Nk, a->B, a->v_batch_stride, a->v_row_stride))) return rc;
+  const int n_groups = (int)((a->Nq + 2 * BT - 1) / (2 * BT));
+  const int64_t acc_elems = a->B * a->Nk * a->H * BD;           // one fp32 accumulator (dK; dV follows)
+  if (n_groups > 1) {
+    // several query groups per (b, h): fp32 half tiles [128 x 32] reduce-added into the workspace
+    if (!a->dq_accum)
+      return set_error(SAV_ERR_ARG, "sav_attn_bwd: Nq > 256 needs the fp32 workspace (2 * B * Nk * H * 64 floats)");
+    uint64_t dims[3] = {(uint64_t)(a->H * BD), (uint64_t)a->Nk, (uint64_t)a->B};
+    uint64_t str[3] = {0, (uint64_t)(a->H * BD) * 4, (uint64_t)(a->Nk * a->H * BD) * 4};
+    uint32_t box[3] = {32, BT, 1};
+    if ((rc = make_tmap_nd(&tdk, a->dq_accum, 4, 3, dims, str, box))) return rc;
+    if ((rc = make_tmap_nd(&tdv, a->dq_accum + acc_elems, 4, 3, dims, str, box))) return rc;
+  } else {
+    if ((rc = make_bnhd_map128(&tdk, a->dk, a->H, a->Nk, a->B, a->k_batch_stride, a->k_row_stride))) return rc;
+    if ((rc = make_bnhd_map128(&tdv, a->dv, a->H, a->Nk, a->B, a->v_batch_stride, a->v_row_stride))) return rc;
+  }
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(attn_bwd3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwd2Smem);
@@ -698,11 +752,7 @@ int launch_attn_bwd2(const sav_attn_bwd_args* a, cudaStream_t st) {
   p.n_items = p.B * p.H * p.G;
   p.nkt = (p.Nk + BT - 1) / BT;
   p.nqt = (p.Nq + BT - 1) / BT;
-  if (p.G > 1) {
-    // several query groups per (b, h): their dK / dV partial tiles are reduce-added into zeros
-    if ((rc = zero_bnhd(a->dk, a->B, a->Nk, a->H, a->k_batch_stride, a->k_row_stride, st))) return rc;
-    if ((rc = zero_bnhd(a->dv, a->B, a->Nk, a->H, a->v_batch_stride, a->v_row_stride, st))) return rc;
-  }
+  if (p.G > 1 && (rc = sav_fill_f32(a->dq_accum, 0.f, 2 * acc_elems, st))) return rc;
   p.scale = a->scale; p.scale_log2 = a->scale * B_LOG2E;
   p.dbg = reinterpret_cast<long long*>(sav_debug_buffer());
   int sms = 148, dev = 0;
@@ -712,7 +762,13 @@ int launch_attn_bwd2(const sav_attn_bwd_args* a, cudaStream_t st) {
   if (p.G > 1) attn_bwd3_kernel<true><<<grid, kBwdThreads, kBwd2Smem, st>>>(tq, tk, tv, tdo, tdq, tdk, tdv, p);
   else attn_bwd3_kernel<false><<<grid, kBwdThreads, kBwd2Smem, st>>>(tq, tk, tv, tdo, tdq, tdk, tdv, p);
   count_launch();
-  return check_launch("sav_attn_bwd (resident-Q path)");
+  if ((rc = check_launch("sav_attn_bwd (resident-Q path)"))) return rc;
+  if (p.G > 1) {
+    if ((rc = acc_to_bnhd(a->dq_accum, a->dk, a->B, a->Nk, a->H, a->k_batch_stride, a->k_row_stride, st))) return rc;
+    if ((rc = acc_to_bnhd(a->dq_accum + acc_elems, a->dv, a->B, a->Nk, a->H, a->v_batch_stride, a->v_row_stride, st)))
+      return rc;
+  }
+  return SAV_OK;
 }
 
 }  // namespace sav

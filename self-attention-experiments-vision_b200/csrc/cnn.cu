@@ -64,19 +64,22 @@ __global__ void bn_act_fwd_kernel(const bf16* __restrict__ y, const float* __res
 
 // per channel: s1 = sum dbn, s2 = sum dbn yhat with dbn = dz act'(bn); block = 64 channel pairs x 4
 // row lanes (same shape as bn_stats_kernel)
+// TXP = channel pairs per block (64, or 32 for C <= 64 so that no lane idles on the widest tensors)
+template <int TXP>
 __global__ void __launch_bounds__(256)
 bn_act_bwd_reduce_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ y,
                          const float* __restrict__ mean, const float* __restrict__ rstd,
                          const float* __restrict__ gamma, const float* __restrict__ beta, int64_t rows,
                          int C, int kind, float* __restrict__ s1, float* __restrict__ s2) {
-  __shared__ float red[4][64][4];
-  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
-  const int c = (blockIdx.x * 64 + tx) * 2;
+  constexpr int TYP = 256 / TXP;
+  __shared__ float red[TYP][TXP][4];
+  const int tx = threadIdx.x % TXP, ty = threadIdx.x / TXP;
+  const int c = (blockIdx.x * TXP + tx) * 2;
   float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
   if (c < C) {
     const float m0 = mean[c], m1 = mean[c + 1], r0 = rstd[c], r1 = rstd[c + 1];
     const float g0 = gamma[c], g1 = gamma[c + 1], e0 = beta[c], e1 = beta[c + 1];
-    for (int64_t r = (int64_t)blockIdx.y * 4 + ty; r < rows; r += (int64_t)gridDim.y * 4) {
+    for (int64_t r = (int64_t)blockIdx.y * TYP + ty; r < rows; r += (int64_t)gridDim.y * TYP) {
       const float2 v = unpack_bf16(*reinterpret_cast<const uint32_t*>(y + r * C + c));
       const float2 g = unpack_bf16(*reinterpret_cast<const uint32_t*>(dz + r * C + c));
       const float h0 = (v.x - m0) * r0, h1 = (v.y - m1) * r1;
@@ -87,7 +90,7 @@ bn_act_bwd_reduce_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ y
   red[ty][tx][0] = a0; red[ty][tx][1] = a1; red[ty][tx][2] = b0; red[ty][tx][3] = b1;
   __syncthreads();
   if (ty == 0 && c < C) {
-    for (int k = 1; k < 4; ++k) {
+    for (int k = 1; k < TYP; ++k) {
       a0 += red[k][tx][0]; a1 += red[k][tx][1]; b0 += red[k][tx][2]; b1 += red[k][tx][3];
     }
     atomicAdd(s1 + c, a0); atomicAdd(s1 + c + 1, a1);
@@ -276,6 +279,221 @@ __global__ void maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* _
   }
 }
 
+// ---- eight channels (16 bytes) per thread for C % 8 == 0 and 16-byte aligned tensors.  The 4-byte
+// kernels above leave these memory-bound passes at a third of the HBM rate on B200
+// (profiles/r02az_timeline_botnet_t3.txt: BatchNorm + activation backward 393 us on the 103 MB stem
+// tensor against an 85 us floor); they stay as the fallback for odd channel counts.
+__device__ __forceinline__ void ld8(const bf16* p, float (&f)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float2 v = unpack_bf16(w[e]);
+    f[2 * e] = v.x;
+    f[2 * e + 1] = v.y;
+  }
+}
+__device__ __forceinline__ void st8(bf16* p, const float (&f)[8]) {
+  *reinterpret_cast<uint4*>(p) = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]),
+                                            pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+__device__ __forceinline__ void ldp8(const float* p, float (&f)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+__global__ void bn_act_fwd_vec8_kernel(const bf16* __restrict__ y, const float* __restrict__ mean,
+                                       const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                       const float* __restrict__ beta, bf16* __restrict__ z, int64_t rows,
+                                       int C8, int kind) {
+  // the launcher makes gridDim.x * blockDim.x a multiple of C8: a thread keeps its channel octet, so
+  // the per-channel parameters are loaded once, folded to z = act(y * sc + sh)
+  const int64_t total = rows * C8;
+  const int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int c = (int)(i0 % C8) * 8;
+  float m[8], r[8], g[8], b[8];
+  ldp8(mean + c, m); ldp8(rstd + c, r); ldp8(gamma + c, g); ldp8(beta + c, b);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) { r[e] *= g[e]; b[e] -= m[e] * r[e]; }
+  for (int64_t i = i0; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    float v[8];
+    ld8(y + i * 8, v);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = act_apply(fmaf(v[e], r[e], b[e]), kind);
+    st8(z + i * 8, v);
+  }
+}
+
+__global__ void bn_act_bwd_apply_vec8_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ y,
+                                             const float* __restrict__ mean, const float* __restrict__ rstd,
+                                             const float* __restrict__ gamma, const float* __restrict__ beta,
+                                             const float* __restrict__ s1, const float* __restrict__ s2,
+                                             float inv_n, bf16* __restrict__ dy, int64_t rows, int C8, int kind) {
+  const int64_t total = rows * C8;
+  const int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int c = (int)(i0 % C8) * 8;      // fixed per thread (thread count is a multiple of C8)
+  float m[8], r[8], g[8], b[8], a1[8], a2[8];
+  ldp8(mean + c, m); ldp8(rstd + c, r); ldp8(gamma + c, g); ldp8(beta + c, b);
+  ldp8(s1 + c, a1); ldp8(s2 + c, a2);
+  for (int64_t i = i0; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    float v[8], d[8];
+    ld8(y + i * 8, v);
+    ld8(dz + i * 8, d);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float h = (v[e] - m[e]) * r[e];
+      const float dd = d[e] * act_grad(h * g[e] + b[e], kind);
+      v[e] = g[e] * r[e] * (dd - a1[e] * inv_n - h * a2[e] * inv_n);
+    }
+    st8(dy + i * 8, v);
+  }
+}
+
+// per-channel reductions over the rows, eight channels per thread: block = TX channel octets x
+// (256 / TX) row lanes; partials meet by shuffle inside the warp, across warps in shared memory, one
+// atomicAdd per channel and block.  kMode 0: (sum y, sum y^2) = batch statistics;
+// kMode 1: (sum dbn, sum dbn yhat) with dbn = dz act'(bn(y)).
+template <int kMode>
+__global__ void __launch_bounds__(256)
+bn_reduce_vec8_kernel(const bf16* __restrict__ y, const bf16* __restrict__ dz, const float* __restrict__ mean,
+                      const float* __restrict__ rstd, const float* __restrict__ gamma,
+                      const float* __restrict__ beta, int64_t rows, int C8, int TX, int kind,
+                      float* __restrict__ o1, float* __restrict__ o2) {
+  __shared__ float red[8][8][16];
+  const int tx = threadIdx.x % TX, ty = threadIdx.x / TX, TY = 256 / TX;
+  const int oct = blockIdx.x * TX + tx;
+  float a[8], b[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) { a[e] = 0.f; b[e] = 0.f; }
+  if (oct < C8) {
+    const int c = oct * 8;
+    float m[8], r[8], g[8], bt[8];
+    if (kMode == 1) { ldp8(mean + c, m); ldp8(rstd + c, r); ldp8(gamma + c, g); ldp8(beta + c, bt); }
+    for (int64_t row = (int64_t)blockIdx.y * TY + ty; row < rows; row += (int64_t)gridDim.y * TY) {
+      float v[8];
+      ld8(y + (row * C8 + oct) * 8, v);
+      if (kMode == 0) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { a[e] += v[e]; b[e] += v[e] * v[e]; }
+      } else {
+        float d[8];
+        ld8(dz + (row * C8 + oct) * 8, d);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float h = (v[e] - m[e]) * r[e];
+          const float dd = d[e] * act_grad(h * g[e] + bt[e], kind);
+          a[e] += dd;
+          b[e] += dd * h;
+        }
+      }
+    }
+  }
+  // lanes of equal tx inside the warp (TX divides 32)
+  for (int off = TX; off < 32; off <<= 1) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      a[e] += __shfl_xor_sync(0xffffffffu, a[e], off);
+      b[e] += __shfl_xor_sync(0xffffffffu, b[e], off);
+    }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane < TX) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { red[warp][lane][e] = a[e]; red[warp][lane][8 + e] = b[e]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < TX * 16) {
+    const int x = threadIdx.x / 16, q = threadIdx.x % 16;
+    const int oc = blockIdx.x * TX + x;
+    if (oc < C8) {
+      float sum = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) sum += red[w][x][q];
+      atomicAdd((q < 8 ? o1 : o2) + oc * 8 + (q & 7), sum);
+    }
+  }
+}
+
+__global__ void gate_res_act_fwd_vec8_kernel(const bf16* __restrict__ x, const bf16* __restrict__ gate,
+                                             const bf16* __restrict__ res, bf16* __restrict__ out,
+                                             int64_t rows, int64_t rows_per_sample, int C8, int kind) {
+  const int64_t total = rows * C8;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / C8;
+    const int c8 = (int)(i - r * C8);
+    float v[8];
+    ld8(x + i * 8, v);
+    if (gate) {
+      float s[8];
+      ld8(gate + ((r / rows_per_sample) * C8 + c8) * 8, s);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] *= s[e];
+    }
+    if (res) {
+      float q[8];
+      ld8(res + i * 8, q);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] += q[e];
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = act_apply(v[e], kind);
+    st8(out + i * 8, v);
+  }
+}
+
+static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+static void launch_bn_act_bwd_reduce(const void* dz, const void* y, const float* mean, const float* rstd,
+                                     const float* gamma, const float* beta, int64_t rows, int64_t C, int kind,
+                                     float* scratch, cudaStream_t st) {
+  const int txp = C <= 64 ? 32 : 64;
+  const int gx = (int)((C / 2 + txp - 1) / txp);
+  int64_t gy = (rows + 63) / 64;
+  const int64_t cap = (148 * 8 + gx - 1) / gx;
+  if (gy > cap) gy = cap;
+  if (gy < 1) gy = 1;
+  if (txp == 32)
+    bn_act_bwd_reduce_kernel<32><<<dim3(gx, (unsigned)gy), 256, 0, st>>>(
+        reinterpret_cast<const bf16*>(dz), reinterpret_cast<const bf16*>(y), mean, rstd, gamma, beta, rows,
+        (int)C, kind, scratch, scratch + C);
+  else
+    bn_act_bwd_reduce_kernel<64><<<dim3(gx, (unsigned)gy), 256, 0, st>>>(
+        reinterpret_cast<const bf16*>(dz), reinterpret_cast<const bf16*>(y), mean, rstd, gamma, beta, rows,
+        (int)C, kind, scratch, scratch + C);
+}
+// blocks of 256 threads for `work` octets such that the thread count is a multiple of C8
+static int vec8_blocks(int64_t work, int C8) {
+  int64_t b = (work + 255) / 256;
+  const int64_t cap = 148 * 16;
+  if (b > cap) b = cap;
+  int gcd = C8, x = 256;
+  while (x) { const int t = gcd % x; gcd = x; x = t; }
+  const int mult = C8 / gcd;
+  b = (b + mult - 1) / mult * mult;
+  return (int)(b < mult ? mult : b);
+}
+// launch geometry of bn_reduce_vec8_kernel
+static void reduce8_geom(int64_t rows, int C8, int& TX, dim3& grid) {
+  TX = C8 >= 8 ? 8 : (C8 >= 4 ? 4 : (C8 >= 2 ? 2 : 1));
+  const int gx = (C8 + TX - 1) / TX;
+  const int TY = 256 / TX;
+  int64_t gy = (rows + 4 * TY - 1) / (4 * TY);      // >= 4 rows per thread
+  const int64_t cap = (148 * 8 + gx - 1) / gx;
+  if (gy > cap) gy = cap;
+  if (gy < 1) gy = 1;
+  grid = dim3((unsigned)gx, (unsigned)gy);
+}
+
+// batch statistics entry for conv2d.cu's sav_bn_stats (sum / sumsq zeroed by the caller)
+bool bn_stats_vec8(const void* y, int64_t rows, int64_t C, float* sum, float* sumsq, cudaStream_t st) {
+  if (C % 8 || !al16(y)) return false;
+  int TX;
+  dim3 grid;
+  reduce8_geom(rows, (int)(C / 8), TX, grid);
+  bn_reduce_vec8_kernel<0><<<grid, 256, 0, st>>>(reinterpret_cast<const bf16*>(y), nullptr, nullptr, nullptr,
+                                                 nullptr, nullptr, rows, (int)(C / 8), TX, 0, sum, sumsq);
+  return true;
+}
+
 static int cnn_blocks(int64_t work) {
   int64_t b = (work + 255) / 256;
   const int64_t cap = 148 * 16;
@@ -308,6 +526,12 @@ extern "C" int sav_act_bwd(const void* x, const void* dy, void* dx, int64_t n, i
 extern "C" int sav_bn_act_fwd(const void* y, const float* mean, const float* rstd, const float* gamma,
                               const float* beta, void* z, int64_t rows, int64_t C, int32_t kind, void* stream) {
   if (rows <= 0 || C <= 0 || C % 2) return set_error(SAV_ERR_SHAPE, "sav_bn_act_fwd: C %% 2");
+  if (C % 8 == 0 && al16(y) && al16(z) && al16(mean) && al16(rstd) && al16(gamma) && al16(beta)) {
+    bn_act_fwd_vec8_kernel<<<vec8_blocks(rows * (C / 8), (int)(C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const bf16*>(y), mean, rstd, gamma, beta, reinterpret_cast<bf16*>(z), rows, (int)(C / 8), kind);
+    count_launch();
+    return check_launch("sav_bn_act_fwd");
+  }
   bn_act_fwd_kernel<<<cnn_blocks(rows * (C / 2)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const bf16*>(y), mean, rstd, gamma, beta, reinterpret_cast<bf16*>(z), rows, (int)(C / 2), kind);
   count_launch();
@@ -321,19 +545,25 @@ extern "C" int sav_bn_act_bwd(const void* dz, const void* y, const float* mean, 
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   int rc = sav_fill_f32(scratch, 0.f, 2 * C, stream);
   if (rc) return rc;
-  const int gx = (int)((C / 2 + 63) / 64);
-  int64_t gy = (rows + 63) / 64;
-  const int64_t cap = (148 * 8 + gx - 1) / gx;
-  if (gy > cap) gy = cap;
-  if (gy < 1) gy = 1;
-  bn_act_bwd_reduce_kernel<<<dim3(gx, (unsigned)gy), 256, 0, st>>>(
-      reinterpret_cast<const bf16*>(dz), reinterpret_cast<const bf16*>(y), mean, rstd, gamma, beta, rows,
-      (int)C, kind, scratch, scratch + C);
-  count_launch();
-  bn_act_bwd_apply_kernel<<<cnn_blocks(rows * (C / 2)), 256, 0, st>>>(
-      reinterpret_cast<const bf16*>(dz), reinterpret_cast<const bf16*>(y), mean, rstd, gamma, beta, scratch,
-      scratch + C, 1.f / (float)rows, reinterpret_cast<bf16*>(dy), rows, (int)(C / 2), kind);
-  count_launch();
+  if (C % 8 == 0 && al16(dz) && al16(y) && al16(dy) && al16(mean) && al16(rstd) && al16(gamma) && al16(beta) &&
+      al16(scratch)) {
+    // (the per-channel sums stay on the 4-byte kernel: the eight-channel reduction measured slower
+    // here -- 16 accumulators and 32 parameter registers per thread cost more occupancy than the wider
+    // loads return, profiles/r02bb_timeline_botnet_t3.txt)
+    launch_bn_act_bwd_reduce(dz, y, mean, rstd, gamma, beta, rows, C, kind, scratch, st);
+    count_launch();
+    bn_act_bwd_apply_vec8_kernel<<<vec8_blocks(rows * (C / 8), (int)(C / 8)), 256, 0, st>>>(
+        reinterpret_cast<const bf16*>(dz), reinterpret_cast<const bf16*>(y), mean, rstd, gamma, beta, scratch,
+        scratch + C, 1.f / (float)rows, reinterpret_cast<bf16*>(dy), rows, (int)(C / 8), kind);
+    count_launch();
+  } else {
+    launch_bn_act_bwd_reduce(dz, y, mean, rstd, gamma, beta, rows, C, kind, scratch, st);
+    count_launch();
+    bn_act_bwd_apply_kernel<<<cnn_blocks(rows * (C / 2)), 256, 0, st>>>(
+        reinterpret_cast<const bf16*>(dz), reinterpret_cast<const bf16*>(y), mean, rstd, gamma, beta, scratch,
+        scratch + C, 1.f / (float)rows, reinterpret_cast<bf16*>(dy), rows, (int)(C / 2), kind);
+    count_launch();
+  }
   // dbeta += s1, dgamma += s2 (parameter gradients accumulate: the arena is zeroed once per step)
   axpy2b_kernel<<<(int)((C + 255) / 256), 256, 0, st>>>(scratch, dbeta, scratch + C, dgamma, (int)C);
   count_launch();
@@ -343,6 +573,13 @@ extern "C" int sav_bn_act_bwd(const void* dz, const void* y, const float* mean, 
 extern "C" int sav_gate_res_act_fwd(const void* x, const void* gate, const void* residual, void* out,
                                     int64_t B, int64_t rows_per_sample, int64_t C, int32_t kind, void* stream) {
   if (B <= 0 || rows_per_sample <= 0 || C <= 0 || C % 2) return set_error(SAV_ERR_SHAPE, "sav_gate_res_act_fwd: C %% 2");
+  if (C % 8 == 0 && al16(x) && al16(out) && (!gate || al16(gate)) && (!residual || al16(residual))) {
+    gate_res_act_fwd_vec8_kernel<<<cnn_blocks(B * rows_per_sample * (C / 8)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(gate), reinterpret_cast<const bf16*>(residual),
+        reinterpret_cast<bf16*>(out), B * rows_per_sample, rows_per_sample, (int)(C / 8), kind);
+    count_launch();
+    return check_launch("sav_gate_res_act_fwd");
+  }
   gate_res_act_fwd_kernel<<<cnn_blocks(B * rows_per_sample * (C / 2)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(gate), reinterpret_cast<const bf16*>(residual),
       reinterpret_cast<bf16*>(out), B * rows_per_sample, rows_per_sample, (int)(C / 2), kind);

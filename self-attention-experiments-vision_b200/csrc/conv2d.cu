@@ -15,6 +15,9 @@
 
 namespace sav {
 
+// cnn.cu: eight-channels-per-thread batch statistics (false: shape / alignment not eligible)
+bool bn_stats_vec8(const void* y, int64_t rows, int64_t C, float* sum, float* sumsq, cudaStream_t st);
+
 struct Im2colGeom {
   int B, H, W, C, Ho, Wo, kh, kw, sh, sw, pt, pl;
   int64_t xs_b, xs_h, xs_w, xs_c;   // element strides of x
@@ -304,6 +307,11 @@ extern "C" int sav_bn_stats(const void* y, int64_t rows, int64_t C, float* sum, 
   if (rows <= 0 || C <= 0 || C % 2) return set_error(SAV_ERR_SHAPE, "sav_bn_stats: C %% 2");
   int rc;
   if ((rc = sav_fill_f32(sum, 0.f, C, stream)) || (rc = sav_fill_f32(sumsq, 0.f, C, stream))) return rc;
+  if (!(reinterpret_cast<uintptr_t>(sum) & 15) && !(reinterpret_cast<uintptr_t>(sumsq) & 15) &&
+      bn_stats_vec8(y, rows, C, sum, sumsq, reinterpret_cast<cudaStream_t>(stream))) {
+    count_launch();
+    return check_launch("sav_bn_stats");
+  }
   const int gx = (int)((C / 2 + 63) / 64);
   int64_t gy = (rows + 63) / 64;
   const int64_t cap = (148 * 8 + gx - 1) / gx;

@@ -232,9 +232,9 @@ def attn_bwd(q, k, v, o2, d_o, lse, dq, dk, dv, scale=None):
     assert d_o.stride() == o.stride()
     assert dq.stride() == q.stride() and dk.stride() == k.stride() and dv.stride() == v.stride()
     delta = torch.empty((B, H, Nq), dtype=F32, device=q.device)
-    dq_acc = None    # (only the development build's older long-sequence kernel wants this workspace)
-    if Nq > 256 and os.environ.get("SAV_ATTN_BWD_GENERIC"):
-        dq_acc = torch.empty((B, Nq, H, D), dtype=F32, device=q.device)
+    # sequences beyond 256 queries run as query groups: fp32 accumulators of dK and dV (zeroed by
+    # the callee), large enough for the development build's older kernel (dQ accumulator) as well
+    dq_acc = torch.empty((max(2 * B * Nk, B * Nq), H, D), dtype=F32, device=q.device) if Nq > 256 else None
     a = AttnBwdArgs()
     a.q, a.k, a.v, a.o, a.d_o, a.lse = (q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(),
                                         d_o.data_ptr(), lse.data_ptr())

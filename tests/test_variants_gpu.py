@@ -354,10 +354,14 @@ def test_cvt_model_logits_and_all_grads():
         errs[path] = _rel(ours[path], g_ref)
         l2[path] = float((ours[path].float().cpu() - g_ref).norm() / g_ref.norm())
     ref = dict(O.tree_leaves(grads_ref))
+    zero_ratio = {}
     for path in zero_ref:
         sib = ref[path.replace("ConvProjectionBlock_1", "ConvProjectionBlock_2")]
-        assert float(ours[path].float().abs().max().cpu()) < 2e-2 * float(sib.abs().max())
+        zero_ratio[path] = float(ours[path].float().abs().max().cpu()) / float(sib.abs().max())
+    print("cvt zero-gradient biases / sibling:", sorted(zero_ratio.items(), key=lambda kv: -kv[1])[:2])
+    print("cvt worst max-norm:", sorted(errs.items(), key=lambda kv: -kv[1])[:3])
     print("cvt worst relative L2:", sorted(l2.items(), key=lambda kv: -kv[1])[:4])
+    assert max(zero_ratio.values()) < 2e-2, zero_ratio
     # Few tokens per weight gradient (36 .. 576 per image x 16 images) and three more bf16 operand
     # sites per attention than ViT (depthwise-conv output, BatchNorm output, per projection): the
     # edge-shape tolerance of tests/test_vit_parity_gpu.py applies to the max-norm, every tensor must
