@@ -5,7 +5,11 @@
 // not even 16-byte aligned per head -- so this path is plain FP32 CUDA-core work and HBM-bound:
 // one warp owns one (sequence, head), stages q, k, v (and dO) in shared memory, a lane owns one
 // query row (forward, dq) and then one key row (dk, dv).  Nothing is saved for the backward pass:
-// P is recomputed from q, k (N <= 32 keys, D <= 16).
+// P is recomputed from q, k (N <= 32 keys, D <= 16).  Sequences of up to 16 tokens (TNT: exactly 16)
+// use the NM = 16 instantiation: two (sequence, head) items per warp, one per half-warp, with the
+// token loops, register arrays and shared-memory tiles sized for 16 -- the 32-token layout left half
+// of every warp idle and ran the 12 544 x 4 items of a 64-image TNT-S step at 260 / 592 us
+// (forward / backward) against a 10 / 25 us HBM floor (profiles/r02ay_timeline_tnt_s_patch16.txt).
 #include "common.cuh"
 #include "host.h"
 
@@ -13,19 +17,21 @@ namespace sav {
 
 constexpr int SM_N = 32;      // max tokens per sequence
 constexpr int SM_D = 16;      // max head dim
-constexpr int SM_WARPS = 2;   // (sequence, head) items per block
+constexpr int SM_WARPS = 2;   // warps per block
 
+template <int NM>              // NM = 16 or 32: token capacity of one item's tiles
 struct SmallAttnSmem {
-  float q[SM_N][SM_D + 1], k[SM_N][SM_D + 1], v[SM_N][SM_D + 1], g[SM_N][SM_D + 1];
-  float p[SM_N][SM_N + 1], ds[SM_N][SM_N + 1];
+  float q[NM][SM_D + 1], k[NM][SM_D + 1], v[NM][SM_D + 1], g[NM][SM_D + 1];
+  float p[NM][NM + 1], ds[NM][NM + 1];
 };
 
 // row i of softmax(scale q k^T): p[j] for j < N (0 beyond)
-__device__ __forceinline__ void small_softmax_row(const SmallAttnSmem& s, int i, int N, int D, float scale,
-                                                  float (&p)[SM_N]) {
+template <int NM>
+__device__ __forceinline__ void small_softmax_row(const SmallAttnSmem<NM>& s, int i, int N, int D, float scale,
+                                                  float (&p)[NM]) {
   float mx = -INFINITY;
 #pragma unroll
-  for (int j = 0; j < SM_N; ++j) {
+  for (int j = 0; j < NM; ++j) {
     float a = 0.f;
     if (j < N) {
       for (int d = 0; d < D; ++d) a += s.q[i][d] * s.k[j][d];
@@ -36,29 +42,32 @@ __device__ __forceinline__ void small_softmax_row(const SmallAttnSmem& s, int i,
   }
   float sum = 0.f;
 #pragma unroll
-  for (int j = 0; j < SM_N; ++j) {
+  for (int j = 0; j < NM; ++j) {
     p[j] = j < N ? __expf(p[j] - mx) : 0.f;         // attention.py:48
     sum += p[j];
   }
   const float inv = 1.f / sum;
 #pragma unroll
-  for (int j = 0; j < SM_N; ++j) p[j] *= inv;
+  for (int j = 0; j < NM; ++j) p[j] *= inv;
 }
 
-template <bool BWD>
+template <bool BWD, int NM>
 __global__ void __launch_bounds__(SM_WARPS * 32)
 attn_small_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ d_o, bf16* __restrict__ out,
-                  int64_t items, int N, int H, int D, float scale) {
-  __shared__ SmallAttnSmem smem[SM_WARPS];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t item = (int64_t)blockIdx.x * SM_WARPS + warp;
-  if (item >= items) return;
-  SmallAttnSmem& s = smem[warp];
-  const int64_t b = item / H;
+                  int64_t items, int N_, int H, int D, float scale) {
+  constexpr int IPW = 32 / NM;                       // items per warp (one per NM-lane group)
+  __shared__ SmallAttnSmem<NM> smem[SM_WARPS * IPW];
+  const int warp = threadIdx.x >> 5, wl = threadIdx.x & 31;
+  const int sub = wl / NM, lane = wl % NM;           // `lane` = position inside the item's lane group
+  const int64_t item = ((int64_t)blockIdx.x * SM_WARPS + warp) * IPW + sub;
+  // a lane group without an item walks the code with N = 0 (the warp-wide syncs stay convergent)
+  const int N = item < items ? N_ : 0;
+  SmallAttnSmem<NM>& s = smem[warp * IPW + sub];
+  const int64_t b = item < items ? item / H : 0;
   const int h = (int)(item % H);
   const int64_t row_pitch = (int64_t)3 * H * D;     // one token of [B, N, 3, H, D]
   const bf16* base = qkv + b * N * row_pitch + (int64_t)h * D;
-  for (int idx = lane; idx < N * D; idx += 32) {
+  for (int idx = lane; idx < N * D; idx += NM) {
     const int n = idx / D, d = idx - n * D;
     const bf16* tok = base + (int64_t)n * row_pitch + d;
     s.q[n][d] = __bfloat162float(tok[0]);
@@ -67,24 +76,24 @@ attn_small_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ d_o, bf
     if (BWD) s.g[n][d] = __bfloat162float(d_o[((b * N + n) * H + h) * D + d]);
   }
   __syncwarp();
-  float p[SM_N];
+  float p[NM];
   if (lane < N) {
     const int i = lane;
-    small_softmax_row(s, i, N, D, scale, p);
+    small_softmax_row<NM>(s, i, N, D, scale, p);
     if (!BWD) {
       bf16* o = out + ((b * N + i) * H + h) * D;     // [B, N, H, D]
       for (int d = 0; d < D; ++d) {
         float a = 0.f;
 #pragma unroll
-        for (int j = 0; j < SM_N; ++j)
+        for (int j = 0; j < NM; ++j)
           if (j < N) a += p[j] * s.v[j][d];          // attention.py:57
         o[d] = __float2bfloat16(a);
       }
     } else {
       float delta = 0.f;
-      float dp[SM_N];
+      float dp[NM];
 #pragma unroll
-      for (int j = 0; j < SM_N; ++j) {
+      for (int j = 0; j < NM; ++j) {
         float a = 0.f;
         if (j < N)
           for (int d = 0; d < D; ++d) a += s.g[i][d] * s.v[j][d];
@@ -92,7 +101,7 @@ attn_small_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ d_o, bf
         delta += p[j] * a;
       }
 #pragma unroll
-      for (int j = 0; j < SM_N; ++j) {
+      for (int j = 0; j < NM; ++j) {
         if (j < N) {
           s.p[i][j] = p[j];
           s.ds[i][j] = p[j] * (dp[j] - delta);
@@ -102,7 +111,7 @@ attn_small_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ d_o, bf
       for (int d = 0; d < D; ++d) {
         float a = 0.f;
 #pragma unroll
-        for (int j = 0; j < SM_N; ++j)
+        for (int j = 0; j < NM; ++j)
           if (j < N) a += p[j] * (dp[j] - delta) * s.k[j][d];
         dq[d] = __float2bfloat16(a * scale);
       }
@@ -144,10 +153,13 @@ extern "C" int sav_attn_small_fwd(const void* qkv, void* o, int64_t B, int64_t N
                                   float scale, void* stream) {
   if (int rc = small_check("sav_attn_small_fwd", qkv, o, B, N, H, D)) return rc;
   const int64_t items = B * H;
-  attn_small_kernel<false><<<(unsigned)((items + SM_WARPS - 1) / SM_WARPS), SM_WARPS * 32, 0,
-                             reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const bf16*>(qkv), nullptr, reinterpret_cast<bf16*>(o), items, (int)N, (int)H,
-      (int)D, scale);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (N <= 16)
+    attn_small_kernel<false, 16><<<(unsigned)((items + 2 * SM_WARPS - 1) / (2 * SM_WARPS)), SM_WARPS * 32, 0, st>>>(
+        reinterpret_cast<const bf16*>(qkv), nullptr, reinterpret_cast<bf16*>(o), items, (int)N, (int)H, (int)D, scale);
+  else
+    attn_small_kernel<false, 32><<<(unsigned)((items + SM_WARPS - 1) / SM_WARPS), SM_WARPS * 32, 0, st>>>(
+        reinterpret_cast<const bf16*>(qkv), nullptr, reinterpret_cast<bf16*>(o), items, (int)N, (int)H, (int)D, scale);
   count_launch();
   return check_launch("sav_attn_small_fwd");
 }
@@ -157,10 +169,15 @@ extern "C" int sav_attn_small_bwd(const void* qkv, const void* d_o, void* dqkv, 
   if (int rc = small_check("sav_attn_small_bwd", qkv, dqkv, B, N, H, D)) return rc;
   if (!d_o) return set_error(SAV_ERR_ARG, "sav_attn_small_bwd: d_o is null");
   const int64_t items = B * H;
-  attn_small_kernel<true><<<(unsigned)((items + SM_WARPS - 1) / SM_WARPS), SM_WARPS * 32, 0,
-                            reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const bf16*>(qkv), reinterpret_cast<const bf16*>(d_o),
-      reinterpret_cast<bf16*>(dqkv), items, (int)N, (int)H, (int)D, scale);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (N <= 16)
+    attn_small_kernel<true, 16><<<(unsigned)((items + 2 * SM_WARPS - 1) / (2 * SM_WARPS)), SM_WARPS * 32, 0, st>>>(
+        reinterpret_cast<const bf16*>(qkv), reinterpret_cast<const bf16*>(d_o), reinterpret_cast<bf16*>(dqkv),
+        items, (int)N, (int)H, (int)D, scale);
+  else
+    attn_small_kernel<true, 32><<<(unsigned)((items + SM_WARPS - 1) / SM_WARPS), SM_WARPS * 32, 0, st>>>(
+        reinterpret_cast<const bf16*>(qkv), reinterpret_cast<const bf16*>(d_o), reinterpret_cast<bf16*>(dqkv),
+        items, (int)N, (int)H, (int)D, scale);
   count_launch();
   return check_launch("sav_attn_small_bwd");
 }
