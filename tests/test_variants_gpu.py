@@ -366,7 +366,13 @@ def test_cvt_model_logits_and_all_grads():
     # sites per attention than ViT (depthwise-conv output, BatchNorm output, per projection): the
     # edge-shape tolerance of tests/test_vit_parity_gpu.py applies to the max-norm, every tensor must
     # be within 3e-2 in relative L2, the logits within the north-star 2e-2.
-    _check("cvt_small", errs, tol=3.5e-2)
+    # Run-to-run spread (12 runs of this test on one B200, profiles/r02bg_cvt_parity_spread.txt): worst
+    # max-norm 2.44e-2 .. 3.33e-2 (always a BatchNorm / depthwise-conv parameter of the 576-token stage),
+    # worst relative L2 2.04e-2 .. 2.69e-2.  The fp32 reductions that arrive in a different order from
+    # run to run (split-K dW, BatchNorm sums, the attention backward's dK / dV groups) differ by 1e-7,
+    # but a flipped bf16 rounding behind a batch-16 BatchNorm moves a whole channel; the max-norm bound
+    # therefore leaves 2 sigma above the observed maximum, the L2 bound stays.
+    _check("cvt_small", errs, tol=4e-2)
     assert max(l2.values()) <= 3e-2, sorted(l2.items(), key=lambda kv: -kv[1])[:5]
     assert errs["logits"] <= TOL
 
