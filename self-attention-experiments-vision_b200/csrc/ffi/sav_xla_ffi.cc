@@ -132,7 +132,7 @@ XLA_FFI_DEFINE_HANDLER_SYMBOL(SavAttnFwd, AttnFwd,
 static ffi::Error AttnBwd(cudaStream_t stream, ffi::Buffer<ffi::BF16> qkv, ffi::Buffer<ffi::BF16> o,
                           ffi::Buffer<ffi::BF16> o_lo, ffi::Buffer<ffi::BF16> d_o,
                           ffi::Buffer<ffi::F32> lse, float scale, ffi::ResultBuffer<ffi::BF16> dqkv,
-                          ffi::ResultBuffer<ffi::F32> delta) {
+                          ffi::ResultBuffer<ffi::F32> delta, ffi::ResultBuffer<ffi::F32> work) {
   sav_attn_bwd_args a{};
   int64_t row, batch;
   qkv_views(qkv, &a.q, &a.k, &a.v, &a.B, &a.Nq, &a.H, &a.D, &row, &batch);
@@ -143,6 +143,9 @@ static ffi::Error AttnBwd(cudaStream_t stream, ffi::Buffer<ffi::BF16> qkv, ffi::
   a.dq = g; a.dk = g + a.H * a.D; a.dv = g + 2 * a.H * a.D;
   a.o = o.untyped_data(); a.o_lo = o_lo.untyped_data(); a.d_o = d_o.untyped_data();
   a.lse = lse.typed_data(); a.delta = delta->typed_data();
+  // scratch result: fp32 [2, B, N, H, D] when N > 256 (the dK / dV accumulators of the query groups),
+  // any 1-element buffer otherwise
+  a.dq_accum = a.Nq > 256 ? work->typed_data() : nullptr;
   a.o_row_stride = a.H * a.D; a.o_batch_stride = a.Nq * a.H * a.D;
   a.scale = scale;
   return status(sav_attn_bwd(&a, stream));
@@ -151,7 +154,7 @@ XLA_FFI_DEFINE_HANDLER_SYMBOL(SavAttnBwd, AttnBwd,
     ffi::Ffi::Bind().Ctx<ffi::PlatformStream<cudaStream_t>>()
         .Arg<ffi::Buffer<ffi::BF16>>().Arg<ffi::Buffer<ffi::BF16>>().Arg<ffi::Buffer<ffi::BF16>>()
         .Arg<ffi::Buffer<ffi::BF16>>().Arg<ffi::Buffer<ffi::F32>>().Attr<float>("scale")
-        .Ret<ffi::Buffer<ffi::BF16>>().Ret<ffi::Buffer<ffi::F32>>(),
+        .Ret<ffi::Buffer<ffi::BF16>>().Ret<ffi::Buffer<ffi::F32>>().Ret<ffi::Buffer<ffi::F32>>(),
     {xla::ffi::Traits::kCmdBufferCompatible});
 
 // train.py:80-81 + patch_embed.py:19-22: images fp32 [H,W,C,N] -> bf16 patch rows
