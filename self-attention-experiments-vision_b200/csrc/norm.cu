@@ -378,6 +378,122 @@ ln_bwd_pieces_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __re
   }
 }
 
+// Rows of 513 .. 1024 columns (ViT-B / Mixer-B 768, TNT-S 640, ViT-L 1024): the same lean kernel with
+// a warp PAIR per row, each warp holding half of the row's pieces, so the register budget -- and the
+// three (two with column sums) resident blocks per SM -- of the C <= 512 kernel carries over.  The
+// chunk kernel above keeps 1 block per SM at these widths and adds the column sums with
+// shared-memory atomics per element: 2.4 TB/s (profiles/r02ay_timeline_mixer_b_patch16.txt).
+template <int PIECES, bool DSUM>
+__global__ void __launch_bounds__(256, (PIECES <= 3 && !DSUM) ? 3 : 2)
+ln_bwd_pieces2_kernel(const bf16* __restrict__ dy, int64_t ldy, const float* __restrict__ x,
+                     int64_t ldx, const float* __restrict__ scale, const float* __restrict__ mean_in,
+                     const float* __restrict__ rstd_in, const float* __restrict__ dx_add,
+                     float* __restrict__ dx, bf16* __restrict__ dx16, float* __restrict__ dscale,
+                     float* __restrict__ dbias, float* __restrict__ dsum, int64_t rows, int C) {
+  extern __shared__ float sacc[];  // [2 or 3][C]
+  __shared__ float xchg[4][2][2][2];   // [pair][row parity][half][s1, s2]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int pair = warp >> 1, half = warp & 1;
+  const int pbase = half * PIECES * 32;                 // first piece of this warp's half row
+  const int64_t warp_global = (int64_t)blockIdx.x * 4 + pair;      // a warp PAIR owns a row
+  const int64_t warps_total = (int64_t)gridDim.x * 4;
+  const int npiece = C / 4;
+  uint32_t parity = 0;
+  const int nacc = (DSUM ? 3 : 2) * C;
+  for (int i = threadIdx.x; i < nacc; i += blockDim.x) sacc[i] = 0.f;
+  __syncthreads();
+  float4 ds[PIECES], db[PIECES], g[PIECES], dc[DSUM ? PIECES : 1];
+#pragma unroll
+  for (int i = 0; i < PIECES; ++i) {
+    const int pc = pbase + lane + i * 32;
+    ds[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    db[i] = ds[i];
+    if (DSUM) dc[i] = ds[i];
+    g[i] = pc < npiece ? *reinterpret_cast<const float4*>(scale + pc * 4) : ds[i];
+  }
+  for (int64_t row = warp_global; row < rows; row += warps_total) {
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float4 xh[PIECES], add[PIECES];
+    uint2 dvp[PIECES];
+    // all global loads of the row are issued before the first reduction (one latency per row)
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) {
+      const int pc = pbase + lane + i * 32;
+      if (pc < npiece) {
+        if (dx_add) add[i] = *reinterpret_cast<const float4*>(dx_add + row * ldx + pc * 4);
+        xh[i] = *reinterpret_cast<const float4*>(x + row * ldx + pc * 4);
+        dvp[i] = *reinterpret_cast<const uint2*>(dy + row * ldy + pc * 4);
+      }
+    }
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) {
+      const int pc = pbase + lane + i * 32;
+      if (pc < npiece) {
+        const float2 d01 = unpack_bf16(dvp[i].x), d23 = unpack_bf16(dvp[i].y);
+        xh[i].x = (xh[i].x - mean) * rstd; xh[i].y = (xh[i].y - mean) * rstd;
+        xh[i].z = (xh[i].z - mean) * rstd; xh[i].w = (xh[i].w - mean) * rstd;
+        const float g0 = d01.x * g[i].x, g1 = d01.y * g[i].y, g2 = d23.x * g[i].z, g3 = d23.y * g[i].w;
+        s1 += (g0 + g1) + (g2 + g3);
+        s2 += (g0 * xh[i].x + g1 * xh[i].y) + (g2 * xh[i].z + g3 * xh[i].w);
+        ds[i].x += d01.x * xh[i].x; ds[i].y += d01.y * xh[i].y;
+        ds[i].z += d23.x * xh[i].z; ds[i].w += d23.y * xh[i].w;
+        db[i].x += d01.x; db[i].y += d01.y; db[i].z += d23.x; db[i].w += d23.y;
+      }
+    }
+    // the two halves of the row meet in shared memory (slots alternate with the row parity, so one
+    // 64-thread barrier per row is enough)
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    if (lane == 0) { xchg[pair][parity][half][0] = s1; xchg[pair][parity][half][1] = s2; }
+    named_barrier_sync(1 + pair, 64);
+    s1 = (xchg[pair][parity][0][0] + xchg[pair][parity][1][0]) / (float)C;
+    s2 = (xchg[pair][parity][0][1] + xchg[pair][parity][1][1]) / (float)C;
+    parity ^= 1;
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) {
+      const int pc = pbase + lane + i * 32;
+      if (pc < npiece) {
+        const float2 d01 = unpack_bf16(dvp[i].x), d23 = unpack_bf16(dvp[i].y);
+        float4 o;
+        o.x = rstd * (d01.x * g[i].x - s1 - xh[i].x * s2);
+        o.y = rstd * (d01.y * g[i].y - s1 - xh[i].y * s2);
+        o.z = rstd * (d23.x * g[i].z - s1 - xh[i].z * s2);
+        o.w = rstd * (d23.y * g[i].w - s1 - xh[i].w * s2);
+        if (dx_add) { o.x += add[i].x; o.y += add[i].y; o.z += add[i].z; o.w += add[i].w; }
+        *reinterpret_cast<float4*>(dx + row * ldx + pc * 4) = o;
+        if (dx16) {
+          const uint32_t p01 = pack_bf16(o.x, o.y), p23 = pack_bf16(o.z, o.w);
+          *reinterpret_cast<uint2*>(dx16 + row * ldx + pc * 4) = make_uint2(p01, p23);
+          if (DSUM) {
+            const float2 r01 = unpack_bf16(p01), r23 = unpack_bf16(p23);
+            dc[i].x += r01.x; dc[i].y += r01.y; dc[i].z += r23.x; dc[i].w += r23.y;
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < PIECES; ++i) {
+    const int pc = pbase + lane + i * 32;
+    if (pc < npiece) {
+      float* a = sacc + pc * 4;
+      atomicAdd(a, ds[i].x); atomicAdd(a + 1, ds[i].y); atomicAdd(a + 2, ds[i].z); atomicAdd(a + 3, ds[i].w);
+      a += C;
+      atomicAdd(a, db[i].x); atomicAdd(a + 1, db[i].y); atomicAdd(a + 2, db[i].z); atomicAdd(a + 3, db[i].w);
+      if (DSUM) {
+        a += C;
+        atomicAdd(a, dc[i].x); atomicAdd(a + 1, dc[i].y); atomicAdd(a + 2, dc[i].z); atomicAdd(a + 3, dc[i].w);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < nacc; i += blockDim.x) {
+    float* out = (i < C) ? (dscale + i) : (i < 2 * C ? dbias + (i - C) : dsum + (i - 2 * C));
+    atomicAdd(out, sacc[i]);
+  }
+}
+
 static int ln_grid(int64_t rows) {
   int64_t g = (rows + 7) / 8;
   const int64_t cap = 148 * 4;
@@ -469,6 +585,21 @@ extern "C" int sav_layernorm_bwd_colsum(const void* dy, int64_t ldy, const float
       }
     }
 #undef LN_BWDP
+    count_launch();
+    return check_launch("sav_layernorm_bwd");
+  }
+  if (C > 512 && dx_bf16) {
+    const int pieces = (int)((C / 4 + 63) / 64);       // per warp of the pair
+    const int grid_p = (int)((rows + 3) / 4 < 148 * 6 ? ((rows + 3) / 4 < 1 ? 1 : (rows + 3) / 4) : 148 * 6);
+#define LN_BWDP2(PC, DS)                                                                         \
+  ln_bwd_pieces2_kernel<PC, DS><<<grid_p, 256, sm, st>>>(reinterpret_cast<const bf16*>(dy), ldy, x, ldx, \
+      scale, mean, rstd, dx_add, dx, reinterpret_cast<bf16*>(dx_bf16), dscale, dbias, dsum, rows, (int)C)
+    if (dsum) {
+      if (pieces <= 3) LN_BWDP2(3, true); else LN_BWDP2(4, true);
+    } else {
+      if (pieces <= 3) LN_BWDP2(3, false); else LN_BWDP2(4, false);
+    }
+#undef LN_BWDP2
     count_launch();
     return check_launch("sav_layernorm_bwd");
   }
