@@ -85,3 +85,19 @@ def test_reference_shaped_dict_roundtrip_and_ext_types():
     big = {"__msgpack_chunked_array__": True, "shape": [2, 3],
            "chunks": {"0": np.arange(4, dtype=np.float32), "1": np.arange(4, 6, dtype=np.float32)}}
     assert C.from_bytes(C.to_bytes({"w": big}))["w"].tolist() == [[0, 1, 2], [3, 4, 5]]
+
+
+def test_state_dict_keeps_batch_stats_beside_the_parameters():
+    """The reference TrainState stores the whole model.init() variables under `params` (train.py:31-37):
+    for a BatchNorm model that is {'params': ..., 'batch_stats': ...}.  Both nestings restore."""
+    import numpy as np
+    from sav import checkpoint as C
+    tree = {"Dense_0": {"kernel": np.ones((2, 3), np.float32)}}
+    stats = {"BatchNorm_0": {"mean": np.zeros(3, np.float32), "var": np.ones(3, np.float32)}}
+    assert C._strip_params_level({"params": tree}) is tree
+    assert C._strip_params_level({"params": tree, "batch_stats": stats}) is tree
+    assert C._strip_params_level(tree) is tree                      # round-1 files: the tree itself
+    sd = {"step": np.asarray(3, np.int32), "params": {"params": tree, "batch_stats": stats}}
+    back = C.from_bytes(C.to_bytes(sd))
+    assert set(back["params"]) == {"params", "batch_stats"}
+    np.testing.assert_array_equal(back["params"]["batch_stats"]["BatchNorm_0"]["var"], stats["BatchNorm_0"]["var"])
