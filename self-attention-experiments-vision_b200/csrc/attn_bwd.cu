@@ -525,8 +525,7 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
     uint32_t gk = 0, nstore = 0;
     // one [128 x 64] bf16 tile: registers -> staging buffer (nstore & 1) -> TMA store.  The buffer
     // is reused every second store: the leader keeps at most one store group reading.
-    auto store_tile = [&](const CUtensorMap* map, const uint32_t (&pk)[32], int c0, int c1, int c2,
-                          bool reduce) {
+    auto store_tile = [&](const CUtensorMap* map, const uint32_t (&pk)[32], int c0, int c1, int c2) {
       uint8_t* stage = sStage + (nstore & 1) * BT_BYTES;
       if (leader) tma_store_wait_read<1>();
       named_barrier_sync(2, 128);
@@ -534,8 +533,7 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       fence_proxy_async_smem();
       named_barrier_sync(2, 128);
       if (leader) {
-        if (reduce) tma_reduce_add_3d(map, stage, c0, c1, c2);   // partial of one query group
-        else tma_store_3d(map, stage, c0, c1, c2);
+        tma_store_3d(map, stage, c0, c1, c2);
         tma_store_commit();
       }
       ++nstore;
@@ -585,12 +583,12 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           reduce_tile_f32(&tdk, tdK + lane_off, p.scale, h * BD, j * BT, b, true);
         } else {
           tmem_row64_to_bf16(tdV + lane_off, 1.f, pk);
-          store_tile(&tdv, pk, h * BD, j * BT, b, false);   // key rows >= Nk are clipped by the map
+          store_tile(&tdv, pk, h * BD, j * BT, b);   // key rows >= Nk are clipped by the map
           tmem_row64_to_bf16(tdK + lane_off, p.scale, pk);
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(dkv_free);        // next key tile may overwrite dV / dK
-          store_tile(&tdk, pk, h * BD, j * BT, b, false);
+          store_tile(&tdk, pk, h * BD, j * BT, b);
         }
         BWD_STAMP(5, 44);
       }
@@ -606,13 +604,13 @@ attn_bwd3_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           __syncwarp();
           if (lane == 0) mbar_arrive(dq_free);       // next item may overwrite dQ
         }
-        store_tile(&tdq, pk, h * BD, it.q0, b, false);   // rows >= Nq clipped
+        store_tile(&tdq, pk, h * BD, it.q0, b);   // rows >= Nq clipped
         if (it.nqt > 1) {
           tmem_row64_to_bf16(tdQ + BD + lane_off, p.scale, pk);
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(dq_free);
-          store_tile(&tdq, pk, h * BD, it.q0 + BT, b, false);
+          store_tile(&tdq, pk, h * BD, it.q0 + BT, b);
         }
       }
     }

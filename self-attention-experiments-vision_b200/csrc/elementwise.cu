@@ -282,6 +282,56 @@ transpose_pad_kernel(const TIn* __restrict__ in, int64_t ld_in, TOut* __restrict
     }
   }
 }
+
+// 64 x 64 tiles with two adjacent elements per access (bf16x2 = 4 bytes, fp32x2 = 8 bytes) on both
+// sides: the 32 x 32 / one-element kernel above moves 64 bytes per warp row for bf16 and ran the
+// activation transposes of Mixer-B/16 (38.5 MB each way) at half the HBM rate
+// (profiles/r02ay_timeline_mixer_b_patch16.txt).  Needs even pitches and aligned bases.
+__device__ __forceinline__ float2 ld2(const float* p) { return *reinterpret_cast<const float2*>(p); }
+__device__ __forceinline__ float2 ld2(const bf16* p) { return unpack_bf16(*reinterpret_cast<const uint32_t*>(p)); }
+__device__ __forceinline__ void st2(float* p, float a, float b) { *reinterpret_cast<float2*>(p) = make_float2(a, b); }
+__device__ __forceinline__ void st2(bf16* p, float a, float b) { *reinterpret_cast<uint32_t*>(p) = pack_bf16(a, b); }
+
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(256)
+transpose_pad64_kernel(const TIn* __restrict__ in, int64_t ld_in, TOut* __restrict__ out, int64_t ld_out,
+                       const float* __restrict__ res, int64_t ld_res, int64_t R, int64_t C,
+                       int64_t out_cols) {
+  __shared__ float tile[64][65];
+  const int64_t b = blockIdx.z;
+  const int64_t r0 = (int64_t)blockIdx.x * 64, c0 = (int64_t)blockIdx.y * 64;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+  const TIn* src = in + b * R * ld_in;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int rl = ty + i * 8;
+    const int64_t r = r0 + rl, c = c0 + 2 * tx;
+    float2 v = make_float2(0.f, 0.f);
+    if (r < R) {
+      if (c + 1 < C) v = ld2(src + r * ld_in + c);
+      else if (c < C) v.x = to_f32(src[r * ld_in + c]);
+    }
+    tile[rl][2 * tx] = v.x;
+    tile[rl][2 * tx + 1] = v.y;
+  }
+  __syncthreads();
+  TOut* dst = out + b * C * ld_out;
+  const float* rs = res ? res + b * C * ld_res : nullptr;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int cl = ty + i * 8;
+    const int64_t c = c0 + cl, r = r0 + 2 * tx;
+    if (c < C && r < out_cols) {
+      float v0 = tile[2 * tx][cl], v1 = tile[2 * tx + 1][cl];
+      if (rs) {
+        if (r + 1 < R) { const float2 q = ld2(rs + c * ld_res + r); v0 += q.x; v1 += q.y; }
+        else if (r < R) v0 += rs[c * ld_res + r];
+      }
+      if (r + 1 < out_cols) st2(dst + c * ld_out + r, v0, v1);
+      else from_f32(dst[c * ld_out + r], v0);
+    }
+  }
+}
 }  // namespace sav
 
 extern "C" int sav_transpose_pad(const void* in, int32_t in_fp32, int64_t ld_in, void* out,
@@ -293,8 +343,26 @@ extern "C" int sav_transpose_pad(const void* in, int32_t in_fp32, int64_t ld_in,
   if (!in || !out || out_cols < R || ld_out < out_cols || ld_in < C || (residual && ld_res < R) ||
       B > 65535 || (C + 31) / 32 > 65535)
     return set_error(SAV_ERR_SHAPE, "sav_transpose_pad: R <= out_cols <= ld_out, C <= ld_in, B <= 65535");
-  const dim3 grid((unsigned)((out_cols + 31) / 32), (unsigned)((C + 31) / 32), (unsigned)B), block(32, 8);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // two elements per access when every pitch is even and the bases are aligned for the pair
+  const uintptr_t am_in = in_fp32 ? 7 : 3, am_out = out_fp32 ? 7 : 3;
+  if (R >= 32 && C >= 32 && ld_in % 2 == 0 && ld_out % 2 == 0 && (!residual || ld_res % 2 == 0) &&
+      !(reinterpret_cast<uintptr_t>(in) & am_in) && !(reinterpret_cast<uintptr_t>(out) & am_out) &&
+      !(reinterpret_cast<uintptr_t>(residual) & 7) && (R * ld_in) % 2 == 0 && (C * ld_out) % 2 == 0 &&
+      (C * ld_res) % 2 == 0) {
+    const dim3 grid64((unsigned)((out_cols + 63) / 64), (unsigned)((C + 63) / 64), (unsigned)B);
+#define SAV_TP64(TI, TO)                                                                          \
+  transpose_pad64_kernel<TI, TO><<<grid64, 256, 0, st>>>(reinterpret_cast<const TI*>(in), ld_in,   \
+      reinterpret_cast<TO*>(out), ld_out, residual, ld_res, R, C, out_cols)
+    if (in_fp32 && out_fp32) SAV_TP64(float, float);
+    else if (in_fp32) SAV_TP64(float, bf16);
+    else if (out_fp32) SAV_TP64(bf16, float);
+    else SAV_TP64(bf16, bf16);
+#undef SAV_TP64
+    count_launch();
+    return check_launch("sav_transpose_pad");
+  }
+  const dim3 grid((unsigned)((out_cols + 31) / 32), (unsigned)((C + 31) / 32), (unsigned)B), block(32, 8);
 #define SAV_TP(TI, TO)                                                                          \
   transpose_pad_kernel<TI, TO><<<grid, block, 0, st>>>(reinterpret_cast<const TI*>(in), ld_in,  \
       reinterpret_cast<TO*>(out), ld_out, residual, ld_res, R, C, out_cols)
