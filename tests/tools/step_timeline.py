@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--replays", type=int, default=10)
     ap.add_argument("--model", default="deit_s_patch16")
+    ap.add_argument("--img", type=int, default=224)
     a = ap.parse_args()
     import sav  # noqa: F401
     from models import create_model
@@ -57,12 +58,12 @@ def main():
     _abi._lib = Proxy()
 
     torch.cuda.set_device(0)
-    images, labels = O.synthetic_batch(a.batch, 224, seed=0)
+    images, labels = O.synthetic_batch(a.batch, a.img, seed=0)
     model = create_model(a.model)
     x = HWCN(images.cuda())
     try:
         cfg = O.vit_config(a.model)
-        variables = sav.load_params(model, O.synthetic_vit_params(cfg, 224, seed=42), x, is_training=True)
+        variables = sav.load_params(model, O.synthetic_vit_params(cfg, a.img, seed=42), x, is_training=True)
     except KeyError:
         # any other create_model name (cait / cvt / botnet / mixer / tnt / ceit): random parameters
         variables = model.init({"params": 0, "stochastic_depth": 1}, x, is_training=True)
@@ -104,7 +105,7 @@ def main():
         total += start.elapsed_time(log[-1][1]) * 1e3
     slot = [v / a.replays for v in acc]
     total /= a.replays
-    print(f"# {a.model} batch {a.batch}: {len(log)} launching ABI calls per step, step (first..last event) "
+    print(f"# {a.model} {a.img}^2 batch {a.batch}: {len(log)} launching ABI calls per step, step (first..last event) "
           f"{total / 1e3:.3f} ms, mean of {a.replays} replays; slot = kernel(s) of the call + gap to the next")
     by = collections.OrderedDict()
     for n, v in zip(names, slot):
